@@ -1,0 +1,161 @@
+/* rela_b200.h -- C ABI of the B200-native prioritized replay.
+ *
+ * This is the drop-in boundary for rela's replay hot path: every entry point
+ * below replaces one member of the reference's `rela::PrioritizedReplay<T>`
+ * (rela/prioritized_replay.h) as bound in rela/pybind.cc:37-59, or one piece
+ * of actor-side arithmetic (rela/dqn_actor.h, pyrela/apex.py, pyrela/r2d2.py).
+ * Plain pointers and sizes only; no torch types. The library is
+ * rela_b200/librela_b200.so, built from rela_b200/csrc/ with nvcc for
+ * sm_100a. There is no CPU fallback: every call that needs the device fails
+ * with RR_ERR_CUDA when no B200 is present.
+ *
+ * Storage model. A replay holds S = (int)(1.25 * capacity) slots
+ * (prioritized_replay.h:181). An element is a record of `nfields` byte rows
+ * (one per leaf tensor of FFTransition / RNNTransition, types.h:18-73). Each
+ * field lives in its own HBM slab `[S, row_bytes]` (structure of arrays).
+ * A field with `chunks == T > 1` is stored element-major `[T, chunk]` and is
+ * gathered TIME-major into `[T, B, chunk]`, which is what
+ * RNNTransition::makeBatch's stack(dim=1) produces (types.cc:140-167); with
+ * `chunks == 1` the gather is `[B, row]` = FFTransition::makeBatch's
+ * stack(dim=0) (types.cc:8-32).
+ *
+ * Threading. rr_add* may be called from many host threads at once (the
+ * reference's blockAppend protocol, prioritized_replay.h:43-78, including its
+ * blocking when all S slots are in flight). rr_sample and rr_update_priority
+ * must come from one thread at a time (the reference holds mSampler_).
+ * All device work is issued on one internal stream in the order the calls
+ * commit; rr_sample / rr_update_priority hand-shake with the caller's stream
+ * by events and never block the host.
+ */
+#ifndef RELA_B200_H_
+#define RELA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RR_OK 0
+#define RR_ERR_ARG 1    /* bad argument / schema mismatch                       */
+#define RR_ERR_CUDA 2   /* CUDA failure or no device                            */
+#define RR_ERR_STATE 3  /* protocol violation, e.g. sample before update        */
+#define RR_ERR_EMPTY 4  /* sample from an empty buffer (reference: assert)      */
+#define RR_ERR_NOMEM 5  /* slabs do not fit in HBM                              */
+#define RR_ERR_OVERRUN 6 /* prefix walk ran past the last element
+                            (prioritized_replay.h:297-302)                      */
+
+/* flags for rr_add / rr_add_rows / rr_update_priority */
+#define RR_ROWS_DEVICE 0x1u    /* row pointers are device pointers (default: host) */
+#define RR_PRIO_DEVICE 0x2u    /* priority pointer is a device pointer             */
+#define RR_PRIO_IS_WEIGHT 0x4u /* priority is already priority^alpha: skip the
+                                  device pow (bit-parity mode)          */
+
+typedef struct rr_replay rr_replay;
+
+typedef struct rr_field {
+  const char* name;   /* informational, e.g. "obs.s"; copied                  */
+  uint64_t row_bytes; /* bytes of this field per stored element               */
+  uint32_t chunks;    /* T; row = T chunks of row_bytes/T bytes; 1 = batch-major */
+  uint32_t reserved;
+} rr_field;
+
+typedef struct rr_stats {
+  uint64_t kernel_launches;   /* kernels this replay has launched             */
+  uint64_t samples;           /* completed rr_sample calls                    */
+  uint64_t samples_exact;     /* ... that took the parallel (exact) selection */
+  uint64_t samples_ordered;   /* ... that fell back to the ordered walk       */
+  uint64_t pops;              /* elements evicted                             */
+  uint64_t device_errors;     /* sticky device-side error flags (RR_ERR_*)    */
+  uint64_t slab_bytes;        /* HBM held by the field slabs                  */
+  uint64_t h2d_bytes;         /* bytes copied host->device by rr_add*         */
+} rr_stats;
+
+/* Thread-local text of the last error returned on this thread. */
+const char* rr_last_error(void);
+
+/* PrioritizedReplay(capacity, seed, alpha, beta, prefetch)
+ * (prioritized_replay.h:176-184, pybind.cc:39-43) on CUDA device `device`. */
+int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta,
+              int prefetch, int device);
+int rr_destroy(rr_replay* r);
+
+/* Freeze the element layout and allocate the slabs. The reference is
+ * schema-agnostic (TensorDict); callers derive the fields from the first
+ * batch they add. Must be called once before the first add. */
+int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields);
+
+/* add(batch, priority) (prioritized_replay.h:186-200): n elements, field f of
+ * element i at field_base[f] + i * row_stride[f] (row_stride == NULL: rows are
+ * packed, stride = row_bytes). priority: n floats. Blocks while fewer than n
+ * of the S slots are free (prioritized_replay.h:47). Host rows have been
+ * copied out of the caller's memory when the call returns. */
+int rr_add(rr_replay* r, int n, const void* const* field_base,
+           const uint64_t* row_stride, const float* priority, unsigned flags);
+
+/* Same with one pointer per row: row_ptrs[f * n + i]
+ * (add(vector<RNNTransition>), r2d2_actor.h:301). */
+int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs,
+                const float* priority, unsigned flags);
+
+/* sample(batchsize, device) (prioritized_replay.h:202-233, 258-328):
+ * stratified proportional selection, eviction down to capacity, importance
+ * weights, and the gather into out_fields[f] (DEVICE pointers, layout above)
+ * and out_weights[batch] (device). `stream` is the caller's cudaStream_t (NULL
+ * = legacy default stream): results are ordered on it when the call returns.
+ * With prefetch > 0 the call returns the batch selected `prefetch` calls ago,
+ * exactly like the reference's future queue. RR_ERR_STATE if the previous
+ * batch's priorities were not updated (prioritized_replay.h:203-206). */
+int rr_sample(rr_replay* r, int batch, void* const* out_fields,
+              float* out_weights, void* stream);
+
+/* updatePriority(priority) (prioritized_replay.h:235-245, 105-119): n must be
+ * the size of the batch last returned by rr_sample. Evicted ids are skipped. */
+int rr_update_priority(rr_replay* r, int n, const float* priority,
+                       unsigned flags, void* stream);
+
+int rr_size(const rr_replay* r);    /* safeSize_ (prioritized_replay.h:247) */
+int rr_num_add(const rr_replay* r); /* numAdd_   (prioritized_replay.h:251) */
+
+/* Wait for all device work issued so far; returns the sticky device error
+ * (RR_OK if none) and clears it. */
+int rr_sync(rr_replay* r);
+int rr_get_stats(rr_replay* r, rr_stats* out);
+
+/* Test/debug introspection (synchronises). ids: the physical slot ids of the
+ * batch last returned by rr_sample (the reference's sampledIds_). */
+int rr_last_sample_ids(rr_replay* r, int n, int32_t* out_ids_host);
+int rr_debug_state(rr_replay* r, int* head, int* tail, int* size,
+                   int* safe_size, double* sum);
+int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host);
+
+/* ---------------------------------------------------------------------------
+ * Actor-side transition assembly (device pointers, async on `stream`).
+ *
+ * rr_nstep_return: MultiStepTransitionBuffer::popTransition
+ * (dqn_actor.h:58-106). reward, terminal: [n_step + 1, K] history rows
+ * (row 0 = oldest). Outputs [K]: discounted return, bootstrap flag, and
+ * terminal (= history row 0). contract_fma != 0 evaluates r + gamma * R as one
+ * fused multiply-add (what -O3 -march=native compiles dqn_actor.h:95 to).
+ *
+ * rr_td_priority: |reward + bootstrap * gamma_n * q_next - q_sa|
+ * (apex.py:44-45,77-78; r2d2.py:98-99). gamma_n = gamma ** n_step.
+ *
+ * rr_aggregate_priority: eta * max + (1 - eta) * mean over each sequence
+ * (r2d2.py:103-120). priority [nseq, seq_len], len [nseq] (float, includes
+ * burn-in as in r2d2_actor.h:107). */
+int rr_nstep_return(int n_step, int K, float gamma, const float* reward,
+                    const uint8_t* terminal, float* out_reward,
+                    float* out_bootstrap, uint8_t* out_terminal,
+                    int contract_fma, void* stream);
+int rr_td_priority(int K, const float* reward, const float* bootstrap,
+                   const float* q_next, const float* q_sa, float gamma_n,
+                   float* out_priority, void* stream);
+int rr_aggregate_priority(int nseq, int seq_len, const float* priority,
+                          const float* len, float eta, int burn_in,
+                          float* out_priority, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RELA_B200_H_ */

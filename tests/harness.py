@@ -1,0 +1,407 @@
+"""Test harness: ctypes bindings for the checker side (oracle/ and oracle/_ref).
+
+TEST INFRASTRUCTURE. The product never imports this module. Both wrappers speak
+the same "flat rows" protocol as the C ABI in include/rela_b200.h so that the
+parity tests can drive all three implementations with identical inputs.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libref_replay.so")
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+_DT = {"uint8": 0, "float32": 1, "int64": 2, "bool": 3, "int32": 4, "float64": 5}
+
+
+class Field:
+    """One leaf tensor of a transition. `shape` is per element (no batch dim).
+
+    chunks == T > 1 means the element is [T, ...] and batches time-major
+    [T, B, ...] (RNNTransition::makeBatch, reference rela/types.cc:161-166).
+    """
+
+    def __init__(self, name, dtype, shape, chunks=1):
+        self.name = name
+        self.dtype = np.dtype(dtype)
+        self.shape = tuple(int(s) for s in shape)
+        self.chunks = int(chunks)
+        self.row_bytes = int(np.prod(self.shape, dtype=np.int64)) * self.dtype.itemsize
+        assert self.row_bytes % self.chunks == 0
+
+    def batch_shape(self, B):
+        if self.chunks == 1:
+            return (B,) + self.shape
+        assert self.shape[0] == self.chunks
+        return (self.chunks, B) + self.shape[1:]
+
+
+def ff_schema(frame=(4, 84, 84), n_actions=18):
+    """FFTransition leaves as the Atari env + DQNActor produce them
+    (reference rela/types.h:18-51, atari/atari_env.h)."""
+    return [
+        Field("obs.s", "uint8", frame),
+        Field("obs.eps", "float32", (1,)),
+        Field("obs.legal_move", "float32", (n_actions,)),
+        Field("action.a", "int64", ()),
+        Field("reward", "float32", ()),
+        Field("terminal", "bool", ()),
+        Field("bootstrap", "float32", ()),
+        Field("next_obs.s", "uint8", frame),
+        Field("next_obs.eps", "float32", (1,)),
+        Field("next_obs.legal_move", "float32", (n_actions,)),
+    ]
+
+
+def rnn_schema(T=123, frame=(4, 84, 84), n_actions=18, hid=512, layers=1):
+    """RNNTransition leaves (reference rela/types.h:53-73, r2d2_actor.h:21)."""
+    return [
+        Field("obs.s", "uint8", (T,) + tuple(frame), chunks=T),
+        Field("obs.eps", "float32", (T, 1), chunks=T),
+        Field("obs.legal_move", "float32", (T, n_actions), chunks=T),
+        Field("h0.h0", "float32", (layers, hid), chunks=layers),
+        Field("h0.c0", "float32", (layers, hid), chunks=layers),
+        Field("action.a", "int64", (T,), chunks=T),
+        Field("reward", "float32", (T,), chunks=T),
+        Field("terminal", "bool", (T,), chunks=T),
+        Field("bootstrap", "float32", (T,), chunks=T),
+        Field("seq_len", "float32", (1,)),
+    ]
+
+
+def make_rows(schema, n, rng, serial0=0):
+    """n synthetic elements, one contiguous array [n, *shape] per field.
+    `action.a` carries a running serial (the reference's own trick of tagging
+    elements, rela/tests/test_prioritized_replay.cc:12-15)."""
+    rows = []
+    for f in schema:
+        shape = (n,) + f.shape
+        if f.name == "action.a":
+            a = np.arange(serial0, serial0 + n, dtype=np.int64)
+            a = np.broadcast_to(a.reshape((n,) + (1,) * len(f.shape)), shape).copy()
+        elif f.dtype == np.uint8:
+            a = rng.integers(0, 256, size=shape, dtype=np.uint8)
+        elif f.dtype == np.bool_:
+            a = rng.random(size=shape) < 0.05
+        elif f.dtype == np.int64:
+            a = rng.integers(0, 1 << 40, size=shape, dtype=np.int64)
+        elif f.name == "seq_len":
+            a = rng.integers(41, 121, size=shape).astype(np.float32)
+        else:
+            a = rng.standard_normal(size=shape).astype(f.dtype)
+        rows.append(np.ascontiguousarray(a))
+    return rows
+
+
+def _ptr_array(arrays):
+    arr = (C.c_void_p * max(1, len(arrays)))()
+    for i, a in enumerate(arrays):
+        arr[i] = a.ctypes.data if a is not None else None
+    return arr
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR, "liboracle.so"], check=True)
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+_oracle_lib = None
+
+
+def oracle_lib():
+    global _oracle_lib
+    if _oracle_lib is None:
+        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+            os.path.join(ORACLE_DIR, "replay_oracle.c")
+        ):
+            build_oracle()
+        lib = C.CDLL(ORACLE_SO)
+        lib.orc_create.restype = C.c_void_p
+        lib.orc_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
+                                   C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_destroy.argtypes = [C.c_void_p]
+        lib.orc_add.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_sample.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.orc_update_priority.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        for fn in (lib.orc_size, lib.orc_num_add, lib.orc_slots):
+            fn.argtypes = [C.c_void_p]
+        lib.orc_state.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        lib.orc_weights.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.orc_nstep_return.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_td_priority.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_float, C.c_void_p]
+        lib.orc_aggregate_priority.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
+                                               C.c_int, C.c_void_p]
+        _oracle_lib = lib
+    return _oracle_lib
+
+
+class _Base:
+    """Shared helpers: output allocation in makeBatch layout."""
+
+    def alloc_batch(self, B):
+        return [np.zeros(f.batch_shape(B), dtype=f.dtype) for f in self.schema]
+
+    def state(self):
+        raise NotImplementedError
+
+
+class Oracle(_Base):
+    """oracle/replay_oracle.c"""
+
+    def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0, contract_fma=1):
+        self.lib = oracle_lib()
+        self.schema = schema
+        rb = np.array([f.row_bytes for f in schema], dtype=np.uint64)
+        ch = np.array([f.chunks for f in schema], dtype=np.uint32)
+        self.h = self.lib.orc_create(capacity, seed, alpha, beta, prefetch, len(schema),
+                                     rb.ctypes.data, ch.ctypes.data, contract_fma)
+        self.S = self.lib.orc_slots(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.orc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def add(self, rows, weights):
+        """weights: already priority ** alpha (float32)."""
+        w = np.ascontiguousarray(weights, dtype=np.float32)
+        rc = self.lib.orc_add(self.h, len(w), _ptr_array(rows), None, w.ctypes.data, 1)
+        assert rc == 0, "oracle add would block"
+
+    def sample(self, B, want_rows=True):
+        out = self.alloc_batch(B) if want_rows else None
+        w = np.zeros(B, dtype=np.float32)
+        ids = np.zeros(B, dtype=np.int32)
+        rc = self.lib.orc_sample(self.h, B, _ptr_array(out) if out else None, w.ctypes.data,
+                                 ids.ctypes.data)
+        return rc, out, w, ids
+
+    def update(self, weights):
+        w = np.ascontiguousarray(weights, dtype=np.float32)
+        return self.lib.orc_update_priority(self.h, len(w), w.ctypes.data, 1)
+
+    def size(self):
+        return self.lib.orc_size(self.h)
+
+    def num_add(self):
+        return self.lib.orc_num_add(self.h)
+
+    def state(self):
+        v = [C.c_int() for _ in range(4)]
+        s = C.c_double()
+        self.lib.orc_state(self.h, *[C.addressof(x) for x in v], C.addressof(s))
+        return dict(head=v[0].value, tail=v[1].value, size=v[2].value, safe_size=v[3].value,
+                    sum=s.value)
+
+    def weights(self):
+        w = np.zeros(self.S, dtype=np.float32)
+        e = np.zeros(self.S, dtype=np.uint8)
+        self.lib.orc_weights(self.h, w.ctypes.data, e.ctypes.data)
+        return w, e
+
+
+_ref_lib = None
+
+
+def ref_lib():
+    """oracle/_ref/libref_replay.so: the unmodified reference behind ref_driver.cc."""
+    global _ref_lib
+    if _ref_lib is None:
+        import torch  # noqa: F401  (loads libtorch with RTLD_GLOBAL deps resolved)
+
+        lib = C.CDLL(REF_SO)
+        for kind in ("ff", "rnn"):
+            getattr(lib, f"ref_{kind}_create").restype = C.c_void_p
+            getattr(lib, f"ref_{kind}_create").argtypes = [C.c_int, C.c_int, C.c_float, C.c_float,
+                                                           C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                           C.c_void_p, C.c_void_p]
+            getattr(lib, f"ref_{kind}_destroy").argtypes = [C.c_void_p]
+            getattr(lib, f"ref_{kind}_add").argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                        C.c_int]
+            getattr(lib, f"ref_{kind}_sample").argtypes = [C.c_void_p, C.c_int, C.c_void_p,
+                                                           C.c_void_p, C.c_void_p]
+            getattr(lib, f"ref_{kind}_update").argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            getattr(lib, f"ref_{kind}_size").argtypes = [C.c_void_p]
+            getattr(lib, f"ref_{kind}_num_add").argtypes = [C.c_void_p]
+            getattr(lib, f"ref_{kind}_cycle_loop").restype = C.c_double
+            getattr(lib, f"ref_{kind}_cycle_loop").argtypes = [C.c_void_p, C.c_int, C.c_int,
+                                                               C.c_void_p, C.c_int]
+        lib.ref_ff_state.argtypes = [C.c_void_p] * 6
+        lib.ref_ff_weights.argtypes = [C.c_void_p] * 3
+        lib.ref_nstep_pop.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.ref_nstep_loop.restype = C.c_double
+        lib.ref_nstep_loop.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int]
+        lib.ref_build_info.restype = C.c_char_p
+        _ref_lib = lib
+    return _ref_lib
+
+
+class RefReplay(_Base):
+    """The reference's own FFPrioritizedReplay / RNNPrioritizedReplay."""
+
+    def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0):
+        self.lib = ref_lib()
+        self.schema = schema
+        self.kind = "rnn" if any(f.name == "seq_len" for f in schema) else "ff"
+        self.S = int(1.25 * capacity)
+        names = (C.c_char_p * len(schema))(*[f.name.encode() for f in schema])
+        dts = np.array([_DT[f.dtype.name] for f in schema], dtype=np.int32)
+        nd = np.array([len(f.shape) for f in schema], dtype=np.int32)
+        shp = np.zeros((max(1, len(schema)), 6), dtype=np.int64)
+        for i, f in enumerate(schema):
+            shp[i, : len(f.shape)] = f.shape
+        self.h = getattr(self.lib, f"ref_{self.kind}_create")(
+            capacity, seed, alpha, beta, prefetch, len(schema), names, dts.ctypes.data,
+            nd.ctypes.data, shp.ctypes.data)
+        self._keep = []
+
+    def close(self):
+        if self.h:
+            getattr(self.lib, f"ref_{self.kind}_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def add(self, rows, priority, alias=False):
+        """priority: RAW priorities; the reference applies torch::pow itself."""
+        p = np.ascontiguousarray(priority, dtype=np.float32)
+        if alias:
+            self._keep.append(rows)
+        getattr(self.lib, f"ref_{self.kind}_add")(self.h, len(p), _ptr_array(rows), p.ctypes.data,
+                                                  1 if alias else 0)
+
+    def sample(self, B, want_rows=True):
+        out = self.alloc_batch(B) if want_rows else None
+        w = np.zeros(B, dtype=np.float32)
+        ids = np.zeros(B, dtype=np.int32)
+        n = getattr(self.lib, f"ref_{self.kind}_sample")(
+            self.h, B, _ptr_array(out) if out else None, w.ctypes.data, ids.ctypes.data)
+        assert n == B
+        return 0, out, w, ids
+
+    def update(self, priority):
+        p = np.ascontiguousarray(priority, dtype=np.float32)
+        getattr(self.lib, f"ref_{self.kind}_update")(self.h, len(p), p.ctypes.data)
+        return 0
+
+    def size(self):
+        return getattr(self.lib, f"ref_{self.kind}_size")(self.h)
+
+    def num_add(self):
+        return getattr(self.lib, f"ref_{self.kind}_num_add")(self.h)
+
+    def state(self):
+        assert self.kind == "ff"
+        v = [C.c_int() for _ in range(4)]
+        s = C.c_double()
+        self.lib.ref_ff_state(self.h, *[C.addressof(x) for x in v], C.addressof(s))
+        return dict(head=v[0].value, tail=v[1].value, size=v[2].value, safe_size=v[3].value,
+                    sum=s.value)
+
+    def weights(self):
+        assert self.kind == "ff"
+        w = np.zeros(self.S, dtype=np.float32)
+        e = np.zeros(self.S, dtype=np.uint8)
+        self.lib.ref_ff_weights(self.h, w.ctypes.data, e.ctypes.data)
+        return w, e
+
+    def cycle_loop(self, B, cycles, prio_pool):
+        pool = np.ascontiguousarray(prio_pool, dtype=np.float32)
+        assert pool.ndim == 2 and pool.shape[1] == B
+        return getattr(self.lib, f"ref_{self.kind}_cycle_loop")(self.h, B, cycles, pool.ctypes.data,
+                                                                pool.shape[0])
+
+
+def torch_pow(priority, alpha):
+    """priority ** alpha with the function the reference calls (torch::pow on
+    a CPU float tensor with a scalar exponent, prioritized_replay.h:188,239)."""
+    import torch
+
+    t = torch.from_numpy(np.ascontiguousarray(priority, dtype=np.float32))
+    return torch.pow(t, float(np.float32(alpha))).numpy()
+
+
+def gen_trace(schema, capacity, seed, n_cycles, K, B, adds_per_cycle=(0, 3), prefill=None,
+              prio=lambda rng, n: rng.random(n).astype(np.float32) + 0.01, zero_frac=0.0):
+    """A scripted, deterministic op list that exercises fill, wrap-around and
+    eviction without ever blocking (size + n <= S) or sampling an empty buffer.
+    Ops: ("add", rows, priority) | ("sample", B) | ("update", priority)."""
+    rng = np.random.default_rng(seed)
+    S = int(1.25 * capacity)
+    ops = []
+    size = 0
+    serial = 0
+
+    def add(n):
+        nonlocal size, serial
+        rows = make_rows(schema, n, rng, serial)
+        p = prio(rng, n)
+        if zero_frac > 0:
+            p[rng.random(n) < zero_frac] = 0.0
+        ops.append(("add", rows, p))
+        serial += n
+        size += n
+
+    if prefill is None:
+        prefill = capacity // 2
+    while size < prefill:
+        add(min(K, prefill - size))
+    for _ in range(n_cycles):
+        for _ in range(int(rng.integers(adds_per_cycle[0], adds_per_cycle[1] + 1))):
+            if size + K <= S:
+                add(K)
+        ops.append(("sample", B))
+        if size > capacity:  # eviction inside sample_
+            size = capacity
+        p = prio(rng, B)
+        ops.append(("update", p))
+    return ops
+
+
+def apply_trace(impl, ops, alpha, raw_priority, want_rows=True):
+    """Run ops on an implementation. raw_priority: the implementation applies
+    ** alpha itself (reference; CUDA with device pow); otherwise it is handed
+    torch_pow(priority, alpha), the exact function the reference calls."""
+    rec = []
+    for op in ops:
+        if op[0] == "add":
+            p = op[2] if raw_priority else torch_pow(op[2], alpha)
+            impl.add(op[1], p)
+        elif op[0] == "sample":
+            rc, rows, w, ids = impl.sample(op[1], want_rows)
+            assert rc == 0, f"sample failed rc={rc}"
+            rec.append(dict(ids=ids, w=w, rows=rows, size=impl.size()))
+        elif op[0] == "update":
+            p = op[1] if raw_priority else torch_pow(op[1], alpha)
+            rc = impl.update(p)
+            assert rc == 0
+    return rec
+
+
+def compare_records(a, b, what="", w_rtol=1e-6, rows=True):
+    """ids and gathered bytes bit-exact; IS weights within w_rtol relative."""
+    assert len(a) == len(b)
+    for k, (x, y) in enumerate(zip(a, b)):
+        assert x["size"] == y["size"], f"{what} sample {k}: size {x['size']} vs {y['size']}"
+        np.testing.assert_array_equal(x["ids"], y["ids"], err_msg=f"{what} sample {k}: ids")
+        np.testing.assert_allclose(x["w"], y["w"], rtol=w_rtol, atol=0,
+                                   err_msg=f"{what} sample {k}: IS weights")
+        if rows and x["rows"] is not None and y["rows"] is not None:
+            for f, (ra, rb) in enumerate(zip(x["rows"], y["rows"])):
+                assert ra.shape == rb.shape
+                assert ra.tobytes() == rb.tobytes(), f"{what} sample {k}: field {f} bytes differ"
