@@ -89,14 +89,18 @@ int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields);
  * element i at field_base[f] + i * row_stride[f] (row_stride == NULL: rows are
  * packed, stride = row_bytes). priority: n floats. Blocks while fewer than n
  * of the S slots are free (prioritized_replay.h:47). Host rows have been
- * copied out of the caller's memory when the call returns. */
+ * copied out of the caller's memory when the call returns. `stream` matters
+ * only with RR_ROWS_DEVICE / RR_PRIO_DEVICE: it is the cudaStream_t on which
+ * those device buffers were produced; the insert is ordered after it and the
+ * stream is made to wait until the replay has read them. */
 int rr_add(rr_replay* r, int n, const void* const* field_base,
-           const uint64_t* row_stride, const float* priority, unsigned flags);
+           const uint64_t* row_stride, const float* priority, unsigned flags,
+           void* stream);
 
 /* Same with one pointer per row: row_ptrs[f * n + i]
  * (add(vector<RNNTransition>), r2d2_actor.h:301). */
 int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs,
-                const float* priority, unsigned flags);
+                const float* priority, unsigned flags, void* stream);
 
 /* sample(batchsize, device) (prioritized_replay.h:202-233, 258-328):
  * stratified proportional selection, eviction down to capacity, importance
@@ -121,6 +125,18 @@ int rr_num_add(const rr_replay* r); /* numAdd_   (prioritized_replay.h:251) */
  * (RR_OK if none) and clears it. */
 int rr_sync(rr_replay* r);
 int rr_get_stats(rr_replay* r, rr_stats* out);
+
+/* Make `stream` (caller's cudaStream_t) wait for everything issued so far on
+ * the replay's internal stream. Does not block the host. */
+int rr_stream_fence(rr_replay* r, void* stream);
+
+/* Gather-kernel timing for the roofline: while enabled, every gather launch is
+ * bracketed by CUDA events on the internal stream. rr_gather_time synchronises,
+ * returns the accumulated kernel milliseconds and launch count since enabling,
+ * and resets both. */
+int rr_set_profiling(rr_replay* r, int enabled);
+int rr_gather_time(rr_replay* r, double* total_ms, uint64_t* launches,
+                   uint64_t* bytes_per_launch);
 
 /* Test/debug introspection (synchronises). ids: the physical slot ids of the
  * batch last returned by rr_sample (the reference's sampledIds_). */

@@ -1,0 +1,79 @@
+"""ctypes view of include/rela_b200.h (the C ABI of librela_b200.so).
+
+The library is the product; this module only declares its signatures. There
+is no fallback: if the library is missing or no CUDA device is present the
+calls raise.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librela_b200.so")
+
+RR_OK, RR_ERR_ARG, RR_ERR_CUDA, RR_ERR_STATE, RR_ERR_EMPTY, RR_ERR_NOMEM, RR_ERR_OVERRUN = range(7)
+RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
+
+SYMBOLS = [
+    "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
+    "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
+    "rr_debug_state", "rr_debug_weights", "rr_stream_fence", "rr_set_profiling", "rr_gather_time", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
+]
+
+
+class RRField(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("row_bytes", C.c_uint64), ("chunks", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
+class RRStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "kernel_launches", "samples", "samples_exact", "samples_ordered", "pops", "device_errors",
+        "slab_bytes", "h2d_bytes")]
+
+
+class ReplayError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"rela_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(rela_b200 has no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp, i, f, u = C.c_void_p, C.c_int, C.c_float, C.c_uint
+        L.rr_last_error.restype = C.c_char_p
+        L.rr_create.argtypes = [C.POINTER(vp), i, i, f, f, i, i]
+        L.rr_destroy.argtypes = [vp]
+        L.rr_set_schema.argtypes = [vp, i, C.POINTER(RRField)]
+        L.rr_add.argtypes = [vp, i, vp, vp, vp, u, vp]
+        L.rr_add_rows.argtypes = [vp, i, vp, vp, u, vp]
+        L.rr_sample.argtypes = [vp, i, vp, vp, vp]
+        L.rr_update_priority.argtypes = [vp, i, vp, u, vp]
+        L.rr_size.argtypes = [vp]
+        L.rr_num_add.argtypes = [vp]
+        L.rr_sync.argtypes = [vp]
+        L.rr_get_stats.argtypes = [vp, C.POINTER(RRStats)]
+        L.rr_last_sample_ids.argtypes = [vp, i, vp]
+        L.rr_debug_state.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.rr_debug_weights.argtypes = [vp, vp, vp]
+        L.rr_stream_fence.argtypes = [vp, vp]
+        L.rr_set_profiling.argtypes = [vp, i]
+        L.rr_gather_time.argtypes = [vp, vp, vp, vp]
+        L.rr_nstep_return.argtypes = [i, i, f, vp, vp, vp, vp, vp, i, vp]
+        L.rr_td_priority.argtypes = [i, vp, vp, vp, vp, f, vp, vp]
+        L.rr_aggregate_priority.argtypes = [i, i, vp, vp, f, i, vp, vp]
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != RR_OK:
+        raise ReplayError(rc, lib().rr_last_error().decode())

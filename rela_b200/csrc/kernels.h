@@ -1,0 +1,114 @@
+// kernels.h -- launch interface between the host-side replay (replay.cu) and
+// the sm_100a kernels (row_copy.cu, select.cu, actor_math.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace rr {
+
+// ---------------------------------------------------------------- row copy
+// One kernel moves rows for both directions:
+//   GATHER (K6): src row = slab[ids[b]], dst = batch tensor in makeBatch
+//                layout [T, B, chunk] (reference rela/types.cc:8-46,140-182)
+//   INSERT (K1): src row = producer batch row b, dst = slab[(start + b) % S]
+//                (reference rela/prioritized_replay.h:61-66)
+constexpr int kMaxCopyFields = 24;
+
+struct CopyField {
+  const uint8_t* src;        // gather: slab base; insert: producer base (or null with row_ptrs)
+  uint8_t* dst;              // gather: batch tensor base; insert: slab base
+  const uint8_t* const* row_ptrs;  // insert only: one device pointer per row, or null
+  uint64_t src_row_stride;   // bytes between consecutive source rows
+  uint64_t dst_row_stride;   // gather: chunk_bytes; insert: row_bytes
+  uint64_t dst_chunk_stride; // gather: B * chunk_bytes; insert: chunk_bytes
+  uint32_t chunk_bytes;
+  uint32_t chunks;           // T
+  uint32_t pieces;           // bulk path: pieces per chunk
+  uint32_t piece_bytes;      // bulk path: bytes per piece (last piece may be shorter)
+  uint32_t vec;              // simt path: bytes per unit (1,2,4,8,16)
+  uint32_t begin;            // first item (bulk) / unit (simt) of this field in the flat index
+};
+
+struct CopyParams {
+  CopyField bulk[kMaxCopyFields];  // fields moved by cp.async.bulk through shared memory
+  CopyField simt[kMaxCopyFields];  // fields moved by ld/st (narrow or unaligned)
+  int n_bulk, n_simt;
+  uint32_t bulk_items;  // total bulk items
+  uint64_t simt_units;  // total simt units
+  const int32_t* ids;   // gather: B sampled slot ids (device); insert: null
+  int rows;             // B (gather) or n (insert)
+  int insert_start;     // insert: first slot
+  int slots;            // insert: S
+  int stages;           // smem ring depth
+  uint32_t stage_bytes; // smem bytes per stage (>= max piece_bytes)
+};
+
+// shared-memory header of row_copy_kernel: barriers + per-stage piece records
+constexpr uint32_t kCopyHeaderBytes = 384;
+constexpr int kMaxCopyStages = 16;
+
+struct CopyLaunch {
+  int grid;
+  int block;
+  size_t smem;
+};
+
+cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream);
+
+// ------------------------------------------------------------- selection
+constexpr int kGroup = 32;     // slots per level-1 group
+constexpr int kTile = 1024;    // slots per level-2 tile
+
+// Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
+// PrioritizedReplay (reference rela/prioritized_replay.h:166,343).
+struct Ctl {
+  double sum;
+  uint32_t mt[624];
+  int mti;
+  int error;                       // sticky RR_ERR_* raised by a kernel
+  unsigned long long n_exact;      // samples selected by the parallel search
+  unsigned long long n_ordered;    // samples that needed the ordered walk
+  unsigned long long n_popped;
+};
+
+struct SelectArgs {
+  Ctl* ctl;
+  float* w;             // [S_pad] priority^alpha per slot; dead slots hold 0
+  uint8_t* evicted;     // [S]
+  double* l1;           // [S_pad / 32]
+  double* l2;           // [S_pad / 1024]
+  float* l2min;         // [S_pad / 1024] min non-zero weight per tile
+  int S, S_pad;
+  int head;             // ring head at selection time
+  int size;             // safeSize_: elements the walk may visit
+  int size_is;          // size_ re-read before the pop (prioritized_replay.h:312)
+  int pop_n;            // elements to evict after selection
+  int B;
+  int32_t* ids;         // out [B]
+  float* is_weights;    // out [B] (caller memory)
+  float beta;
+  int contract_fma;
+  int force_ordered;    // test hook: always take the ordered walk
+};
+
+cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream);
+cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
+
+// add commit (K2 + weights write + sum_, prioritized_replay.h:58-73,188)
+cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const float* prio,
+                          float alpha, int is_weight, cudaStream_t stream);
+
+// updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
+cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int32_t* ids, int n,
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
+
+// ------------------------------------------------------------ actor math
+cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,
+                         float* out_reward, float* out_bootstrap, uint8_t* out_terminal, int fma,
+                         cudaStream_t stream);
+cudaError_t launch_td_priority(int K, const float* reward, const float* bootstrap, const float* q_next,
+                               const float* q_sa, float gamma_n, float* out, cudaStream_t stream);
+cudaError_t launch_aggregate(int nseq, int L, const float* priority, const float* len, float eta,
+                             int burn_in, float* out, cudaStream_t stream);
+
+}  // namespace rr

@@ -1,0 +1,1008 @@
+// replay.cu -- host side of the B200 replay behind the C ABI (include/rela_b200.h).
+//
+// Host state is control only: the ring counters of the reference's
+// ConcurrentQueue (head_, tail_, size_, safeTail_, safeSize_;
+// rela/prioritized_replay.h:156-164), its two condition variables, and the
+// bookkeeping of outstanding sampled-id sets. Everything with payload lives in
+// HBM: field slabs, weights, evicted flags, the prefix hierarchy, sum_ and the
+// mt19937 state (struct Ctl). All kernels are issued on one internal stream
+// under mutex m_, so "order of commits on the host" == "order of effects on
+// the device", which is the reference's mutex protocol.
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rela_b200.h"
+#include "kernels.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define RR_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t e_ = (expr);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(RR_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_),   \
+                  __FILE__, __LINE__);                                                    \
+  } while (0)
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+void mt_seed(uint32_t* mt, uint32_t seed) {
+  // std::mt19937::seed(value): the published MT19937 initialisation
+  mt[0] = seed;
+  for (int i = 1; i < 624; ++i) {
+    uint32_t x = mt[i - 1];
+    mt[i] = 1812433253u * (x ^ (x >> 30)) + (uint32_t)i;
+  }
+}
+
+struct FieldInfo {
+  std::string name;
+  uint64_t row_bytes;
+  uint32_t chunks;
+  uint32_t chunk_bytes;
+  uint8_t* slab;
+};
+
+// A producer lane: private stream + pinned staging, so that concurrent rr_add
+// calls overlap their host packing and H2D copies (the unlocked middle section
+// of blockAppend, rela/prioritized_replay.h:57-67).
+struct Lane {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t copied = nullptr;     // rows + priorities are in HBM
+  cudaEvent_t committed = nullptr;  // commit kernel consumed dprio
+  cudaEvent_t in = nullptr;         // marker on the caller's stream (device-resident inputs)
+  uint8_t* pinned = nullptr;
+  size_t pinned_cap = 0;
+  float* dprio = nullptr;
+  size_t dprio_cap = 0;
+  uint8_t** dptrs = nullptr;  // device copy of per-row pointers (rr_add_rows, device rows)
+  size_t dptrs_cap = 0;
+  bool busy = false;
+};
+
+struct PrioStage {
+  float* pinned = nullptr;
+  float* dev = nullptr;
+  size_t cap = 0;
+  cudaEvent_t done = nullptr;
+};
+
+struct Prefetched {
+  std::vector<uint8_t*> fields;
+  float* weights = nullptr;
+  int idslot = -1;
+  int B = 0;
+};
+
+uint32_t pow2_divisor(uint64_t v, uint32_t cap) {
+  uint32_t d = cap;
+  while (d > 1 && (v % d) != 0) d >>= 1;
+  return d;
+}
+
+}  // namespace
+
+struct rr_replay {
+  // configuration
+  int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
+  float alpha = 0, beta = 0;
+  int contract_fma = 1, force_ordered = 0;
+  int sm_count = 148;
+  int g_stages = 8, g_piece = 8192, g_ctas = 2, g_simt_only = 0;
+  std::vector<FieldInfo> fields;
+  bool schema_set = false;
+  uint64_t slab_bytes = 0;
+
+  // device state
+  float* w = nullptr;
+  uint8_t* evicted = nullptr;
+  double* l1 = nullptr;
+  double* l2 = nullptr;
+  float* l2min = nullptr;
+  rr::Ctl* ctl = nullptr;
+
+  // ring counters (rela/prioritized_replay.h:156-164)
+  mutable std::mutex m_;
+  std::condition_variable cvSize_, cvTail_;
+  int head_ = 0, tail_ = 0, size_ = 0, safeTail_ = 0, safeSize_ = 0;
+  std::atomic<int> numAdd_{0};
+
+  // streams / events
+  cudaStream_t main = nullptr;
+  cudaEvent_t evIn = nullptr, evOut = nullptr, evGather = nullptr;
+
+  // producer lanes
+  std::mutex laneM_;
+  std::condition_variable laneCv_;
+  std::vector<Lane> lanes;
+
+  // sampled ids: ring of device buffers; cur = batch handed to the learner
+  std::vector<int32_t*> idbuf;
+  std::vector<int> idcap;
+  std::vector<bool> idbusy;
+  int cur_ids = -1, cur_B = 0;
+  std::deque<Prefetched> queue;
+  std::vector<Prefetched> pool;
+
+  std::vector<PrioStage> pstage;
+  int pstage_next = 0;
+
+  // stats
+  std::atomic<uint64_t> launches{0}, samples{0}, h2d_bytes{0};
+
+  // optional gather timing (rr_set_profiling)
+  bool profiling = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+  size_t prof_used = 0;
+  double prof_ms = 0;
+  uint64_t prof_n = 0, prof_bytes = 0;
+};
+
+namespace {
+
+using rr::CopyField;
+using rr::CopyLaunch;
+using rr::CopyParams;
+
+struct CopyPlan {
+  CopyParams p;
+  CopyLaunch cfg;
+};
+
+// Split the fields of one row-copy launch into the bulk (cp.async.bulk through
+// shared memory) and simt (vector ld/st) paths and size the launch.
+int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>& in, const int32_t* ids,
+              int insert_start, CopyPlan* out) {
+  CopyParams& p = out->p;
+  memset(&p, 0, sizeof(p));
+  p.ids = ids;
+  p.rows = rows;
+  p.insert_start = insert_start;
+  p.slots = r->S;
+  uint32_t items = 0;
+  uint64_t units = 0;
+  uint32_t max_piece = 0;
+  for (const CopyField& f0 : in) {
+    CopyField f = f0;
+    if (f.chunk_bytes == 0) continue;
+    uint64_t align_bits = (uint64_t)(uintptr_t)f.src | (uint64_t)(uintptr_t)f.dst | f.src_row_stride |
+                          f.dst_row_stride | f.dst_chunk_stride | f.chunk_bytes;
+    if (f.row_ptrs != nullptr) align_bits |= f.vec;  // caller passes the OR of the row pointers in vec
+    const bool aligned16 = (align_bits % 16) == 0;
+    const bool bulk = !r->g_simt_only && aligned16 && f.chunk_bytes >= 1024;
+    if (bulk) {
+      if (p.n_bulk >= rr::kMaxCopyFields) return fail(RR_ERR_ARG, "too many wide fields");
+      f.pieces = (f.chunk_bytes + (uint32_t)r->g_piece - 1) / (uint32_t)r->g_piece;
+      uint32_t pb = (f.chunk_bytes + f.pieces - 1) / f.pieces;
+      f.piece_bytes = (pb + 15u) & ~15u;
+      f.begin = items;
+      uint64_t n = (uint64_t)rows * f.chunks * f.pieces;
+      if (items + n > 0x7fffffffull) return fail(RR_ERR_ARG, "row copy too large for one launch");
+      items += (uint32_t)n;
+      max_piece = std::max(max_piece, f.piece_bytes);
+      p.bulk[p.n_bulk++] = f;
+    } else {
+      if (p.n_simt >= rr::kMaxCopyFields) return fail(RR_ERR_ARG, "too many narrow fields");
+      f.vec = pow2_divisor(align_bits, 16);
+      f.begin = (uint32_t)units;
+      units += (uint64_t)rows * f.chunks * (f.chunk_bytes / f.vec);
+      if (units > 0xffffffffull) return fail(RR_ERR_ARG, "row copy too large for one launch");
+      p.simt[p.n_simt++] = f;
+    }
+  }
+  p.bulk_items = items;
+  p.simt_units = units;
+  p.stages = std::min(std::max(r->g_stages, 3), rr::kMaxCopyStages);
+  p.stage_bytes = (max_piece + 127u) & ~127u;
+  CopyLaunch& c = out->cfg;
+  const uint32_t ids_bytes = ids ? (uint32_t)rows * 4u : 0u;
+  if (p.n_bulk > 0) {
+    c.block = 128;
+    size_t hdr = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
+    size_t lim = 227 * 1024;
+    while (p.stages > 3 && hdr + (size_t)p.stages * p.stage_bytes > lim / (size_t)r->g_ctas) p.stages--;
+    c.smem = hdr + (size_t)p.stages * p.stage_bytes;
+    if (c.smem > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
+    int want = r->sm_count * r->g_ctas;
+    c.grid = (int)std::min<uint64_t>((uint64_t)want, std::max<uint64_t>(items, 1));
+    // enough simt threads for the narrow fields
+    uint64_t simt_ctas = (units + 96 * 8 - 1) / (96 * 8);
+    if (simt_ctas > (uint64_t)c.grid) c.grid = (int)std::min<uint64_t>(simt_ctas, (uint64_t)want);
+  } else {
+    c.block = 256;
+    c.smem = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
+    uint64_t ctas = (units + 256 * 4 - 1) / (256 * 4);
+    c.grid = (int)std::max<uint64_t>(1, std::min<uint64_t>(ctas, (uint64_t)r->sm_count * 8));
+  }
+  return RR_OK;
+}
+
+int launch_plan(rr_replay* r, const CopyPlan& plan, cudaStream_t s) {
+  if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) return RR_OK;
+  RR_CUDA(rr::launch_row_copy(plan.p, plan.cfg, s));
+  r->launches++;
+  return RR_OK;
+}
+
+}  // namespace
+
+// ============================================================== C ABI
+extern "C" {
+
+const char* rr_last_error(void) {
+  return g_err.c_str();
+}
+
+int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, int prefetch, int device) {
+  if (out == nullptr || capacity <= 0 || prefetch < 0) return fail(RR_ERR_ARG, "rr_create: bad argument");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    return fail(RR_ERR_CUDA, "rr_create: no CUDA device (%s); this library has no CPU path",
+                cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= ndev) return fail(RR_ERR_ARG, "rr_create: device %d of %d", device, ndev);
+  RR_CUDA(cudaSetDevice(device));
+  rr_replay* r = new rr_replay();
+  r->capacity = capacity;
+  r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
+  r->S_pad = ((r->S + rr::kTile - 1) / rr::kTile) * rr::kTile;
+  r->seed = seed;
+  r->alpha = alpha;
+  r->beta = beta;
+  r->prefetch = prefetch;
+  r->device = device;
+  r->contract_fma = env_int("RR_CONTRACT_FMA", 1);
+  r->force_ordered = env_int("RR_FORCE_ORDERED", 0);
+  r->g_stages = env_int("RR_GATHER_STAGES", 8);
+  r->g_piece = std::max(1024, env_int("RR_GATHER_PIECE", 8192)) & ~15;
+  r->g_ctas = std::max(1, env_int("RR_GATHER_CTAS_PER_SM", 2));
+  r->g_simt_only = env_int("RR_GATHER_SIMT", 0);
+  cudaDeviceProp prop;
+  RR_CUDA(cudaGetDeviceProperties(&prop, device));
+  r->sm_count = prop.multiProcessorCount;
+
+  RR_CUDA(cudaStreamCreateWithFlags(&r->main, cudaStreamNonBlocking));
+  RR_CUDA(cudaEventCreateWithFlags(&r->evIn, cudaEventDisableTiming));
+  RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
+  RR_CUDA(cudaEventCreateWithFlags(&r->evGather, cudaEventDisableTiming));
+
+  const size_t nt2 = (size_t)r->S_pad / rr::kTile;
+  RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
+  RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
+  RR_CUDA(cudaMalloc(&r->l1, sizeof(double) * (size_t)r->S_pad / rr::kGroup));
+  RR_CUDA(cudaMalloc(&r->l2, sizeof(double) * nt2));
+  RR_CUDA(cudaMalloc(&r->l2min, sizeof(float) * nt2));
+  RR_CUDA(cudaMalloc(&r->ctl, sizeof(rr::Ctl)));
+  RR_CUDA(cudaMemsetAsync(r->w, 0, sizeof(float) * (size_t)r->S_pad, r->main));
+  RR_CUDA(cudaMemsetAsync(r->evicted, 0, (size_t)r->S_pad, r->main));
+  rr::Ctl h;
+  memset(&h, 0, sizeof(h));
+  mt_seed(h.mt, (uint32_t)seed);  // rng_.seed(seed), rela/prioritized_replay.h:183
+  h.mti = 624;
+  RR_CUDA(cudaMemcpyAsync(r->ctl, &h, sizeof(h), cudaMemcpyHostToDevice, r->main));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+
+  const int nl = std::max(1, env_int("RR_ADD_LANES", 4));
+  r->lanes.resize(nl);
+  for (auto& l : r->lanes) {
+    RR_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+    RR_CUDA(cudaEventCreateWithFlags(&l.copied, cudaEventDisableTiming));
+    RR_CUDA(cudaEventCreateWithFlags(&l.committed, cudaEventDisableTiming));
+    RR_CUDA(cudaEventCreateWithFlags(&l.in, cudaEventDisableTiming));
+  }
+  r->pstage.resize(4);
+  for (auto& s : r->pstage) RR_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  const int nid = prefetch + 2;
+  r->idbuf.assign(nid, nullptr);
+  r->idcap.assign(nid, 0);
+  r->idbusy.assign(nid, false);
+  *out = r;
+  return RR_OK;
+}
+
+int rr_destroy(rr_replay* r) {
+  if (r == nullptr) return RR_OK;
+  cudaSetDevice(r->device);
+  cudaDeviceSynchronize();
+  for (auto& f : r->fields) cudaFree(f.slab);
+  cudaFree(r->w);
+  cudaFree(r->evicted);
+  cudaFree(r->l1);
+  cudaFree(r->l2);
+  cudaFree(r->l2min);
+  cudaFree(r->ctl);
+  for (auto& l : r->lanes) {
+    if (l.pinned) cudaFreeHost(l.pinned);
+    cudaFree(l.dprio);
+    cudaFree(l.dptrs);
+    cudaEventDestroy(l.copied);
+    cudaEventDestroy(l.committed);
+    cudaEventDestroy(l.in);
+    cudaStreamDestroy(l.stream);
+  }
+  for (auto& s : r->pstage) {
+    if (s.pinned) cudaFreeHost(s.pinned);
+    cudaFree(s.dev);
+    cudaEventDestroy(s.done);
+  }
+  for (auto* p : r->idbuf) cudaFree(p);
+  auto free_pre = [](Prefetched& p) {
+    for (auto* f : p.fields) cudaFree(f);
+    cudaFree(p.weights);
+  };
+  for (auto& p : r->queue) free_pre(p);
+  for (auto& p : r->pool) free_pre(p);
+  for (auto& pe : r->prof_events) {
+    cudaEventDestroy(pe.first);
+    cudaEventDestroy(pe.second);
+  }
+  cudaEventDestroy(r->evIn);
+  cudaEventDestroy(r->evOut);
+  cudaEventDestroy(r->evGather);
+  cudaStreamDestroy(r->main);
+  delete r;
+  return RR_OK;
+}
+
+int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields) {
+  if (r == nullptr || nfields < 0 || (nfields > 0 && fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_set_schema: bad argument");
+  if (r->schema_set) return fail(RR_ERR_STATE, "rr_set_schema: schema already set");
+  if (nfields > 2 * rr::kMaxCopyFields) return fail(RR_ERR_ARG, "rr_set_schema: too many fields");
+  RR_CUDA(cudaSetDevice(r->device));
+  uint64_t total = 0;
+  for (int i = 0; i < nfields; ++i) {
+    const rr_field& f = fields[i];
+    if (f.chunks == 0 || f.row_bytes % f.chunks != 0 || f.row_bytes >= (1ull << 32))
+      return fail(RR_ERR_ARG, "rr_set_schema: field %d: row_bytes %llu chunks %u", i,
+                  (unsigned long long)f.row_bytes, f.chunks);
+    total += f.row_bytes * (uint64_t)r->S;
+  }
+  size_t free_b = 0, total_b = 0;
+  RR_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  if (total + (1ull << 30) > free_b) {
+    return fail(RR_ERR_NOMEM, "rr_set_schema: slabs need %.1f GB, %.1f GB of HBM free",
+                total / 1e9, free_b / 1e9);
+  }
+  for (int i = 0; i < nfields; ++i) {
+    FieldInfo fi;
+    fi.name = fields[i].name ? fields[i].name : "";
+    fi.row_bytes = fields[i].row_bytes;
+    fi.chunks = fields[i].chunks;
+    fi.chunk_bytes = (uint32_t)(fi.row_bytes / fi.chunks);
+    fi.slab = nullptr;
+    if (fi.row_bytes > 0) {
+      cudaError_t e = cudaMalloc(&fi.slab, fi.row_bytes * (uint64_t)r->S);
+      if (e != cudaSuccess) {
+        for (auto& g : r->fields) cudaFree(g.slab);
+        r->fields.clear();
+        return fail(RR_ERR_NOMEM, "rr_set_schema: cudaMalloc of %.1f GB failed: %s",
+                    fi.row_bytes * (double)r->S / 1e9, cudaGetErrorString(e));
+      }
+    }
+    r->fields.push_back(fi);
+  }
+  r->slab_bytes = total;
+  r->schema_set = true;
+  return RR_OK;
+}
+
+int rr_size(const rr_replay* r) {
+  std::unique_lock<std::mutex> lk(r->m_);
+  return r->safeSize_;
+}
+
+int rr_num_add(const rr_replay* r) {
+  return r->numAdd_.load();
+}
+
+}  // extern "C"
+
+// ============================================================== add
+namespace {
+
+struct LaneGuard {
+  rr_replay* r;
+  Lane* lane = nullptr;
+  explicit LaneGuard(rr_replay* rr_) : r(rr_) {
+    std::unique_lock<std::mutex> lk(r->laneM_);
+    for (;;) {
+      for (auto& l : r->lanes) {
+        if (!l.busy) {
+          l.busy = true;
+          lane = &l;
+          return;
+        }
+      }
+      r->laneCv_.wait(lk);
+    }
+  }
+  ~LaneGuard() {
+    {
+      std::lock_guard<std::mutex> lk(r->laneM_);
+      lane->busy = false;
+    }
+    r->laneCv_.notify_one();
+  }
+};
+
+// add(...) = blockAppend (rela/prioritized_replay.h:43-78): reserve under the
+// lock, move the rows without it, commit in reservation order.
+int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t* row_stride,
+             const void* const* row_ptrs, const float* priority, unsigned flags, cudaStream_t cs) {
+  if (r == nullptr || n < 0 || priority == nullptr) return fail(RR_ERR_ARG, "rr_add: bad argument");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_add: rr_set_schema has not been called");
+  if (n == 0) return RR_OK;
+  if (n > r->S) return fail(RR_ERR_ARG, "rr_add: block of %d exceeds the %d slots", n, r->S);
+  const int nf = (int)r->fields.size();
+  const bool rows_dev = (flags & RR_ROWS_DEVICE) != 0;
+  const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
+  const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
+  RR_CUDA(cudaSetDevice(r->device));
+
+  // -- reserve [start, start + n) (rela/prioritized_replay.h:46-55); blocks while full
+  int start;
+  {
+    std::unique_lock<std::mutex> lk(r->m_);
+    r->cvSize_.wait(lk, [&] { return r->size_ + n <= r->S; });
+    start = r->tail_;
+    r->tail_ = (r->tail_ + n) % r->S;
+    r->size_ += n;
+  }
+  const int end = (start + n) % r->S;
+  const int n1 = std::min(n, r->S - start);  // rows before the wrap
+
+  LaneGuard guard(r);
+  Lane& L = *guard.lane;
+  int rc = RR_OK;
+  auto body = [&]() -> int {
+    // previous use of this lane: staging consumed, commit kernel done with dprio
+    RR_CUDA(cudaEventSynchronize(L.copied));
+    RR_CUDA(cudaStreamWaitEvent(L.stream, L.committed, 0));
+    // rows being overwritten may still be read by an in-flight gather
+    RR_CUDA(cudaStreamWaitEvent(L.stream, r->evGather, 0));
+    if ((rows_dev || prio_dev)) {
+      // order after the producer of the device-resident inputs
+      RR_CUDA(cudaEventRecord(L.in, cs));
+      RR_CUDA(cudaStreamWaitEvent(L.stream, L.in, 0));
+    }
+    size_t row_total = 0;
+    for (auto& f : r->fields) row_total += f.row_bytes;
+    size_t need = (rows_dev ? 0 : row_total * (size_t)n) + sizeof(float) * (size_t)n +
+                  (row_ptrs && rows_dev ? sizeof(void*) * (size_t)n * nf : 0);
+    if (need > L.pinned_cap) {
+      if (L.pinned) RR_CUDA(cudaFreeHost(L.pinned));
+      L.pinned = nullptr;
+      L.pinned_cap = 0;
+      size_t cap = std::max(need, (size_t)1 << 20);
+      RR_CUDA(cudaHostAlloc(&L.pinned, cap, cudaHostAllocDefault));
+      L.pinned_cap = cap;
+    }
+    if ((size_t)n > L.dprio_cap) {
+      RR_CUDA(cudaFree(L.dprio));
+      L.dprio = nullptr;
+      size_t cap = std::max((size_t)n, (size_t)4096);
+      RR_CUDA(cudaMalloc(&L.dprio, sizeof(float) * cap));
+      L.dprio_cap = cap;
+    }
+    uint8_t* stage = L.pinned;
+    if (!rows_dev) {
+      // pack host rows into pinned memory, then one or two H2D copies per field
+      // straight into the slab (the block's slots are contiguous modulo S)
+      for (int fi = 0; fi < nf; ++fi) {
+        const FieldInfo& f = r->fields[fi];
+        if (f.row_bytes == 0) continue;
+        const uint64_t stride = row_stride ? row_stride[fi] : f.row_bytes;
+        if (!row_ptrs && stride == f.row_bytes) {
+          memcpy(stage, field_base[fi], f.row_bytes * (size_t)n);
+        } else {
+          for (int i = 0; i < n; ++i) {
+            const void* src = row_ptrs ? row_ptrs[(size_t)fi * n + i]
+                                       : static_cast<const uint8_t*>(field_base[fi]) + (size_t)i * stride;
+            memcpy(stage + (size_t)i * f.row_bytes, src, f.row_bytes);
+          }
+        }
+        RR_CUDA(cudaMemcpyAsync(f.slab + (size_t)start * f.row_bytes, stage, f.row_bytes * (size_t)n1,
+                                cudaMemcpyHostToDevice, L.stream));
+        if (n1 < n) {
+          RR_CUDA(cudaMemcpyAsync(f.slab, stage + (size_t)n1 * f.row_bytes, f.row_bytes * (size_t)(n - n1),
+                                  cudaMemcpyHostToDevice, L.stream));
+        }
+        stage += f.row_bytes * (size_t)n;
+      }
+      r->h2d_bytes += row_total * (uint64_t)n;
+    } else {
+      // K1: device-resident rows -> slab with the row-copy kernel
+      const uint8_t* const* dptrs = nullptr;
+      std::vector<uint64_t> ptr_or(nf, 0);
+      if (row_ptrs) {
+        size_t bytes = sizeof(void*) * (size_t)n * nf;
+        if (bytes > L.dptrs_cap) {
+          RR_CUDA(cudaFree(L.dptrs));
+          L.dptrs = nullptr;
+          RR_CUDA(cudaMalloc(&L.dptrs, bytes));
+          L.dptrs_cap = bytes;
+        }
+        uint8_t* hp = stage + sizeof(float) * (size_t)n;
+        memcpy(hp, row_ptrs, bytes);
+        RR_CUDA(cudaMemcpyAsync(L.dptrs, hp, bytes, cudaMemcpyHostToDevice, L.stream));
+        dptrs = L.dptrs;
+        for (int fi = 0; fi < nf; ++fi)
+          for (int i = 0; i < n; ++i) ptr_or[fi] |= (uint64_t)(uintptr_t)row_ptrs[(size_t)fi * n + i];
+      }
+      std::vector<CopyField> cf;
+      for (int fi = 0; fi < nf; ++fi) {
+        const FieldInfo& f = r->fields[fi];
+        if (f.row_bytes == 0) continue;
+        CopyField c;
+        memset(&c, 0, sizeof(c));
+        c.dst = f.slab;
+        c.chunks = 1;
+        c.chunk_bytes = (uint32_t)f.row_bytes;
+        c.dst_row_stride = f.row_bytes;
+        c.dst_chunk_stride = f.row_bytes;
+        if (row_ptrs) {
+          c.row_ptrs = dptrs + (size_t)fi * n;
+          c.vec = (uint32_t)(ptr_or[fi] & 15u) | 16u;  // alignment evidence for plan_copy
+          c.src_row_stride = 0;
+        } else {
+          c.src = static_cast<const uint8_t*>(field_base[fi]);
+          c.src_row_stride = row_stride ? row_stride[fi] : f.row_bytes;
+        }
+        cf.push_back(c);
+      }
+      CopyPlan plan;
+      int prc = plan_copy(r, false, n, cf, nullptr, start, &plan);
+      if (prc != RR_OK) return prc;
+      prc = launch_plan(r, plan, L.stream);
+      if (prc != RR_OK) return prc;
+    }
+    if (!prio_dev) {
+      float* hp = reinterpret_cast<float*>(L.pinned + (rows_dev ? 0 : row_total * (size_t)n));
+      memcpy(hp, priority, sizeof(float) * (size_t)n);
+      RR_CUDA(cudaMemcpyAsync(L.dprio, hp, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, L.stream));
+    }
+    RR_CUDA(cudaEventRecord(L.copied, L.stream));
+    return RR_OK;
+  };
+  rc = body();
+
+  // -- commit in reservation order (rela/prioritized_replay.h:69-77)
+  {
+    std::unique_lock<std::mutex> lk(r->m_);
+    r->cvTail_.wait(lk, [&] { return r->safeTail_ == start; });
+    if (rc == RR_OK) {
+      cudaError_t e = cudaStreamWaitEvent(r->main, L.copied, 0);
+      if (e == cudaSuccess) {
+        e = rr::launch_commit(r->ctl, r->w, r->S, start, n, prio_dev ? priority : L.dprio, r->alpha,
+                              is_weight, r->main);
+        r->launches++;
+      }
+      if (e == cudaSuccess) e = cudaEventRecord(L.committed, r->main);
+      if (e == cudaSuccess && (rows_dev || prio_dev)) e = cudaStreamWaitEvent(cs, L.committed, 0);
+      if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "rr_add commit: %s", cudaGetErrorString(e));
+    }
+    // On failure the slots are still committed (weight 0 keeps them unsampled)
+    // so that the ring invariants of later calls hold.
+    r->safeTail_ = end;
+    r->safeSize_ += n;
+  }
+  r->cvTail_.notify_all();
+  if (rc == RR_OK) r->numAdd_ += n;
+  return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rr_add(rr_replay* r, int n, const void* const* field_base, const uint64_t* row_stride,
+           const float* priority, unsigned flags, void* stream) {
+  if (r != nullptr && !r->fields.empty() && field_base == nullptr && n > 0)
+    return fail(RR_ERR_ARG, "rr_add: field_base is null");
+  return add_impl(r, n, field_base, row_stride, nullptr, priority, flags, static_cast<cudaStream_t>(stream));
+}
+
+int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs, const float* priority, unsigned flags,
+                void* stream) {
+  if (r != nullptr && !r->fields.empty() && row_ptrs == nullptr && n > 0)
+    return fail(RR_ERR_ARG, "rr_add_rows: row_ptrs is null");
+  return add_impl(r, n, nullptr, nullptr, row_ptrs, priority, flags, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"
+
+// ============================================================== sample / update
+namespace {
+
+int ensure_idbuf(rr_replay* r, int slot, int B) {
+  if (r->idcap[slot] < B) {
+    RR_CUDA(cudaFree(r->idbuf[slot]));
+    r->idbuf[slot] = nullptr;
+    int cap = std::max(B, 1024);
+    RR_CUDA(cudaMalloc(&r->idbuf[slot], sizeof(int32_t) * (size_t)cap));
+    r->idcap[slot] = cap;
+  }
+  return RR_OK;
+}
+
+int free_idslot(rr_replay* r) {
+  for (size_t i = 0; i < r->idbusy.size(); ++i)
+    if (!r->idbusy[i]) return (int)i;
+  return -1;
+}
+
+// sample_ (rela/prioritized_replay.h:258-328): selection, eviction, IS weights
+// and makeBatch, issued as three kernels on the internal stream. The caller's
+// stream has already been ordered before `main` (evIn) by rr_sample.
+int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot) {
+  int rc = ensure_idbuf(r, idslot, B);
+  if (rc != RR_OK) return rc;
+  std::unique_lock<std::mutex> lk(r->m_);
+  if (r->safeSize_ == 0) return fail(RR_ERR_EMPTY, "rr_sample: buffer is empty");
+  rr::SelectArgs a;
+  memset(&a, 0, sizeof(a));
+  a.ctl = r->ctl;
+  a.w = r->w;
+  a.evicted = r->evicted;
+  a.l1 = r->l1;
+  a.l2 = r->l2;
+  a.l2min = r->l2min;
+  a.S = r->S;
+  a.S_pad = r->S_pad;
+  a.head = r->head_;
+  a.size = r->safeSize_;
+  a.size_is = r->size_;  // storage_.size(), re-read at line 312: includes in-flight appends
+  a.pop_n = r->size_ > r->capacity ? r->size_ - r->capacity : 0;
+  if (a.pop_n > r->safeSize_)
+    return fail(RR_ERR_STATE, "rr_sample: eviction of %d exceeds the %d committed elements", a.pop_n,
+                r->safeSize_);
+  a.B = B;
+  a.ids = r->idbuf[idslot];
+  a.is_weights = out_w;
+  a.beta = r->beta;
+  a.contract_fma = r->contract_fma;
+  a.force_ordered = r->force_ordered;
+  RR_CUDA(rr::launch_build_hierarchy(a, r->main));
+  RR_CUDA(rr::launch_select(a, r->main));
+  r->launches += 2;
+
+  std::vector<CopyField> cf;
+  for (size_t fi = 0; fi < r->fields.size(); ++fi) {
+    const FieldInfo& f = r->fields[fi];
+    if (f.row_bytes == 0) continue;
+    CopyField c;
+    memset(&c, 0, sizeof(c));
+    c.src = f.slab;
+    c.dst = static_cast<uint8_t*>(out_fields[fi]);
+    c.src_row_stride = f.row_bytes;
+    c.dst_row_stride = f.chunk_bytes;
+    c.dst_chunk_stride = (uint64_t)B * f.chunk_bytes;
+    c.chunk_bytes = f.chunk_bytes;
+    c.chunks = f.chunks;
+    cf.push_back(c);
+  }
+  CopyPlan plan;
+  rc = plan_copy(r, true, B, cf, a.ids, 0, &plan);
+  if (rc != RR_OK) return rc;
+  std::pair<cudaEvent_t, cudaEvent_t>* pe = nullptr;
+  if (r->profiling) {
+    if (r->prof_used == r->prof_events.size()) {
+      cudaEvent_t a0, a1;
+      RR_CUDA(cudaEventCreate(&a0));
+      RR_CUDA(cudaEventCreate(&a1));
+      r->prof_events.emplace_back(a0, a1);
+    }
+    pe = &r->prof_events[r->prof_used++];
+    RR_CUDA(cudaEventRecord(pe->first, r->main));
+  }
+  rc = launch_plan(r, plan, r->main);
+  if (rc != RR_OK) return rc;
+  if (pe) {
+    RR_CUDA(cudaEventRecord(pe->second, r->main));
+    uint64_t rowb = 0;
+    for (auto& f : r->fields) rowb += f.row_bytes;
+    r->prof_bytes = 2 * rowb * (uint64_t)B;
+  }
+  RR_CUDA(cudaEventRecord(r->evGather, r->main));
+
+  // blockPop bookkeeping (rela/prioritized_replay.h:94-102)
+  if (a.pop_n > 0) {
+    r->head_ = (r->head_ + a.pop_n) % r->S;
+    r->safeSize_ -= a.pop_n;
+    r->size_ -= a.pop_n;
+  }
+  lk.unlock();
+  if (a.pop_n > 0) r->cvSize_.notify_all();
+  r->samples++;
+  return RR_OK;
+}
+
+int acquire_prefetch_buffers(rr_replay* r, int B, Prefetched* out) {
+  for (size_t i = 0; i < r->pool.size(); ++i) {
+    if (r->pool[i].B == B) {
+      *out = r->pool[i];
+      r->pool.erase(r->pool.begin() + (long)i);
+      return RR_OK;
+    }
+  }
+  Prefetched p;
+  p.B = B;
+  for (auto& f : r->fields) {
+    uint8_t* d = nullptr;
+    if (f.row_bytes > 0) RR_CUDA(cudaMalloc(&d, f.row_bytes * (size_t)B));
+    p.fields.push_back(d);
+  }
+  RR_CUDA(cudaMalloc(&p.weights, sizeof(float) * (size_t)B));
+  *out = p;
+  return RR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
+  if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_sample: bad argument");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
+  if (r->cur_ids >= 0) {
+    // "Error: previous samples' priority has not been updated." (line 204)
+    return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
+  }
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  RR_CUDA(cudaSetDevice(r->device));
+  // out buffers may have been used on the caller's stream before
+  RR_CUDA(cudaEventRecord(r->evIn, cs));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+
+  int rc;
+  int slot;
+  if (r->prefetch == 0 || r->queue.empty()) {
+    slot = free_idslot(r);
+    rc = sample_into(r, batch, out_fields, out_weights, slot);
+    if (rc != RR_OK) return rc;
+  } else {
+    // futures_.front().get() (line 220): the batch selected earlier
+    Prefetched p = r->queue.front();
+    if (p.B != batch) return fail(RR_ERR_ARG, "rr_sample: batch %d differs from the prefetched %d", batch, p.B);
+    r->queue.pop_front();
+    for (size_t fi = 0; fi < r->fields.size(); ++fi) {
+      if (r->fields[fi].row_bytes == 0) continue;
+      RR_CUDA(cudaMemcpyAsync(out_fields[fi], p.fields[fi], r->fields[fi].row_bytes * (size_t)batch,
+                              cudaMemcpyDeviceToDevice, r->main));
+    }
+    RR_CUDA(cudaMemcpyAsync(out_weights, p.weights, sizeof(float) * (size_t)batch, cudaMemcpyDeviceToDevice,
+                            r->main));
+    slot = p.idslot;
+    p.idslot = -1;
+    r->pool.push_back(p);
+  }
+  r->idbusy[slot] = true;
+  r->cur_ids = slot;
+  r->cur_B = batch;
+  RR_CUDA(cudaEventRecord(r->evOut, r->main));
+  RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+
+  // top the queue up to `prefetch` batches (lines 223-230); they are selected
+  // now, i.e. before this batch's updatePriority, like the reference's futures
+  while ((int)r->queue.size() < r->prefetch) {
+    Prefetched p;
+    rc = acquire_prefetch_buffers(r, batch, &p);
+    if (rc != RR_OK) return rc;
+    p.idslot = free_idslot(r);
+    std::vector<void*> ptrs(p.fields.begin(), p.fields.end());
+    rc = sample_into(r, batch, ptrs.data(), p.weights, p.idslot);
+    if (rc != RR_OK) {
+      r->pool.push_back(p);
+      return rc;
+    }
+    r->idbusy[p.idslot] = true;
+    r->queue.push_back(p);
+  }
+  return RR_OK;
+}
+
+int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flags, void* stream) {
+  if (r == nullptr || priority == nullptr || n < 0) return fail(RR_ERR_ARG, "rr_update_priority: bad argument");
+  if (r->cur_ids < 0) return fail(RR_ERR_STATE, "rr_update_priority: no sampled batch is outstanding");
+  if (n != r->cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
+    return fail(RR_ERR_ARG, "rr_update_priority: %d priorities for a batch of %d", n, r->cur_B);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  RR_CUDA(cudaSetDevice(r->device));
+  const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
+  const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
+  const float* dprio = priority;
+  std::unique_lock<std::mutex> lk(r->m_);
+  if (prio_dev) {
+    RR_CUDA(cudaEventRecord(r->evIn, cs));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  } else {
+    PrioStage& st = r->pstage[r->pstage_next];
+    r->pstage_next = (r->pstage_next + 1) % (int)r->pstage.size();
+    RR_CUDA(cudaEventSynchronize(st.done));
+    if ((size_t)n > st.cap) {
+      if (st.pinned) RR_CUDA(cudaFreeHost(st.pinned));
+      RR_CUDA(cudaFree(st.dev));
+      st.pinned = nullptr;
+      st.dev = nullptr;
+      size_t cap = std::max((size_t)n, (size_t)4096);
+      RR_CUDA(cudaHostAlloc(&st.pinned, sizeof(float) * cap, cudaHostAllocDefault));
+      RR_CUDA(cudaMalloc(&st.dev, sizeof(float) * cap));
+      st.cap = cap;
+    }
+    memcpy(st.pinned, priority, sizeof(float) * (size_t)n);
+    RR_CUDA(cudaMemcpyAsync(st.dev, st.pinned, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, r->main));
+    RR_CUDA(cudaEventRecord(st.done, r->main));
+    dprio = st.dev;
+  }
+  RR_CUDA(rr::launch_update(r->ctl, r->w, r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha, is_weight,
+                            r->main));
+  r->launches++;
+  if (prio_dev) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
+  r->idbusy[r->cur_ids] = false;  // sampledIds_.clear(), line 244
+  r->cur_ids = -1;
+  r->cur_B = 0;
+  return RR_OK;
+}
+
+int rr_sync(rr_replay* r) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_sync: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  for (auto& l : r->lanes) RR_CUDA(cudaStreamSynchronize(l.stream));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  int err = 0;
+  RR_CUDA(cudaMemcpy(&err, &r->ctl->error, sizeof(int), cudaMemcpyDeviceToHost));
+  if (err != 0) {
+    int zero = 0;
+    RR_CUDA(cudaMemcpy(&r->ctl->error, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    return fail(err, "device-side error %d (%s)", err,
+                err == RR_ERR_OVERRUN ? "prefix walk overran the buffer, reference asserts here" : "?");
+  }
+  return RR_OK;
+}
+
+int rr_stream_fence(rr_replay* r, void* stream) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  std::unique_lock<std::mutex> lk(r->m_);
+  RR_CUDA(cudaEventRecord(r->evOut, r->main));
+  RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
+  return RR_OK;
+}
+
+int rr_set_profiling(rr_replay* r, int enabled) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_set_profiling: null");
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  r->profiling = enabled != 0;
+  r->prof_used = 0;
+  r->prof_ms = 0;
+  r->prof_n = 0;
+  return RR_OK;
+}
+
+int rr_gather_time(rr_replay* r, double* total_ms, uint64_t* launches, uint64_t* bytes_per_launch) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_gather_time: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  double ms = 0;
+  for (size_t i = 0; i < r->prof_used; ++i) {
+    float t = 0;
+    RR_CUDA(cudaEventElapsedTime(&t, r->prof_events[i].first, r->prof_events[i].second));
+    ms += t;
+  }
+  if (total_ms) *total_ms = ms;
+  if (launches) *launches = r->prof_used;
+  if (bytes_per_launch) *bytes_per_launch = r->prof_bytes;
+  r->prof_used = 0;
+  return RR_OK;
+}
+
+int rr_get_stats(rr_replay* r, rr_stats* out) {
+  if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_get_stats: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  rr::Ctl h;
+  RR_CUDA(cudaMemcpy(&h, r->ctl, sizeof(h), cudaMemcpyDeviceToHost));
+  out->kernel_launches = r->launches.load();
+  out->samples = r->samples.load();
+  out->samples_exact = h.n_exact;
+  out->samples_ordered = h.n_ordered;
+  out->pops = h.n_popped;
+  out->device_errors = (uint64_t)h.error;
+  out->slab_bytes = r->slab_bytes;
+  out->h2d_bytes = r->h2d_bytes.load();
+  return RR_OK;
+}
+
+int rr_last_sample_ids(rr_replay* r, int n, int32_t* out) {
+  if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_last_sample_ids: null");
+  if (r->cur_ids < 0 || n != r->cur_B) return fail(RR_ERR_STATE, "rr_last_sample_ids: no batch of %d outstanding", n);
+  RR_CUDA(cudaSetDevice(r->device));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_CUDA(cudaMemcpy(out, r->idbuf[r->cur_ids], sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+  return RR_OK;
+}
+
+int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size, double* sum) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_state: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  {
+    std::unique_lock<std::mutex> lk(r->m_);
+    if (head) *head = r->head_;
+    if (tail) *tail = r->tail_;
+    if (size) *size = r->size_;
+    if (safe_size) *safe_size = r->safeSize_;
+  }
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  if (sum) RR_CUDA(cudaMemcpy(sum, &r->ctl->sum, sizeof(double), cudaMemcpyDeviceToHost));
+  return RR_OK;
+}
+
+int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_weights: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  if (out_w) RR_CUDA(cudaMemcpy(out_w, r->w, sizeof(float) * (size_t)r->S, cudaMemcpyDeviceToHost));
+  if (out_evicted) RR_CUDA(cudaMemcpy(out_evicted, r->evicted, (size_t)r->S, cudaMemcpyDeviceToHost));
+  return RR_OK;
+}
+
+// -------------------------------------------------------------- actor math
+int rr_nstep_return(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,
+                    float* out_reward, float* out_bootstrap, uint8_t* out_terminal, int contract_fma,
+                    void* stream) {
+  if (n_step < 1 || K < 0 || !reward || !terminal || !out_reward || !out_bootstrap || !out_terminal)
+    return fail(RR_ERR_ARG, "rr_nstep_return: bad argument");
+  RR_CUDA(rr::launch_nstep(n_step, K, gamma, reward, terminal, out_reward, out_bootstrap, out_terminal,
+                           contract_fma, static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
+int rr_td_priority(int K, const float* reward, const float* bootstrap, const float* q_next, const float* q_sa,
+                   float gamma_n, float* out_priority, void* stream) {
+  if (K < 0 || !reward || !bootstrap || !q_next || !q_sa || !out_priority)
+    return fail(RR_ERR_ARG, "rr_td_priority: bad argument");
+  RR_CUDA(rr::launch_td_priority(K, reward, bootstrap, q_next, q_sa, gamma_n, out_priority,
+                                 static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
+int rr_aggregate_priority(int nseq, int seq_len, const float* priority, const float* len, float eta,
+                          int burn_in, float* out_priority, void* stream) {
+  if (nseq < 0 || seq_len < 1 || !priority || !len || !out_priority)
+    return fail(RR_ERR_ARG, "rr_aggregate_priority: bad argument");
+  RR_CUDA(rr::launch_aggregate(nseq, seq_len, priority, len, eta, burn_in, out_priority,
+                               static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
+}  // extern "C"

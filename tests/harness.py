@@ -405,3 +405,119 @@ def compare_records(a, b, what="", w_rtol=1e-6, rows=True):
             for f, (ra, rb) in enumerate(zip(x["rows"], y["rows"])):
                 assert ra.shape == rb.shape
                 assert ra.tobytes() == rb.tobytes(), f"{what} sample {k}: field {f} bytes differ"
+
+
+class CudaReplay(_Base):
+    """The product, driven through the C ABI (include/rela_b200.h) with the
+    same flat-rows protocol as Oracle / RefReplay. Host numpy rows go in via
+    rr_add (or device tensors with device_rows=True); batches are gathered on
+    the GPU and copied back for comparison."""
+
+    def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0, is_weight=True,
+                 device_rows=False, device=0):
+        import torch
+        from rela_b200 import capi
+
+        self.torch, self.capi = torch, capi
+        self.lib = capi.lib()
+        self.schema = schema
+        self.S = int(1.25 * capacity)
+        self.is_weight = is_weight
+        self.device_rows = device_rows
+        self.dev = torch.device("cuda", device)
+        h = C.c_void_p()
+        capi.check(self.lib.rr_create(C.byref(h), capacity, seed, alpha, beta, prefetch, device))
+        self.h = h
+        arr = (capi.RRField * max(1, len(schema)))()
+        self._names = [f.name.encode() for f in schema]
+        for i, f in enumerate(schema):
+            arr[i].name = self._names[i]
+            arr[i].row_bytes = f.row_bytes
+            arr[i].chunks = f.chunks
+        capi.check(self.lib.rr_set_schema(h, len(schema), arr))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.rr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _flags(self):
+        return self.capi.RR_PRIO_IS_WEIGHT if self.is_weight else 0
+
+    def add(self, rows, priority):
+        p = np.ascontiguousarray(priority, dtype=np.float32)
+        flags = self._flags()
+        stream = None
+        if self.device_rows:
+            t = self.torch
+            keep = [t.from_numpy(np.ascontiguousarray(r).view(np.uint8).reshape(-1)).to(self.dev) for r in rows]
+            ptrs = (C.c_void_p * max(1, len(keep)))(*[k.data_ptr() for k in keep])
+            flags |= self.capi.RR_ROWS_DEVICE
+            stream = C.c_void_p(t.cuda.current_stream(self.dev).cuda_stream)
+        else:
+            ptrs = _ptr_array(rows)
+        self.capi.check(self.lib.rr_add(self.h, len(p), ptrs, None, p.ctypes.data, flags, stream))
+
+    def add_rows(self, rows, priority):
+        """Same elements through rr_add_rows (one pointer per row)."""
+        p = np.ascontiguousarray(priority, dtype=np.float32)
+        n = len(p)
+        ptrs = (C.c_void_p * max(1, len(rows) * n))()
+        for f, r in enumerate(rows):
+            rb = self.schema[f].row_bytes
+            for i in range(n):
+                ptrs[f * n + i] = r.ctypes.data + i * rb
+        self.capi.check(self.lib.rr_add_rows(self.h, n, ptrs, p.ctypes.data, self._flags(), None))
+
+    def sample(self, B, want_rows=True):
+        t = self.torch
+        outs = [t.empty(max(1, f.row_bytes * B), dtype=t.uint8, device=self.dev) for f in self.schema]
+        w = t.empty(B, dtype=t.float32, device=self.dev)
+        ptrs = (C.c_void_p * max(1, len(outs)))(*[o.data_ptr() for o in outs])
+        stream = C.c_void_p(t.cuda.current_stream(self.dev).cuda_stream)
+        rc = self.lib.rr_sample(self.h, B, ptrs, w.data_ptr(), stream)
+        if rc != 0:
+            return rc, None, None, None
+        ids = np.zeros(B, dtype=np.int32)
+        self.capi.check(self.lib.rr_last_sample_ids(self.h, B, ids.ctypes.data))
+        rows = None
+        if want_rows:
+            rows = []
+            for f, o in zip(self.schema, outs):
+                a = o.cpu().numpy()[: f.row_bytes * B]
+                rows.append(a.view(f.dtype).reshape(f.batch_shape(B)))
+        return 0, rows, w.cpu().numpy(), ids
+
+    def update(self, priority):
+        p = np.ascontiguousarray(priority, dtype=np.float32)
+        return self.lib.rr_update_priority(self.h, len(p), p.ctypes.data, self._flags(), None)
+
+    def size(self):
+        return self.lib.rr_size(self.h)
+
+    def num_add(self):
+        return self.lib.rr_num_add(self.h)
+
+    def sync(self):
+        return self.lib.rr_sync(self.h)
+
+    def state(self):
+        v = [C.c_int() for _ in range(4)]
+        s = C.c_double()
+        self.capi.check(self.lib.rr_debug_state(self.h, *[C.addressof(x) for x in v], C.addressof(s)))
+        return dict(head=v[0].value, tail=v[1].value, size=v[2].value, safe_size=v[3].value,
+                    sum=s.value)
+
+    def weights(self):
+        w = np.zeros(self.S, dtype=np.float32)
+        e = np.zeros(self.S, dtype=np.uint8)
+        self.capi.check(self.lib.rr_debug_weights(self.h, w.ctypes.data, e.ctypes.data))
+        return w, e
+
+    def stats(self):
+        st = self.capi.RRStats()
+        self.capi.check(self.lib.rr_get_stats(self.h, C.byref(st)))
+        return {n: getattr(st, n) for n, _ in st._fields_}
