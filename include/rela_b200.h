@@ -144,6 +144,8 @@ int rr_last_sample_ids(rr_replay* r, int n, int32_t* out_ids_host);
 int rr_debug_state(rr_replay* r, int* head, int* tail, int* size,
                    int* safe_size, double* sum);
 int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host);
+/* clock64 stamps at the phase boundaries of the last selection kernel (16 x u64). */
+int rr_debug_select_probe(rr_replay* r, uint64_t* out16);
 
 /* ---------------------------------------------------------------------------
  * Actor-side transition assembly (device pointers, async on `stream`).

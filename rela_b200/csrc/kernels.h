@@ -41,11 +41,12 @@ struct CopyParams {
   int slots;            // insert: S
   int stages;           // smem ring depth
   uint32_t stage_bytes; // smem bytes per stage (>= max piece_bytes)
+  unsigned long long* probe;  // debug: 8 timestamps per CTA (tools/gather_probe.cu), else null
 };
 
 // shared-memory header of row_copy_kernel: barriers + per-stage piece records
-constexpr uint32_t kCopyHeaderBytes = 384;
-constexpr int kMaxCopyStages = 16;
+constexpr uint32_t kCopyHeaderBytes = 256;
+constexpr int kMaxCopyStages = 32;
 
 struct CopyLaunch {
   int grid;
@@ -69,6 +70,7 @@ struct Ctl {
   unsigned long long n_exact;      // samples selected by the parallel search
   unsigned long long n_ordered;    // samples that needed the ordered walk
   unsigned long long n_popped;
+  unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel
 };
 
 struct SelectArgs {

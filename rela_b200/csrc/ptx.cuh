@@ -89,4 +89,10 @@ __device__ __forceinline__ void stg_stream16(void* p, const uint4& v) {
                : "memory");
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 }  // namespace rr

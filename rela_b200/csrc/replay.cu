@@ -112,7 +112,7 @@ struct rr_replay {
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
   int sm_count = 148;
-  int g_stages = 8, g_piece = 8192, g_ctas = 2, g_simt_only = 0;
+  int g_stages = 32, g_piece = 8192, g_ctas = 1, g_simt_only = 0;
   std::vector<FieldInfo> fields;
   bool schema_set = false;
   uint64_t slab_bytes = 0;
@@ -216,19 +216,21 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
   }
   p.bulk_items = items;
   p.simt_units = units;
-  p.stages = std::min(std::max(r->g_stages, 3), rr::kMaxCopyStages);
   p.stage_bytes = (max_piece + 127u) & ~127u;
   CopyLaunch& c = out->cfg;
   const uint32_t ids_bytes = ids ? (uint32_t)rows * 4u : 0u;
   if (p.n_bulk > 0) {
     c.block = 128;
-    size_t hdr = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
-    size_t lim = 227 * 1024;
-    while (p.stages > 3 && hdr + (size_t)p.stages * p.stage_bytes > lim / (size_t)r->g_ctas) p.stages--;
-    c.smem = hdr + (size_t)p.stages * p.stage_bytes;
-    if (c.smem > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
-    int want = r->sm_count * r->g_ctas;
+    const size_t hdr = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
+    const size_t lim = (size_t)227 * 1024 / (size_t)r->g_ctas - 1024;  // 1 KB per-CTA system reserve
+    if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
+    const int want = r->sm_count * r->g_ctas;
     c.grid = (int)std::min<uint64_t>((uint64_t)want, std::max<uint64_t>(items, 1));
+    // one stage per item of the busiest CTA, as many as fit
+    int per_cta = (int)((items + (uint32_t)c.grid - 1) / (uint32_t)c.grid);
+    int fit = (int)((lim - hdr) / p.stage_bytes);
+    p.stages = std::max(1, std::min(std::min(per_cta, fit), std::min(r->g_stages, rr::kMaxCopyStages)));
+    c.smem = hdr + (size_t)p.stages * p.stage_bytes;
     // enough simt threads for the narrow fields
     uint64_t simt_ctas = (units + 96 * 8 - 1) / (96 * 8);
     if (simt_ctas > (uint64_t)c.grid) c.grid = (int)std::min<uint64_t>(simt_ctas, (uint64_t)want);
@@ -278,9 +280,9 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   r->device = device;
   r->contract_fma = env_int("RR_CONTRACT_FMA", 1);
   r->force_ordered = env_int("RR_FORCE_ORDERED", 0);
-  r->g_stages = env_int("RR_GATHER_STAGES", 8);
+  r->g_stages = env_int("RR_GATHER_STAGES", 32);
   r->g_piece = std::max(1024, env_int("RR_GATHER_PIECE", 8192)) & ~15;
-  r->g_ctas = std::max(1, env_int("RR_GATHER_CTAS_PER_SM", 2));
+  r->g_ctas = std::max(1, env_int("RR_GATHER_CTAS_PER_SM", 1));
   r->g_simt_only = env_int("RR_GATHER_SIMT", 0);
   cudaDeviceProp prop;
   RR_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -964,6 +966,14 @@ int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size
   }
   RR_CUDA(cudaStreamSynchronize(r->main));
   if (sum) RR_CUDA(cudaMemcpy(sum, &r->ctl->sum, sizeof(double), cudaMemcpyDeviceToHost));
+  return RR_OK;
+}
+
+int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
+  if (r == nullptr || out16 == nullptr) return fail(RR_ERR_ARG, "rr_debug_select_probe: null");
+  RR_CUDA(cudaSetDevice(r->device));
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_CUDA(cudaMemcpy(out16, r->ctl->probe, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
   return RR_OK;
 }
 

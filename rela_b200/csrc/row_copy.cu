@@ -83,59 +83,59 @@ __device__ __forceinline__ Item decode_item(const CopyParams& p, const int32_t* 
 
 __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ CopyParams p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
-  // layout: 16 mbarriers | 16 x (dst, bytes) of the piece held by each stage |
-  //         ids[rows] (gather) | pad to 128 | stages * stage_bytes
+  // layout: 32 mbarriers | ids[rows] (gather) | pad to 128 | stages * stage_bytes
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
-  uint8_t** st_dst = reinterpret_cast<uint8_t**>(smem_raw + 128);
-  uint32_t* st_bytes = reinterpret_cast<uint32_t*>(smem_raw + 256);
   int32_t* s_ids = reinterpret_cast<int32_t*>(smem_raw + kCopyHeaderBytes);
   const uint32_t ids_bytes = p.ids != nullptr ? (uint32_t)p.rows * 4u : 0u;
   uint8_t* stage0 = smem_raw + ((kCopyHeaderBytes + ids_bytes + 127u) & ~127u);
 
   const int tid = threadIdx.x;
+  unsigned long long* probe = p.probe ? p.probe + (size_t)blockIdx.x * 8 : nullptr;
+  if (probe && tid == 0) {
+    probe[0] = globaltimer_ns();
+    probe[1] = clock64();
+  }
   if (p.ids != nullptr) {
     for (int i = tid; i < p.rows; i += blockDim.x) s_ids[i] = p.ids[i];
   }
-  if (tid == 0 && p.n_bulk > 0) {
-    for (int s = 0; s < p.stages; ++s) mbar_init(&full[s], 1);
-    mbar_fence_init();
-  }
+  if (tid < p.stages && p.n_bulk > 0) mbar_init(&full[tid], 1);
+  if (tid < 32 && p.n_bulk > 0) mbar_fence_init();
   __syncthreads();
 
   const bool bulk_warp = (p.n_bulk > 0) && (tid < 32);
   if (bulk_warp) {
-    if (tid == 0) {
-      // ---- bulk pipeline over items blockIdx.x, +gridDim.x, ...
-      // Loads run `stages - 2` pieces ahead of the stores; the stage refilled
-      // at step k was read by store k - 2, so one store may still be draining.
+    // ---- bulk path. Lane l owns stage l: it streams the CTA's items
+    // l, l + stages, ... through its own shared-memory stage, so up to
+    // `stages` loads per CTA are in flight and the per-item address
+    // arithmetic is spread over the warp instead of serialised on one thread.
+    const uint32_t NS = (uint32_t)p.stages;
+    if ((uint32_t)tid < NS) {
       const uint32_t n_items = p.bulk_items;
       const uint32_t first = blockIdx.x;
       const uint32_t step = gridDim.x;
       const uint32_t mine = first < n_items ? (n_items - first + step - 1) / step : 0;
-      const uint32_t NS = (uint32_t)p.stages;
-      const uint32_t ahead = NS - 2;
-      uint32_t issued = 0;
-      auto issue_load = [&](uint32_t j) {
-        Item it = decode_item(p, s_ids, first + j * step);
-        uint32_t s = j % NS;
-        st_dst[s] = it.dst;
-        st_bytes[s] = it.bytes;
-        mbar_expect_tx(&full[s], it.bytes);
-        bulk_g2s(stage0 + (size_t)s * p.stage_bytes, it.src, it.bytes, &full[s]);
-      };
-      for (; issued < mine && issued < ahead; ++issued) issue_load(issued);
-      for (uint32_t k = 0; k < mine; ++k) {
-        if (issued < mine) {
-          if (k >= 2) bulk_wait_read<1>();
-          issue_load(issued);
-          ++issued;
-        }
-        uint32_t s = k % NS;
-        mbar_wait(&full[s], (k / NS) & 1u);
-        bulk_s2g(st_dst[s], stage0 + (size_t)s * p.stage_bytes, st_bytes[s]);
+      uint8_t* stage = stage0 + (size_t)tid * p.stage_bytes;
+      uint64_t* bar = &full[tid];
+      uint32_t use = 0;
+      if (probe && tid == 0) probe[2] = clock64();
+      for (uint32_t j = (uint32_t)tid; j < mine; j += NS, ++use) {
+        if (use > 0) bulk_wait_read<0>();  // my previous store has drained the stage
+        const Item it = decode_item(p, s_ids, first + j * step);
+        mbar_expect_tx(bar, it.bytes);
+        bulk_g2s(stage, it.src, it.bytes, bar);
+        if (probe && tid == 0 && use == 0) probe[3] = clock64();
+        mbar_wait(bar, use & 1u);
+        if (probe && tid == 0 && use == 0) probe[4] = clock64();
+        bulk_s2g(it.dst, stage, it.bytes);
         bulk_commit();
       }
+      if (probe && tid == 0) probe[5] = clock64();
       bulk_wait_all<0>();
+      __syncwarp(__activemask());
+      if (probe && tid == 0) {
+        probe[6] = clock64();
+        probe[7] = globaltimer_ns();
+      }
     }
     return;
   }

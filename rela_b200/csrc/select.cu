@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   const int lane = tid & 31, warp = tid >> 5;
   Ctl* ctl = a.ctl;
 
+  if (tid == 0) ctl->probe[0] = clock64();
   // ---- 1. inclusive scan of tile sums into shared memory, min non-zero weight
   double carry = 0.0;
   float mn = FLT_MAX;
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
   __syncthreads();
 
+  if (tid == 0) ctl->probe[1] = clock64();
   // ---- 2. exactness test, offset of head, totals
   if (warp == 0) {
     float m = red_f[lane];
@@ -265,6 +267,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   __syncthreads();
 
+  if (tid == 0) ctl->probe[2] = clock64();
   // ---- 3. targets: rand_i = U[0, segment) + i * segment, clamped (lines 265-280)
   const float sumf = (float)ctl->sum;
   const float segment = __fdiv_rn(sumf, (float)a.B);
@@ -300,6 +303,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   __syncthreads();
 
+  if (tid == 0) ctl->probe[3] = clock64();
   // ---- 4. selection
   const int size = a.size;
   if (sh_exact) {
@@ -387,10 +391,12 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   __syncthreads();
 
+  if (tid == 0) ctl->probe[4] = clock64();
   // ---- 5. mark sampled slots live (getElementAndMark, line 126)
   for (int i = tid; i < a.B; i += kSelThreads) a.evicted[a.ids[i]] = 0;
   __syncthreads();
 
+  if (tid == 0) ctl->probe[5] = clock64();
   // ---- 6. eviction (blockPop, lines 84-103), after the marks like the reference
   if (a.pop_n > 0) {
     double part = 0.0;
@@ -426,6 +432,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     }
   }
 
+  if (tid == 0) ctl->probe[6] = clock64();
   // ---- 7. importance weights (lines 320-322)
   float mx = -INFINITY;
   for (int i = tid; i < a.B; i += kSelThreads) {
@@ -450,6 +457,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   for (int i = tid; i < a.B; i += kSelThreads) a.is_weights[i] = __fdiv_rn(wsel[i], sh_max);
 
   if (tid == 0) {
+    ctl->probe[7] = clock64();
     if (sh_exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
     ctl->n_popped += (unsigned long long)a.pop_n;
     if (sh_fail) ctl->error = RR_ERR_OVERRUN;
@@ -490,8 +498,12 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, int S,
 
 // ------------------------------------------------------ K7 priority update
 // ConcurrentQueue::update (rela/prioritized_replay.h:105-119): in index order,
-// skip evicted ids, diff += (float)(new - old), weights_[id] = new; duplicate
-// ids see the value written by the previous occurrence.
+// skip evicted ids, diff += (float)(new - old), weights_[id] = new; a repeated
+// id sees the value written by its previous occurrence. Sampled ids are
+// non-decreasing in ring order (the reference's walk never rewinds), so
+// repeats are always adjacent: occurrence i reads new[i-1], the last one writes.
+// The double accumulation of the float differences is done in parallel when
+// it is provably exact (sum |d| < 2^52 * ulp(min |d|)), else in order.
 __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
                                                       const int32_t* __restrict__ ids, int n,
                                                       const float* __restrict__ prio, float alpha,
@@ -500,42 +512,76 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
   float* s_diff = s_new + n;
-  int32_t* s_wr = reinterpret_cast<int32_t*>(s_diff + n);
+  __shared__ double r_sum[32], r_abs[32];
+  __shared__ float r_min[32];
+  __shared__ int sh_exact;
   const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = ids[i];
     const float p = prio[i];
+    const bool ev = evicted[id] != 0;
     s_new[i] = is_weight ? p : pow_alpha(p, alpha);
-    s_id[i] = evicted[id] ? -1 : id;
+    s_id[i] = ev ? -1 : id;
   }
   __syncthreads();
+  double sum = 0.0, asum = 0.0;
+  float mn = FLT_MAX;
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = s_id[i];
     float d = 0.0f;
     if (id >= 0) {
-      int prev = -1;
-      bool last = true;
-      for (int j = 0; j < n; ++j) {
-        if (s_id[j] == id) {
-          if (j < i) prev = j;
-          if (j > i) last = false;
-        }
-      }
-      const float old = prev >= 0 ? s_new[prev] : w[id];
+      const bool has_prev = i > 0 && s_id[i - 1] == id;
+      const float old = has_prev ? s_new[i - 1] : w[id];
       d = __fsub_rn(s_new[i], old);
-      s_wr[i] = last ? 1 : 0;
+      sum += (double)d;
+      asum += fabs((double)d);
+      if (d != 0.0f) mn = fminf(mn, fabsf(d));
     }
     s_diff[i] = d;
   }
-  __syncthreads();
+  __syncthreads();  // all reads of the old weights are done
   for (int i = tid; i < n; i += blockDim.x) {
-    if (s_id[i] >= 0 && s_wr[i]) w[s_id[i]] = s_new[i];
+    const int id = s_id[i];
+    const bool last = !(i + 1 < n && s_id[i + 1] == id);
+    if (id >= 0 && last) w[id] = s_new[i];
   }
-  if (tid == 0) {
-    double diff = 0.0;
-    for (int i = 0; i < n; ++i) {
-      if (s_id[i] >= 0) diff += (double)s_diff[i];
+  sum = warp_sum(sum);
+  asum = warp_sum(asum);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  if (lane == 0) {
+    r_sum[warp] = sum;
+    r_abs[warp] = asum;
+    r_min[warp] = mn;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = blockDim.x >> 5;
+    double a = lane < nw ? r_sum[lane] : 0.0;
+    double b = lane < nw ? r_abs[lane] : 0.0;
+    float m = lane < nw ? r_min[lane] : FLT_MAX;
+    a = warp_sum(a);
+    b = warp_sum(b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) {
+      int exact = 1;
+      if (m != FLT_MAX) {
+        int e;
+        frexpf(m, &e);
+        int ulp_exp = (e - 1) - 23;
+        if (ulp_exp < -149) ulp_exp = -149;
+        exact = b < ldexp(1.0, ulp_exp + 52);
+      }
+      sh_exact = exact;
+      if (exact) ctl->sum += a;
     }
+  }
+  __syncthreads();
+  if (!sh_exact && tid == 0) {
+    double diff = 0.0;
+    for (int i = 0; i < n; ++i) diff += (double)s_diff[i];  // evicted entries hold +0.0f
     ctl->sum += diff;
   }
 }
@@ -566,7 +612,7 @@ cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const flo
 
 cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, cudaStream_t stream) {
-  const size_t smem = (size_t)n * 16;
+  const size_t smem = (size_t)n * 12;
   static size_t configured = 0;
   if (smem > 40 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -34,6 +34,8 @@ def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, **cuda_kw):
     (3000, 80, 512, 0.6, 0.4, 0),
     (256, 20, 32, 0.6, 0.4, 1),
     (256, 20, 32, 0.6, 0.4, 2),
+    (40, 10, 64, 0.6, 0.4, 0),   # B > size: many repeated ids in one batch
+    (40, 10, 64, 0.6, 0.4, 1),
 ])
 def test_ff_trace(cap, K, B, alpha, beta, prefetch):
     schema = ff_schema(frame=(4, 12, 12), n_actions=6)
