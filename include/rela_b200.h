@@ -130,13 +130,17 @@ int rr_get_stats(rr_replay* r, rr_stats* out);
  * the replay's internal stream. Does not block the host. */
 int rr_stream_fence(rr_replay* r, void* stream);
 
-/* Gather-kernel timing for the roofline: while enabled, every gather launch is
- * bracketed by CUDA events on the internal stream. rr_gather_time synchronises,
- * returns the accumulated kernel milliseconds and launch count since enabling,
- * and resets both. */
-int rr_set_profiling(rr_replay* r, int enabled);
-int rr_gather_time(rr_replay* r, double* total_ms, uint64_t* launches,
-                   uint64_t* bytes_per_launch);
+/* Gather-kernel timing for the roofline. While profiling is enabled every
+ * rr_sample also keeps a copy of its sampled ids (ring of 16 sets).
+ * rr_gather_bench then re-launches the gather kernel for those recorded id sets,
+ * back to back on the internal stream, `reps` times over all sets, rotating
+ * over n_out_sets output batches (out_fields[o * nfields + f], device), and
+ * times the whole region with one CUDA-event pair: ms_per_launch is the
+ * kernel's average duration without per-launch event overhead. */
+int rr_set_profiling(rr_replay* r, int enabled, int max_batch);
+int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields,
+                    int reps, double* ms_per_launch, uint64_t* launches,
+                    uint64_t* bytes_per_launch);
 
 /* Test/debug introspection (synchronises). ids: the physical slot ids of the
  * batch last returned by rr_sample (the reference's sampledIds_). */

@@ -16,7 +16,7 @@ RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
-    "rr_debug_state", "rr_debug_weights", "rr_debug_select_probe", "rr_stream_fence", "rr_set_profiling", "rr_gather_time", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
+    "rr_debug_state", "rr_debug_weights", "rr_debug_select_probe", "rr_stream_fence", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
 ]
 
 
@@ -66,8 +66,8 @@ def lib():
         L.rr_debug_weights.argtypes = [vp, vp, vp]
         L.rr_debug_select_probe.argtypes = [vp, vp]
         L.rr_stream_fence.argtypes = [vp, vp]
-        L.rr_set_profiling.argtypes = [vp, i]
-        L.rr_gather_time.argtypes = [vp, vp, vp, vp]
+        L.rr_set_profiling.argtypes = [vp, i, i]
+        L.rr_gather_bench.argtypes = [vp, i, vp, i, vp, vp, vp]
         L.rr_nstep_return.argtypes = [i, i, f, vp, vp, vp, vp, vp, i, vp]
         L.rr_td_priority.argtypes = [i, vp, vp, vp, vp, f, vp, vp]
         L.rr_aggregate_priority.argtypes = [i, i, vp, vp, f, i, vp, vp]

@@ -3,6 +3,7 @@
 // SASS: UBLKCP / SYNCS), 128-bit streaming loads and stores.
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 namespace rr {
@@ -89,10 +90,42 @@ __device__ __forceinline__ void stg_stream16(void* p, const uint4& v) {
                : "memory");
 }
 
+// Programmatic dependent launch (PDL): let the next kernel in the stream start
+// its prologue now, and block until every prerequisite grid has completed and
+// its writes are visible. Both are no-ops for kernels launched without the
+// programmatic-stream-serialization attribute.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
+}
+
+// Host: launch with the PDL attribute (RR_PDL=0 disables it).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  static const bool enabled = [] {
+    const char* v = getenv("RR_PDL");
+    return !(v && v[0] == '0');
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = enabled ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 }  // namespace rr

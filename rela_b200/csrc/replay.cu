@@ -75,6 +75,7 @@ struct Lane {
   cudaEvent_t copied = nullptr;     // rows + priorities are in HBM
   cudaEvent_t committed = nullptr;  // commit kernel consumed dprio
   cudaEvent_t in = nullptr;         // marker on the caller's stream (device-resident inputs)
+  cudaEvent_t gate = nullptr;       // marker on the internal stream at reservation time
   uint8_t* pinned = nullptr;
   size_t pinned_cap = 0;
   float* dprio = nullptr;
@@ -154,12 +155,11 @@ struct rr_replay {
   // stats
   std::atomic<uint64_t> launches{0}, samples{0}, h2d_bytes{0};
 
-  // optional gather timing (rr_set_profiling)
+  // optional: history of sampled id sets for rr_gather_bench (rr_set_profiling)
   bool profiling = false;
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
-  size_t prof_used = 0;
-  double prof_ms = 0;
-  uint64_t prof_n = 0, prof_bytes = 0;
+  std::vector<int32_t*> hist;
+  size_t hist_n = 0;
+  int hist_B = 0, hist_cap = 0;
 };
 
 namespace {
@@ -218,10 +218,9 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
   p.simt_units = units;
   p.stage_bytes = (max_piece + 127u) & ~127u;
   CopyLaunch& c = out->cfg;
-  const uint32_t ids_bytes = ids ? (uint32_t)rows * 4u : 0u;
   if (p.n_bulk > 0) {
     c.block = 128;
-    const size_t hdr = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
+    const size_t hdr = rr::kCopyHeaderBytes;
     const size_t lim = (size_t)227 * 1024 / (size_t)r->g_ctas - 1024;  // 1 KB per-CTA system reserve
     if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
     const int want = r->sm_count * r->g_ctas;
@@ -236,7 +235,7 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
     if (simt_ctas > (uint64_t)c.grid) c.grid = (int)std::min<uint64_t>(simt_ctas, (uint64_t)want);
   } else {
     c.block = 256;
-    c.smem = (rr::kCopyHeaderBytes + ids_bytes + 127u) & ~127u;
+    c.smem = 0;
     uint64_t ctas = (units + 256 * 4 - 1) / (256 * 4);
     c.grid = (int)std::max<uint64_t>(1, std::min<uint64_t>(ctas, (uint64_t)r->sm_count * 8));
   }
@@ -316,6 +315,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     RR_CUDA(cudaEventCreateWithFlags(&l.copied, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.committed, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.in, cudaEventDisableTiming));
+    RR_CUDA(cudaEventCreateWithFlags(&l.gate, cudaEventDisableTiming));
   }
   r->pstage.resize(4);
   for (auto& s : r->pstage) RR_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
@@ -345,6 +345,7 @@ int rr_destroy(rr_replay* r) {
     cudaEventDestroy(l.copied);
     cudaEventDestroy(l.committed);
     cudaEventDestroy(l.in);
+    cudaEventDestroy(l.gate);
     cudaStreamDestroy(l.stream);
   }
   for (auto& s : r->pstage) {
@@ -359,10 +360,7 @@ int rr_destroy(rr_replay* r) {
   };
   for (auto& p : r->queue) free_pre(p);
   for (auto& p : r->pool) free_pre(p);
-  for (auto& pe : r->prof_events) {
-    cudaEventDestroy(pe.first);
-    cudaEventDestroy(pe.second);
-  }
+  for (auto* hp : r->hist) cudaFree(hp);
   cudaEventDestroy(r->evIn);
   cudaEventDestroy(r->evOut);
   cudaEventDestroy(r->evGather);
@@ -467,27 +465,33 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
   const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
   RR_CUDA(cudaSetDevice(r->device));
 
+  LaneGuard guard(r);
+  Lane& L = *guard.lane;
+
   // -- reserve [start, start + n) (rela/prioritized_replay.h:46-55); blocks while full
   int start;
+  cudaError_t gate_err;
   {
     std::unique_lock<std::mutex> lk(r->m_);
     r->cvSize_.wait(lk, [&] { return r->size_ + n <= r->S; });
     start = r->tail_;
     r->tail_ = (r->tail_ + n) % r->S;
     r->size_ += n;
+    // the slots being reused may still be read by gathers already issued on
+    // the internal stream: the row copies below are ordered after this marker
+    gate_err = cudaEventRecord(L.gate, r->main);
   }
   const int end = (start + n) % r->S;
   const int n1 = std::min(n, r->S - start);  // rows before the wrap
 
-  LaneGuard guard(r);
-  Lane& L = *guard.lane;
   int rc = RR_OK;
   auto body = [&]() -> int {
     // previous use of this lane: staging consumed, commit kernel done with dprio
     RR_CUDA(cudaEventSynchronize(L.copied));
     RR_CUDA(cudaStreamWaitEvent(L.stream, L.committed, 0));
     // rows being overwritten may still be read by an in-flight gather
-    RR_CUDA(cudaStreamWaitEvent(L.stream, r->evGather, 0));
+    if (gate_err != cudaSuccess) return fail(RR_ERR_CUDA, "rr_add: %s", cudaGetErrorString(gate_err));
+    RR_CUDA(cudaStreamWaitEvent(L.stream, L.gate, 0));
     if ((rows_dev || prio_dev)) {
       // order after the producer of the device-resident inputs
       RR_CUDA(cudaEventRecord(L.in, cs));
@@ -712,26 +716,17 @@ int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int 
   CopyPlan plan;
   rc = plan_copy(r, true, B, cf, a.ids, 0, &plan);
   if (rc != RR_OK) return rc;
-  std::pair<cudaEvent_t, cudaEvent_t>* pe = nullptr;
-  if (r->profiling) {
-    if (r->prof_used == r->prof_events.size()) {
-      cudaEvent_t a0, a1;
-      RR_CUDA(cudaEventCreate(&a0));
-      RR_CUDA(cudaEventCreate(&a1));
-      r->prof_events.emplace_back(a0, a1);
-    }
-    pe = &r->prof_events[r->prof_used++];
-    RR_CUDA(cudaEventRecord(pe->first, r->main));
-  }
   rc = launch_plan(r, plan, r->main);
   if (rc != RR_OK) return rc;
-  if (pe) {
-    RR_CUDA(cudaEventRecord(pe->second, r->main));
-    uint64_t rowb = 0;
-    for (auto& f : r->fields) rowb += f.row_bytes;
-    r->prof_bytes = 2 * rowb * (uint64_t)B;
+  if (r->profiling) {
+    // keep this batch's ids for rr_gather_bench (a copy node here breaks the
+    // kernel-to-kernel PDL chain, which is why it is opt-in)
+    const size_t k = r->hist_n % r->hist.size();
+    if (r->hist_cap < B) return fail(RR_ERR_ARG, "profiling: batch larger than at rr_set_profiling");
+    RR_CUDA(cudaMemcpyAsync(r->hist[k], a.ids, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToDevice, r->main));
+    r->hist_n++;
+    r->hist_B = B;
   }
-  RR_CUDA(cudaEventRecord(r->evGather, r->main));
 
   // blockPop bookkeeping (rela/prioritized_replay.h:94-102)
   if (a.pop_n > 0) {
@@ -901,30 +896,79 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   return RR_OK;
 }
 
-int rr_set_profiling(rr_replay* r, int enabled) {
+int rr_set_profiling(rr_replay* r, int enabled, int max_batch) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_set_profiling: null");
+  RR_CUDA(cudaSetDevice(r->device));
   RR_CUDA(cudaStreamSynchronize(r->main));
+  if (enabled && r->hist_cap < max_batch) {
+    for (auto* hp : r->hist) RR_CUDA(cudaFree(hp));
+    r->hist.assign(16, nullptr);
+    for (auto& hp : r->hist) RR_CUDA(cudaMalloc(&hp, sizeof(int32_t) * (size_t)max_batch));
+    r->hist_cap = max_batch;
+  }
   r->profiling = enabled != 0;
-  r->prof_used = 0;
-  r->prof_ms = 0;
-  r->prof_n = 0;
+  if (enabled) r->hist_n = 0;
   return RR_OK;
 }
 
-int rr_gather_time(rr_replay* r, double* total_ms, uint64_t* launches, uint64_t* bytes_per_launch) {
-  if (r == nullptr) return fail(RR_ERR_ARG, "rr_gather_time: null");
+int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int reps, double* ms_per_launch,
+                    uint64_t* launches, uint64_t* bytes_per_launch) {
+  if (r == nullptr || out_fields == nullptr || n_out_sets <= 0 || reps <= 0)
+    return fail(RR_ERR_ARG, "rr_gather_bench: bad argument");
+  const int nsets = (int)std::min(r->hist_n, r->hist.size());
+  if (nsets == 0) return fail(RR_ERR_STATE, "rr_gather_bench: no sampled id sets recorded (rr_set_profiling)");
   RR_CUDA(cudaSetDevice(r->device));
-  RR_CUDA(cudaStreamSynchronize(r->main));
-  double ms = 0;
-  for (size_t i = 0; i < r->prof_used; ++i) {
-    float t = 0;
-    RR_CUDA(cudaEventElapsedTime(&t, r->prof_events[i].first, r->prof_events[i].second));
-    ms += t;
+  std::unique_lock<std::mutex> lk(r->m_);
+  const int B = r->hist_B;
+  const size_t nf = r->fields.size();
+  std::vector<CopyPlan> plans((size_t)nsets * (size_t)n_out_sets);
+  for (int s = 0; s < nsets; ++s) {
+    for (int o = 0; o < n_out_sets; ++o) {
+      std::vector<CopyField> cf;
+      for (size_t fi = 0; fi < nf; ++fi) {
+        const FieldInfo& f = r->fields[fi];
+        if (f.row_bytes == 0) continue;
+        CopyField c;
+        memset(&c, 0, sizeof(c));
+        c.src = f.slab;
+        c.dst = static_cast<uint8_t*>(out_fields[(size_t)o * nf + fi]);
+        c.src_row_stride = f.row_bytes;
+        c.dst_row_stride = f.chunk_bytes;
+        c.dst_chunk_stride = (uint64_t)B * f.chunk_bytes;
+        c.chunk_bytes = f.chunk_bytes;
+        c.chunks = f.chunks;
+        cf.push_back(c);
+      }
+      int rc = plan_copy(r, true, B, cf, r->hist[s], 0, &plans[(size_t)s * n_out_sets + o]);
+      if (rc != RR_OK) return rc;
+    }
   }
-  if (total_ms) *total_ms = ms;
-  if (launches) *launches = r->prof_used;
-  if (bytes_per_launch) *bytes_per_launch = r->prof_bytes;
-  r->prof_used = 0;
+  cudaEvent_t e0, e1;
+  RR_CUDA(cudaEventCreate(&e0));
+  RR_CUDA(cudaEventCreate(&e1));
+  uint64_t n = 0;
+  for (int k = 0; k < nsets; ++k) {  // warm-up pass
+    int rc = launch_plan(r, plans[(size_t)k * n_out_sets + (k % n_out_sets)], r->main);
+    if (rc != RR_OK) return rc;
+  }
+  RR_CUDA(cudaEventRecord(e0, r->main));
+  for (int rep = 0; rep < reps; ++rep) {
+    for (int k = 0; k < nsets; ++k, ++n) {
+      int rc = launch_plan(r, plans[(size_t)k * n_out_sets + (n % (uint64_t)n_out_sets)], r->main);
+      if (rc != RR_OK) return rc;
+    }
+  }
+  RR_CUDA(cudaEventRecord(e1, r->main));
+  RR_CUDA(cudaEventSynchronize(e1));
+  float ms = 0;
+  RR_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  uint64_t rowb = 0;
+  for (auto& f : r->fields) rowb += f.row_bytes;
+  if (ms_per_launch) *ms_per_launch = (double)ms / (double)n;
+  if (launches) *launches = n;
+  if (bytes_per_launch) *bytes_per_launch = 2 * rowb * (uint64_t)B;
   return RR_OK;
 }
 

@@ -32,62 +32,59 @@ __device__ __forceinline__ void copy_unit(uint8_t* dst, const uint8_t* src, uint
 }
 
 // Source / destination of (field, row b, chunk t) at byte offset `off` in the chunk.
-struct RowAddr {
-  const uint8_t* src;
-  uint8_t* dst;
-};
-
-__device__ __forceinline__ RowAddr row_addr(const CopyParams& p, const CopyField& f, const int32_t* s_ids,
-                                            uint32_t b, uint32_t t, uint32_t off) {
-  RowAddr a;
-  const uint64_t inner = (uint64_t)t * f.chunk_bytes + off;
-  if (p.ids != nullptr) {
-    // gather: slab row ids[b] -> batch [t, b, :]
-    a.src = f.src + (uint64_t)(uint32_t)s_ids[b] * f.src_row_stride + inner;
-    a.dst = f.dst + (uint64_t)t * f.dst_chunk_stride + (uint64_t)b * f.dst_row_stride + off;
-  } else {
-    // insert: producer row b -> slab row (start + b) % S
-    uint32_t slot = (uint32_t)p.insert_start + b;
-    if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;
-    a.src = (f.row_ptrs != nullptr ? f.row_ptrs[b] : f.src + (uint64_t)b * f.src_row_stride) + inner;
-    a.dst = f.dst + (uint64_t)slot * f.dst_row_stride + inner;
+// The destination never depends on the sampled ids, so it can be computed
+// before the kernel's dependencies have resolved.
+__device__ __forceinline__ uint8_t* row_dst(const CopyParams& p, const CopyField& f, uint32_t b, uint32_t t,
+                                            uint32_t off) {
+  if (p.ids != nullptr) {  // gather: batch [t, b, :]
+    return f.dst + (uint64_t)t * f.dst_chunk_stride + (uint64_t)b * f.dst_row_stride + off;
   }
-  return a;
+  uint32_t slot = (uint32_t)p.insert_start + b;  // insert: slab row (start + b) % S
+  if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;
+  return f.dst + (uint64_t)slot * f.dst_row_stride + (uint64_t)t * f.chunk_bytes + off;
+}
+
+__device__ __forceinline__ const uint8_t* row_src(const CopyParams& p, const CopyField& f, uint32_t b, uint32_t t,
+                                                  uint32_t off) {
+  const uint64_t inner = (uint64_t)t * f.chunk_bytes + off;
+  if (p.ids != nullptr) return f.src + (uint64_t)(uint32_t)__ldg(p.ids + b) * f.src_row_stride + inner;
+  return (f.row_ptrs != nullptr ? f.row_ptrs[b] : f.src + (uint64_t)b * f.src_row_stride) + inner;
 }
 
 struct Item {
-  const uint8_t* src;
+  const CopyField* f;
   uint8_t* dst;
-  uint32_t bytes;
+  uint32_t b, t, off, bytes;
 };
 
-__device__ __forceinline__ Item decode_item(const CopyParams& p, const int32_t* s_ids, uint32_t item) {
+// Everything about an item except its source address (which needs ids[b]).
+__device__ __forceinline__ Item decode_item(const CopyParams& p, uint32_t item) {
   int fi = 0;
 #pragma unroll 1
   for (int k = 1; k < p.n_bulk; ++k) {
     if (item >= p.bulk[k].begin) fi = k;
   }
   const CopyField& f = p.bulk[fi];
-  uint32_t local = item - f.begin;
-  uint32_t piece = local % f.pieces;
-  uint32_t ct = local / f.pieces;  // row * chunks + chunk
-  uint32_t t = ct % f.chunks;
-  uint32_t b = ct / f.chunks;
-  uint32_t off = piece * f.piece_bytes;
-  uint32_t bytes = min(f.piece_bytes, f.chunk_bytes - off);
-  RowAddr a = row_addr(p, f, s_ids, b, t, off);
-  return Item{a.src, a.dst, bytes};
+  Item it;
+  it.f = &f;
+  const uint32_t local = item - f.begin;
+  const uint32_t piece = local % f.pieces;
+  const uint32_t ct = local / f.pieces;  // row * chunks + chunk
+  it.t = ct % f.chunks;
+  it.b = ct / f.chunks;
+  it.off = piece * f.piece_bytes;
+  it.bytes = min(f.piece_bytes, f.chunk_bytes - it.off);
+  it.dst = row_dst(p, f, it.b, it.t, it.off);
+  return it;
 }
 
 }  // namespace
 
 __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ CopyParams p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
-  // layout: 32 mbarriers | ids[rows] (gather) | pad to 128 | stages * stage_bytes
+  // layout: 32 mbarriers | stages * stage_bytes
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
-  int32_t* s_ids = reinterpret_cast<int32_t*>(smem_raw + kCopyHeaderBytes);
-  const uint32_t ids_bytes = p.ids != nullptr ? (uint32_t)p.rows * 4u : 0u;
-  uint8_t* stage0 = smem_raw + ((kCopyHeaderBytes + ids_bytes + 127u) & ~127u);
+  uint8_t* stage0 = smem_raw + kCopyHeaderBytes;
 
   const int tid = threadIdx.x;
   unsigned long long* probe = p.probe ? p.probe + (size_t)blockIdx.x * 8 : nullptr;
@@ -95,34 +92,42 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     probe[0] = globaltimer_ns();
     probe[1] = clock64();
   }
-  if (p.ids != nullptr) {
-    for (int i = tid; i < p.rows; i += blockDim.x) s_ids[i] = p.ids[i];
-  }
-  if (tid < p.stages && p.n_bulk > 0) mbar_init(&full[tid], 1);
-  if (tid < 32 && p.n_bulk > 0) mbar_fence_init();
-  __syncthreads();
-
   const bool bulk_warp = (p.n_bulk > 0) && (tid < 32);
   if (bulk_warp) {
-    // ---- bulk path. Lane l owns stage l: it streams the CTA's items
-    // l, l + stages, ... through its own shared-memory stage, so up to
-    // `stages` loads per CTA are in flight and the per-item address
-    // arithmetic is spread over the warp instead of serialised on one thread.
+    // ---- bulk path. Lane l owns stage l and its own mbarrier: it streams the
+    // CTA's items l, l + stages, ... through that stage, so up to `stages`
+    // loads per CTA are in flight and the per-item address arithmetic is spread
+    // over the warp. Everything that does not depend on the sampled ids
+    // (barrier init, item decode, destination) runs before pdl_wait(), i.e.
+    // overlapped with the tail of the selection kernel.
     const uint32_t NS = (uint32_t)p.stages;
-    if ((uint32_t)tid < NS) {
-      const uint32_t n_items = p.bulk_items;
-      const uint32_t first = blockIdx.x;
-      const uint32_t step = gridDim.x;
-      const uint32_t mine = first < n_items ? (n_items - first + step - 1) / step : 0;
-      uint8_t* stage = stage0 + (size_t)tid * p.stage_bytes;
-      uint64_t* bar = &full[tid];
+    const bool active = (uint32_t)tid < NS;
+    const uint32_t n_items = p.bulk_items;
+    const uint32_t first = blockIdx.x;
+    const uint32_t step = gridDim.x;
+    const uint32_t mine = first < n_items ? (n_items - first + step - 1) / step : 0;
+    uint8_t* stage = stage0 + (size_t)tid * p.stage_bytes;
+    uint64_t* bar = &full[active ? tid : 0];
+    Item it;
+    it.bytes = 0;
+    if (active) {
+      mbar_init(bar, 1);
+      mbar_fence_init();
+      if ((uint32_t)tid < mine) it = decode_item(p, first + (uint32_t)tid * step);
+    }
+    pdl_launch_dependents();
+    pdl_wait();
+    if (probe && tid == 0) probe[2] = clock64();
+    if (active) {
       uint32_t use = 0;
-      if (probe && tid == 0) probe[2] = clock64();
       for (uint32_t j = (uint32_t)tid; j < mine; j += NS, ++use) {
-        if (use > 0) bulk_wait_read<0>();  // my previous store has drained the stage
-        const Item it = decode_item(p, s_ids, first + j * step);
+        if (use > 0) {
+          it = decode_item(p, first + j * step);
+          bulk_wait_read<0>();  // my previous store has drained the stage
+        }
+        const uint8_t* src = row_src(p, *it.f, it.b, it.t, it.off);
         mbar_expect_tx(bar, it.bytes);
-        bulk_g2s(stage, it.src, it.bytes, bar);
+        bulk_g2s(stage, src, it.bytes, bar);
         if (probe && tid == 0 && use == 0) probe[3] = clock64();
         mbar_wait(bar, use & 1u);
         if (probe && tid == 0 && use == 0) probe[4] = clock64();
@@ -130,8 +135,9 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
         bulk_commit();
       }
       if (probe && tid == 0) probe[5] = clock64();
-      bulk_wait_all<0>();
-      __syncwarp(__activemask());
+      // the stores only have to be done READING shared memory before the CTA
+      // exits; kernel completion makes them visible
+      bulk_wait_read<0>();
       if (probe && tid == 0) {
         probe[6] = clock64();
         probe[7] = globaltimer_ns();
@@ -141,6 +147,8 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
   }
 
   // ---- narrow fields: grid-strided units over the non-bulk warps
+  pdl_launch_dependents();
+  pdl_wait();
   if (p.n_simt == 0) return;
   const uint32_t lane_base = (p.n_bulk > 0) ? 32u : 0u;
   const uint64_t per_cta = blockDim.x - lane_base;
@@ -153,14 +161,13 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       if (u >= p.simt[k].begin) fi = k;
     }
     const CopyField& f = p.simt[fi];
-    uint64_t local = u - f.begin;
-    uint32_t upc = f.chunk_bytes / f.vec;  // units per chunk
-    uint32_t v = (uint32_t)(local % upc);
-    uint64_t ct = local / upc;
-    uint32_t t = (uint32_t)(ct % f.chunks);
-    uint32_t b = (uint32_t)(ct / f.chunks);
-    RowAddr a = row_addr(p, f, s_ids, b, t, v * f.vec);
-    copy_unit(a.dst, a.src, f.vec);
+    const uint64_t local = u - f.begin;
+    const uint32_t upc = f.chunk_bytes / f.vec;  // units per chunk
+    const uint32_t v = (uint32_t)(local % upc);
+    const uint64_t ct = local / upc;
+    const uint32_t t = (uint32_t)(ct % f.chunks);
+    const uint32_t b = (uint32_t)(ct / f.chunks);
+    copy_unit(row_dst(p, f, b, t, v * f.vec), row_src(p, f, b, t, v * f.vec), f.vec);
   }
 }
 
@@ -172,8 +179,7 @@ cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStre
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  row_copy_kernel<<<cfg.grid, cfg.block, cfg.smem, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(row_copy_kernel, dim3(cfg.grid), dim3(cfg.block), cfg.smem, stream, p);
 }
 
 }  // namespace rr

@@ -20,17 +20,20 @@
 // Dead slots hold weight 0 (zeroed on eviction; the reference never reads a
 // popped slot's weight again: update() skips evicted ids and append overwrites
 // the slot), so physical prefixes need no live-range mask.
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 
 #include "../../include/rela_b200.h"
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace rr {
 
 namespace {
 
 constexpr int kSelThreads = 1024;
+constexpr int kSelChunk = 512;  // targets staged through shared memory per round
 
 __device__ __forceinline__ float pow_alpha(float p, float alpha) {
   // K2: priority ^ alpha. alpha == 1 is the identity (ATen copies in that
@@ -55,6 +58,8 @@ __global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __res
                                                               float* __restrict__ l2min) {
   const int tile = blockIdx.x;
   const int tid = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const float4 v = reinterpret_cast<const float4*>(w)[(size_t)tile * (kTile / 4) + tid];
   double s = ((double)v.x + (double)v.y) + ((double)v.z + (double)v.w);
   float mn = FLT_MAX;
@@ -128,47 +133,41 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
-// Physical inclusive prefix helpers -------------------------------------
-struct Hier {
-  const float* w;
-  const double* l1;
-  const double* p2;  // inclusive prefix of tile sums (shared memory)
-  int nt2;
-};
-
-// predicate of the reference walk on a logical prefix value
-__device__ __forceinline__ bool hit(double v, double target) {
-  return v > 0.0 && v >= target;
+// Exact integer view of the prefix hierarchy ---------------------------------
+// Under the exactness condition every weight, group sum, tile sum and prefix
+// is an integer multiple of u = 2^ue below 2^52 * u. The search works on those
+// integers ("q" values): no fp64 dependency chains, and comparisons against a
+// target t become P >= ceil(t / u) (and "accSum > 0" becomes P >= 1).
+__device__ __forceinline__ unsigned long long f2q(float w, int ue) {
+  const uint32_t bits = __float_as_uint(w) & 0x7fffffffu;
+  if (bits == 0u) return 0ull;
+  const uint32_t e = bits >> 23;
+  const unsigned long long m = e ? ((bits & 0x7fffffu) | 0x800000u) : (bits & 0x7fffffu);
+  const int shift = (int)(e ? e : 1u) - 150 - ue;  // >= 0: ulp(w) >= u
+  return shift < 40 ? (m << shift) : ~0ull >> 2;   // >= 2^62 can never be below a key
 }
 
-// smallest physical slot s in [0, S_pad) with hit(P(s) + delta, target), or -1.
-__device__ int search_slot(const Hier& h, double delta, double target) {
-  // level 2: binary search over tile prefixes
-  int lo = 0, hi = h.nt2;  // first tile with hit(p2[tile] + delta)
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (hit(h.p2[mid] + delta, target)) hi = mid; else lo = mid + 1;
+// x / 2^ue for a double that is a multiple of 2^ue; *inexact is raised when it
+// is not, or when the quotient does not fit 2^62.
+__device__ __forceinline__ unsigned long long d2q(double x, int ue, int* inexact) {
+  const unsigned long long bits = (unsigned long long)__double_as_longlong(x) & 0x7fffffffffffffffull;
+  if (bits == 0ull) return 0ull;
+  const int e = (int)(bits >> 52);
+  const unsigned long long m = (bits & 0xfffffffffffffull) | (e ? 0x10000000000000ull : 0ull);
+  const int shift = (e ? e : 1) - 1075 - ue;
+  if (shift >= 0) {
+    if (shift > 9) {
+      *inexact = 1;
+      return ~0ull >> 2;
+    }
+    return m << shift;
   }
-  if (lo >= h.nt2) return -1;
-  const int tile = lo;
-  double acc = (tile > 0 ? h.p2[tile - 1] : 0.0);
-  // level 1: groups of the tile, in order
-  const double* g = h.l1 + (size_t)tile * (kTile / kGroup);
-  int grp = 0;
-  for (; grp < kTile / kGroup - 1; ++grp) {
-    double nxt = acc + g[grp];
-    if (hit(nxt + delta, target)) break;
-    acc = nxt;
+  if (shift <= -64) {
+    *inexact = 1;
+    return 0ull;
   }
-  // level 0: slots of the group, in order
-  const float* ws = h.w + (size_t)tile * kTile + (size_t)grp * kGroup;
-  int j = 0;
-  for (; j < kGroup - 1; ++j) {
-    double nxt = acc + (double)ws[j];
-    if (hit(nxt + delta, target)) break;
-    acc = nxt;
-  }
-  return tile * kTile + grp * kGroup + j;
+  if (m & ((1ull << (-shift)) - 1ull)) *inexact = 1;
+  return m >> (-shift);
 }
 
 }  // namespace
@@ -178,13 +177,17 @@ __device__ int search_slot(const Hier& h, double delta, double target) {
 __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
   const int nt2 = a.S_pad / kTile;
-  double* p2 = reinterpret_cast<double*>(sm_raw);
-  float* targets = reinterpret_cast<float*>(p2 + nt2);
+  double* p2d = reinterpret_cast<double*>(sm_raw);
+  unsigned long long* p2q = reinterpret_cast<unsigned long long*>(sm_raw);
+  float* targets = reinterpret_cast<float*>(p2d + nt2);
   float* wsel = targets + a.B;
+  int* s_tile = reinterpret_cast<int*>(wsel + a.B);
+  double* stage_d = reinterpret_cast<double*>(s_tile + kSelChunk + ((2 * a.B) & 1));  // 8-byte aligned
+  float* stage_f = reinterpret_cast<float*>(stage_d);
   __shared__ uint32_t mt[624];
-  __shared__ double red_d[32];
+  __shared__ unsigned long long red_q[32];
   __shared__ float red_f[32];
-  __shared__ double sh_total, sh_offset;
+  __shared__ unsigned long long sh_total, sh_offset;
   __shared__ float sh_max;
   __shared__ int sh_exact, sh_fail;
 
@@ -192,75 +195,98 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   const int lane = tid & 31, warp = tid >> 5;
   Ctl* ctl = a.ctl;
 
+  pdl_launch_dependents();
+  pdl_wait();
   if (tid == 0) ctl->probe[0] = clock64();
-  // ---- 1. inclusive scan of tile sums into shared memory, min non-zero weight
-  double carry = 0.0;
+  // ---- 1. tile sums -> shared memory, min non-zero weight -> u = 2^ue,
+  //         integer inclusive prefix of the tile sums (one pass, contiguous
+  //         chunk per thread)
+  const int per = (nt2 + kSelThreads - 1) / kSelThreads;
+  const int c0 = min(tid * per, nt2), c1 = min(c0 + per, nt2);
   float mn = FLT_MAX;
-  for (int base = 0; base < nt2; base += kSelThreads) {
-    int i = base + tid;
-    double v = (i < nt2) ? a.l2[i] : 0.0;
-    if (i < nt2) mn = fminf(mn, a.l2min[i]);
-    // warp inclusive scan
-    double x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      double y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) red_d[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-      double t = red_d[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        double y = __shfl_up_sync(0xffffffffu, t, o);
-        if (lane >= o) t += y;
-      }
-      red_d[lane] = t;  // inclusive over warps
-    }
-    __syncthreads();
-    double woff = (warp > 0) ? red_d[warp - 1] : 0.0;
-    if (i < nt2) p2[i] = carry + woff + x;
-    carry += red_d[31];
-    __syncthreads();
+  for (int i = c0; i < c1; ++i) {
+    p2d[i] = a.l2[i];
+    mn = fminf(mn, a.l2min[i]);
   }
+  // values needed after the barriers: issue their loads now
+  double head_l1 = 0.0;  // group sums / weights in front of head, for the offset O
+  float head_w = 0.0f;
+  if (warp == 0 && a.head > 0) {
+    const int last = a.head - 1;
+    const int t = last / kTile, g = (last % kTile) / kGroup, o = last % kGroup;
+    if (lane < g) head_l1 = a.l1[(size_t)t * (kTile / kGroup) + lane];
+    if (lane <= o) head_w = a.w[(size_t)t * kTile + (size_t)g * kGroup + lane];
+  }
+  const float sum_f_early = (float)ctl->sum;
+  const int mti_early = ctl->mti;
+  for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
   if (lane == 0) red_f[warp] = mn;
-  // mt19937 state
-  for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
   __syncthreads();
-
-  if (tid == 0) ctl->probe[1] = clock64();
-  // ---- 2. exactness test, offset of head, totals
-  if (warp == 0) {
+  {
     float m = red_f[lane];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    // O = physical inclusive prefix at head - 1
-    double part = 0.0;
-    if (a.head > 0) {
+    mn = m;  // every warp now holds the global min non-zero weight
+  }
+  int ue = -149;
+  if (mn != FLT_MAX) {
+    int e;
+    frexpf(mn, &e);       // mn = f * 2^e, f in [0.5, 1)
+    ue = (e - 1) - 23;    // ulp of a normal float
+    if (ue < -149) ue = -149;
+  }
+  int inexact = 0;
+  unsigned long long run = 0ull;
+  for (int i = c0; i < c1; ++i) {
+    run += d2q(p2d[i], ue, &inexact);
+    p2q[i] = run;  // same 8 bytes as p2d[i]: each thread converts its own chunk in place
+  }
+  // block exclusive scan of the per-thread totals
+  unsigned long long x = run;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) red_q[warp] = x;
+  inexact = __syncthreads_or(inexact);
+  if (warp == 0) {
+    unsigned long long t = red_q[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned long long y = __shfl_up_sync(0xffffffffu, t, o);
+      if (lane >= o) t += y;
+    }
+    red_q[lane] = t;
+  }
+  __syncthreads();
+  {
+    const unsigned long long off = (warp > 0 ? red_q[warp - 1] : 0ull) + (x - run);
+    for (int i = c0; i < c1; ++i) p2q[i] += off;
+  }
+  __syncthreads();
+
+  if (tid == 0) ctl->probe[1] = clock64();
+  // ---- 2. exactness test, offset of head (physical inclusive prefix at head - 1)
+  if (warp == 0) {
+    const unsigned long long total = p2q[nt2 - 1];
+    int exact = !inexact && total < (1ull << 52);
+    if (a.force_ordered) exact = 0;
+    unsigned long long part = 0ull;
+    if (exact && a.head > 0) {
       const int last = a.head - 1;
-      const int t = last / kTile, g = (last % kTile) / kGroup, o = last % kGroup;
-      if (lane < g) part += a.l1[(size_t)t * (kTile / kGroup) + lane];
-      if (lane <= o) part += (double)a.w[(size_t)t * kTile + (size_t)g * kGroup + lane];
-      part = warp_sum(part);
-      if (t > 0) part += p2[t - 1];
+      const int t = last / kTile;
+      int dummy = 0;
+      part = d2q(head_l1, ue, &dummy) + f2q(head_w, ue);
+#pragma unroll
+      for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
+      if (t > 0) part += p2q[t - 1];
     }
     if (lane == 0) {
-      const double total = p2[nt2 - 1];
       sh_total = total;
       sh_offset = part;
-      int exact = 1;
-      if (m != FLT_MAX) {
-        // ulp(m) * 2^53: every multiple of ulp(m) below it is a double
-        int e;
-        frexpf(m, &e);                           // m = f * 2^e, f in [0.5, 1)
-        int ulp_exp = (e - 1) - 23;              // ulp of a normal float
-        if (ulp_exp < -149) ulp_exp = -149;      // denormals
-        exact = total < ldexp(1.0, ulp_exp + 52);  // 2^52, not 2^53: margin for an inexact `total`
-      }
-      if (a.force_ordered) exact = 0;
       sh_exact = exact;
       sh_fail = 0;
     }
@@ -269,10 +295,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
 
   if (tid == 0) ctl->probe[2] = clock64();
   // ---- 3. targets: rand_i = U[0, segment) + i * segment, clamped (lines 265-280)
-  const float sumf = (float)ctl->sum;
+  const float sumf = sum_f_early;
   const float segment = __fdiv_rn(sumf, (float)a.B);
   {
-    int pos = ctl->mti;
+    int pos = mti_early;
     int done = 0;
     while (done < a.B) {
       if (pos >= 624) {
@@ -307,26 +333,131 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   // ---- 4. selection
   const int size = a.size;
   if (sh_exact) {
-    Hier h{a.w, a.l1, p2, nt2};
-    const double total = sh_total, off = sh_offset;
-    const double m1 = total - off;  // mass of [head, S)
-    for (int i = tid; i < a.B; i += kSelThreads) {
-      const double target = (double)targets[i];
-      int slot;
-      if (hit(m1, target)) {
-        slot = search_slot(h, -off, target);
-      } else {
-        slot = search_slot(h, m1, target);
-        if (slot >= a.head) slot = -1;  // ran past the wrapped part
+    // Both cases reduce to "first physical slot whose prefix reaches a key":
+    //   unwrapped part [head, S):  P(s) - O >= t'   <=>  P(s) >= t' + O
+    //   wrapped part   [0, head):  M1 + P(s) >= t'  <=>  P(s) >= t' - M1
+    // with t' = max(ceil(target / u), 1) (the reference's accSum > 0 && accSum >= target),
+    // O = prefix at head - 1 and M1 = total - O the mass of the unwrapped part.
+    // The per-target group sums and weights are fetched by whole warps (one
+    // coalesced 256 B / 128 B request per target) into padded shared-memory rows
+    // and then walked by the target's own thread: scattered per-thread loads
+    // would cost one L1 wavefront per lane per load on this single SM.
+    const unsigned long long total = sh_total, off = sh_offset;
+    const unsigned long long m1 = total - off;
+    const double qscale = ldexp(1.0, -ue);  // 1 / u
+    for (int i0 = 0; i0 < a.B; i0 += kSelChunk) {
+      const int nT = min(kSelChunk, a.B - i0);
+      int tile = -1, wrapped = 0;
+      unsigned long long rem = 0ull;
+      if (tid < nT) {
+        const float tf = targets[i0 + tid];
+        unsigned long long tq = 1ull;
+        if (tf > 0.0f) {
+          const double scaled = ldexp((double)tf, -ue);  // exact: power-of-two scaling
+          tq = scaled >= 4.0e18 ? (1ull << 62) : (unsigned long long)__double2ll_ru(scaled);
+          if (tq == 0ull) tq = 1ull;
+        }
+        wrapped = !(m1 >= tq);
+        const unsigned long long key = wrapped ? tq - m1 : tq + off;
+        int lo = 0, hi = nt2;  // first tile whose inclusive prefix reaches the key
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (p2q[mid] >= key) hi = mid; else lo = mid + 1;
+        }
+        if (lo < nt2) {
+          tile = lo;
+          rem = key - (tile > 0 ? p2q[tile - 1] : 0ull);  // 1 <= rem <= tile sum
+        }
+        s_tile[tid] = tile;
       }
-      int logical = -1;
-      if (slot >= 0) logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
-      if (slot < 0 || slot >= a.S || logical >= size) {
-        sh_fail = 1;  // reference: assert(false) at lines 297-302
-        slot = a.head;
+      if (tid == 0) ctl->probe[8] = clock64();
+      __syncthreads();
+      if (tid == 0) ctl->probe[9] = clock64();
+      {
+        // all loads of the warp's targets are issued before the first store
+        constexpr int kPerWarp = kSelChunk / (kSelThreads / 32);
+        double v[kPerWarp];
+#pragma unroll
+        for (int k = 0; k < kPerWarp; ++k) {
+          const int t = warp + k * (kSelThreads / 32);
+          const int tl = t < nT ? s_tile[t] : -1;
+          v[k] = tl >= 0 ? a.l1[(size_t)tl * (kTile / kGroup) + lane] : 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < kPerWarp; ++k) {
+          const int t = warp + k * (kSelThreads / 32);
+          if (t < nT) stage_d[t * 33 + lane] = v[k];
+        }
       }
-      a.ids[i] = slot;
-      wsel[i] = a.w[slot];
+      __syncthreads();
+      if (tid == 0) ctl->probe[10] = clock64();
+      int base = -1;
+      // walks in fp64 on q-scaled values: every term is an integer below 2^52,
+      // so the fused multiply-adds are exact and order-independent
+      double remd = (double)rem;
+      if (tid < nT && tile >= 0) {
+        double acc = 0.0, before = 0.0;
+        int grp = 0;
+#pragma unroll 8
+        for (int k = 0; k < kTile / kGroup; ++k) {
+          acc = fma(stage_d[tid * 33 + k], qscale, acc);
+          if (acc < remd) {
+            ++grp;
+            before = acc;
+          }
+        }
+        if (grp >= kTile / kGroup) grp = kTile / kGroup - 1;
+        remd -= before;
+        base = tile * kTile + grp * kGroup;
+      }
+      if (tid < nT) s_tile[tid] = base;
+      if (tid == 0) ctl->probe[11] = clock64();
+      __syncthreads();
+      {
+        constexpr int kPerWarp = kSelChunk / (kSelThreads / 32);
+        float v[kPerWarp];
+#pragma unroll
+        for (int k = 0; k < kPerWarp; ++k) {
+          const int t = warp + k * (kSelThreads / 32);
+          const int bs = t < nT ? s_tile[t] : -1;
+          v[k] = bs >= 0 ? a.w[(size_t)bs + lane] : 0.0f;
+        }
+#pragma unroll
+        for (int k = 0; k < kPerWarp; ++k) {
+          const int t = warp + k * (kSelThreads / 32);
+          if (t < nT) stage_f[t * 33 + lane] = v[k];
+        }
+      }
+      __syncthreads();
+      if (tid == 0) ctl->probe[12] = clock64();
+      if (tid < nT) {
+        int slot = -1;
+        float wv = 0.0f;
+        if (base >= 0) {
+          double acc = 0.0;
+          int j = 0;
+#pragma unroll 8
+          for (int k = 0; k < kGroup; ++k) {
+            acc = fma((double)stage_f[tid * 33 + k], qscale, acc);
+            j += (acc < remd);
+          }
+          if (j >= kGroup) j = kGroup - 1;
+          slot = base + j;
+          wv = stage_f[tid * 33 + j];
+          if (wrapped && slot >= a.head) slot = -1;  // ran past the wrapped part
+        }
+        int logical = -1;
+        if (slot >= 0) logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
+        if (slot < 0 || slot >= a.S || logical >= size) {
+          sh_fail = 1;  // reference: assert(false) at lines 297-302
+          slot = a.head;
+          wv = a.w[slot];
+        }
+        a.ids[i0 + tid] = slot;
+        wsel[i0 + tid] = wv;
+      }
+      if (tid == 0) ctl->probe[13] = clock64();
+      __syncthreads();
     }
   } else {
     // ordered walk: the reference's loop (lines 274-308), staged 1024 weights
@@ -399,20 +530,22 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   if (tid == 0) ctl->probe[5] = clock64();
   // ---- 6. eviction (blockPop, lines 84-103), after the marks like the reference
   if (a.pop_n > 0) {
-    double part = 0.0;
     if (sh_exact) {
+      unsigned long long part = 0ull;
       for (int j = tid; j < a.pop_n; j += kSelThreads) {
         int slot = a.head + j;
         if (slot >= a.S) slot -= a.S;
-        part += (double)a.w[slot];
+        part += f2q(a.w[slot], ue);
       }
-      part = warp_sum(part);
-      if (lane == 0) red_d[warp] = part;
+#pragma unroll
+      for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
+      if (lane == 0) red_q[warp] = part;
       __syncthreads();
       if (tid == 0) {
-        double tot = 0.0;
-        for (int k = 0; k < kSelThreads / 32; ++k) tot += red_d[k];
-        ctl->sum += -tot;
+        unsigned long long tot = 0ull;
+        for (int k = 0; k < kSelThreads / 32; ++k) tot += red_q[k];
+        // diff = -(w_0 + w_1 + ...) exactly (< 2^52 u), then sum_ += diff (line 96)
+        ctl->sum += -ldexp((double)tot, ue);
       }
     } else if (tid == 0) {
       double diff = 0.0;
@@ -517,6 +650,8 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   __shared__ int sh_exact;
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
+  pdl_launch_dependents();
+  pdl_wait();
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = ids[i];
     const float p = prio[i];
@@ -588,20 +723,19 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
 
 // ----------------------------------------------------------------- launches
 cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
-  build_hierarchy_kernel<<<a.S_pad / kTile, 256, 0, stream>>>(a.w, a.l1, a.l2, a.l2min);
-  return cudaGetLastError();
+  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kTile), dim3(256), 0, stream, a.w, a.l1, a.l2, a.l2min);
 }
 
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
-  const size_t smem = (size_t)(a.S_pad / kTile) * sizeof(double) + (size_t)a.B * 2 * sizeof(float);
+  const size_t smem = (size_t)(a.S_pad / kTile) * sizeof(double) + (size_t)a.B * 2 * sizeof(float) +
+                      (size_t)(kSelChunk + 2) * sizeof(int) + (size_t)std::min(a.B, kSelChunk) * 33 * sizeof(double);
   static size_t configured = 0;
   if (smem > 40 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  select_kernel<<<1, kSelThreads, smem, stream>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(select_kernel, dim3(1), dim3(kSelThreads), smem, stream, a);
 }
 
 cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const float* prio, float alpha,
@@ -619,8 +753,7 @@ cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int3
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  update_kernel<<<1, 1024, smem, stream>>>(ctl, w, evicted, ids, n, prio, alpha, is_weight);
-  return cudaGetLastError();
+  return launch_pdl(update_kernel, dim3(1), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio, alpha, is_weight);
 }
 
 }  // namespace rr

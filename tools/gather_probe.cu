@@ -66,7 +66,7 @@ int main(int argc, char** argv) {
   rr::CopyLaunch cfg;
   cfg.block = 128;
   cfg.grid = std::min<int>(sms * ctas_per_sm, (int)items);
-  size_t hdr = (rr::kCopyHeaderBytes + B * 4 + 127) & ~127;
+  size_t hdr = rr::kCopyHeaderBytes;
   size_t lim = 227 * 1024 / ctas_per_sm - 1024;
   int per_cta = (items + cfg.grid - 1) / cfg.grid;
   int fit = (int)((lim - hdr) / p.stage_bytes);
@@ -132,7 +132,7 @@ int main(int argc, char** argv) {
   }
   printf("probe: kernel span (globaltimer) %.2f us; last CTA started %.2f us after the first\n", (g1 - g0) / 1e3,
          (gs_max - g0) / 1e3);
-  const char* names[5] = {"start->ids in smem", "decode+issue first load", "first load latency", "remaining items loop",
+  const char* names[5] = {"start->pdl_wait passed", "ids + issue first load", "first load latency", "remaining items loop",
                           "drain stores"};
   for (int i = 0; i < 5; ++i) printf("  %-26s avg %8.0f cyc  max %8.0f cyc\n", names[i], a[i], mx[i]);
   return 0;

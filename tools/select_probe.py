@@ -38,3 +38,4 @@ names = ["scan tile sums", "exactness+offset", "targets (mt19937)", "selection",
 for nm, v in zip(names, acc[:7] / N):
     print(f"{nm:22s} {v:9.0f} cyc  {v/1.9e3:6.2f} us")
 print("total", acc[:7].sum() / N / 1.9e3, "us")
+print("selection sub-phases (last call, cycles): t0->A", int(pr[8]-pr[3]), "sync", int(pr[9]-pr[8]), "copy l1+sync", int(pr[10]-pr[9]), "walk groups", int(pr[11]-pr[10]), "copy w+sync", int(pr[12]-pr[11]), "walk slots", int(pr[13]-pr[12]), "tail", int(pr[4]-pr[13]))
