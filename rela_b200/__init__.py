@@ -4,6 +4,13 @@ Public surface (mirrors reference rela/pybind.cc:19-59):
     FFTransition, RNNTransition, FFPrioritizedReplay, RNNPrioritizedReplay
 plus the actor-side arithmetic kernels nstep_return / td_priority /
 aggregate_priority. Everything runs in librela_b200.so (CUDA, sm_100a).
+
+Two host layers sit on the C ABI (include/rela_b200.h):
+  rela_b200.rela   the C++ host layer + pybind module (rela_b200/cpp/, built as
+                   rela_b200/_C.so): same class and method names as the
+                   reference's `rela` module; `import rela_b200.rela as rela`.
+  rela_b200.*      a ctypes mirror of the same classes (replay.py), used by the
+                   parity tests and the bench because it exposes the raw handle.
 """
 from .capi import ReplayError, lib  # noqa: F401
 from .replay import (  # noqa: F401
@@ -15,3 +22,11 @@ from .replay import (  # noqa: F401
     nstep_return,
     td_priority,
 )
+
+
+def __getattr__(name):
+    if name == "rela":
+        from . import _C  # built by rela_b200.build.build_shim(); no fallback
+
+        return _C
+    raise AttributeError(name)

@@ -1,0 +1,88 @@
+// replay_core.h -- C++ host layer of the B200 replay, above the C ABI
+// (include/rela_b200.h) and below the PrioritizedReplay<T> template
+// (rela_b200/prioritized_replay.h).
+//
+// The reference stores an element as a struct of tensor dictionaries
+// (rela/types.h:18-73) and is schema-agnostic. The host layer flattens a
+// transition into an ordered list of named leaves; the list of the first add
+// fixes the schema (names, dtypes, per-element shapes) of the HBM slabs.
+// PyTorch appears here only as the tensor hand-off: it allocates the batch
+// tensors that rr_sample fills and supplies the caller's CUDA stream.
+#pragma once
+
+#include <cstdint>
+#include <mutex>
+#include <string>
+#include <tuple>
+#include <utility>
+#include <vector>
+
+#include <torch/extension.h>
+
+struct rr_replay;
+
+namespace rela_b200 {
+
+struct Leaf {
+  std::string name;
+  torch::Tensor t;
+};
+using Leaves = std::vector<Leaf>;
+
+struct LeafSpec {
+  std::string name;
+  torch::ScalarType dtype;
+  std::vector<int64_t> shape;  // per stored element
+  uint32_t chunks;             // 1: gathered [B, shape...]; T: gathered [T, B, shape[1:]...]
+  uint64_t row_bytes;
+};
+
+class ReplayCore {
+ public:
+  // PrioritizedReplay(capacity, seed, alpha, beta, prefetch)
+  // (rela/prioritized_replay.h:176-184). The slabs live on CUDA device
+  // `device`; -1 = $RELA_B200_DEVICE, else the current device.
+  ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device = -1);
+  ~ReplayCore();
+  ReplayCore(const ReplayCore&) = delete;
+  ReplayCore& operator=(const ReplayCore&) = delete;
+
+  // add(const DataType& batch, priority): every leaf is [n, ...]; row i is
+  // element i (FFTransition::index, rela/types.cc:48-67).
+  void addBatch(const Leaves& batch, const torch::Tensor& priority);
+  // add(const std::vector<DataType>&, priority): one leaf list per element.
+  // time_major: leaves are [T, ...] sequences gathered into [T, B, ...]
+  // (RNNTransition::makeBatch, rela/types.cc:140-167).
+  void addElements(const std::vector<Leaves>& elements, const torch::Tensor& priority, bool time_major);
+
+  // sample(batchsize, device) (rela/prioritized_replay.h:202-233)
+  std::pair<Leaves, torch::Tensor> sample(int batchsize, const std::string& device);
+  // updatePriority(priority) (rela/prioritized_replay.h:235-245)
+  void updatePriority(const torch::Tensor& priority);
+
+  int size() const;
+  int numAdd() const;
+
+  void sync();  // waits for the device; throws on a sticky device-side error
+  rr_replay* handle() const { return h_; }
+  int device() const { return device_; }
+  const std::vector<LeafSpec>& schema() const { return schema_; }
+
+ private:
+  void ensureSchema(const Leaves& first, bool per_element, bool time_major);
+  void checkLeaf(size_t i, const torch::Tensor& t, bool per_element, int64_t n) const;
+  torch::Tensor weightsOf(const torch::Tensor& priority, unsigned* flags) const;
+
+  rr_replay* h_ = nullptr;
+  int device_ = 0;
+  float alpha_ = 1.0f;
+  bool host_pow_ = true;
+  std::once_flag schema_once_;
+  std::vector<LeafSpec> schema_;
+  bool schema_set_ = false;
+  mutable std::mutex schema_m_;
+};
+
+[[noreturn]] void throwLast(int code, const char* where);
+
+}  // namespace rela_b200

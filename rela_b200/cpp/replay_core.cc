@@ -1,0 +1,244 @@
+// replay_core.cc -- host layer above the C ABI; see rela_b200/replay_core.h.
+#include "rela_b200/replay_core.h"
+
+#include <algorithm>
+#include <cstdlib>
+#include <stdexcept>
+
+#include <c10/cuda/CUDAFunctions.h>
+#include <c10/cuda/CUDAStream.h>
+
+#include "rela_b200.h"
+
+namespace rela_b200 {
+
+void throwLast(int code, const char* where) {
+  std::string msg = std::string(where) + ": rela_b200 error " + std::to_string(code) + ": " + rr_last_error();
+  throw std::runtime_error(msg);
+}
+
+namespace {
+
+inline void check(int rc, const char* where) {
+  if (rc != RR_OK) throwLast(rc, where);
+}
+
+int pickDevice(int device) {
+  if (device >= 0) return device;
+  if (const char* e = std::getenv("RELA_B200_DEVICE")) {
+    std::string s(e);
+    auto pos = s.find(':');
+    return std::atoi(pos == std::string::npos ? s.c_str() : s.c_str() + pos + 1);
+  }
+  if (!torch::cuda::is_available()) return 0;  // rr_create reports the missing device
+  return (int)c10::cuda::current_device();
+}
+
+inline void* streamOf(int device) {
+  return (void*)c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
+}
+
+uint64_t numelOf(const std::vector<int64_t>& shape) {
+  uint64_t n = 1;
+  for (auto s : shape) n *= (uint64_t)s;
+  return n;
+}
+
+}  // namespace
+
+ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device)
+    : alpha_(alpha) {
+  device_ = pickDevice(device);
+  // Host priorities are raised with the function the reference calls
+  // (torch::pow on the CPU, rela/prioritized_replay.h:188,239), which makes the
+  // stored weights -- and through them the sampled indices -- bit-identical to
+  // the reference's. RELA_B200_DEVICE_POW=1 raises them in the kernel instead
+  // (fp64 pow rounded once; <= 1e-6 relative).
+  const char* e = std::getenv("RELA_B200_DEVICE_POW");
+  host_pow_ = !(e && std::atoi(e) != 0);
+  check(rr_create(&h_, capacity, seed, alpha, beta, prefetch, device_), "PrioritizedReplay");
+}
+
+ReplayCore::~ReplayCore() {
+  if (h_ != nullptr) rr_destroy(h_);
+}
+
+int ReplayCore::size() const { return rr_size(h_); }
+int ReplayCore::numAdd() const { return rr_num_add(h_); }
+void ReplayCore::sync() { check(rr_sync(h_), "sync"); }
+
+void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_major) {
+  std::lock_guard<std::mutex> lk(schema_m_);
+  if (schema_set_) return;
+  std::vector<LeafSpec> specs;
+  for (const Leaf& lf : first) {
+    if (!lf.t.defined()) throw std::runtime_error("add: leaf '" + lf.name + "' is undefined");
+    LeafSpec s;
+    s.name = lf.name;
+    s.dtype = lf.t.scalar_type();
+    auto sz = lf.t.sizes();
+    if (per_element) {
+      s.shape.assign(sz.begin(), sz.end());
+      if (s.shape.empty()) s.shape.push_back(1);  // 0-dim seqLen (r2d2_actor.h:109)
+      // sequences [T, ...] and hidden states [layers, hid] are gathered on
+      // dim 1; seq_len is gathered on dim 0 (rela/types.cc:161-167)
+      const bool scalar = lf.t.dim() == 0 || (lf.t.dim() == 1 && sz[0] == 1 && lf.name == "seq_len");
+      s.chunks = (time_major && !scalar) ? (uint32_t)s.shape[0] : 1u;
+    } else {
+      if (lf.t.dim() < 1) throw std::runtime_error("add: leaf '" + lf.name + "' has no batch dimension");
+      s.shape.assign(sz.begin() + 1, sz.end());
+      s.chunks = 1;
+    }
+    s.row_bytes = numelOf(s.shape) * (uint64_t)c10::elementSize(s.dtype);
+    if (s.chunks == 0) s.chunks = 1;
+    specs.push_back(std::move(s));
+  }
+  std::vector<rr_field> fields(specs.size() ? specs.size() : 1);
+  for (size_t i = 0; i < specs.size(); ++i) {
+    fields[i].name = specs[i].name.c_str();
+    fields[i].row_bytes = specs[i].row_bytes;
+    fields[i].chunks = specs[i].chunks;
+    fields[i].reserved = 0;
+  }
+  check(rr_set_schema(h_, (int)specs.size(), fields.data()), "add (schema)");
+  schema_ = std::move(specs);
+  schema_set_ = true;
+}
+
+void ReplayCore::checkLeaf(size_t i, const torch::Tensor& t, bool per_element, int64_t n) const {
+  const LeafSpec& s = schema_[i];
+  bool ok = t.defined() && t.scalar_type() == s.dtype;
+  if (ok) {
+    const uint64_t want = per_element ? numelOf(s.shape) : numelOf(s.shape) * (uint64_t)n;
+    ok = (uint64_t)t.numel() == want && (per_element || (t.dim() >= 1 && t.size(0) == n));
+  }
+  if (!ok) throw std::runtime_error("add: leaf '" + s.name + "' does not match the schema of the first add");
+}
+
+torch::Tensor ReplayCore::weightsOf(const torch::Tensor& priority, unsigned* flags) const {
+  if (priority.dim() != 1)  // assert(priority.dim() == 1), rela/prioritized_replay.h:187,236
+    throw std::runtime_error("priority must be a 1-D tensor");
+  if (priority.scalar_type() != torch::kFloat32)  // accessor<float, 1>, :59,107
+    throw std::runtime_error("priority must be float32");
+  torch::Tensor p = priority.detach().contiguous();
+  if (p.is_cuda()) {
+    if (p.get_device() != device_) p = p.to(torch::Device(torch::kCUDA, (c10::DeviceIndex)device_));
+    *flags |= RR_PRIO_DEVICE;
+    return p;
+  }
+  if (host_pow_ && alpha_ != 1.0f) {
+    *flags |= RR_PRIO_IS_WEIGHT;
+    return torch::pow(p, alpha_);
+  }
+  return p;
+}
+
+void ReplayCore::addBatch(const Leaves& batch, const torch::Tensor& priority) {
+  unsigned flags = 0;
+  torch::Tensor w = weightsOf(priority, &flags);
+  const int64_t n = w.size(0);
+  if (!schema_set_) ensureSchema(batch, false, false);
+  if (batch.size() != schema_.size()) throw std::runtime_error("add: number of leaves differs from the schema");
+  std::vector<torch::Tensor> keep(batch.size());
+  std::vector<const void*> ptrs(batch.size() ? batch.size() : 1, nullptr);
+  bool any_cuda = false, any_cpu = false;
+  for (size_t i = 0; i < batch.size(); ++i) {
+    checkLeaf(i, batch[i].t, false, n);
+    keep[i] = batch[i].t.contiguous();
+    (keep[i].is_cuda() ? any_cuda : any_cpu) = true;
+  }
+  if (any_cuda && any_cpu) {
+    for (auto& t : keep)
+      if (t.is_cuda()) t = t.cpu();
+    any_cuda = false;
+  }
+  for (size_t i = 0; i < keep.size(); ++i) {
+    if (any_cuda && keep[i].get_device() != device_)
+      keep[i] = keep[i].to(torch::Device(torch::kCUDA, (c10::DeviceIndex)device_));
+    ptrs[i] = keep[i].data_ptr();
+  }
+  if (any_cuda) flags |= RR_ROWS_DEVICE;
+  void* stream = (flags & (RR_ROWS_DEVICE | RR_PRIO_DEVICE)) ? streamOf(device_) : nullptr;
+  check(rr_add(h_, (int)n, ptrs.data(), nullptr, w.data_ptr<float>(), flags, stream), "add");
+}
+
+void ReplayCore::addElements(const std::vector<Leaves>& elements, const torch::Tensor& priority,
+                             bool time_major) {
+  unsigned flags = 0;
+  torch::Tensor w = weightsOf(priority, &flags);
+  const int64_t n = w.size(0);
+  if ((int64_t)elements.size() != n) throw std::runtime_error("add: priority length differs from the elements");
+  if (n == 0) return;
+  if (!schema_set_) ensureSchema(elements[0], true, time_major);
+  const size_t nf = schema_.size();
+  std::vector<torch::Tensor> keep;
+  keep.reserve(nf * (size_t)n);
+  std::vector<const void*> ptrs(std::max<size_t>(nf * (size_t)n, 1), nullptr);
+  bool any_cuda = false, any_cpu = false;
+  for (int64_t e = 0; e < n; ++e) {
+    if (elements[e].size() != nf) throw std::runtime_error("add: number of leaves differs from the schema");
+    for (size_t f = 0; f < nf; ++f) {
+      checkLeaf(f, elements[e][f].t, true, 1);
+      keep.push_back(elements[e][f].t.contiguous());
+      (keep.back().is_cuda() ? any_cuda : any_cpu) = true;
+    }
+  }
+  if (any_cuda && any_cpu) {
+    for (auto& t : keep)
+      if (t.is_cuda()) t = t.cpu();
+    any_cuda = false;
+  }
+  for (int64_t e = 0; e < n; ++e)
+    for (size_t f = 0; f < nf; ++f) ptrs[f * (size_t)n + (size_t)e] = keep[(size_t)e * nf + f].data_ptr();
+  if (any_cuda) flags |= RR_ROWS_DEVICE;
+  void* stream = (flags & (RR_ROWS_DEVICE | RR_PRIO_DEVICE)) ? streamOf(device_) : nullptr;
+  check(rr_add_rows(h_, (int)n, ptrs.data(), w.data_ptr<float>(), flags, stream), "add");
+}
+
+std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::string& device) {
+  if (!schema_set_) {
+    // the reference prints "cannot find enough samples" and asserts (:297-302)
+    throw std::runtime_error("sample: the replay buffer is empty");
+  }
+  const int64_t B = batchsize;
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  Leaves out;
+  out.reserve(schema_.size());
+  std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
+  std::vector<int64_t> shape;
+  for (size_t i = 0; i < schema_.size(); ++i) {
+    const LeafSpec& s = schema_[i];
+    shape.clear();
+    if (s.chunks == 1) {
+      shape.push_back(B);
+      shape.insert(shape.end(), s.shape.begin(), s.shape.end());
+    } else {
+      shape.push_back(s.shape[0]);
+      shape.push_back(B);
+      shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
+    }
+    torch::Tensor t = torch::empty(shape, torch::TensorOptions().dtype(s.dtype).device(home));
+    ptrs[i] = t.data_ptr();
+    out.push_back(Leaf{s.name, std::move(t)});
+  }
+  torch::Tensor weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+  check(rr_sample(h_, batchsize, ptrs.data(), weights.data_ptr<float>(), streamOf(device_)), "sample");
+  const torch::Device want(device);
+  if (want != home && !(want.is_cuda() && !want.has_index())) {
+    // the reference assembles on the host and copies to `device`
+    // (rela/types.cc:34-43); here the batch is assembled in HBM and moved only
+    // if the learner asked for another device
+    for (auto& lf : out) lf.t = lf.t.to(want);
+    weights = weights.to(want);
+  }
+  return {std::move(out), std::move(weights)};
+}
+
+void ReplayCore::updatePriority(const torch::Tensor& priority) {
+  unsigned flags = 0;
+  torch::Tensor w = weightsOf(priority, &flags);
+  check(rr_update_priority(h_, (int)w.size(0), w.data_ptr<float>(), flags, streamOf(device_)),
+        "update_priority");
+}
+
+}  // namespace rela_b200

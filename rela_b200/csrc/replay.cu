@@ -99,6 +99,20 @@ struct Prefetched {
   int B = 0;
 };
 
+// Make the replay's device current for the duration of one C ABI call and put
+// the caller's device back afterwards (the caller may be a torch program whose
+// current device is another GPU).
+struct DeviceScope {
+  int prev = -1, dev;
+  explicit DeviceScope(int d) : dev(d) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceScope() {
+    if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+  }
+};
+
 uint32_t pow2_divisor(uint64_t v, uint32_t cap) {
   uint32_t d = cap;
   while (d > 1 && (v % d) != 0) d >>= 1;
@@ -267,7 +281,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
                 cudaGetErrorString(e));
   }
   if (device < 0 || device >= ndev) return fail(RR_ERR_ARG, "rr_create: device %d of %d", device, ndev);
-  RR_CUDA(cudaSetDevice(device));
+  DeviceScope dev_scope(device);
   rr_replay* r = new rr_replay();
   r->capacity = capacity;
   r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
@@ -329,7 +343,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
 
 int rr_destroy(rr_replay* r) {
   if (r == nullptr) return RR_OK;
-  cudaSetDevice(r->device);
+  DeviceScope dev_scope(r->device);
   cudaDeviceSynchronize();
   for (auto& f : r->fields) cudaFree(f.slab);
   cudaFree(r->w);
@@ -374,7 +388,7 @@ int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields) {
     return fail(RR_ERR_ARG, "rr_set_schema: bad argument");
   if (r->schema_set) return fail(RR_ERR_STATE, "rr_set_schema: schema already set");
   if (nfields > 2 * rr::kMaxCopyFields) return fail(RR_ERR_ARG, "rr_set_schema: too many fields");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   uint64_t total = 0;
   for (int i = 0; i < nfields; ++i) {
     const rr_field& f = fields[i];
@@ -463,7 +477,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
   const bool rows_dev = (flags & RR_ROWS_DEVICE) != 0;
   const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
   const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
 
   LaneGuard guard(r);
   Lane& L = *guard.lane;
@@ -773,7 +787,7 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
   }
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   // out buffers may have been used on the caller's stream before
   RR_CUDA(cudaEventRecord(r->evIn, cs));
   RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
@@ -831,7 +845,7 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   if (n != r->cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
     return fail(RR_ERR_ARG, "rr_update_priority: %d priorities for a batch of %d", n, r->cur_B);
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
   const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
   const float* dprio = priority;
@@ -873,7 +887,7 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
 
 int rr_sync(rr_replay* r) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_sync: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   for (auto& l : r->lanes) RR_CUDA(cudaStreamSynchronize(l.stream));
   RR_CUDA(cudaStreamSynchronize(r->main));
   int err = 0;
@@ -889,7 +903,7 @@ int rr_sync(rr_replay* r) {
 
 int rr_stream_fence(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
   RR_CUDA(cudaEventRecord(r->evOut, r->main));
   RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
@@ -898,7 +912,7 @@ int rr_stream_fence(rr_replay* r, void* stream) {
 
 int rr_set_profiling(rr_replay* r, int enabled, int max_batch) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_set_profiling: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   RR_CUDA(cudaStreamSynchronize(r->main));
   if (enabled && r->hist_cap < max_batch) {
     for (auto* hp : r->hist) RR_CUDA(cudaFree(hp));
@@ -917,7 +931,7 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
     return fail(RR_ERR_ARG, "rr_gather_bench: bad argument");
   const int nsets = (int)std::min(r->hist_n, r->hist.size());
   if (nsets == 0) return fail(RR_ERR_STATE, "rr_gather_bench: no sampled id sets recorded (rr_set_profiling)");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
   const int B = r->hist_B;
   const size_t nf = r->fields.size();
@@ -974,7 +988,7 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
 
 int rr_get_stats(rr_replay* r, rr_stats* out) {
   if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_get_stats: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   RR_CUDA(cudaStreamSynchronize(r->main));
   rr::Ctl h;
   RR_CUDA(cudaMemcpy(&h, r->ctl, sizeof(h), cudaMemcpyDeviceToHost));
@@ -992,7 +1006,7 @@ int rr_get_stats(rr_replay* r, rr_stats* out) {
 int rr_last_sample_ids(rr_replay* r, int n, int32_t* out) {
   if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_last_sample_ids: null");
   if (r->cur_ids < 0 || n != r->cur_B) return fail(RR_ERR_STATE, "rr_last_sample_ids: no batch of %d outstanding", n);
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   RR_CUDA(cudaStreamSynchronize(r->main));
   RR_CUDA(cudaMemcpy(out, r->idbuf[r->cur_ids], sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
   return RR_OK;
@@ -1000,7 +1014,7 @@ int rr_last_sample_ids(rr_replay* r, int n, int32_t* out) {
 
 int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size, double* sum) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_state: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   {
     std::unique_lock<std::mutex> lk(r->m_);
     if (head) *head = r->head_;
@@ -1015,7 +1029,7 @@ int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size
 
 int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
   if (r == nullptr || out16 == nullptr) return fail(RR_ERR_ARG, "rr_debug_select_probe: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   RR_CUDA(cudaStreamSynchronize(r->main));
   RR_CUDA(cudaMemcpy(out16, r->ctl->probe, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
   return RR_OK;
@@ -1023,7 +1037,7 @@ int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
 
 int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_weights: null");
-  RR_CUDA(cudaSetDevice(r->device));
+  DeviceScope dev_scope(r->device);
   RR_CUDA(cudaStreamSynchronize(r->main));
   if (out_w) RR_CUDA(cudaMemcpy(out_w, r->w, sizeof(float) * (size_t)r->S, cudaMemcpyDeviceToHost));
   if (out_evicted) RR_CUDA(cudaMemcpy(out_evicted, r->evicted, (size_t)r->S, cudaMemcpyDeviceToHost));

@@ -527,6 +527,86 @@ class CudaReplay(_Base):
         return {n: getattr(st, n) for n, _ in st._fields_}
 
 
+class CppReplay(CudaReplay):
+    """The product through its C++ host layer: rela_b200._C (pybind module with
+    rela's class names, rela_b200/cpp/). Priorities are passed RAW: the host
+    layer raises them with torch::pow on the CPU like the reference does."""
+
+    def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0, device=0):
+        import torch
+        from rela_b200 import _C, capi
+
+        self.torch, self.capi, self._C = torch, capi, _C
+        self.lib = capi.lib()
+        self.schema = schema
+        self.S = int(1.25 * capacity)
+        self.dev = torch.device("cuda", device)
+        self.rnn = any(f.name == "seq_len" for f in schema)
+        cls = _C.RNNPrioritizedReplay if self.rnn else _C.FFPrioritizedReplay
+        self.r = cls(capacity, seed, alpha, beta, prefetch, device)
+        self.h = C.c_void_p(self.r.handle())
+
+    def close(self):
+        self.r = None
+        self.h = None
+
+    def _record(self, tensors):
+        """tensors: one per schema field -> _C.FFTransition / _C.RNNTransition"""
+        groups = {"obs": {}, "action": {}, "next_obs": {}, "h0": {}}
+        scalars = {}
+        for f, t in zip(self.schema, tensors):
+            grp, _, key = f.name.partition(".")
+            if key:
+                groups[grp][key] = t
+            else:
+                scalars[f.name] = t
+        if self.rnn:
+            return self._C.RNNTransition(groups["obs"], groups["h0"], groups["action"], scalars["reward"],
+                                         scalars["terminal"], scalars["bootstrap"], scalars["seq_len"])
+        return self._C.FFTransition(groups["obs"], groups["action"], scalars["reward"], scalars["terminal"],
+                                    scalars["bootstrap"], groups["next_obs"])
+
+    def add(self, rows, priority):
+        t = self.torch
+        p = t.from_numpy(np.ascontiguousarray(priority, dtype=np.float32))
+        tens = [t.from_numpy(np.ascontiguousarray(r)) for r in rows]
+        if self.rnn:
+            self.r.add([self._record([x[i] for x in tens]) for i in range(len(p))], p)
+        else:
+            self.r.add(self._record(tens), p)
+
+    def sample(self, B, want_rows=True):
+        batch, w = self.r.sample(B, str(self.dev))
+        ids = np.zeros(B, dtype=np.int32)
+        self.capi.check(self.lib.rr_last_sample_ids(self.h, B, ids.ctypes.data))
+        rows = None
+        if want_rows:
+            rows = []
+            attr = {"obs": batch.obs, "action": batch.action, "h0": getattr(batch, "h0", None),
+                    "next_obs": getattr(batch, "next_obs", None)}
+            for f in self.schema:
+                grp, _, key = f.name.partition(".")
+                x = attr[grp][key] if key else getattr(batch, f.name)
+                assert x.is_cuda
+                a = x.cpu().numpy()
+                if f.name == "seq_len":
+                    assert a.shape == (B,)
+                    a = a.reshape(B, 1)
+                assert a.shape == f.batch_shape(B), (f.name, a.shape)
+                rows.append(a)
+        return 0, rows, w.cpu().numpy(), ids
+
+    def update(self, priority):
+        self.r.update_priority(self.torch.from_numpy(np.ascontiguousarray(priority, dtype=np.float32)))
+        return 0
+
+    def size(self):
+        return self.r.size()
+
+    def num_add(self):
+        return self.r.num_add()
+
+
 # ---------------------------------------------------------------- golden vectors
 # Generated from the unmodified reference by tests/golden/make_golden.py.
 GOLDEN_CASES = {
@@ -556,7 +636,7 @@ def digest(a):
     return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8)
 
 
-def check_against_golden(name, make_impl, w_rtol=1e-6):
+def check_against_golden(name, make_impl, w_rtol=1e-6, raw_priority=False):
     """Replay the golden trace `name` on make_impl(schema, cap, seed, alpha,
     beta, prefetch) (an implementation that takes priority ** alpha computed by
     torch_pow) and compare with what the reference produced."""
@@ -565,7 +645,7 @@ def check_against_golden(name, make_impl, w_rtol=1e-6):
     ops = gen_trace(schema, cap, tseed, cycles, K, B)
     g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     impl = make_impl(schema, cap, seed, alpha, beta, pf)
-    rec = apply_trace(impl, ops, alpha, False)
+    rec = apply_trace(impl, ops, alpha, raw_priority)
     assert len(rec) == g["ids"].shape[0]
     for k, r in enumerate(rec):
         np.testing.assert_array_equal(r["ids"], g["ids"][k], err_msg=f"{name} sample {k}: ids")
