@@ -212,7 +212,7 @@ def workload_config(args, where):
 def fill_device(replay, torch, dev, capacity, extra, block=8192, seed=1):
     """Write real bytes to every slot: fresh random frames generated on the
     device, added through add() in blocks (device-resident rows -> K1 insert)."""
-    from rela_b200 import FFTransition
+    from rela_b200.rela import FFTransition  # the C++ host layer's record type
 
     g = torch.Generator(device=dev)
     g.manual_seed(seed)
@@ -239,6 +239,7 @@ def run_ours(args):
     import numpy as np
     import torch
     import rela_b200
+    import rela_b200.rela
     from rela_b200 import capi
 
     rank = int(os.environ.get("RANK", "0"))
@@ -256,15 +257,32 @@ def run_ours(args):
 
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
     L = capi.lib()
-    replay = rela_b200.FFPrioritizedReplay(args.capacity, 7 + rank, args.alpha, args.beta, 0, device=dev)
+    # One replay, built and filled through the C++ host layer (rela_b200/_C.so,
+    # rela's class names); the device-resident leg below drives the same object
+    # through the C ABI by its handle.
+    replay = rela_b200.rela.FFPrioritizedReplay(args.capacity, 7 + rank, args.alpha, args.beta, 0, local_rank)
     t0 = time.time()
     fill_device(replay, torch, dev, args.capacity, 64, seed=1 + rank)
     fill_s = time.time() - t0
     assert replay.size() == args.capacity + 64
-    schema = replay._schema
+
+    class Leaf:
+        def __init__(self, name, dtype, shape, chunks, row_bytes):
+            self.name, self.dtype, self.shape, self.chunks = name, dtype, tuple(shape), chunks
+
+        def batch_shape(self, n):
+            return (n,) + self.shape if self.chunks == 1 else (self.shape[0], n) + self.shape[1:]
+
+    schema = [Leaf(*t) for t in replay.schema()]
+    assert sum(t[4] for t in replay.schema()) == ROW_BYTES
     stream = torch.cuda.current_stream(dev)
     sp = C.c_void_p(stream.cuda_stream)
-    h = replay._h
+    h = C.c_void_p(replay.handle())
+
+    def get_stats():
+        st = capi.RRStats()
+        capi.check(L.rr_get_stats(h, C.byref(st)))
+        return {n: getattr(st, n) for n, _ in st._fields_}
 
     # 8 rotating output batches (232 MB > L2) and device-resident priorities
     R = 8
@@ -304,11 +322,11 @@ def run_ours(args):
     # ---- value: device-resident inputs, C ABI
     for k in range(W):
         cycle_dev(k)
-    st0 = replay.stats()
+    st0 = get_stats()
     clocks = ClockSampler(local_rank)
     clocks.start()
     ms = timed(cycle_dev, K)
-    st1 = replay.stats()
+    st1 = get_stats()
     launches = st1["kernel_launches"] - st0["kernel_launches"]
 
     # ---- roofline: record the id sets of 16 real samples, then re-launch the
@@ -326,8 +344,10 @@ def run_ours(args):
     gather_us = ms_pl.value * 1e3
 
     # ---- e2e: public API, priorities from pinned host memory, weights read back
+    dev_str = "cuda:%d" % local_rank
+
     def cycle_e2e(k):
-        batch, w = replay.sample(B, dev)
+        batch, w = replay.sample(B, dev_str)
         w_host = w.cpu()  # D2H read of the step's result (also the learner's sync point)
         replay.update_priority(prio_host[k % 16])
         return w_host
@@ -337,7 +357,7 @@ def run_ours(args):
     ms_e2e = timed(cycle_e2e, K)
     clk = clocks.stop()
     replay.sync()
-    st2 = replay.stats()
+    st2 = get_stats()
     assert st2["samples_ordered"] == 0, "benchmark weights must take the exact parallel selection"
     assert st2["device_errors"] == 0
 
@@ -365,7 +385,7 @@ def run_ours(args):
         "config": workload_config(args, "1 GPU" if world == 1 else "%d independent capacity shards" % world),
         "e2e": {"value": e2e, "unit": "transitions/s", "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B,
                 "ms_per_step": ms_e2e / K,
-                "api": "rela_b200.FFPrioritizedReplay.sample(B,'cuda') + weights.cpu() + update_priority(pinned cpu)"},
+                "api": "rela_b200.rela.FFPrioritizedReplay (C++ host layer, rela/pybind.cc names): sample(B,'cuda:0') + weights.cpu() + update_priority(pinned cpu tensor)"},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

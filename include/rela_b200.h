@@ -118,6 +118,31 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields,
 int rr_update_priority(rr_replay* r, int n, const float* priority,
                        unsigned flags, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * Capacity sharding over the GPUs of one NVSwitch box (no reference
+ * counterpart). One process per GPU. Every shard keeps
+ * the FULL control state (weights, evicted flags, prefix hierarchy, sum_, RNG:
+ * 4 B per slot) and applies every add / sample / update in the same order, so
+ * all shards select the same ids -- bit-identical to the single-buffer
+ * reference -- with no collective in the sampling path. Only the payload slabs
+ * are partitioned: shard `rank` stores slots [rank * ceil(S / world), ...).
+ *   rr_add*  receives the whole block; rows of other shards are skipped.
+ *   rr_sample gathers only the rows this shard owns, straight into
+ *            out_fields, which on non-learner shards are peer-mapped pointers
+ *            (rr_ipc_open) into the learner GPU's batch tensors: NVLink stores.
+ * Call rr_set_shard before rr_set_schema. prefetch must be 0. */
+int rr_set_shard(rr_replay* r, int rank, int world);
+int rr_shard_range(const rr_replay* r, int* lo, int* hi);
+
+/* Peer-memory plumbing for the learner's batch buffers: cudaMalloc'ed on the
+ * learner GPU, exported as a 64-byte CUDA IPC handle, opened by the other
+ * shards' processes with peer access over NVLink. */
+int rr_device_alloc(int device, uint64_t bytes, void** out_ptr);
+int rr_device_free(int device, void* ptr);
+int rr_ipc_export(int device, const void* ptr, void* handle64_out);
+int rr_ipc_open(int device, const void* handle64, void** out_ptr);
+int rr_ipc_close(int device, void* ptr);
+
 int rr_size(const rr_replay* r);    /* safeSize_ (prioritized_replay.h:247) */
 int rr_num_add(const rr_replay* r); /* numAdd_   (prioritized_replay.h:251) */
 

@@ -23,10 +23,3 @@ from .replay import (  # noqa: F401
     td_priority,
 )
 
-
-def __getattr__(name):
-    if name == "rela":
-        from . import _C  # built by rela_b200.build.build_shim(); no fallback
-
-        return _C
-    raise AttributeError(name)

@@ -39,6 +39,11 @@ struct CopyParams {
   int rows;             // B (gather) or n (insert)
   int insert_start;     // insert: first slot
   int slots;            // insert: S
+  // Capacity sharding: this GPU's slabs hold only slots
+  // [own_lo, own_hi) of the ring, slab row = slot - own_lo. Rows whose slot is
+  // outside the range are skipped by both directions (another shard moves
+  // them). Unsharded: [0, S).
+  int own_lo, own_hi;
   int stages;           // smem ring depth
   uint32_t stage_bytes; // smem bytes per stage (>= max piece_bytes)
   unsigned long long* probe;  // debug: 8 timestamps per CTA (tools/gather_probe.cu), else null

@@ -126,6 +126,8 @@ struct rr_replay {
   int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
+  // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
+  int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
   int sm_count = 148;
   int g_stages = 32, g_piece = 8192, g_ctas = 1, g_simt_only = 0;
   std::vector<FieldInfo> fields;
@@ -197,6 +199,8 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
   p.rows = rows;
   p.insert_start = insert_start;
   p.slots = r->S;
+  p.own_lo = r->own_lo;
+  p.own_hi = r->own_hi;
   uint32_t items = 0;
   uint64_t units = 0;
   uint32_t max_piece = 0;
@@ -286,6 +290,8 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   r->capacity = capacity;
   r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
   r->S_pad = ((r->S + rr::kTile - 1) / rr::kTile) * rr::kTile;
+  r->own_lo = 0;
+  r->own_hi = r->S;
   r->seed = seed;
   r->alpha = alpha;
   r->beta = beta;
@@ -395,7 +401,7 @@ int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields) {
     if (f.chunks == 0 || f.row_bytes % f.chunks != 0 || f.row_bytes >= (1ull << 32))
       return fail(RR_ERR_ARG, "rr_set_schema: field %d: row_bytes %llu chunks %u", i,
                   (unsigned long long)f.row_bytes, f.chunks);
-    total += f.row_bytes * (uint64_t)r->S;
+    total += f.row_bytes * (uint64_t)(r->own_hi - r->own_lo);
   }
   size_t free_b = 0, total_b = 0;
   RR_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -411,18 +417,76 @@ int rr_set_schema(rr_replay* r, int nfields, const rr_field* fields) {
     fi.chunk_bytes = (uint32_t)(fi.row_bytes / fi.chunks);
     fi.slab = nullptr;
     if (fi.row_bytes > 0) {
-      cudaError_t e = cudaMalloc(&fi.slab, fi.row_bytes * (uint64_t)r->S);
+      cudaError_t e = cudaMalloc(&fi.slab, std::max<uint64_t>(fi.row_bytes * (uint64_t)(r->own_hi - r->own_lo), 16));
       if (e != cudaSuccess) {
         for (auto& g : r->fields) cudaFree(g.slab);
         r->fields.clear();
         return fail(RR_ERR_NOMEM, "rr_set_schema: cudaMalloc of %.1f GB failed: %s",
-                    fi.row_bytes * (double)r->S / 1e9, cudaGetErrorString(e));
+                    fi.row_bytes * (double)(r->own_hi - r->own_lo) / 1e9, cudaGetErrorString(e));
       }
     }
     r->fields.push_back(fi);
   }
   r->slab_bytes = total;
   r->schema_set = true;
+  return RR_OK;
+}
+
+int rr_set_shard(rr_replay* r, int rank, int world) {
+  if (r == nullptr || world < 1 || rank < 0 || rank >= world) return fail(RR_ERR_ARG, "rr_set_shard: bad argument");
+  if (r->schema_set) return fail(RR_ERR_STATE, "rr_set_shard: must precede rr_set_schema");
+  if (world > 1 && r->prefetch > 0)
+    return fail(RR_ERR_ARG, "rr_set_shard: prefetch is not supported on a sharded replay");
+  const int per = (r->S + world - 1) / world;
+  r->shard_rank = rank;
+  r->shard_world = world;
+  r->own_lo = std::min(r->S, rank * per);
+  r->own_hi = std::min(r->S, r->own_lo + per);
+  return RR_OK;
+}
+
+int rr_shard_range(const rr_replay* r, int* lo, int* hi) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_shard_range: null");
+  if (lo) *lo = r->own_lo;
+  if (hi) *hi = r->own_hi;
+  return RR_OK;
+}
+
+int rr_device_alloc(int device, uint64_t bytes, void** out) {
+  if (out == nullptr || bytes == 0) return fail(RR_ERR_ARG, "rr_device_alloc: bad argument");
+  DeviceScope dev_scope(device);
+  RR_CUDA(cudaMalloc(out, bytes));
+  return RR_OK;
+}
+
+int rr_device_free(int device, void* ptr) {
+  DeviceScope dev_scope(device);
+  RR_CUDA(cudaFree(ptr));
+  return RR_OK;
+}
+
+int rr_ipc_export(int device, const void* ptr, void* handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  if (ptr == nullptr || handle64 == nullptr) return fail(RR_ERR_ARG, "rr_ipc_export: null");
+  DeviceScope dev_scope(device);
+  cudaIpcMemHandle_t h;
+  RR_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+  memcpy(handle64, &h, sizeof(h));
+  return RR_OK;
+}
+
+int rr_ipc_open(int device, const void* handle64, void** out) {
+  if (handle64 == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_ipc_open: null");
+  DeviceScope dev_scope(device);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  RR_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return RR_OK;
+}
+
+int rr_ipc_close(int device, void* ptr) {
+  DeviceScope dev_scope(device);
+  RR_CUDA(cudaIpcCloseMemHandle(ptr));
   return RR_OK;
 }
 
@@ -547,15 +611,20 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
             memcpy(stage + (size_t)i * f.row_bytes, src, f.row_bytes);
           }
         }
-        RR_CUDA(cudaMemcpyAsync(f.slab + (size_t)start * f.row_bytes, stage, f.row_bytes * (size_t)n1,
-                                cudaMemcpyHostToDevice, L.stream));
-        if (n1 < n) {
-          RR_CUDA(cudaMemcpyAsync(f.slab, stage + (size_t)n1 * f.row_bytes, f.row_bytes * (size_t)(n - n1),
-                                  cudaMemcpyHostToDevice, L.stream));
+        // the block's slots are [start, start + n1) and, after the wrap,
+        // [0, n - n1); only the part this shard owns is stored
+        const int seg_slot[2] = {start, 0}, seg_len[2] = {n1, n - n1}, seg_row[2] = {0, n1};
+        for (int sgi = 0; sgi < 2; ++sgi) {
+          const int lo = std::max(seg_slot[sgi], r->own_lo);
+          const int hi = std::min(seg_slot[sgi] + seg_len[sgi], r->own_hi);
+          if (lo >= hi) continue;
+          RR_CUDA(cudaMemcpyAsync(f.slab + (size_t)(lo - r->own_lo) * f.row_bytes,
+                                  stage + (size_t)(seg_row[sgi] + lo - seg_slot[sgi]) * f.row_bytes,
+                                  f.row_bytes * (size_t)(hi - lo), cudaMemcpyHostToDevice, L.stream));
+          r->h2d_bytes += f.row_bytes * (uint64_t)(hi - lo);
         }
         stage += f.row_bytes * (size_t)n;
       }
-      r->h2d_bytes += row_total * (uint64_t)n;
     } else {
       // K1: device-resident rows -> slab with the row-copy kernel
       const uint8_t* const* dptrs = nullptr;

@@ -34,26 +34,38 @@ __device__ __forceinline__ void copy_unit(uint8_t* dst, const uint8_t* src, uint
 // Source / destination of (field, row b, chunk t) at byte offset `off` in the chunk.
 // The destination never depends on the sampled ids, so it can be computed
 // before the kernel's dependencies have resolved.
+// Slot of row b: the sampled id (gather) or (start + b) % S (insert); false if
+// another shard owns it.
+__device__ __forceinline__ bool row_slot(const CopyParams& p, uint32_t b, uint32_t* local) {
+  uint32_t slot;
+  if (p.ids != nullptr) {
+    slot = (uint32_t)__ldg(p.ids + b);
+  } else {
+    slot = (uint32_t)p.insert_start + b;
+    if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;
+  }
+  *local = slot - (uint32_t)p.own_lo;
+  return slot >= (uint32_t)p.own_lo && slot < (uint32_t)p.own_hi;
+}
+
 __device__ __forceinline__ uint8_t* row_dst(const CopyParams& p, const CopyField& f, uint32_t b, uint32_t t,
-                                            uint32_t off) {
+                                            uint32_t off, uint32_t local) {
   if (p.ids != nullptr) {  // gather: batch [t, b, :]
     return f.dst + (uint64_t)t * f.dst_chunk_stride + (uint64_t)b * f.dst_row_stride + off;
   }
-  uint32_t slot = (uint32_t)p.insert_start + b;  // insert: slab row (start + b) % S
-  if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;
-  return f.dst + (uint64_t)slot * f.dst_row_stride + (uint64_t)t * f.chunk_bytes + off;
+  return f.dst + (uint64_t)local * f.dst_row_stride + (uint64_t)t * f.chunk_bytes + off;  // insert: slab row
 }
 
 __device__ __forceinline__ const uint8_t* row_src(const CopyParams& p, const CopyField& f, uint32_t b, uint32_t t,
-                                                  uint32_t off) {
+                                                  uint32_t off, uint32_t local) {
   const uint64_t inner = (uint64_t)t * f.chunk_bytes + off;
-  if (p.ids != nullptr) return f.src + (uint64_t)(uint32_t)__ldg(p.ids + b) * f.src_row_stride + inner;
+  if (p.ids != nullptr) return f.src + (uint64_t)local * f.src_row_stride + inner;
   return (f.row_ptrs != nullptr ? f.row_ptrs[b] : f.src + (uint64_t)b * f.src_row_stride) + inner;
 }
 
 struct Item {
   const CopyField* f;
-  uint8_t* dst;
+  uint8_t* dst;  // gather only (an insert's destination needs the slot)
   uint32_t b, t, off, bytes;
 };
 
@@ -74,7 +86,7 @@ __device__ __forceinline__ Item decode_item(const CopyParams& p, uint32_t item) 
   it.b = ct / f.chunks;
   it.off = piece * f.piece_bytes;
   it.bytes = min(f.piece_bytes, f.chunk_bytes - it.off);
-  it.dst = row_dst(p, f, it.b, it.t, it.off);
+  it.dst = p.ids != nullptr ? row_dst(p, f, it.b, it.t, it.off, 0u) : nullptr;
   return it;
 }
 
@@ -120,12 +132,13 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     if (probe && tid == 0) probe[2] = clock64();
     if (active) {
       uint32_t use = 0;
-      for (uint32_t j = (uint32_t)tid; j < mine; j += NS, ++use) {
-        if (use > 0) {
-          it = decode_item(p, first + j * step);
-          bulk_wait_read<0>();  // my previous store has drained the stage
-        }
-        const uint8_t* src = row_src(p, *it.f, it.b, it.t, it.off);
+      for (uint32_t j = (uint32_t)tid; j < mine; j += NS) {
+        if (j != (uint32_t)tid) it = decode_item(p, first + j * step);
+        uint32_t local;
+        if (!row_slot(p, it.b, &local)) continue;  // another shard's row
+        if (use > 0) bulk_wait_read<0>();  // my previous store has drained the stage
+        const uint8_t* src = row_src(p, *it.f, it.b, it.t, it.off, local);
+        if (p.ids == nullptr) it.dst = row_dst(p, *it.f, it.b, it.t, it.off, local);
         mbar_expect_tx(bar, it.bytes);
         bulk_g2s(stage, src, it.bytes, bar);
         if (probe && tid == 0 && use == 0) probe[3] = clock64();
@@ -133,6 +146,7 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
         if (probe && tid == 0 && use == 0) probe[4] = clock64();
         bulk_s2g(it.dst, stage, it.bytes);
         bulk_commit();
+        ++use;
       }
       if (probe && tid == 0) probe[5] = clock64();
       // the stores only have to be done READING shared memory before the CTA
@@ -167,7 +181,9 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     const uint64_t ct = local / upc;
     const uint32_t t = (uint32_t)(ct % f.chunks);
     const uint32_t b = (uint32_t)(ct / f.chunks);
-    copy_unit(row_dst(p, f, b, t, v * f.vec), row_src(p, f, b, t, v * f.vec), f.vec);
+    uint32_t row;
+    if (!row_slot(p, b, &row)) continue;
+    copy_unit(row_dst(p, f, b, t, v * f.vec, row), row_src(p, f, b, t, v * f.vec, row), f.vec);
   }
 }
 
