@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--alpha", type=float, default=0.6)
     ap.add_argument("--beta", type=float, default=0.4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sharded", action="store_true")
     ap.add_argument("--cpu-cycles", type=int, default=300)
     return ap.parse_args()
 
@@ -235,6 +236,71 @@ def fill_device(replay, torch, dev, capacity, extra, block=8192, seed=1):
     replay.sync()
 
 
+def run_sharded(args, torch, dist, dev, rank, world, local_rank):
+    """BASELINE.json configs[4]: ONE replay of world * capacity transitions whose
+    payload is partitioned over the GPUs (rela_b200/sharded.py); every batch is
+    assembled on the learner GPU (rank 0) by bulk stores over NVLink. Returns the
+    object reported under "sharded" (informational; `value` stays the
+    independent-shards number)."""
+    from rela_b200.sharded import FF_LEAVES, ShardedPrioritizedReplay
+
+    B, K, W = args.batch, min(args.steps, 5000), max(args.warmup, 3)
+    total_cap = args.capacity * world
+    rep = ShardedPrioritizedReplay(total_cap, 7, args.alpha, args.beta, FF_LEAVES, device=dev, batch_sets=2)
+    g = torch.Generator(device=dev)
+    g.manual_seed(100 + rank)
+    t0 = time.time()
+    block = 2048  # rows per rank per collective add
+    rounds = (total_cap + 64 + block * world - 1) // (block * world)
+    for it in range(rounds):
+        n = block
+        term = torch.rand(n, device=dev, generator=g) < 0.005
+        leaves = [torch.randint(0, 256, (n,) + FRAME, dtype=torch.uint8, device=dev, generator=g),
+                  torch.rand((n, 1), device=dev, generator=g), torch.ones((n, N_ACT), device=dev),
+                  torch.arange(n, dtype=torch.int64, device=dev) + (it * world + rank) * n,
+                  torch.randn(n, device=dev, generator=g), term, 1.0 - term.float(),
+                  torch.randint(0, 256, (n,) + FRAME, dtype=torch.uint8, device=dev, generator=g),
+                  torch.rand((n, 1), device=dev, generator=g), torch.ones((n, N_ACT), device=dev)]
+        if rep._size + n * world > rep.S:
+            break
+        rep.add(leaves, torch.rand(n, device=dev, generator=g) + 0.01)
+    torch.cuda.synchronize(dev)
+    fill_s = time.time() - t0
+    prio = torch.rand((16, B), device=dev, generator=g) + 0.01
+
+    def cycle(k):
+        tens, w = rep.sample(B, 0)
+        rep.update_priority(prio[k % 16] if rank == 0 else None)
+
+    for k in range(W):
+        cycle(k)
+    dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(K):
+        cycle(k)
+    e1.record()
+    dist.barrier()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    rep.engine.sync()
+    size = rep.size()
+    rep.engine.close()
+    tps = B * K / (ms * 1e-3)
+    return {"workload": "one replay of %d transitions striped over %d GPUs (%.1f GB of slabs per GPU), batch %d "
+                        "assembled on GPU 0 over NVLink, sample+update_priority" %
+                        (total_cap, world, int(1.25 * total_cap) / world * ROW_BYTES / 1e9, B),
+            "value": tps, "unit": "transitions/s", "ms_per_step": ms / K, "steps": K, "size": size,
+            "learner_nvlink_ingress_gbs": tps * ROW_BYTES * (world - 1) / world / 1e9,
+            "nvlink_peak_gbs_per_direction": 900.0, "fill_s": fill_s,
+            "collectives_per_step": "1 x 4-byte all-reduce (completion of the peer stores) + 1 x %d-byte broadcast "
+                                    "(new priorities); none on the selection path" % (4 * B)}
+
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -257,6 +323,11 @@ def run_ours(args):
 
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
     L = capi.lib()
+    sharded = None
+    if world > 1 and not args.no_sharded:
+        sharded = run_sharded(args, torch, dist, dev, rank, world, local_rank)
+        torch.cuda.synchronize(dev)
+        torch.cuda.empty_cache()
     # One replay, built and filled through the C++ host layer (rela_b200/_C.so,
     # rela's class names); the device-resident leg below drives the same object
     # through the C ABI by its handle.
@@ -396,6 +467,8 @@ def run_ours(args):
                      "step_share": gather_us * 1e-3 / (ms / K)},
         "fill_s": fill_s, "slab_gb": st2["slab_bytes"] / 1e9,
     }
+    if sharded is not None:
+        line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         from harness import have_ref
 
