@@ -113,6 +113,14 @@ int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs,
 int rr_sample(rr_replay* r, int batch, void* const* out_fields,
               float* out_weights, void* stream);
 
+/* rr_sample in two steps, so that a host layer can allocate the batch tensors
+ * while the selection kernels already run: rr_sample_select issues the prefix
+ * hierarchy, selection, eviction and importance weights (sample_ lines
+ * 258-325); rr_sample_gather issues makeBatch (line 326) into out_fields and
+ * orders the results on `stream`. rr_sample == select + gather. */
+int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream);
+int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream);
+
 /* updatePriority(priority) (prioritized_replay.h:235-245, 105-119): n must be
  * the size of the batch last returned by rr_sample. Evicted ids are skipped. */
 int rr_update_priority(rr_replay* r, int n, const float* priority,

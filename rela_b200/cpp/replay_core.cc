@@ -202,6 +202,11 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
   }
   const int64_t B = batchsize;
   const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  // The selection kernels are issued first; the batch tensors are allocated
+  // while they run, then the gather is issued behind them.
+  torch::Tensor weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+  void* stream = streamOf(device_);
+  check(rr_sample_select(h_, batchsize, weights.data_ptr<float>(), stream), "sample");
   Leaves out;
   out.reserve(schema_.size());
   std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
@@ -221,8 +226,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
     ptrs[i] = t.data_ptr();
     out.push_back(Leaf{s.name, std::move(t)});
   }
-  torch::Tensor weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
-  check(rr_sample(h_, batchsize, ptrs.data(), weights.data_ptr<float>(), streamOf(device_)), "sample");
+  check(rr_sample_gather(h_, ptrs.data(), stream), "sample");
   const torch::Device want(device);
   if (want != home && !(want.is_cuda() && !want.has_index())) {
     // the reference assembles on the host and copies to `device`

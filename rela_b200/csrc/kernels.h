@@ -62,8 +62,16 @@ struct CopyLaunch {
 cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream);
 
 // ------------------------------------------------------------- selection
-constexpr int kGroup = 32;     // slots per level-1 group
-constexpr int kTile = 1024;    // slots per level-2 tile
+// Two-level prefix structure over the S_pad weights: tiles of (1 << tile_log2)
+// slots (256 ... 2048, chosen so that there are at most kMaxTiles tiles) whose
+// sums are rebuilt per sample by build_hierarchy_kernel, scanned in shared
+// memory by every CTA of select_kernel, and searched per target; the slot
+// inside the tile is found by one warp reading the tile's weights.
+constexpr int kBuildSpan = 2048;   // slots per CTA of build_hierarchy_kernel; S_pad is a multiple
+constexpr int kMinTileLog2 = 8;
+constexpr int kMaxTileLog2 = 11;
+constexpr int kMaxTiles = 16384;   // tile prefixes held in shared memory (128 KB)
+constexpr int kSelTargets = 32;    // targets per CTA of select_kernel
 
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
 // PrioritizedReplay (reference rela/prioritized_replay.h:166,343).
@@ -72,20 +80,23 @@ struct Ctl {
   uint32_t mt[624];
   int mti;
   int error;                       // sticky RR_ERR_* raised by a kernel
+  unsigned int done_ctas;          // select_kernel: CTAs that finished their targets
+  int sel_fail;                    // select_kernel: a target ran past the buffer
   unsigned long long n_exact;      // samples selected by the parallel search
   unsigned long long n_ordered;    // samples that needed the ordered walk
   unsigned long long n_popped;
-  unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel
+  unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel (CTA 0)
 };
 
 struct SelectArgs {
   Ctl* ctl;
   float* w;             // [S_pad] priority^alpha per slot; dead slots hold 0
   uint8_t* evicted;     // [S]
-  double* l1;           // [S_pad / 32]
-  double* l2;           // [S_pad / 1024]
-  float* l2min;         // [S_pad / 1024] min non-zero weight per tile
+  double* l2;           // [S_pad >> tile_log2] tile sums
+  float* l2min;         // [S_pad >> tile_log2] min non-zero weight per tile
+  float* wsel;          // [>= B] scratch: weight of each selected slot
   int S, S_pad;
+  int tile_log2;
   int head;             // ring head at selection time
   int size;             // safeSize_: elements the walk may visit
   int size_is;          // size_ re-read before the pop (prioritized_replay.h:312)

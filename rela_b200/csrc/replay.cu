@@ -123,6 +123,9 @@ uint32_t pow2_divisor(uint64_t v, uint32_t cap) {
 
 struct rr_replay {
   // configuration
+  int tile_log2 = 8;
+  float* wsel = nullptr;
+  int wsel_cap = 0;
   int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
@@ -137,7 +140,6 @@ struct rr_replay {
   // device state
   float* w = nullptr;
   uint8_t* evicted = nullptr;
-  double* l1 = nullptr;
   double* l2 = nullptr;
   float* l2min = nullptr;
   rr::Ctl* ctl = nullptr;
@@ -162,6 +164,8 @@ struct rr_replay {
   std::vector<int> idcap;
   std::vector<bool> idbusy;
   int cur_ids = -1, cur_B = 0;
+  float* pend_w = nullptr;
+  int pend_slot = -1, pend_B = 0, pend_pop = 0;  // rr_sample_select done, rr_sample_gather pending
   std::deque<Prefetched> queue;
   std::vector<Prefetched> pool;
 
@@ -289,7 +293,14 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   rr_replay* r = new rr_replay();
   r->capacity = capacity;
   r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
-  r->S_pad = ((r->S + rr::kTile - 1) / rr::kTile) * rr::kTile;
+  r->S_pad = ((r->S + rr::kBuildSpan - 1) / rr::kBuildSpan) * rr::kBuildSpan;
+  r->tile_log2 = std::min(rr::kMaxTileLog2, std::max(rr::kMinTileLog2, env_int("RR_TILE_LOG2", rr::kMinTileLog2)));
+  while ((r->S_pad >> r->tile_log2) > rr::kMaxTiles && r->tile_log2 < rr::kMaxTileLog2) ++r->tile_log2;
+  if ((r->S_pad >> r->tile_log2) > rr::kMaxTiles) {
+    delete r;
+    return fail(RR_ERR_ARG, "rr_create: capacity %d exceeds the %d slots one replay can index", capacity,
+                rr::kMaxTiles << rr::kMaxTileLog2);
+  }
   r->own_lo = 0;
   r->own_hi = r->S;
   r->seed = seed;
@@ -312,10 +323,9 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evGather, cudaEventDisableTiming));
 
-  const size_t nt2 = (size_t)r->S_pad / rr::kTile;
+  const size_t nt2 = (size_t)r->S_pad >> r->tile_log2;
   RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
   RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
-  RR_CUDA(cudaMalloc(&r->l1, sizeof(double) * (size_t)r->S_pad / rr::kGroup));
   RR_CUDA(cudaMalloc(&r->l2, sizeof(double) * nt2));
   RR_CUDA(cudaMalloc(&r->l2min, sizeof(float) * nt2));
   RR_CUDA(cudaMalloc(&r->ctl, sizeof(rr::Ctl)));
@@ -354,7 +364,7 @@ int rr_destroy(rr_replay* r) {
   for (auto& f : r->fields) cudaFree(f.slab);
   cudaFree(r->w);
   cudaFree(r->evicted);
-  cudaFree(r->l1);
+  cudaFree(r->wsel);
   cudaFree(r->l2);
   cudaFree(r->l2min);
   cudaFree(r->ctl);
@@ -746,12 +756,23 @@ int free_idslot(rr_replay* r) {
   return -1;
 }
 
-// sample_ (rela/prioritized_replay.h:258-328): selection, eviction, IS weights
-// and makeBatch, issued as three kernels on the internal stream. The caller's
-// stream has already been ordered before `main` (evIn) by rr_sample.
-int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot) {
+// sample_ (rela/prioritized_replay.h:258-328) in two stream-ordered steps on
+// the internal stream: (1) prefix hierarchy + selection + eviction + IS
+// weights, (2) makeBatch = the gather. The caller's stream has already been
+// ordered before `main` (evIn). The host-side blockPop bookkeeping is applied
+// in step 2: until the gather has been issued, a concurrent add must not be
+// able to reserve (and overwrite) the evicted slots the gather still reads.
+int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
   int rc = ensure_idbuf(r, idslot, B);
   if (rc != RR_OK) return rc;
+  if (r->wsel_cap < B) {
+    RR_CUDA(cudaStreamSynchronize(r->main));
+    RR_CUDA(cudaFree(r->wsel));
+    r->wsel = nullptr;
+    const int cap = std::max(B, 1024);
+    RR_CUDA(cudaMalloc(&r->wsel, sizeof(float) * (size_t)cap));
+    r->wsel_cap = cap;
+  }
   std::unique_lock<std::mutex> lk(r->m_);
   if (r->safeSize_ == 0) return fail(RR_ERR_EMPTY, "rr_sample: buffer is empty");
   rr::SelectArgs a;
@@ -759,11 +780,12 @@ int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int 
   a.ctl = r->ctl;
   a.w = r->w;
   a.evicted = r->evicted;
-  a.l1 = r->l1;
   a.l2 = r->l2;
   a.l2min = r->l2min;
   a.S = r->S;
   a.S_pad = r->S_pad;
+  a.tile_log2 = r->tile_log2;
+  a.wsel = r->wsel;
   a.head = r->head_;
   a.size = r->safeSize_;
   a.size_is = r->size_;  // storage_.size(), re-read at line 312: includes in-flight appends
@@ -780,7 +802,13 @@ int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int 
   RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   RR_CUDA(rr::launch_select(a, r->main));
   r->launches += 2;
+  *pop_out = a.pop_n;
+  return RR_OK;
+}
 
+int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int pop_n) {
+  std::unique_lock<std::mutex> lk(r->m_);
+  const int32_t* ids = r->idbuf[idslot];
   std::vector<CopyField> cf;
   for (size_t fi = 0; fi < r->fields.size(); ++fi) {
     const FieldInfo& f = r->fields[fi];
@@ -797,30 +825,39 @@ int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int 
     cf.push_back(c);
   }
   CopyPlan plan;
-  rc = plan_copy(r, true, B, cf, a.ids, 0, &plan);
-  if (rc != RR_OK) return rc;
-  rc = launch_plan(r, plan, r->main);
-  if (rc != RR_OK) return rc;
-  if (r->profiling) {
+  int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
+  if (rc == RR_OK) rc = launch_plan(r, plan, r->main);
+  if (rc == RR_OK && r->profiling) {
     // keep this batch's ids for rr_gather_bench (a copy node here breaks the
     // kernel-to-kernel PDL chain, which is why it is opt-in)
     const size_t k = r->hist_n % r->hist.size();
-    if (r->hist_cap < B) return fail(RR_ERR_ARG, "profiling: batch larger than at rr_set_profiling");
-    RR_CUDA(cudaMemcpyAsync(r->hist[k], a.ids, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToDevice, r->main));
-    r->hist_n++;
-    r->hist_B = B;
+    if (r->hist_cap < B) {
+      rc = fail(RR_ERR_ARG, "profiling: batch larger than at rr_set_profiling");
+    } else {
+      cudaError_t e = cudaMemcpyAsync(r->hist[k], ids, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToDevice, r->main);
+      if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "profiling copy: %s", cudaGetErrorString(e));
+      r->hist_n++;
+      r->hist_B = B;
+    }
   }
-
-  // blockPop bookkeeping (rela/prioritized_replay.h:94-102)
-  if (a.pop_n > 0) {
-    r->head_ = (r->head_ + a.pop_n) % r->S;
-    r->safeSize_ -= a.pop_n;
-    r->size_ -= a.pop_n;
+  // blockPop bookkeeping (rela/prioritized_replay.h:94-102): the device side of
+  // the eviction already ran in the selection kernel
+  if (pop_n > 0) {
+    r->head_ = (r->head_ + pop_n) % r->S;
+    r->safeSize_ -= pop_n;
+    r->size_ -= pop_n;
   }
   lk.unlock();
-  if (a.pop_n > 0) r->cvSize_.notify_all();
+  if (pop_n > 0) r->cvSize_.notify_all();
   r->samples++;
-  return RR_OK;
+  return rc;
+}
+
+int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot) {
+  int pop_n = 0;
+  int rc = select_launch(r, B, out_w, idslot, &pop_n);
+  if (rc != RR_OK) return rc;
+  return gather_launch(r, B, out_fields, idslot, pop_n);
 }
 
 int acquire_prefetch_buffers(rr_replay* r, int B, Prefetched* out) {
@@ -905,6 +942,50 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     r->idbusy[p.idslot] = true;
     r->queue.push_back(p);
   }
+  return RR_OK;
+}
+
+int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) {
+  if (r == nullptr || batch <= 0 || out_weights == nullptr) return fail(RR_ERR_ARG, "rr_sample_select: bad argument");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
+  if (r->cur_ids >= 0 || r->pend_slot >= 0)
+    return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
+  r->pend_B = batch;
+  if (r->prefetch > 0) {  // batches come out of the prefetch queue: everything happens in rr_sample_gather
+    r->pend_slot = 1 << 30;
+    r->pend_w = out_weights;
+    return RR_OK;
+  }
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  DeviceScope dev_scope(r->device);
+  RR_CUDA(cudaEventRecord(r->evIn, cs));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  const int slot = free_idslot(r);
+  int rc = select_launch(r, batch, out_weights, slot, &r->pend_pop);
+  if (rc != RR_OK) return rc;
+  r->pend_slot = slot;
+  return RR_OK;
+}
+
+int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
+  if (r == nullptr || (!r->fields.empty() && out_fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_sample_gather: bad argument");
+  if (r->pend_slot < 0) return fail(RR_ERR_STATE, "rr_sample_gather: no rr_sample_select is pending");
+  const int slot = r->pend_slot, batch = r->pend_B;
+  r->pend_slot = -1;
+  if (r->prefetch > 0) return rr_sample(r, batch, out_fields, r->pend_w, stream);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  DeviceScope dev_scope(r->device);
+  // the out buffers may have been used on the caller's stream before
+  RR_CUDA(cudaEventRecord(r->evIn, cs));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  int rc = gather_launch(r, batch, out_fields, slot, r->pend_pop);
+  if (rc != RR_OK) return rc;
+  r->idbusy[slot] = true;
+  r->cur_ids = slot;
+  r->cur_B = batch;
+  RR_CUDA(cudaEventRecord(r->evOut, r->main));
+  RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
   return RR_OK;
 }
 

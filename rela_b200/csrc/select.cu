@@ -12,7 +12,7 @@
 // all weights are multiples of u = ulp(smallest non-zero weight) and the total
 // is < 2^53 * u. Then every value this file computes (group sums, tile sums,
 // prefixes, differences of prefixes) is an integer multiple of u below
-// 2^53 * u, hence exact, and the three-level search below is bit-identical to
+// 2^53 * u, hence exact, and the two-level search below is bit-identical to
 // the sequential walk. When the condition fails (weights spanning > 29 binades
 // relative to the total) the kernel takes the ordered walk instead, which is
 // the reference's loop verbatim, and counts it in Ctl::n_ordered.
@@ -32,8 +32,7 @@ namespace rr {
 
 namespace {
 
-constexpr int kSelThreads = 1024;
-constexpr int kSelChunk = 512;  // targets staged through shared memory per round
+constexpr int kSelThreads = 512;
 
 __device__ __forceinline__ float pow_alpha(float p, float alpha) {
   // K2: priority ^ alpha. alpha == 1 is the identity (ATen copies in that
@@ -50,48 +49,46 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // ------------------------------------------------------------------ K3 build
-// One CTA of 256 threads per 1024-slot tile: each thread owns 4 consecutive
-// slots (one 16-byte load), 8 threads form a 32-slot group.
+// One CTA of 256 threads per 2048 slots: each thread owns 8 consecutive slots
+// (two 16-byte loads), a warp covers 256 slots. Tiles are 256 << k slots, i.e.
+// 1 << k consecutive warps.
 __global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __restrict__ w,
-                                                              double* __restrict__ l1,
                                                               double* __restrict__ l2,
-                                                              float* __restrict__ l2min) {
-  const int tile = blockIdx.x;
+                                                              float* __restrict__ l2min, int tile_log2) {
   const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
   pdl_launch_dependents();
   pdl_wait();
-  const float4 v = reinterpret_cast<const float4*>(w)[(size_t)tile * (kTile / 4) + tid];
-  double s = ((double)v.x + (double)v.y) + ((double)v.z + (double)v.w);
+  const float4* src = reinterpret_cast<const float4*>(w) + (size_t)blockIdx.x * (kBuildSpan / 4) + tid * 2;
+  const float4 a = src[0], b = src[1];
+  double s = (((double)a.x + (double)a.y) + ((double)a.z + (double)a.w)) +
+             (((double)b.x + (double)b.y) + ((double)b.z + (double)b.w));
   float mn = FLT_MAX;
-  if (v.x != 0.0f) mn = fminf(mn, fabsf(v.x));
-  if (v.y != 0.0f) mn = fminf(mn, fabsf(v.y));
-  if (v.z != 0.0f) mn = fminf(mn, fabsf(v.z));
-  if (v.w != 0.0f) mn = fminf(mn, fabsf(v.w));
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-  for (int o = 4; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if ((tid & 7) == 0) l1[(size_t)tile * (kTile / kGroup) + (tid >> 3)] = s;
-  // tile reduction: 4 groups per warp, 8 warps
-  __shared__ double ws[8];
-  __shared__ float wm[8];
-  double t = s;
-  if ((tid & 7) != 0) t = 0.0;
-  t = warp_sum(t);
+  for (int k = 0; k < 8; ++k)
+    if (v[k] != 0.0f) mn = fminf(mn, fabsf(v[k]));
+  s = warp_sum(s);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-  if ((tid & 31) == 0) {
-    ws[tid >> 5] = t;
-    wm[tid >> 5] = mn;
+  __shared__ double ws[8];
+  __shared__ float wm[8];
+  if (lane == 0) {
+    ws[warp] = s;
+    wm[warp] = mn;
   }
   __syncthreads();
-  if (tid == 0) {
+  const int wpt = 1 << (tile_log2 - 8);  // warps per tile
+  const int tiles = 8 / wpt;             // tiles per CTA
+  if (tid < tiles) {
     double tot = 0.0;
     float m = FLT_MAX;
-    for (int k = 0; k < 8; ++k) {
-      tot += ws[k];
-      m = fminf(m, wm[k]);
+    for (int k = 0; k < wpt; ++k) {
+      tot += ws[tid * wpt + k];
+      m = fminf(m, wm[tid * wpt + k]);
     }
-    l2[tile] = tot;
-    l2min[tile] = m;
+    l2[(size_t)blockIdx.x * tiles + tid] = tot;
+    l2min[(size_t)blockIdx.x * tiles + tid] = m;
   }
 }
 
@@ -107,19 +104,25 @@ __device__ __forceinline__ uint32_t mt_mix(uint32_t a, uint32_t b, uint32_t m) {
 }
 
 __device__ void mt_twist(uint32_t* mt) {
-  const int tid = threadIdx.x;
-  uint32_t v = 0;
-  if (tid < 227) v = mt_mix(mt[tid], mt[tid + 1], mt[tid + 397]);
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  uint32_t v[2] = {0u, 0u};  // blockDim.x >= 227: at most two words per thread per phase
+  int n = 0;
+  for (int k = tid; k < 227; k += nthr) v[n++] = mt_mix(mt[k], mt[k + 1], mt[k + 397]);
   __syncthreads();
-  if (tid < 227) mt[tid] = v;
+  n = 0;
+  for (int k = tid; k < 227; k += nthr) mt[k] = v[n++];
   __syncthreads();
-  if (tid >= 227 && tid < 454) v = mt_mix(mt[tid], mt[tid + 1], mt[tid - 227]);
+  n = 0;
+  for (int k = 227 + tid; k < 454; k += nthr) v[n++] = mt_mix(mt[k], mt[k + 1], mt[k - 227]);
   __syncthreads();
-  if (tid >= 227 && tid < 454) mt[tid] = v;
+  n = 0;
+  for (int k = 227 + tid; k < 454; k += nthr) mt[k] = v[n++];
   __syncthreads();
-  if (tid >= 454 && tid < 623) v = mt_mix(mt[tid], mt[tid + 1], mt[tid - 227]);
+  n = 0;
+  for (int k = 454 + tid; k < 623; k += nthr) v[n++] = mt_mix(mt[k], mt[k + 1], mt[k - 227]);
   __syncthreads();
-  if (tid >= 454 && tid < 623) mt[tid] = v;
+  n = 0;
+  for (int k = 454 + tid; k < 623; k += nthr) mt[k] = v[n++];
   __syncthreads();
   if (tid == 0) mt[623] = mt_mix(mt[623], mt[0], mt[396]);
   __syncthreads();
@@ -170,62 +173,96 @@ __device__ __forceinline__ unsigned long long d2q(double x, int ue, int* inexact
   return m >> (-shift);
 }
 
+// Targets d_lo .. d_hi-1 of a batch of B draws (rela/prioritized_replay.h:265-280)
+// from the mt19937 state `mt` / `mti` in shared memory: libstdc++'s
+// generate_canonical<float, 24> (one 32-bit draw, * 2^-32, clamp to
+// nextafter(1, 0)) then rand = u * segment + i * segment, clamped to sum - 0.2.
+// On return `mt` holds the state after all B draws and *mti_out its index.
+// Called by every thread of the CTA (the twist synchronises).
+__device__ void gen_targets(uint32_t* mt, int mti, int B, int d_lo, int d_hi, float sumf, int contract_fma,
+                            float* out, int* mti_out) {
+  const float segment = __fdiv_rn(sumf, (float)B);
+  const float cap = __fsub_rn(sumf, 0.2f);
+  const int gen_end = (mti + B - 1) / 624;  // twists needed for the whole batch
+  for (int gen = 0; gen <= gen_end; ++gen) {
+    if (gen > 0) mt_twist(mt);
+    for (int d = d_lo + (int)threadIdx.x; d < d_hi; d += (int)blockDim.x) {
+      const int g = mti + d;
+      if (g / 624 != gen) continue;
+      const uint32_t y = mt_temper(mt[g % 624]);
+      float u = __fmul_rn(__uint2float_rn(y), 2.3283064365386963e-10f);
+      if (u >= 1.0f) u = 0.99999994f;  // nextafterf(1, 0)
+      float r;
+      if (contract_fma) {
+        r = __fmaf_rn((float)d, segment, __fmaf_rn(u, segment, 0.0f));
+      } else {
+        r = __fadd_rn(__fadd_rn(__fmul_rn(u, segment), 0.0f), __fmul_rn((float)d, segment));
+      }
+      out[d - d_lo] = (cap < r) ? cap : r;
+    }
+    __syncthreads();
+  }
+  *mti_out = (mti + B - 1) % 624 + 1;
+}
+
 }  // namespace
 
 // -------------------------------------------------------------- K4/K5 select
-// Single CTA. Dynamic shared memory: p2[nt2] doubles | targets[B] | wsel[B].
+// Grid: one CTA of 512 threads per 32 targets. Every CTA scans the tile sums
+// (replicated: at most 16 K doubles from L2) and regenerates the mt19937
+// stream for its own targets, so the CTAs never wait for each other; the CTA
+// that finishes last (ticket in Ctl::done_ctas) evicts, turns the selected
+// weights into importance weights (block-wide max) and writes the RNG state
+// back. Dynamic shared memory: the tile prefixes (8 B x tiles), reused for the
+// targets of the ordered walk.
 __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
-  const int nt2 = a.S_pad / kTile;
+  const int tl = a.tile_log2;
+  const int nt = a.S_pad >> tl;
   double* p2d = reinterpret_cast<double*>(sm_raw);
   unsigned long long* p2q = reinterpret_cast<unsigned long long*>(sm_raw);
-  float* targets = reinterpret_cast<float*>(p2d + nt2);
-  float* wsel = targets + a.B;
-  int* s_tile = reinterpret_cast<int*>(wsel + a.B);
-  double* stage_d = reinterpret_cast<double*>(s_tile + kSelChunk + ((2 * a.B) & 1));  // 8-byte aligned
-  float* stage_f = reinterpret_cast<float*>(stage_d);
   __shared__ uint32_t mt[624];
-  __shared__ unsigned long long red_q[32];
-  __shared__ float red_f[32];
-  __shared__ unsigned long long sh_total, sh_offset;
+  __shared__ unsigned long long red_q[kSelThreads / 32];
+  __shared__ float red_f[kSelThreads / 32];
+  __shared__ float s_target[kSelTargets];
+  __shared__ int s_tile[kSelTargets];
+  __shared__ int s_wrapped[kSelTargets];
+  __shared__ unsigned long long s_rem[kSelTargets];
+  __shared__ unsigned long long sh_offset;
   __shared__ float sh_max;
-  __shared__ int sh_exact, sh_fail;
+  __shared__ int sh_last, sh_mti;
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kSelThreads / 32;
   Ctl* ctl = a.ctl;
+  const int i0 = (int)blockIdx.x * kSelTargets;
+  const int nT = min(kSelTargets, a.B - i0);
+  const bool probing = blockIdx.x == 0 && tid == 0;
 
   pdl_launch_dependents();
   pdl_wait();
-  if (tid == 0) ctl->probe[0] = clock64();
-  // ---- 1. tile sums -> shared memory, min non-zero weight -> u = 2^ue,
-  //         integer inclusive prefix of the tile sums (one pass, contiguous
-  //         chunk per thread)
-  const int per = (nt2 + kSelThreads - 1) / kSelThreads;
-  const int c0 = min(tid * per, nt2), c1 = min(c0 + per, nt2);
+  if (probing) ctl->probe[0] = clock64();
+  // ---- 1. every load that depends on nothing but the kernel arguments
+  const double sum_d = ctl->sum;
+  const int mti0 = ctl->mti;
+  for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
   float mn = FLT_MAX;
-  for (int i = c0; i < c1; ++i) {
+  for (int i = tid; i < nt; i += kSelThreads) {
     p2d[i] = a.l2[i];
     mn = fminf(mn, a.l2min[i]);
   }
-  // values needed after the barriers: issue their loads now
-  double head_l1 = 0.0;  // group sums / weights in front of head, for the offset O
-  float head_w = 0.0f;
-  if (warp == 0 && a.head > 0) {
+  double head_part = 0.0;  // weights in front of head inside head's tile (for the offset O)
+  if (warp == kWarps - 1 && a.head > 0) {
     const int last = a.head - 1;
-    const int t = last / kTile, g = (last % kTile) / kGroup, o = last % kGroup;
-    if (lane < g) head_l1 = a.l1[(size_t)t * (kTile / kGroup) + lane];
-    if (lane <= o) head_w = a.w[(size_t)t * kTile + (size_t)g * kGroup + lane];
+    for (int k = ((last >> tl) << tl) + lane; k <= last; k += 32) head_part += (double)a.w[k];
   }
-  const float sum_f_early = (float)ctl->sum;
-  const int mti_early = ctl->mti;
-  for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
   if (lane == 0) red_f[warp] = mn;
   __syncthreads();
   {
-    float m = red_f[lane];
+    float m = lane < kWarps ? red_f[lane] : FLT_MAX;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
     mn = m;  // every warp now holds the global min non-zero weight
@@ -237,13 +274,23 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     ue = (e - 1) - 23;    // ulp of a normal float
     if (ue < -149) ue = -149;
   }
+  const float sumf = (float)sum_d;
+
+  // ---- 2. this CTA's targets (needs only the RNG state and sum_)
+  gen_targets(mt, mti0, a.B, i0, i0 + nT, sumf, a.contract_fma, s_target, &sh_mti);
+  if (probing) ctl->probe[1] = clock64();
+
+  // ---- 3. integer inclusive prefix of the tile sums: contiguous chunk per
+  //         thread (odd length: conflict-free 8-byte accesses), block scan of
+  //         the chunk totals, second pass adds the chunk offset
+  const int per = ((nt + kSelThreads - 1) / kSelThreads) | 1;
+  const int c0 = min(tid * per, nt), c1 = min(c0 + per, nt);
   int inexact = 0;
   unsigned long long run = 0ull;
   for (int i = c0; i < c1; ++i) {
     run += d2q(p2d[i], ue, &inexact);
-    p2q[i] = run;  // same 8 bytes as p2d[i]: each thread converts its own chunk in place
+    p2q[i] = run;  // same 8 bytes as p2d[i]
   }
-  // block exclusive scan of the per-thread totals
   unsigned long long x = run;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -253,13 +300,13 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   if (lane == 31) red_q[warp] = x;
   inexact = __syncthreads_or(inexact);
   if (warp == 0) {
-    unsigned long long t = red_q[lane];
+    unsigned long long t = lane < kWarps ? red_q[lane] : 0ull;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       unsigned long long y = __shfl_up_sync(0xffffffffu, t, o);
       if (lane >= o) t += y;
     }
-    red_q[lane] = t;
+    if (lane < kWarps) red_q[lane] = t;
   }
   __syncthreads();
   {
@@ -267,206 +314,138 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     for (int i = c0; i < c1; ++i) p2q[i] += off;
   }
   __syncthreads();
+  const unsigned long long total = p2q[nt - 1];
+  const bool exact = !inexact && total < (1ull << 52) && !a.force_ordered;
+  if (probing) ctl->probe[2] = clock64();
 
-  if (tid == 0) ctl->probe[1] = clock64();
-  // ---- 2. exactness test, offset of head (physical inclusive prefix at head - 1)
-  if (warp == 0) {
-    const unsigned long long total = p2q[nt2 - 1];
-    int exact = !inexact && total < (1ull << 52);
-    if (a.force_ordered) exact = 0;
-    unsigned long long part = 0ull;
-    if (exact && a.head > 0) {
-      const int last = a.head - 1;
-      const int t = last / kTile;
-      int dummy = 0;
-      part = d2q(head_l1, ue, &dummy) + f2q(head_w, ue);
+  if (exact) {
+    // ---- 4. offset of head: physical inclusive prefix at head - 1
+    if (warp == kWarps - 1) {
+      unsigned long long part = 0ull;
+      if (a.head > 0) {
+        int dummy = 0;
+        part = d2q(head_part, ue, &dummy);
 #pragma unroll
-      for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
-      if (t > 0) part += p2q[t - 1];
-    }
-    if (lane == 0) {
-      sh_total = total;
-      sh_offset = part;
-      sh_exact = exact;
-      sh_fail = 0;
-    }
-  }
-  __syncthreads();
-
-  if (tid == 0) ctl->probe[2] = clock64();
-  // ---- 3. targets: rand_i = U[0, segment) + i * segment, clamped (lines 265-280)
-  const float sumf = sum_f_early;
-  const float segment = __fdiv_rn(sumf, (float)a.B);
-  {
-    int pos = mti_early;
-    int done = 0;
-    while (done < a.B) {
-      if (pos >= 624) {
-        mt_twist(mt);
-        pos = 0;
+        for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
+        const int t = (a.head - 1) >> tl;
+        if (t > 0) part += p2q[t - 1];
       }
-      int m = min(a.B - done, 624 - pos);
-      if (tid < m) {
-        uint32_t y = mt_temper(mt[pos + tid]);
-        float u = __fmul_rn(__uint2float_rn(y), 2.3283064365386963e-10f);
-        if (u >= 1.0f) u = 0.99999994f;  // nextafterf(1, 0)
-        const int i = done + tid;
-        float r;
-        if (a.contract_fma) {
-          r = __fmaf_rn((float)i, segment, __fmaf_rn(u, segment, 0.0f));
-        } else {
-          r = __fadd_rn(__fadd_rn(__fmul_rn(u, segment), 0.0f), __fmul_rn((float)i, segment));
-        }
-        const float cap = __fsub_rn(sumf, 0.2f);
-        targets[i] = (cap < r) ? cap : r;
-      }
-      pos += m;
-      done += m;
-      __syncthreads();
+      if (lane == 0) sh_offset = part;
     }
-    for (int i = tid; i < 624; i += kSelThreads) ctl->mt[i] = mt[i];
-    if (tid == 0) ctl->mti = pos;
-  }
-  __syncthreads();
-
-  if (tid == 0) ctl->probe[3] = clock64();
-  // ---- 4. selection
-  const int size = a.size;
-  if (sh_exact) {
-    // Both cases reduce to "first physical slot whose prefix reaches a key":
+    __syncthreads();
+    // ---- 5. tile of each target. Both cases reduce to "first physical slot
+    //   whose prefix reaches a key":
     //   unwrapped part [head, S):  P(s) - O >= t'   <=>  P(s) >= t' + O
     //   wrapped part   [0, head):  M1 + P(s) >= t'  <=>  P(s) >= t' - M1
     // with t' = max(ceil(target / u), 1) (the reference's accSum > 0 && accSum >= target),
     // O = prefix at head - 1 and M1 = total - O the mass of the unwrapped part.
-    // The per-target group sums and weights are fetched by whole warps (one
-    // coalesced 256 B / 128 B request per target) into padded shared-memory rows
-    // and then walked by the target's own thread: scattered per-thread loads
-    // would cost one L1 wavefront per lane per load on this single SM.
-    const unsigned long long total = sh_total, off = sh_offset;
-    const unsigned long long m1 = total - off;
-    const double qscale = ldexp(1.0, -ue);  // 1 / u
-    for (int i0 = 0; i0 < a.B; i0 += kSelChunk) {
-      const int nT = min(kSelChunk, a.B - i0);
-      int tile = -1, wrapped = 0;
-      unsigned long long rem = 0ull;
-      if (tid < nT) {
-        const float tf = targets[i0 + tid];
-        unsigned long long tq = 1ull;
-        if (tf > 0.0f) {
-          const double scaled = ldexp((double)tf, -ue);  // exact: power-of-two scaling
-          tq = scaled >= 4.0e18 ? (1ull << 62) : (unsigned long long)__double2ll_ru(scaled);
-          if (tq == 0ull) tq = 1ull;
-        }
-        wrapped = !(m1 >= tq);
-        const unsigned long long key = wrapped ? tq - m1 : tq + off;
-        int lo = 0, hi = nt2;  // first tile whose inclusive prefix reaches the key
-        while (lo < hi) {
-          const int mid = (lo + hi) >> 1;
-          if (p2q[mid] >= key) hi = mid; else lo = mid + 1;
-        }
-        if (lo < nt2) {
-          tile = lo;
-          rem = key - (tile > 0 ? p2q[tile - 1] : 0ull);  // 1 <= rem <= tile sum
-        }
-        s_tile[tid] = tile;
+    if (tid < nT) {
+      const unsigned long long off = sh_offset;
+      const unsigned long long m1 = total - off;
+      const float tf = s_target[tid];
+      unsigned long long tq = 1ull;
+      if (tf > 0.0f) {
+        const double scaled = ldexp((double)tf, -ue);  // exact: power-of-two scaling
+        tq = scaled >= 4.0e18 ? (1ull << 62) : (unsigned long long)__double2ll_ru(scaled);
+        if (tq == 0ull) tq = 1ull;
       }
-      if (tid == 0) ctl->probe[8] = clock64();
-      __syncthreads();
-      if (tid == 0) ctl->probe[9] = clock64();
-      {
-        // all loads of the warp's targets are issued before the first store
-        constexpr int kPerWarp = kSelChunk / (kSelThreads / 32);
-        double v[kPerWarp];
+      const int wrapped = !(m1 >= tq);
+      const unsigned long long key = wrapped ? tq - m1 : tq + off;
+      int lo = 0, hi = nt;  // first tile whose inclusive prefix reaches the key
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (p2q[mid] >= key) hi = mid; else lo = mid + 1;
+      }
+      s_tile[tid] = lo < nt ? lo : -1;
+      s_rem[tid] = lo < nt ? key - (lo > 0 ? p2q[lo - 1] : 0ull) : 0ull;  // 1 <= rem <= tile sum
+      s_wrapped[tid] = wrapped;
+    }
+    __syncthreads();
+    if (probing) ctl->probe[3] = clock64();
+    // ---- 6. slot inside the tile: one warp per target, two targets per warp.
+    //   Lane l owns tile / 32 consecutive slots; a warp scan of the lane totals
+    //   finds the lane, which then walks its own slots.
+    const int c = 1 << (tl - 5);
+    constexpr int kPer = kSelTargets / kWarps;
+    unsigned long long T[kPer];
+    const float* wp[kPer];
 #pragma unroll
-        for (int k = 0; k < kPerWarp; ++k) {
-          const int t = warp + k * (kSelThreads / 32);
-          const int tl = t < nT ? s_tile[t] : -1;
-          v[k] = tl >= 0 ? a.l1[(size_t)tl * (kTile / kGroup) + lane] : 0.0;
-        }
-#pragma unroll
-        for (int k = 0; k < kPerWarp; ++k) {
-          const int t = warp + k * (kSelThreads / 32);
-          if (t < nT) stage_d[t * 33 + lane] = v[k];
+    for (int k = 0; k < kPer; ++k) {
+      const int t = warp + k * kWarps;
+      const int tile = t < nT ? s_tile[t] : -1;
+      T[k] = 0ull;
+      wp[k] = nullptr;
+      if (tile >= 0) {
+        wp[k] = a.w + ((size_t)tile << tl) + (size_t)lane * c;
+        for (int j = 0; j < c; j += 4) {
+          const float4 v = *reinterpret_cast<const float4*>(wp[k] + j);
+          T[k] += f2q(v.x, ue) + f2q(v.y, ue) + f2q(v.z, ue) + f2q(v.w, ue);
         }
       }
-      __syncthreads();
-      if (tid == 0) ctl->probe[10] = clock64();
-      int base = -1;
-      // walks in fp64 on q-scaled values: every term is an integer below 2^52,
-      // so the fused multiply-adds are exact and order-independent
-      double remd = (double)rem;
-      if (tid < nT && tile >= 0) {
-        double acc = 0.0, before = 0.0;
-        int grp = 0;
-#pragma unroll 8
-        for (int k = 0; k < kTile / kGroup; ++k) {
-          acc = fma(stage_d[tid * 33 + k], qscale, acc);
-          if (acc < remd) {
-            ++grp;
-            before = acc;
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int t = warp + k * kWarps;
+      if (t >= nT) continue;  // warp-uniform
+      const int tile = s_tile[t];
+      int slot = -1;
+      float wv = 0.0f;
+      if (tile >= 0) {
+        const unsigned long long rem = s_rem[t];
+        unsigned long long P = T[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          unsigned long long y = __shfl_up_sync(0xffffffffu, P, o);
+          if (lane >= o) P += y;
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, P >= rem);
+        if (hit != 0u) {
+          const int L = __ffs(hit) - 1;
+          if (lane == L) {
+            const unsigned long long rem_l = rem - (P - T[k]);
+            unsigned long long acc = 0ull;
+            int j = c - 1;
+            for (int q = 0; q < c; ++q) {
+              acc += f2q(wp[k][q], ue);
+              if (acc >= rem_l) {
+                j = q;
+                break;
+              }
+            }
+            slot = (tile << tl) + L * c + j;
+            wv = wp[k][j];
           }
-        }
-        if (grp >= kTile / kGroup) grp = kTile / kGroup - 1;
-        remd -= before;
-        base = tile * kTile + grp * kGroup;
-      }
-      if (tid < nT) s_tile[tid] = base;
-      if (tid == 0) ctl->probe[11] = clock64();
-      __syncthreads();
-      {
-        constexpr int kPerWarp = kSelChunk / (kSelThreads / 32);
-        float v[kPerWarp];
-#pragma unroll
-        for (int k = 0; k < kPerWarp; ++k) {
-          const int t = warp + k * (kSelThreads / 32);
-          const int bs = t < nT ? s_tile[t] : -1;
-          v[k] = bs >= 0 ? a.w[(size_t)bs + lane] : 0.0f;
-        }
-#pragma unroll
-        for (int k = 0; k < kPerWarp; ++k) {
-          const int t = warp + k * (kSelThreads / 32);
-          if (t < nT) stage_f[t * 33 + lane] = v[k];
+          slot = __shfl_sync(0xffffffffu, slot, L);
+          wv = __shfl_sync(0xffffffffu, wv, L);
         }
       }
-      __syncthreads();
-      if (tid == 0) ctl->probe[12] = clock64();
-      if (tid < nT) {
-        int slot = -1;
-        float wv = 0.0f;
-        if (base >= 0) {
-          double acc = 0.0;
-          int j = 0;
-#pragma unroll 8
-          for (int k = 0; k < kGroup; ++k) {
-            acc = fma((double)stage_f[tid * 33 + k], qscale, acc);
-            j += (acc < remd);
-          }
-          if (j >= kGroup) j = kGroup - 1;
-          slot = base + j;
-          wv = stage_f[tid * 33 + j];
-          if (wrapped && slot >= a.head) slot = -1;  // ran past the wrapped part
-        }
+      if (lane == 0) {
+        if (slot >= 0 && s_wrapped[t] && slot >= a.head) slot = -1;  // ran past the wrapped part
         int logical = -1;
         if (slot >= 0) logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
-        if (slot < 0 || slot >= a.S || logical >= size) {
-          sh_fail = 1;  // reference: assert(false) at lines 297-302
+        if (slot < 0 || slot >= a.S || logical >= a.size) {
+          ctl->sel_fail = 1;  // reference: assert(false) at lines 297-302
           slot = a.head;
           wv = a.w[slot];
+          logical = 0;
         }
-        a.ids[i0 + tid] = slot;
-        wsel[i0 + tid] = wv;
+        a.ids[i0 + t] = slot;
+        a.wsel[i0 + t] = wv;
+        // getElementAndMark (line 126). A slot that this call also evicts ends
+        // up evicted (the pop comes after the marks): leave it to the eviction.
+        if (logical >= a.pop_n) a.evicted[slot] = 0;
       }
-      if (tid == 0) ctl->probe[13] = clock64();
-      __syncthreads();
     }
-  } else {
-    // ordered walk: the reference's loop (lines 274-308), staged 1024 weights
-    // at a time through shared memory and consumed by one thread in order
+  } else if (blockIdx.x == 0) {
+    // ordered walk: the reference's loop (lines 274-308) for ALL targets, staged
+    // kSelThreads weights at a time and consumed by one thread in order
+    float* targets = reinterpret_cast<float*>(sm_raw);
     __shared__ float chunk[kSelThreads];
-    __shared__ int sh_next_i;
+    __shared__ int sh_next_i, sh_id;
     __shared__ double sh_acc;
     __shared__ float sh_w;
-    __shared__ int sh_id;
+    __syncthreads();
+    for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
     if (tid == 0) {
       sh_next_i = 0;
       sh_acc = 0.0;
@@ -474,8 +453,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       sh_id = 0;
     }
     __syncthreads();
+    gen_targets(mt, mti0, a.B, 0, a.B, sumf, a.contract_fma, targets, &sh_mti);
+    const int size = a.size;
     for (int base = 0; base <= size; base += kSelThreads) {
-      int idx = base + tid;
+      const int idx = base + tid;
       if (idx < size) {
         int slot = a.head + idx;
         if (slot >= a.S) slot -= a.S;
@@ -493,7 +474,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
           const double target = (double)targets[i];
           if (acc > 0.0 && acc >= target) {
             a.ids[i] = id;
-            wsel[i] = w;
+            a.wsel[i] = w;
             ++i;
             continue;
           }
@@ -513,24 +494,34 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       if (sh_next_i >= a.B) break;
     }
     if (tid == 0 && sh_next_i < a.B) {
-      sh_fail = 1;
+      ctl->sel_fail = 1;
       for (int i = sh_next_i; i < a.B; ++i) {
         a.ids[i] = a.head;
-        wsel[i] = a.w[a.head];
+        a.wsel[i] = a.w[a.head];
       }
     }
+    __syncthreads();
+    for (int i = tid; i < a.B; i += kSelThreads) {
+      const int slot = a.ids[i];
+      const int logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
+      if (logical >= a.pop_n) a.evicted[slot] = 0;
+    }
+  }
+  if (probing) ctl->probe[4] = clock64();
+
+  // ---- 7. the last CTA to get here finishes the call
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    sh_last = atomicAdd(&ctl->done_ctas, 1u) == gridDim.x - 1;
   }
   __syncthreads();
+  if (!sh_last) return;
+  __threadfence();
 
-  if (tid == 0) ctl->probe[4] = clock64();
-  // ---- 5. mark sampled slots live (getElementAndMark, line 126)
-  for (int i = tid; i < a.B; i += kSelThreads) a.evicted[a.ids[i]] = 0;
-  __syncthreads();
-
-  if (tid == 0) ctl->probe[5] = clock64();
-  // ---- 6. eviction (blockPop, lines 84-103), after the marks like the reference
+  // eviction (blockPop, lines 84-103): after the marks like the reference
   if (a.pop_n > 0) {
-    if (sh_exact) {
+    if (exact) {
       unsigned long long part = 0ull;
       for (int j = tid; j < a.pop_n; j += kSelThreads) {
         int slot = a.head + j;
@@ -543,9 +534,9 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       __syncthreads();
       if (tid == 0) {
         unsigned long long tot = 0ull;
-        for (int k = 0; k < kSelThreads / 32; ++k) tot += red_q[k];
+        for (int k = 0; k < kWarps; ++k) tot += red_q[k];
         // diff = -(w_0 + w_1 + ...) exactly (< 2^52 u), then sum_ += diff (line 96)
-        ctl->sum += -ldexp((double)tot, ue);
+        ctl->sum = sum_d + -ldexp((double)tot, ue);
       }
     } else if (tid == 0) {
       double diff = 0.0;
@@ -554,7 +545,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
         if (slot >= a.S) slot -= a.S;
         diff -= (double)a.w[slot];
       }
-      ctl->sum += diff;
+      ctl->sum = sum_d + diff;
     }
     __syncthreads();
     for (int j = tid; j < a.pop_n; j += kSelThreads) {
@@ -565,35 +556,40 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     }
   }
 
-  if (tid == 0) ctl->probe[6] = clock64();
-  // ---- 7. importance weights (lines 320-322)
+  // importance weights (lines 320-322); wsel was written by other SMs: read through L2
+  float* wbuf = reinterpret_cast<float*>(sm_raw);  // the tile prefixes are no longer needed
+  __syncthreads();
   float mx = -INFINITY;
   for (int i = tid; i < a.B; i += kSelThreads) {
-    float x = __fdiv_rn(wsel[i], sumf);
-    x = __fmul_rn((float)a.size_is, x);
-    x = (float)pow((double)x, (double)(-a.beta));
-    wsel[i] = x;
-    mx = fmaxf(mx, x);
+    float v = __fdiv_rn(__ldcg(a.wsel + i), sumf);
+    v = __fmul_rn((float)a.size_is, v);
+    v = (float)pow((double)v, (double)(-a.beta));
+    wbuf[i] = v;
+    mx = fmaxf(mx, v);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  __syncthreads();
   if (lane == 0) red_f[warp] = mx;
   __syncthreads();
   if (warp == 0) {
-    float m = red_f[lane];
+    float m = lane < kWarps ? red_f[lane] : -INFINITY;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0) sh_max = m;
   }
   __syncthreads();
-  for (int i = tid; i < a.B; i += kSelThreads) a.is_weights[i] = __fdiv_rn(wsel[i], sh_max);
+  for (int i = tid; i < a.B; i += kSelThreads) a.is_weights[i] = __fdiv_rn(wbuf[i], sh_max);
 
+  // RNG state after the B draws, counters
+  for (int i = tid; i < 624; i += kSelThreads) ctl->mt[i] = mt[i];
   if (tid == 0) {
-    ctl->probe[7] = clock64();
-    if (sh_exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
+    ctl->mti = sh_mti;
+    if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
     ctl->n_popped += (unsigned long long)a.pop_n;
-    if (sh_fail) ctl->error = RR_ERR_OVERRUN;
+    if (*reinterpret_cast<volatile int*>(&ctl->sel_fail)) ctl->error = RR_ERR_OVERRUN;
+    ctl->sel_fail = 0;
+    ctl->done_ctas = 0u;
+    ctl->probe[5] = clock64();
   }
 }
 
@@ -652,12 +648,15 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   const int lane = tid & 31, warp = tid >> 5;
   pdl_launch_dependents();
   pdl_wait();
+  float* s_old = s_diff;  // old weight, replaced by the difference below
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = ids[i];
     const float p = prio[i];
-    const bool ev = evicted[id] != 0;
+    const bool ev = evicted[id] != 0;  // both dependent loads are issued together
+    const float old = w[id];
     s_new[i] = is_weight ? p : pow_alpha(p, alpha);
     s_id[i] = ev ? -1 : id;
+    s_old[i] = old;
   }
   __syncthreads();
   double sum = 0.0, asum = 0.0;
@@ -667,13 +666,13 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
     float d = 0.0f;
     if (id >= 0) {
       const bool has_prev = i > 0 && s_id[i - 1] == id;
-      const float old = has_prev ? s_new[i - 1] : w[id];
+      const float old = has_prev ? s_new[i - 1] : s_old[i];
       d = __fsub_rn(s_new[i], old);
       sum += (double)d;
       asum += fabs((double)d);
       if (d != 0.0f) mn = fminf(mn, fabsf(d));
     }
-    s_diff[i] = d;
+    s_diff[i] = d;  // same thread read s_old[i] above
   }
   __syncthreads();  // all reads of the old weights are done
   for (int i = tid; i < n; i += blockDim.x) {
@@ -723,19 +722,21 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
 
 // ----------------------------------------------------------------- launches
 cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
-  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kTile), dim3(256), 0, stream, a.w, a.l1, a.l2, a.l2min);
+  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kBuildSpan), dim3(256), 0, stream, a.w, a.l2, a.l2min,
+                    a.tile_log2);
 }
 
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
-  const size_t smem = (size_t)(a.S_pad / kTile) * sizeof(double) + (size_t)a.B * 2 * sizeof(float) +
-                      (size_t)(kSelChunk + 2) * sizeof(int) + (size_t)std::min(a.B, kSelChunk) * 33 * sizeof(double);
+  const size_t nt = (size_t)a.S_pad >> a.tile_log2;
+  const size_t smem = std::max(nt * sizeof(double), (size_t)a.B * sizeof(float)) + 16;
   static size_t configured = 0;
-  if (smem > 40 * 1024 && smem > configured) {
+  if (smem > 32 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  return launch_pdl(select_kernel, dim3(1), dim3(kSelThreads), smem, stream, a);
+  const int grid = (a.B + kSelTargets - 1) / kSelTargets;
+  return launch_pdl(select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
 }
 
 cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const float* prio, float alpha,

@@ -94,3 +94,30 @@ def test_rnn_full_size_rows():
     schema = rnn_schema()  # T=123, 4x84x84 frames, hid 512
     ops = gen_trace(schema, 24, 5, 4, 4, 8, prefill=12)
     _run_pair(schema, 24, 3, 0.9, 0.6, 0, ops)
+
+
+@pytest.mark.parametrize("tile_log2", [9, 10, 11])
+def test_larger_prefix_tiles(monkeypatch, tile_log2):
+    """Replays above 4 M slots use tiles of 512 ... 2048 slots (at most 16 K tile
+    prefixes fit in shared memory); force them at a small capacity."""
+    monkeypatch.setenv("RR_TILE_LOG2", str(tile_log2))
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    ops = gen_trace(schema, 9000, 31 + tile_log2, 40, 80, 200, zero_frac=0.05)
+    cu = _run_pair(schema, 9000, 5, 0.6, 0.4, 0, ops)
+    assert cu.stats()["samples_ordered"] == 0
+
+
+def test_six_million_slots_natural_tile_size():
+    """capacity 6 M -> 7.5 M slots -> 512-slot tiles chosen by rr_create; selection
+    only (tiny rows), a few cycles (the oracle walks 6 M weights per sample)."""
+    schema = [f for f in ff_schema(frame=(1, 1, 1), n_actions=1) if f.name in ("action.a", "reward")]
+    cap = 6_000_000
+    ops = gen_trace(schema, cap, 77, 4, 200_000, 512, prefill=cap, adds_per_cycle=(1, 1))
+    _run_pair(schema, cap, 9, 0.6, 0.4, 0, ops)
+
+
+def test_batch_not_multiple_of_cta_targets():
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    for B in (1, 31, 33, 700):
+        ops = gen_trace(schema, 2000, 41 + B, 10, 40, B)
+        _run_pair(schema, 2000, 5, 0.6, 0.4, 0, ops)

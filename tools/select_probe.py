@@ -25,17 +25,18 @@ while n < cap + 64:
     r.add(tr, torch.rand(k, device=dev, generator=g) + 0.01)
     n += k
 L = capi.lib()
-acc = np.zeros(8)
+acc = np.zeros(5)
 N = 50
+r2 = rela_b200.replay  # noqa: F841
 for it in range(N + 5):
     b, w = r.sample(B, dev)
     r.update_priority(torch.rand(B) + 0.01)
     pr = np.zeros(16, dtype=np.uint64)
     capi.check(L.rr_debug_select_probe(r._h, pr.ctypes.data))
     if it >= 5:
-        acc[:7] += np.diff(pr[:8].astype(np.int64))
-names = ["scan tile sums", "exactness+offset", "targets (mt19937)", "selection", "marks", "eviction", "IS weights"]
-for nm, v in zip(names, acc[:7] / N):
-    print(f"{nm:22s} {v:9.0f} cyc  {v/1.9e3:6.2f} us")
-print("total", acc[:7].sum() / N / 1.9e3, "us")
-print("selection sub-phases (last call, cycles): t0->A", int(pr[8]-pr[3]), "sync", int(pr[9]-pr[8]), "copy l1+sync", int(pr[10]-pr[9]), "walk groups", int(pr[11]-pr[10]), "copy w+sync", int(pr[12]-pr[11]), "walk slots", int(pr[13]-pr[12]), "tail", int(pr[4]-pr[13]))
+        acc += np.diff(pr[:6].astype(np.int64))
+names = ["loads + min + targets (mt19937)", "tile-prefix scan", "offset + tile search", "in-tile search + ids",
+         "ticket + eviction + IS weights"]
+for nm, v in zip(names, acc / N):
+    print(f"{nm:34s} {v:9.0f} cyc  {v/1.9e3:6.2f} us")
+print("CTA 0 span", acc.sum() / N / 1.9e3, "us (the last CTA's tail is attributed to CTA 0 only when it is the last)")
