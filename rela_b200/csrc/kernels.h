@@ -76,8 +76,8 @@ constexpr int kSelTargets = 32;    // targets per CTA of select_kernel
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
 // PrioritizedReplay (reference rela/prioritized_replay.h:166,343).
 struct Ctl {
+  uint32_t mt[624];                // first: 16-byte aligned source of a bulk copy
   double sum;
-  uint32_t mt[624];
   int mti;
   int error;                       // sticky RR_ERR_* raised by a kernel
   unsigned int done_ctas;          // select_kernel: CTAs that finished their targets

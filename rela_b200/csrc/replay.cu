@@ -323,7 +323,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evGather, cudaEventDisableTiming));
 
-  const size_t nt2 = (size_t)r->S_pad >> r->tile_log2;
+  const size_t nt2 = ((((size_t)r->S_pad >> r->tile_log2) + 3) & ~(size_t)3);  // padded: bulk copies move 16-byte units
   RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
   RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
   RR_CUDA(cudaMalloc(&r->l2, sizeof(double) * nt2));

@@ -10,10 +10,9 @@
 // representable in double, that walk returns the same indices as ANY
 // association of the same additions. A sufficient, cheaply checkable condition:
 // all weights are multiples of u = ulp(smallest non-zero weight) and the total
-// is < 2^53 * u. Then every value this file computes (group sums, tile sums,
-// prefixes, differences of prefixes) is an integer multiple of u below
-// 2^53 * u, hence exact, and the two-level search below is bit-identical to
-// the sequential walk. When the condition fails (weights spanning > 29 binades
+// is < 2^52 * u. Then every value this file computes (tile sums, prefixes,
+// differences of prefixes) is a multiple of u below 2^53 * u, hence exact in
+// fp64, and the two-level search below is bit-identical to the sequential walk. When the condition fails (weights spanning > 29 binades
 // relative to the total) the kernel takes the ordered walk instead, which is
 // the reference's loop verbatim, and counts it in Ctl::n_ordered.
 //
@@ -136,43 +135,6 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
-// Exact integer view of the prefix hierarchy ---------------------------------
-// Under the exactness condition every weight, group sum, tile sum and prefix
-// is an integer multiple of u = 2^ue below 2^52 * u. The search works on those
-// integers ("q" values): no fp64 dependency chains, and comparisons against a
-// target t become P >= ceil(t / u) (and "accSum > 0" becomes P >= 1).
-__device__ __forceinline__ unsigned long long f2q(float w, int ue) {
-  const uint32_t bits = __float_as_uint(w) & 0x7fffffffu;
-  if (bits == 0u) return 0ull;
-  const uint32_t e = bits >> 23;
-  const unsigned long long m = e ? ((bits & 0x7fffffu) | 0x800000u) : (bits & 0x7fffffu);
-  const int shift = (int)(e ? e : 1u) - 150 - ue;  // >= 0: ulp(w) >= u
-  return shift < 40 ? (m << shift) : ~0ull >> 2;   // >= 2^62 can never be below a key
-}
-
-// x / 2^ue for a double that is a multiple of 2^ue; *inexact is raised when it
-// is not, or when the quotient does not fit 2^62.
-__device__ __forceinline__ unsigned long long d2q(double x, int ue, int* inexact) {
-  const unsigned long long bits = (unsigned long long)__double_as_longlong(x) & 0x7fffffffffffffffull;
-  if (bits == 0ull) return 0ull;
-  const int e = (int)(bits >> 52);
-  const unsigned long long m = (bits & 0xfffffffffffffull) | (e ? 0x10000000000000ull : 0ull);
-  const int shift = (e ? e : 1) - 1075 - ue;
-  if (shift >= 0) {
-    if (shift > 9) {
-      *inexact = 1;
-      return ~0ull >> 2;
-    }
-    return m << shift;
-  }
-  if (shift <= -64) {
-    *inexact = 1;
-    return 0ull;
-  }
-  if (m & ((1ull << (-shift)) - 1ull)) *inexact = 1;
-  return m >> (-shift);
-}
-
 // Targets d_lo .. d_hi-1 of a batch of B draws (rela/prioritized_replay.h:265-280)
 // from the mt19937 state `mt` / `mti` in shared memory: libstdc++'s
 // generate_canonical<float, 24> (one 32-bit draw, * 2^-32, clamp to
@@ -208,27 +170,40 @@ __device__ void gen_targets(uint32_t* mt, int mti, int B, int d_lo, int d_hi, fl
 }  // namespace
 
 // -------------------------------------------------------------- K4/K5 select
-// Grid: one CTA of 512 threads per 32 targets. Every CTA scans the tile sums
-// (replicated: at most 16 K doubles from L2) and regenerates the mt19937
-// stream for its own targets, so the CTAs never wait for each other; the CTA
-// that finishes last (ticket in Ctl::done_ctas) evicts, turns the selected
-// weights into importance weights (block-wide max) and writes the RNG state
-// back. Dynamic shared memory: the tile prefixes (8 B x tiles), reused for the
-// targets of the ordered walk.
-__global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a) {
-  extern __shared__ __align__(16) uint8_t sm_raw[];
+// Grid: one CTA of 512 threads per 32 targets. Every CTA pulls the tile sums
+// (at most 16 K doubles, L2-resident) into shared memory with one bulk async
+// copy, scans them, and regenerates the mt19937 stream for its own targets, so
+// the CTAs never wait for each other; the CTA that finishes last (ticket in
+// Ctl::done_ctas) evicts, turns the selected weights into importance weights
+// (block-wide max) and writes the RNG state back.
+//
+// All prefix arithmetic is in fp64 on the weights themselves. Under the
+// exactness condition (every weight a multiple of u = ulp(min non-zero weight),
+// total < 2^52 u) every partial sum formed here is a multiple of u below
+// 2^53 u, hence exact and independent of the association. Conversely, if any
+// addition anywhere (tile sums included) had to round, its result is >= 2^53 u
+// and so is the total: the single test `total < 2^52 u` detects every inexact
+// case, and those take the ordered walk.
+//
+// Dynamic shared memory: tile prefixes (8 B x tiles) | tile minima (4 B x tiles);
+// the first region is reused for the targets of the ordered walk and for the
+// importance weights.
+__global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs a) {
+  extern __shared__ __align__(128) uint8_t sm_raw[];
   const int tl = a.tile_log2;
   const int nt = a.S_pad >> tl;
+  const int nt_pad = (nt + 3) & ~3;
   double* p2d = reinterpret_cast<double*>(sm_raw);
-  unsigned long long* p2q = reinterpret_cast<unsigned long long*>(sm_raw);
-  __shared__ uint32_t mt[624];
-  __shared__ unsigned long long red_q[kSelThreads / 32];
+  float* tmin = reinterpret_cast<float*>(sm_raw + (size_t)nt_pad * sizeof(double));
+  __shared__ __align__(16) uint32_t mt[624];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ double red_d[kSelThreads / 32];
   __shared__ float red_f[kSelThreads / 32];
   __shared__ float s_target[kSelTargets];
   __shared__ int s_tile[kSelTargets];
   __shared__ int s_wrapped[kSelTargets];
-  __shared__ unsigned long long s_rem[kSelTargets];
-  __shared__ unsigned long long sh_offset;
+  __shared__ double s_rem[kSelTargets];
+  __shared__ double sh_offset;
   __shared__ float sh_max;
   __shared__ int sh_last, sh_mti;
 
@@ -240,23 +215,33 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   const int nT = min(kSelTargets, a.B - i0);
   const bool probing = blockIdx.x == 0 && tid == 0;
 
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    mbar_fence_init();
+  }
   pdl_launch_dependents();
+  __syncthreads();
   pdl_wait();
   if (probing) ctl->probe[0] = clock64();
-  // ---- 1. every load that depends on nothing but the kernel arguments
+  // ---- 1. everything that depends on nothing but the kernel arguments:
+  //         tile sums, tile minima and the RNG state by bulk copies (TMA)
+  if (tid == 0) {
+    const uint32_t b2 = (uint32_t)nt_pad * 8u, bm = (uint32_t)nt_pad * 4u, br = 624u * 4u;
+    mbar_expect_tx(&bar, b2 + bm + br);
+    bulk_g2s(p2d, a.l2, b2, &bar);
+    bulk_g2s(tmin, a.l2min, bm, &bar);
+    bulk_g2s(mt, ctl->mt, br, &bar);
+  }
   const double sum_d = ctl->sum;
   const int mti0 = ctl->mti;
-  for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
-  float mn = FLT_MAX;
-  for (int i = tid; i < nt; i += kSelThreads) {
-    p2d[i] = a.l2[i];
-    mn = fminf(mn, a.l2min[i]);
-  }
   double head_part = 0.0;  // weights in front of head inside head's tile (for the offset O)
   if (warp == kWarps - 1 && a.head > 0) {
     const int last = a.head - 1;
     for (int k = ((last >> tl) << tl) + lane; k <= last; k += 32) head_part += (double)a.w[k];
   }
+  mbar_wait(&bar, 0);
+  float mn = FLT_MAX;
+  for (int i = tid; i < nt; i += kSelThreads) mn = fminf(mn, tmin[i]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
   if (lane == 0) red_f[warp] = mn;
@@ -274,61 +259,58 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     ue = (e - 1) - 23;    // ulp of a normal float
     if (ue < -149) ue = -149;
   }
+  const double unit = ldexp(1.0, ue);
   const float sumf = (float)sum_d;
 
   // ---- 2. this CTA's targets (needs only the RNG state and sum_)
   gen_targets(mt, mti0, a.B, i0, i0 + nT, sumf, a.contract_fma, s_target, &sh_mti);
   if (probing) ctl->probe[1] = clock64();
 
-  // ---- 3. integer inclusive prefix of the tile sums: contiguous chunk per
-  //         thread (odd length: conflict-free 8-byte accesses), block scan of
-  //         the chunk totals, second pass adds the chunk offset
+  // ---- 3. inclusive prefix of the tile sums: contiguous chunk per thread (odd
+  //         length: conflict-free 8-byte accesses), block scan of the chunk
+  //         totals, second pass adds the chunk offset
   const int per = ((nt + kSelThreads - 1) / kSelThreads) | 1;
   const int c0 = min(tid * per, nt), c1 = min(c0 + per, nt);
-  int inexact = 0;
-  unsigned long long run = 0ull;
+  double run = 0.0;
   for (int i = c0; i < c1; ++i) {
-    run += d2q(p2d[i], ue, &inexact);
-    p2q[i] = run;  // same 8 bytes as p2d[i]
+    run += p2d[i];
+    p2d[i] = run;
   }
-  unsigned long long x = run;
+  double x = run;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+    const double y = __shfl_up_sync(0xffffffffu, x, o);
     if (lane >= o) x += y;
   }
-  if (lane == 31) red_q[warp] = x;
-  inexact = __syncthreads_or(inexact);
+  if (lane == 31) red_d[warp] = x;
+  __syncthreads();
   if (warp == 0) {
-    unsigned long long t = lane < kWarps ? red_q[lane] : 0ull;
+    double t = lane < kWarps ? red_d[lane] : 0.0;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      unsigned long long y = __shfl_up_sync(0xffffffffu, t, o);
+      const double y = __shfl_up_sync(0xffffffffu, t, o);
       if (lane >= o) t += y;
     }
-    if (lane < kWarps) red_q[lane] = t;
+    if (lane < kWarps) red_d[lane] = t;
   }
   __syncthreads();
   {
-    const unsigned long long off = (warp > 0 ? red_q[warp - 1] : 0ull) + (x - run);
-    for (int i = c0; i < c1; ++i) p2q[i] += off;
+    const double off = (warp > 0 ? red_d[warp - 1] : 0.0) + (x - run);
+    for (int i = c0; i < c1; ++i) p2d[i] += off;
   }
   __syncthreads();
-  const unsigned long long total = p2q[nt - 1];
-  const bool exact = !inexact && total < (1ull << 52) && !a.force_ordered;
+  const double total = p2d[nt - 1];
+  const bool exact = (total < ldexp(1.0, ue + 52)) && !a.force_ordered;  // false for NaN / Inf totals too
   if (probing) ctl->probe[2] = clock64();
 
   if (exact) {
     // ---- 4. offset of head: physical inclusive prefix at head - 1
     if (warp == kWarps - 1) {
-      unsigned long long part = 0ull;
+      double part = 0.0;
       if (a.head > 0) {
-        int dummy = 0;
-        part = d2q(head_part, ue, &dummy);
-#pragma unroll
-        for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
+        part = warp_sum(head_part);
         const int t = (a.head - 1) >> tl;
-        if (t > 0) part += p2q[t - 1];
+        if (t > 0) part += p2d[t - 1];
       }
       if (lane == 0) sh_offset = part;
     }
@@ -337,49 +319,59 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     //   whose prefix reaches a key":
     //   unwrapped part [head, S):  P(s) - O >= t'   <=>  P(s) >= t' + O
     //   wrapped part   [0, head):  M1 + P(s) >= t'  <=>  P(s) >= t' - M1
-    // with t' = max(ceil(target / u), 1) (the reference's accSum > 0 && accSum >= target),
+    // with t' = max(target rounded up to a multiple of u, u) (the reference's
+    // accSum > 0 && accSum >= target; every prefix is a multiple of u),
     // O = prefix at head - 1 and M1 = total - O the mass of the unwrapped part.
     if (tid < nT) {
-      const unsigned long long off = sh_offset;
-      const unsigned long long m1 = total - off;
+      const double off = sh_offset;
+      const double m1 = total - off;
       const float tf = s_target[tid];
-      unsigned long long tq = 1ull;
-      if (tf > 0.0f) {
-        const double scaled = ldexp((double)tf, -ue);  // exact: power-of-two scaling
-        tq = scaled >= 4.0e18 ? (1ull << 62) : (unsigned long long)__double2ll_ru(scaled);
-        if (tq == 0ull) tq = 1ull;
-      }
+      double tq = unit;
+      if (tf > 0.0f) tq = fmax(ldexp(ceil(ldexp((double)tf, -ue)), ue), unit);  // exact: power-of-two scalings
       const int wrapped = !(m1 >= tq);
-      const unsigned long long key = wrapped ? tq - m1 : tq + off;
+      const double key = wrapped ? tq - m1 : tq + off;
       int lo = 0, hi = nt;  // first tile whose inclusive prefix reaches the key
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (p2q[mid] >= key) hi = mid; else lo = mid + 1;
+        if (p2d[mid] >= key) hi = mid; else lo = mid + 1;
       }
       s_tile[tid] = lo < nt ? lo : -1;
-      s_rem[tid] = lo < nt ? key - (lo > 0 ? p2q[lo - 1] : 0ull) : 0ull;  // 1 <= rem <= tile sum
+      s_rem[tid] = lo < nt ? key - (lo > 0 ? p2d[lo - 1] : 0.0) : 0.0;  // u <= rem <= tile sum
       s_wrapped[tid] = wrapped;
     }
     __syncthreads();
     if (probing) ctl->probe[3] = clock64();
     // ---- 6. slot inside the tile: one warp per target, two targets per warp.
-    //   Lane l owns tile / 32 consecutive slots; a warp scan of the lane totals
-    //   finds the lane, which then walks its own slots.
+    //   Lane l owns tile / 32 consecutive slots (8 for 256-slot tiles: kept in
+    //   registers); a warp scan of the lane totals finds the lane, which then
+    //   walks its own slots.
     const int c = 1 << (tl - 5);
     constexpr int kPer = kSelTargets / kWarps;
-    unsigned long long T[kPer];
+    double T[kPer];
+    float4 v0[kPer], v1[kPer];
     const float* wp[kPer];
 #pragma unroll
-    for (int k = 0; k < kPer; ++k) {
+    for (int k = 0; k < kPer; ++k) {  // all loads of both targets are issued before the first use
       const int t = warp + k * kWarps;
       const int tile = t < nT ? s_tile[t] : -1;
-      T[k] = 0ull;
-      wp[k] = nullptr;
-      if (tile >= 0) {
-        wp[k] = a.w + ((size_t)tile << tl) + (size_t)lane * c;
-        for (int j = 0; j < c; j += 4) {
-          const float4 v = *reinterpret_cast<const float4*>(wp[k] + j);
-          T[k] += f2q(v.x, ue) + f2q(v.y, ue) + f2q(v.z, ue) + f2q(v.w, ue);
+      wp[k] = tile >= 0 ? a.w + ((size_t)tile << tl) + (size_t)lane * c : nullptr;
+      v0[k] = v1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (wp[k] != nullptr) {
+        v0[k] = *reinterpret_cast<const float4*>(wp[k]);
+        v1[k] = *reinterpret_cast<const float4*>(wp[k] + 4);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      T[k] = (((double)v0[k].x + (double)v0[k].y) + ((double)v0[k].z + (double)v0[k].w)) +
+             (((double)v1[k].x + (double)v1[k].y) + ((double)v1[k].z + (double)v1[k].w));
+      if (c > 8 && wp[k] != nullptr) {
+#pragma unroll 4
+        for (int j = 8; j < c; j += 8) {
+          const float4 p = *reinterpret_cast<const float4*>(wp[k] + j);
+          const float4 q = *reinterpret_cast<const float4*>(wp[k] + j + 4);
+          T[k] += (((double)p.x + (double)p.y) + ((double)p.z + (double)p.w)) +
+                  (((double)q.x + (double)q.y) + ((double)q.z + (double)q.w));
         }
       }
     }
@@ -391,29 +383,44 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       int slot = -1;
       float wv = 0.0f;
       if (tile >= 0) {
-        const unsigned long long rem = s_rem[t];
-        unsigned long long P = T[k];
+        const double rem = s_rem[t];
+        double P = T[k];
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-          unsigned long long y = __shfl_up_sync(0xffffffffu, P, o);
+          const double y = __shfl_up_sync(0xffffffffu, P, o);
           if (lane >= o) P += y;
         }
         const unsigned hit = __ballot_sync(0xffffffffu, P >= rem);
         if (hit != 0u) {
           const int L = __ffs(hit) - 1;
           if (lane == L) {
-            const unsigned long long rem_l = rem - (P - T[k]);
-            unsigned long long acc = 0ull;
+            const double rem_l = rem - (P - T[k]);
+            double acc = 0.0;
             int j = c - 1;
-            for (int q = 0; q < c; ++q) {
-              acc += f2q(wp[k][q], ue);
-              if (acc >= rem_l) {
-                j = q;
-                break;
+            if (c == 8) {
+              const float vv[8] = {v0[k].x, v0[k].y, v0[k].z, v0[k].w, v1[k].x, v1[k].y, v1[k].z, v1[k].w};
+              int found = 0;
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                acc += (double)vv[q];
+                if (!found && acc >= rem_l) {
+                  found = 1;
+                  j = q;
+                  wv = vv[q];
+                }
               }
+              if (!found) wv = vv[7];
+            } else {
+              for (int q = 0; q < c; ++q) {
+                acc += (double)wp[k][q];
+                if (acc >= rem_l) {
+                  j = q;
+                  break;
+                }
+              }
+              wv = wp[k][j];
             }
             slot = (tile << tl) + L * c + j;
-            wv = wp[k][j];
           }
           slot = __shfl_sync(0xffffffffu, slot, L);
           wv = __shfl_sync(0xffffffffu, wv, L);
@@ -518,25 +525,25 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   __syncthreads();
   if (!sh_last) return;
   __threadfence();
+  if (tid == 0) ctl->probe[6] = clock64();
 
   // eviction (blockPop, lines 84-103): after the marks like the reference
   if (a.pop_n > 0) {
     if (exact) {
-      unsigned long long part = 0ull;
+      double part = 0.0;  // exact in any order under the exactness condition
       for (int j = tid; j < a.pop_n; j += kSelThreads) {
         int slot = a.head + j;
         if (slot >= a.S) slot -= a.S;
-        part += f2q(a.w[slot], ue);
+        part += (double)a.w[slot];
       }
-#pragma unroll
-      for (int k = 16; k > 0; k >>= 1) part += __shfl_xor_sync(0xffffffffu, part, k);
-      if (lane == 0) red_q[warp] = part;
+      part = warp_sum(part);
+      if (lane == 0) red_d[warp] = part;
       __syncthreads();
       if (tid == 0) {
-        unsigned long long tot = 0ull;
-        for (int k = 0; k < kWarps; ++k) tot += red_q[k];
-        // diff = -(w_0 + w_1 + ...) exactly (< 2^52 u), then sum_ += diff (line 96)
-        ctl->sum = sum_d + -ldexp((double)tot, ue);
+        double tot = 0.0;
+        for (int k = 0; k < kWarps; ++k) tot += red_d[k];
+        // diff = -(w_0 + w_1 + ...) exactly, then sum_ += diff (line 96)
+        ctl->sum = sum_d + -tot;
       }
     } else if (tid == 0) {
       double diff = 0.0;
@@ -589,7 +596,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     if (*reinterpret_cast<volatile int*>(&ctl->sel_fail)) ctl->error = RR_ERR_OVERRUN;
     ctl->sel_fail = 0;
     ctl->done_ctas = 0u;
-    ctl->probe[5] = clock64();
+    ctl->probe[7] = clock64();
   }
 }
 
@@ -637,7 +644,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
                                                       const int32_t* __restrict__ ids, int n,
                                                       const float* __restrict__ prio, float alpha,
                                                       int is_weight) {
-  extern __shared__ __align__(16) uint8_t sm_raw[];
+  extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
   float* s_diff = s_new + n;
@@ -727,8 +734,8 @@ cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
 }
 
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
-  const size_t nt = (size_t)a.S_pad >> a.tile_log2;
-  const size_t smem = std::max(nt * sizeof(double), (size_t)a.B * sizeof(float)) + 16;
+  const size_t nt_pad = (((size_t)a.S_pad >> a.tile_log2) + 3) & ~(size_t)3;
+  const size_t smem = std::max(nt_pad * (sizeof(double) + sizeof(float)), (size_t)a.B * sizeof(float)) + 16;
   static size_t configured = 0;
   if (smem > 32 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
