@@ -441,6 +441,14 @@ def run_ours(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     gather_bytes = 2 * ROW_BYTES * B
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1c_gather_traffic.json")) as f:
+            tj = json.load(f)
+        if B == 512:
+            traffic = tj["dram_bytes_read_per_launch"] + tj["dram_bytes_write_per_launch"]
+    except (OSError, KeyError, ValueError):
+        pass
     achieved = gather_bytes / (gather_us * 1e-6) / 1e9 if gather_us > 0 else 0.0
 
     if rank != 0:
@@ -460,7 +468,10 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "kernel": "row_copy_kernel (gather)",
+                     "frac": achieved / peak, "traffic": traffic,
+                     "traffic_note": "ncu capture profiles/r1c_gather_ncu_full_details.txt: DRAM reads 29.57 MB = the "
+                                     "algorithmic read half; the 29 MB of stores land in L2 and drain after the kernel",
+                     "kernel": "row_copy_kernel (gather)",
                      "kernel_us": gather_us, "launches_timed": int(n_l.value),
                      "method": "K gather launches over 16 recorded id sets, back to back, one CUDA-event pair",
                      "bytes_per_launch": gather_bytes, "peak_source": peak_src,
