@@ -219,6 +219,7 @@ def fill_device(replay, torch, dev, capacity, extra, block=8192, seed=1):
     g.manual_seed(seed)
     total = capacity + extra
     done = 0
+    pairs = []
     while done < total:
         n = min(block, total - done)
         obs = {"s": torch.randint(0, 256, (n,) + FRAME, dtype=torch.uint8, device=dev, generator=g),
@@ -231,9 +232,25 @@ def fill_device(replay, torch, dev, capacity, extra, block=8192, seed=1):
         tr = FFTransition(obs, {"a": torch.arange(done, done + n, dtype=torch.int64, device=dev)},
                           torch.randn(n, device=dev, generator=g), term, 1.0 - term.float(), nxt)
         prio = torch.rand(n, device=dev, generator=g) + 0.01
+        timed = n == block and len(pairs) < 64 and done >= 4 * block
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         replay.add(tr, prio)
+        if timed:
+            e1.record()
+            pairs.append((e0, e1))
         done += n
     replay.sync()
+    # K1 insert: device-resident rows -> slab rows, 2 x row bytes per transition
+    # (read the producer's row, write the slot), CUDA events around add()
+    if pairs:
+        ms = sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)
+        return {"kernel": "row_copy_kernel (insert) + commit_kernel", "rows_per_add": block,
+                "us_per_add": ms * 1e3, "adds_timed": len(pairs),
+                "achieved_gbs": 2 * ROW_BYTES * block / (ms * 1e-3) / 1e9,
+                "transitions_per_s": block / (ms * 1e-3)}
+    return None
 
 
 def run_sharded(args, torch, dist, dev, rank, world, local_rank):
@@ -333,12 +350,12 @@ def run_ours(args):
     # through the C ABI by its handle.
     replay = rela_b200.rela.FFPrioritizedReplay(args.capacity, 7 + rank, args.alpha, args.beta, 0, local_rank)
     t0 = time.time()
-    fill_device(replay, torch, dev, args.capacity, 64, seed=1 + rank)
+    insert = fill_device(replay, torch, dev, args.capacity, 64, seed=1 + rank)
     fill_s = time.time() - t0
     assert replay.size() == args.capacity + 64
 
     class Leaf:
-        def __init__(self, name, dtype, shape, chunks, row_bytes):
+        def __init__(self, name, dtype, shape, chunks, row_bytes, time_major=False):
             self.name, self.dtype, self.shape, self.chunks = name, dtype, tuple(shape), chunks
 
         def batch_shape(self, n):
@@ -478,6 +495,9 @@ def run_ours(args):
                      "step_share": gather_us * 1e-3 / (ms / K)},
         "fill_s": fill_s, "slab_gb": st2["slab_bytes"] / 1e9,
     }
+    if insert is not None:
+        insert["frac_of_hbm_peak"] = insert["achieved_gbs"] / peak
+        line["insert"] = insert
     if sharded is not None:
         line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:

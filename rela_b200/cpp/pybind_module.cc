@@ -25,7 +25,7 @@ py::list schemaOf(Replay& r) {
   py::list out;
   for (const LeafSpec& s : r.core().schema()) {
     out.append(py::make_tuple(s.name, py::reinterpret_borrow<py::object>((PyObject*)torch::getTHPDtype(s.dtype)),
-                              py::cast(s.shape), s.chunks, s.row_bytes));
+                              py::cast(s.shape), s.chunks, s.row_bytes, s.time_major));
   }
   return out;
 }

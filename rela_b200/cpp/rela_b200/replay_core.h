@@ -33,7 +33,8 @@ struct LeafSpec {
   std::string name;
   torch::ScalarType dtype;
   std::vector<int64_t> shape;  // per stored element
-  uint32_t chunks;             // 1: gathered [B, shape...]; T: gathered [T, B, shape[1:]...]
+  uint32_t chunks;             // T: the row is T chunks, gathered time-major
+  bool time_major;             // gathered [shape[0], B, shape[1:]...] instead of [B, shape...]
   uint64_t row_bytes;
 };
 

@@ -83,11 +83,13 @@ void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_m
       // sequences [T, ...] and hidden states [layers, hid] are gathered on
       // dim 1; seq_len is gathered on dim 0 (rela/types.cc:161-167)
       const bool scalar = lf.t.dim() == 0 || (lf.t.dim() == 1 && sz[0] == 1 && lf.name == "seq_len");
-      s.chunks = (time_major && !scalar) ? (uint32_t)s.shape[0] : 1u;
+      s.time_major = time_major && !scalar;
+      s.chunks = s.time_major ? (uint32_t)s.shape[0] : 1u;
     } else {
       if (lf.t.dim() < 1) throw std::runtime_error("add: leaf '" + lf.name + "' has no batch dimension");
       s.shape.assign(sz.begin() + 1, sz.end());
       s.chunks = 1;
+      s.time_major = false;
     }
     s.row_bytes = numelOf(s.shape) * (uint64_t)c10::elementSize(s.dtype);
     if (s.chunks == 0) s.chunks = 1;
@@ -214,7 +216,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
   for (size_t i = 0; i < schema_.size(); ++i) {
     const LeafSpec& s = schema_[i];
     shape.clear();
-    if (s.chunks == 1) {
+    if (!s.time_major) {
       shape.push_back(B);
       shape.insert(shape.end(), s.shape.begin(), s.shape.end());
     } else {

@@ -80,17 +80,18 @@ class RNNTransition:
 
 
 class _Leaf:
-    __slots__ = ("name", "dtype", "shape", "chunks", "row_bytes")
+    __slots__ = ("name", "dtype", "shape", "chunks", "row_bytes", "time_major")
 
-    def __init__(self, name, dtype, shape, chunks):
+    def __init__(self, name, dtype, shape, chunks, time_major=False):
         self.name, self.dtype, self.shape, self.chunks = name, dtype, tuple(shape), chunks
+        self.time_major = time_major
         n = 1
         for s in self.shape:
             n *= s
         self.row_bytes = n * torch.empty((), dtype=dtype).element_size()
 
     def batch_shape(self, B):
-        if self.chunks == 1:
+        if not self.time_major:
             return (B,) + self.shape
         return (self.shape[0], B) + self.shape[1:]
 
@@ -232,7 +233,7 @@ class RNNPrioritizedReplay(_PrioritizedReplay):
                 if name == "seq_len":
                     leaves.append(_Leaf(name, t.dtype, (1,), 1))
                 else:
-                    leaves.append(_Leaf(name, t.dtype, t.shape, t.shape[0]))
+                    leaves.append(_Leaf(name, t.dtype, t.shape, t.shape[0], True))
             self._set_schema(leaves)
         keep = []
         ptrs = [0] * (len(first) * n)

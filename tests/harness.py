@@ -26,7 +26,8 @@ class Field:
     [T, B, ...] (RNNTransition::makeBatch, reference rela/types.cc:161-166).
     """
 
-    def __init__(self, name, dtype, shape, chunks=1):
+    def __init__(self, name, dtype, shape, chunks=1, time_major=None):
+        self.time_major = (chunks > 1) if time_major is None else time_major
         self.name = name
         self.dtype = np.dtype(dtype)
         self.shape = tuple(int(s) for s in shape)
@@ -35,7 +36,7 @@ class Field:
         assert self.row_bytes % self.chunks == 0
 
     def batch_shape(self, B):
-        if self.chunks == 1:
+        if not self.time_major:
             return (B,) + self.shape
         assert self.shape[0] == self.chunks
         return (self.chunks, B) + self.shape[1:]
@@ -64,8 +65,8 @@ def rnn_schema(T=123, frame=(4, 84, 84), n_actions=18, hid=512, layers=1):
         Field("obs.s", "uint8", (T,) + tuple(frame), chunks=T),
         Field("obs.eps", "float32", (T, 1), chunks=T),
         Field("obs.legal_move", "float32", (T, n_actions), chunks=T),
-        Field("h0.h0", "float32", (layers, hid), chunks=layers),
-        Field("h0.c0", "float32", (layers, hid), chunks=layers),
+        Field("h0.h0", "float32", (layers, hid), chunks=layers, time_major=True),
+        Field("h0.c0", "float32", (layers, hid), chunks=layers, time_major=True),
         Field("action.a", "int64", (T,), chunks=T),
         Field("reward", "float32", (T,), chunks=T),
         Field("terminal", "bool", (T,), chunks=T),

@@ -47,6 +47,47 @@ class CountingAgent(torch.jit.ScriptModule):
         return reward.abs() + 0.1
 
 
+HID = 8
+
+
+class CountingRnnAgent(torch.jit.ScriptModule):
+    """The four TorchScript entry points R2D2Actor calls (rela/r2d2_actor.h:221-249,
+    304-341), shaped like pyrela/r2d2.py:43-120. The "LSTM state" counts the acts
+    since the last reset, so the h0 stored with a sequence is checkable."""
+
+    def __init__(self, eta: float, burn_in: int):
+        super().__init__()
+        self.dummy = torch.nn.Parameter(torch.zeros(1))
+        self.eta = eta
+        self.burn_in = burn_in
+
+    @torch.jit.script_method
+    def get_h0(self, batchsize: int) -> dict[str, torch.Tensor]:
+        return {"h0": torch.zeros(1, batchsize, 8), "c0": torch.zeros(1, batchsize, 8)}
+
+    @torch.jit.script_method
+    def act(self, obs: dict[str, torch.Tensor],
+            hid: dict[str, torch.Tensor]) -> tuple[dict[str, torch.Tensor], dict[str, torch.Tensor]]:
+        tag = obs["tag"]
+        return {"a": (tag[:, 0] + tag[:, 1]) % 3}, {"h0": hid["h0"] + 1.0, "c0": hid["c0"] + 2.0}
+
+    @torch.jit.script_method
+    def compute_priority(self, obs: dict[str, torch.Tensor], action: dict[str, torch.Tensor],
+                         reward: torch.Tensor, terminal: torch.Tensor, bootstrap: torch.Tensor,
+                         next_obs: dict[str, torch.Tensor], hid: dict[str, torch.Tensor],
+                         next_hid: dict[str, torch.Tensor]) -> torch.Tensor:
+        return reward.abs() + 0.1
+
+    @torch.jit.script_method
+    def aggregate_priority(self, priority: torch.Tensor, seq_len: torch.Tensor) -> torch.Tensor:
+        # pyrela/r2d2.py:103-120
+        mask = torch.arange(0, priority.size(1)).unsqueeze(0) < seq_len.unsqueeze(1)
+        priority = priority * mask.float()
+        p_mean = priority.sum(1) / (seq_len - self.burn_in)
+        p_max = priority.max(1)[0]
+        return (self.eta * p_max + (1.0 - self.eta) * p_mean).detach().cpu()
+
+
 def _import_dropin():
     if BUILD not in sys.path:
         sys.path.insert(0, BUILD)
@@ -58,7 +99,10 @@ def _import_dropin():
 
 
 def _period(env_id):
-    return 5 + env_id % 4
+    return PERIOD_BASE + env_id % 4
+
+
+PERIOD_BASE = 5
 
 
 def _reward(env_id, step):
@@ -105,7 +149,22 @@ def test_reference_actors_feed_b200_replay(prefetch):
     are blocked in add() on a full ring (rela/prioritized_replay.h:47) would
     otherwise hang in Context::~Context (rela/context.h:26-33), as it does with
     the reference's own replay."""
-    out = subprocess.run([sys.executable, os.path.abspath(__file__), str(prefetch)], capture_output=True, text=True,
+    out = subprocess.run([sys.executable, os.path.abspath(__file__), "ff", str(prefetch)], capture_output=True,
+                         text=True, timeout=300)
+    assert out.returncode == 0, (out.stdout[-3000:], out.stderr[-3000:])
+    assert "DROPIN_OK" in out.stdout, out.stdout[-2000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not HAVE, reason="tests/dropin/_build missing")
+def test_reference_r2d2_actors_feed_b200_replay():
+    """Same with the reference's R2D2Actor + R2D2TransitionBuffer (sequence assembly,
+    burn-in padding, overlap carry-over; rela/r2d2_actor.h) feeding
+    rela.RNNPrioritizedReplay through add(std::vector<RNNTransition>, priority).
+    Note: with the reference's OWN replay this path throws on torch >= 1.5
+    (RNNTransition::makeBatch squeezes a 0-dim seqLen, rela/types.cc:167); the
+    B200 replay assembles the batch on the device and returns seq_len as [B]."""
+    out = subprocess.run([sys.executable, os.path.abspath(__file__), "rnn", "0"], capture_output=True, text=True,
                          timeout=300)
     assert out.returncode == 0, (out.stdout[-3000:], out.stderr[-3000:])
     assert "DROPIN_OK" in out.stdout, out.stdout[-2000:]
@@ -198,10 +257,93 @@ def test_reference_test_preplay_runs_on_b200_replay():
     assert diff < 6e-4, last
 
 
+def run_r2d2_actors():
+    global PERIOD_BASE
+    PERIOD_BASE = 13
+    rela, counting_env = _import_dropin()
+    n_threads, n_envs, n_step, gamma = 3, 4, 2, 0.99
+    seq_len, burn_in, eta = 8, 4, 0.9
+    T = burn_in + seq_len + n_step
+    frame = (2, 20, 20)
+    capacity, B = 300, 16
+    replay = rela.RNNPrioritizedReplay(capacity, 5, 0.9, 0.6, 0)
+    locker = rela.ModelLocker([CountingRnnAgent(eta, burn_in), CountingRnnAgent(eta, burn_in)], "cpu")
+    ctx = rela.Context()
+    actors = []
+    for t in range(n_threads):
+        venv = rela.VectorEnv()
+        for e in range(n_envs):
+            env_id = t * n_envs + e
+            venv.append(counting_env.CountingEnv(env_id, _period(env_id), *frame))
+        actor = rela.R2D2Actor(locker, n_step, n_envs, gamma, seq_len, burn_in, replay)
+        actors.append(actor)
+        ctx.push_env_thread(rela.BasicThreadLoop(actor, venv, False))
+    ctx.start()
+    t0 = time.time()
+    while replay.size() < 2 * B:
+        assert time.time() - t0 < 60, "actors did not fill the replay"
+        time.sleep(0.01)
+    checked = fresh = carried = 0
+    cycles = 0
+    t_start = time.time()
+    while (cycles < 60 or replay.num_add() < 3 * capacity) and time.time() - t_start < 120:
+        batch, weight = replay.sample(B, "cuda:0")
+        s = batch.obs["s"]
+        assert tuple(s.shape) == (T, B) + frame and s.dtype == torch.uint8 and s.is_cuda
+        assert tuple(batch.h0["h0"].shape) == (1, B, HID) and tuple(batch.seq_len.shape) == (B,)
+        assert tuple(batch.reward.shape) == (T, B) and batch.terminal.dtype == torch.bool
+        tag = batch.obs["tag"].cpu().numpy()          # [T, B, 2]
+        sm = s.reshape(T, B, frame[0], -1)
+        lo, hi = sm.amin(dim=3).cpu().numpy(), sm.amax(dim=3).cpu().numpy()
+        rew, boot = batch.reward.cpu().numpy(), batch.bootstrap.cpu().numpy()
+        term, act = batch.terminal.cpu().numpy(), batch.action["a"].cpu().numpy()
+        h0, c0 = batch.h0["h0"].cpu().numpy(), batch.h0["c0"].cpu().numpy()
+        slen = batch.seq_len.cpu().numpy()
+        for b in range(B):
+            L = int(slen[b])
+            assert burn_in < L <= burn_in + seq_len and slen[b] == L
+            is_fresh = h0[0, b, 0] == 0
+            first = burn_in if is_fresh else 0
+            fresh += is_fresh
+            carried += not is_fresh
+            env_id = int(tag[first, b, 0])
+            s0 = int(tag[first, b, 1])
+            assert np.all(h0[0, b] == s0) and np.all(c0[0, b] == 2 * s0)
+            if is_fresh:
+                assert s0 == 0 and not lo[:first, b].any() and not hi[:first, b].any() and not tag[:first, b].any()
+            for t in range(first, L):
+                step = s0 + (t - first)
+                assert tag[t, b, 0] == env_id and tag[t, b, 1] == step
+                R, bs, t0_, _ = _expected(env_id, step, n_step, gamma)
+                for c in range(frame[0]):
+                    v = (env_id * 7 + step * 3 + c) & 255
+                    assert lo[t, b, c] == v and hi[t, b, c] == v
+                assert act[t, b] == (env_id + step) % 3
+                assert boot[t, b] == bs and bool(term[t, b]) == t0_
+                assert abs(rew[t, b] - R) <= 1e-6 * max(1.0, abs(R))
+                if t0_:
+                    assert t == L - 1 or L == burn_in + seq_len
+            # beyond the sequence: either the n_step overlap rows or terminal padding
+            checked += 1
+        replay.update_priority(torch.rand(B) + 0.01)
+        cycles += 1
+    assert checked >= 60 * B and fresh > 0 and carried > 0, (checked, fresh, carried)
+    ctx.terminate()
+    t0 = time.time()
+    while not ctx.terminated():
+        assert time.time() - t0 < 60
+        replay.sample(B, "cuda:0")
+        replay.update_priority(torch.rand(B) + 0.01)
+        time.sleep(0.001)
+
+
 if __name__ == "__main__":
     code = 1
     try:
-        run_actors(int(sys.argv[1]))
+        if sys.argv[1] == "rnn":
+            run_r2d2_actors()
+        else:
+            run_actors(int(sys.argv[2]))
         print("DROPIN_OK")
         code = 0
     except BaseException:  # noqa: BLE001
