@@ -305,6 +305,7 @@ def run_sharded(args, torch, dist, dev, rank, world, local_rank):
     ms = float(t.item())
     rep.engine.sync()
     size = rep.size()
+    completion = rep.engine.fused_completion
     rep.engine.close()
     tps = B * K / (ms * 1e-3)
     return {"workload": "one replay of %d transitions striped over %d GPUs (%.1f GB of slabs per GPU), batch %d "
@@ -313,8 +314,10 @@ def run_sharded(args, torch, dist, dev, rank, world, local_rank):
             "value": tps, "unit": "transitions/s", "ms_per_step": ms / K, "steps": K, "size": size,
             "learner_nvlink_ingress_gbs": tps * ROW_BYTES * (world - 1) / world / 1e9,
             "nvlink_peak_gbs_per_direction": 900.0, "fill_s": fill_s,
-            "collectives_per_step": "1 x 4-byte all-reduce (completion of the peer stores) + 1 x %d-byte broadcast "
-                                    "(new priorities); none on the selection path" % (4 * B)}
+            "completion": "flag stores from the gather kernels into learner memory + one-warp acquire kernel"
+                          if completion else "4-byte NCCL all-reduce",
+            "collectives_per_step": "1 x %d-byte NCCL broadcast (new priorities); none on the selection or "
+                                    "gather path" % (4 * B)}
 
 
 

@@ -142,10 +142,21 @@ int rr_update_priority(rr_replay* r, int n, const float* priority,
 int rr_set_shard(rr_replay* r, int rank, int world);
 int rr_shard_range(const rr_replay* r, int* lo, int* hi);
 
+/* Completion of a sharded batch without a collective: after this call every
+ * rr_sample's gather kernel ends by publishing a sample counter ("epoch", the
+ * same on all shards because all shards run all samples) at `signal_ptr` -- this
+ * shard's 8-byte flag in the LEARNER's memory (peer-mapped on the other shards)
+ * -- with a system-scope release after its stores. On the learner, pass
+ * `wait_flags` = the base of the `world` flags: its rr_sample then appends a
+ * one-warp kernel that acquires all of them, so the batch is complete, in
+ * stream order, when rr_sample's results are. wait_flags == NULL elsewhere;
+ * signal_ptr == NULL switches the mechanism off. */
+int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world);
+
 /* Peer-memory plumbing for the learner's batch buffers: cudaMalloc'ed on the
  * learner GPU, exported as a 64-byte CUDA IPC handle, opened by the other
  * shards' processes with peer access over NVLink. */
-int rr_device_alloc(int device, uint64_t bytes, void** out_ptr);
+int rr_device_alloc(int device, uint64_t bytes, void** out_ptr); /* zero-filled */
 int rr_device_free(int device, void* ptr);
 int rr_ipc_export(int device, const void* ptr, void* handle64_out);
 int rr_ipc_open(int device, const void* handle64, void** out_ptr);

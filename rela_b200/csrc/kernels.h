@@ -47,6 +47,12 @@ struct CopyParams {
   int stages;           // smem ring depth
   uint32_t stage_bytes; // smem bytes per stage (>= max piece_bytes)
   unsigned long long* probe;  // debug: 8 timestamps per CTA (tools/gather_probe.cu), else null
+  // Completion signal (sharded gather): when `signal` is set, the last CTA to
+  // finish its stores publishes `signal_val` there with a system-scope release.
+  // `signal` may be a peer-mapped pointer into the learner GPU's memory.
+  unsigned int* done_counter;
+  unsigned long long* signal;
+  unsigned long long signal_val;
 };
 
 // shared-memory header of row_copy_kernel: barriers + per-stage piece records
@@ -60,6 +66,11 @@ struct CopyLaunch {
 };
 
 cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream);
+
+// Learner side of the sharded gather: one warp spins (acquire, system scope)
+// until flags[0..n) have all reached `val`; raises *error after timeout_ns.
+cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned long long val, int* error,
+                                unsigned long long timeout_ns, cudaStream_t stream);
 
 // ------------------------------------------------------------- selection
 // Two-level prefix structure over the S_pad weights: tiles of (1 << tile_log2)
@@ -81,6 +92,7 @@ struct Ctl {
   int mti;
   int error;                       // sticky RR_ERR_* raised by a kernel
   unsigned int done_ctas;          // select_kernel: CTAs that finished their targets
+  unsigned int gather_done;        // row_copy_kernel: CTAs that finished their stores (completion signal)
   int sel_fail;                    // select_kernel: a target ran past the buffer
   unsigned long long n_exact;      // samples selected by the parallel search
   unsigned long long n_ordered;    // samples that needed the ordered walk

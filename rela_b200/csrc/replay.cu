@@ -165,6 +165,11 @@ struct rr_replay {
   std::vector<bool> idbusy;
   int cur_ids = -1, cur_B = 0;
   float* pend_w = nullptr;
+  // completion signal of the sharded gather (rr_set_completion)
+  unsigned long long* signal_ptr = nullptr;
+  const unsigned long long* wait_flags = nullptr;
+  int wait_n = 0;
+  unsigned long long signal_epoch = 0;
   int pend_slot = -1, pend_B = 0, pend_pop = 0;  // rr_sample_select done, rr_sample_gather pending
   std::deque<Prefetched> queue;
   std::vector<Prefetched> pool;
@@ -455,6 +460,15 @@ int rr_set_shard(rr_replay* r, int rank, int world) {
   return RR_OK;
 }
 
+int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world) {
+  if (r == nullptr || world < 0 || world > 32) return fail(RR_ERR_ARG, "rr_set_completion: bad argument");
+  std::unique_lock<std::mutex> lk(r->m_);
+  r->signal_ptr = static_cast<unsigned long long*>(signal_ptr);
+  r->wait_flags = static_cast<const unsigned long long*>(wait_flags);
+  r->wait_n = world;
+  return RR_OK;
+}
+
 int rr_shard_range(const rr_replay* r, int* lo, int* hi) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_shard_range: null");
   if (lo) *lo = r->own_lo;
@@ -466,6 +480,7 @@ int rr_device_alloc(int device, uint64_t bytes, void** out) {
   if (out == nullptr || bytes == 0) return fail(RR_ERR_ARG, "rr_device_alloc: bad argument");
   DeviceScope dev_scope(device);
   RR_CUDA(cudaMalloc(out, bytes));
+  RR_CUDA(cudaMemset(*out, 0, bytes));
   return RR_OK;
 }
 
@@ -826,7 +841,20 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
   }
   CopyPlan plan;
   int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
+  if (rc == RR_OK && r->signal_ptr != nullptr) {
+    plan.p.done_counter = &r->ctl->gather_done;
+    plan.p.signal = r->signal_ptr;
+    plan.p.signal_val = ++r->signal_epoch;
+    if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) rc = fail(RR_ERR_ARG, "sharded gather needs at least one field");
+  }
   if (rc == RR_OK) rc = launch_plan(r, plan, r->main);
+  if (rc == RR_OK && r->signal_ptr != nullptr && r->wait_flags != nullptr) {
+    // learner: the batch is complete when every shard has published this epoch
+    cudaError_t e = rr::launch_wait_signals(r->wait_flags, r->wait_n, r->signal_epoch, &r->ctl->error,
+                                            10ull * 1000 * 1000 * 1000, r->main);
+    if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "wait_signals: %s", cudaGetErrorString(e));
+    r->launches++;
+  }
   if (rc == RR_OK && r->profiling) {
     // keep this batch's ids for rr_gather_bench (a copy node here breaks the
     // kernel-to-kernel PDL chain, which is why it is opt-in)

@@ -90,6 +90,8 @@ __device__ __forceinline__ Item decode_item(const CopyParams& p, uint32_t item) 
   return it;
 }
 
+__device__ __forceinline__ void simt_rows(const CopyParams& p);
+
 }  // namespace
 
 __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ CopyParams p) {
@@ -150,19 +152,54 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       }
       if (probe && tid == 0) probe[5] = clock64();
       // the stores only have to be done READING shared memory before the CTA
-      // exits; kernel completion makes them visible
-      bulk_wait_read<0>();
+      // exits; kernel completion makes them visible. With a completion signal
+      // they must be complete before the flag is published.
+      if (p.signal != nullptr) bulk_wait_all<0>(); else bulk_wait_read<0>();
       if (probe && tid == 0) {
         probe[6] = clock64();
         probe[7] = globaltimer_ns();
       }
     }
-    return;
+  } else {
+    // ---- narrow fields: grid-strided units over the non-bulk warps
+    pdl_launch_dependents();
+    pdl_wait();
+    simt_rows(p);
   }
+  if (p.signal == nullptr) return;
+  // ---- completion: the last CTA publishes the epoch (st.release.sys) after
+  // every CTA's stores have been fenced at system scope
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence_system();
+    if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
+      atomicExch(p.done_counter, 0u);
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.signal), "l"(p.signal_val) : "memory");
+    }
+  }
+}
 
-  // ---- narrow fields: grid-strided units over the non-bulk warps
-  pdl_launch_dependents();
-  pdl_wait();
+__global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsigned long long val, int* error,
+                                    unsigned long long timeout_ns) {
+  const int lane = threadIdx.x;
+  if (lane >= n) return;
+  const unsigned long long t0 = globaltimer_ns();
+  for (;;) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + lane) : "memory");
+    if (v >= val) break;
+    if (globaltimer_ns() - t0 > timeout_ns) {
+      *error = 2;  // RR_ERR_CUDA: a shard never signalled
+      break;
+    }
+    __nanosleep(100);
+  }
+}
+
+namespace {
+__device__ __forceinline__ void simt_rows(const CopyParams& p) {
+  const int tid = threadIdx.x;
   if (p.n_simt == 0) return;
   const uint32_t lane_base = (p.n_bulk > 0) ? 32u : 0u;
   const uint64_t per_cta = blockDim.x - lane_base;
@@ -185,6 +222,13 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     if (!row_slot(p, b, &row)) continue;
     copy_unit(row_dst(p, f, b, t, v * f.vec, row), row_src(p, f, b, t, v * f.vec, row), f.vec);
   }
+}
+}  // namespace
+
+cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned long long val, int* error,
+                                unsigned long long timeout_ns, cudaStream_t stream) {
+  wait_signals_kernel<<<1, 32, 0, stream>>>(flags, n, val, error, timeout_ns);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream) {

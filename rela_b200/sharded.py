@@ -81,6 +81,11 @@ class CapiEngine:
         self._scratch_w = None
         self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._count = 0
+        self._flags = {}     # learner -> base pointer of its `world` completion flags (local or peer-mapped)
+        # completion of a batch: flag stores from the gather kernels (default) or a 4-byte all-reduce
+        import os
+
+        self.fused_completion = os.environ.get("RELA_B200_SHARD_ALLREDUCE", "0") != "1"
 
     def close(self):
         if getattr(self, "h", None):
@@ -121,7 +126,16 @@ class CapiEngine:
         sizes = [max(16, lf.row_bytes * B) for lf in self.schema] + [4 * B]
         sets = []
         handles = []
+        need_flags = learner not in self._flags
         if self.rank == learner:
+            if need_flags:
+                p = C.c_void_p()
+                capi.check(self.L.rr_device_alloc(self.index, 256, C.byref(p)))
+                self._owned.append(p)
+                hb = C.create_string_buffer(64)
+                capi.check(self.L.rr_ipc_export(self.index, p, hb))
+                handles.append(hb.raw)
+                self._flags[learner] = p.value
             for _ in range(self.batch_sets):
                 ptrs = []
                 for nb in sizes:
@@ -145,6 +159,12 @@ class CapiEngine:
         if self.rank != learner:
             hs = box[0]
             k = 0
+            if need_flags:
+                p = C.c_void_p()
+                capi.check(self.L.rr_ipc_open(self.index, hs[0], C.byref(p)))
+                self._opened.append(p)
+                self._flags[learner] = p.value
+                k = 1
             for _ in range(self.batch_sets):
                 ptrs = []
                 for _nb in sizes:
@@ -167,8 +187,16 @@ class CapiEngine:
         self._count += 1
         if wptr is None:
             wptr = C.c_void_p(self._scratch_w.data_ptr())
+        fused = self.fused_completion and self.world > 1
+        if fused:
+            # completion without a collective: every shard's gather kernel ends by
+            # publishing the sample epoch in the learner's memory; the learner's
+            # rr_sample appends a one-warp kernel that acquires all `world` flags
+            base = self._flags[learner]
+            capi.check(self.L.rr_set_completion(self.h, C.c_void_p(base + 8 * self.rank),
+                                                C.c_void_p(base) if self.rank == learner else None, self.world))
         capi.check(self.L.rr_sample(self.h, B, ptrs, wptr, self._stream()))
-        if self.world > 1:
+        if self.world > 1 and not fused:
             # completion: when this returns on the learner's stream, every shard's
             # gather kernel (ordered before its contribution) has finished its stores
             dist.all_reduce(self._token, group=self.group)
