@@ -316,8 +316,9 @@ def run_sharded(args, torch, dist, dev, rank, world, local_rank):
             "nvlink_peak_gbs_per_direction": 900.0, "fill_s": fill_s,
             "completion": "flag stores from the gather kernels into learner memory + one-warp acquire kernel"
                           if completion else "4-byte NCCL all-reduce",
-            "collectives_per_step": "1 x %d-byte NCCL broadcast (new priorities); none on the selection or "
-                                    "gather path" % (4 * B)}
+            "collectives_per_step": ("none: rows, completion flags and the %d-byte priority push are one-sided stores "
+                                     "over NVLink peer memory" % (4 * B)) if completion else
+                                    ("1 x 4-byte all-reduce + 1 x %d-byte broadcast (NCCL)" % (4 * B))}
 
 
 

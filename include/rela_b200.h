@@ -153,6 +153,17 @@ int rr_shard_range(const rr_replay* r, int* lo, int* hi);
  * signal_ptr == NULL switches the mechanism off. */
 int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world);
 
+/* One-sided exchange of small messages between shards (the learner's new
+ * priorities -> every other shard) without a collective. rr_peer_put copies
+ * `bytes` from `src` (device) into n peer-mapped buffers and then publishes
+ * `epoch` at each peer's 8-byte flag (system-scope release), on `stream`.
+ * rr_wait_flags enqueues a one-warp kernel on `stream` that acquires until
+ * flags[0..n) >= epoch (10 s timeout -> *device_error = RR_ERR_CUDA;
+ * device_error is a DEVICE pointer). */
+int rr_peer_put(int device, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs, int n,
+                uint64_t epoch, void* stream);
+int rr_wait_flags(int device, const void* flags, int n, uint64_t epoch, int* device_error, void* stream);
+
 /* Peer-memory plumbing for the learner's batch buffers: cudaMalloc'ed on the
  * learner GPU, exported as a 64-byte CUDA IPC handle, opened by the other
  * shards' processes with peer access over NVLink. */

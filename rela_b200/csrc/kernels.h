@@ -72,6 +72,9 @@ cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStre
 cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned long long val, int* error,
                                 unsigned long long timeout_ns, cudaStream_t stream);
 
+cudaError_t launch_peer_put(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
+                            unsigned long long val, cudaStream_t stream);
+
 // ------------------------------------------------------------- selection
 // Two-level prefix structure over the S_pad weights: tiles of (1 << tile_log2)
 // slots (256 ... 2048, chosen so that there are at most kMaxTiles tiles) whose

@@ -469,6 +469,24 @@ int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, in
   return RR_OK;
 }
 
+int rr_peer_put(int device, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs, int n,
+                uint64_t epoch, void* stream) {
+  if (src == nullptr || n < 0 || n > 16 || bytes >= (1ull << 32) || (n > 0 && (!dst_ptrs || !flag_ptrs)))
+    return fail(RR_ERR_ARG, "rr_peer_put: bad argument");
+  if (n == 0) return RR_OK;
+  DeviceScope dev_scope(device);
+  RR_CUDA(rr::launch_peer_put(src, (uint32_t)bytes, dst_ptrs, flag_ptrs, n, epoch, static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
+int rr_wait_flags(int device, const void* flags, int n, uint64_t epoch, int* device_error, void* stream) {
+  if (flags == nullptr || n < 1 || n > 32 || device_error == nullptr) return fail(RR_ERR_ARG, "rr_wait_flags: bad argument");
+  DeviceScope dev_scope(device);
+  RR_CUDA(rr::launch_wait_signals(static_cast<const unsigned long long*>(flags), n, epoch, device_error,
+                                  10ull * 1000 * 1000 * 1000, static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
 int rr_shard_range(const rr_replay* r, int* lo, int* hi) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_shard_range: null");
   if (lo) *lo = r->own_lo;

@@ -197,6 +197,42 @@ __global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsi
   }
 }
 
+// Push `bytes` from `src` to n peer buffers (peer-mapped pointers) and then
+// publish `val` at each peer's flag with a system-scope release: the learner's
+// new priorities travel to the other shards without a collective.
+struct PeerList {
+  void* dst[16];
+  unsigned long long* flag[16];
+};
+
+__global__ void __launch_bounds__(256) peer_put_kernel(const uint8_t* __restrict__ src, uint32_t bytes, PeerList peers,
+                                                       int n, unsigned long long val) {
+  const int tid = threadIdx.x;
+  for (int p = 0; p < n; ++p) {
+    uint8_t* dst = static_cast<uint8_t*>(peers.dst[p]);
+    if ((bytes & 15u) == 0 && ((uintptr_t)src & 15u) == 0 && ((uintptr_t)dst & 15u) == 0) {
+      for (uint32_t i = tid * 16u; i < bytes; i += blockDim.x * 16u)
+        *reinterpret_cast<uint4*>(dst + i) = *reinterpret_cast<const uint4*>(src + i);
+    } else {
+      for (uint32_t i = tid; i < bytes; i += blockDim.x) dst[i] = src[i];
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flag[tid]), "l"(val) : "memory");
+}
+
+cudaError_t launch_peer_put(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
+                            unsigned long long val, cudaStream_t stream) {
+  PeerList pl;
+  for (int i = 0; i < n; ++i) {
+    pl.dst[i] = dst[i];
+    pl.flag[i] = static_cast<unsigned long long*>(flags[i]);
+  }
+  peer_put_kernel<<<1, 256, 0, stream>>>(static_cast<const uint8_t*>(src), bytes, pl, n, val);
+  return cudaGetLastError();
+}
+
 namespace {
 __device__ __forceinline__ void simt_rows(const CopyParams& p) {
   const int tid = threadIdx.x;

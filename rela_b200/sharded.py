@@ -207,6 +207,54 @@ class CapiEngine:
         capi.check(self.L.rr_update_priority(self.h, weights.numel(), C.c_void_p(weights.data_ptr()), flags,
                                              self._stream()))
 
+    INBOX_BYTES = 1 << 20
+
+    def _make_inboxes(self):
+        """Every shard owns one inbox in its HBM (8-byte flag, then data at +256),
+        mapped by every other shard: the learner pushes the new priorities into
+        them with rr_peer_put instead of an NCCL broadcast."""
+        p = C.c_void_p()
+        capi.check(self.L.rr_device_alloc(self.index, 256 + self.INBOX_BYTES, C.byref(p)))
+        self._owned.append(p)
+        hb = C.create_string_buffer(64)
+        capi.check(self.L.rr_ipc_export(self.index, p, hb))
+        handles = [None] * self.world
+        dist.all_gather_object(handles, hb.raw, group=self.group)
+        self._inbox = [None] * self.world
+        self._inbox[self.rank] = p.value
+        for r in range(self.world):
+            if r != self.rank:
+                q = C.c_void_p()
+                capi.check(self.L.rr_ipc_open(self.index, handles[r], C.byref(q)))
+                self._opened.append(q)
+                self._inbox[r] = q.value
+        self._err = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._put_epoch = 0
+
+    def exchange(self, weights, learner, n):
+        """Learner: push `weights` [n] to every other shard. Others: wait for them.
+        Returns the device pointer of the n weights on this shard."""
+        if getattr(self, "_inbox", None) is None:
+            self._make_inboxes()
+        if 4 * n > self.INBOX_BYTES:
+            raise capi.ReplayError(capi.RR_ERR_ARG, "update_priority: batch too large for the peer inbox")
+        self._put_epoch += 1
+        if self.rank == learner:
+            others = [r for r in range(self.world) if r != learner]
+            dst = (C.c_void_p * len(others))(*[self._inbox[r] + 256 for r in others])
+            flg = (C.c_void_p * len(others))(*[self._inbox[r] for r in others])
+            capi.check(self.L.rr_peer_put(self.index, C.c_void_p(weights.data_ptr()), 4 * n, dst, flg, len(others),
+                                          self._put_epoch, self._stream()))
+            return weights.data_ptr()
+        mine = self._inbox[self.rank]
+        capi.check(self.L.rr_wait_flags(self.index, C.c_void_p(mine), 1, self._put_epoch,
+                                        C.c_void_p(self._err.data_ptr()), self._stream()))
+        return mine + 256
+
+    def update_ptr(self, ptr, n):
+        flags = capi.RR_PRIO_DEVICE | capi.RR_PRIO_IS_WEIGHT
+        capi.check(self.L.rr_update_priority(self.h, n, C.c_void_p(ptr), flags, self._stream()))
+
     def size(self):
         return self.L.rr_size(self.h)
 
@@ -215,6 +263,8 @@ class CapiEngine:
 
     def sync(self):
         capi.check(self.L.rr_sync(self.h))
+        if getattr(self, "_err", None) is not None and int(self._err.item()) != 0:
+            raise capi.ReplayError(capi.RR_ERR_CUDA, "a shard never published its priorities (peer flag timeout)")
 
     def last_ids(self, B):
         import numpy as np
@@ -317,10 +367,18 @@ class ShardedPrioritizedReplay:
                 raise capi.ReplayError(capi.RR_ERR_ARG, "update_priority: %d priorities for a batch of %d"
                                        % (w.numel(), self._B))
         else:
-            w = torch.empty(self._B, dtype=torch.float32, device=self.device)
-        if self.world > 1:
-            dist.broadcast(w, src=self._src(self._learner), group=self.group)
-        self.engine.update(w)
+            w = None
+        if self.world > 1 and getattr(self.engine, "fused_completion", False):
+            # one-sided: the learner stores the weights into every shard's inbox
+            ptr = self.engine.exchange(w, self._learner, self._B)
+            self._keep = w  # alive until the put kernel has run (stream-ordered free is fine for torch's allocator)
+            self.engine.update_ptr(ptr, self._B)
+        else:
+            if w is None:
+                w = torch.empty(self._B, dtype=torch.float32, device=self.device)
+            if self.world > 1:
+                dist.broadcast(w, src=self._src(self._learner), group=self.group)
+            self.engine.update(w)
         self._learner = None
 
     def size(self):
