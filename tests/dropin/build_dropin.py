@@ -43,7 +43,7 @@ def build(force=False):
     cpp = os.path.join(ROOT, "rela_b200", "cpp")
     inc = ["-I" + os.path.join(cpp, "dropin"), "-I" + cpp, "-I" + os.path.join(ROOT, "include"), "-I" + REF]
     # the reference builds with asserts live (rela/CMakeLists.txt:4-6)
-    cxx = [f for f in cxx if f != "-Wall"] + ["-Wno-register", "-Wno-unused-variable", "-Wno-unused-but-set-variable"]
+    cxx = ["-O3" if f == "-O2" else f for f in cxx if f != "-Wall"] + ["-Wno-register", "-Wno-unused-variable", "-Wno-unused-but-set-variable"]
     hdrs = [os.path.join(dp, f) for dp, _, fs in os.walk(cpp) for f in fs]
     units = {
         "pybind.o": os.path.join(REF, "rela", "pybind.cc"),
@@ -52,6 +52,11 @@ def build(force=False):
         "counting_env.o": os.path.join(HERE, "counting_env.cc"),
         "test_preplay.o": os.path.join(REF, "rela", "tests", "test_prioritized_replay.cc"),
     }
+    # the UNMODIFIED reference module (its own replay header), for tools/bench_actors.py --impl reference
+    ref_obj = os.path.join(OUT, "pybind_ref.o")
+    ref_proc = None
+    if force or _newer(ref_obj, [units["pybind.o"]]):
+        ref_proc = subprocess.Popen(["g++"] + cxx + ["-I" + REF, "-c", units["pybind.o"], "-o", ref_obj])
     procs = []
     for o, src in units.items():
         obj = os.path.join(OUT, o)
@@ -60,12 +65,17 @@ def build(force=False):
     for p in procs:
         if p.wait() != 0:
             raise RuntimeError("drop-in compile failed")
+    if ref_proc is not None and ref_proc.wait() != 0:
+        raise RuntimeError("reference module compile failed")
     o = lambda n: os.path.join(OUT, n)  # noqa: E731
+    os.makedirs(o("reference"), exist_ok=True)
     lib = ["-L" + os.path.join(ROOT, "rela_b200"), "-lrela_b200",
            "-Wl,-rpath," + os.path.join("$ORIGIN", "..", "..", "..", "rela_b200")]
     subprocess.run(["g++", "-shared", "-o", o("rela.so"), o("pybind.o"), o("types.o"), o("replay_core.o")] + lib + ld,
                    check=True)
     subprocess.run(["g++", "-shared", "-o", o("counting_env.so"), o("counting_env.o")] + ld, check=True)
+    subprocess.run(["g++", "-shared", "-o", os.path.join(o("reference"), "rela.so"), o("pybind_ref.o"), o("types.o")] + ld,
+                   check=True)
     import nvidia.cuda_runtime as cr
 
     ld = ld + ["-L" + os.path.join(list(cr.__path__)[0], "lib"), "-l:libcudart.so.12"]
