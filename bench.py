@@ -180,8 +180,9 @@ def run_reference(args):
         return
     from harness import have_ref
 
-    cycles = max(args.steps, 1)
-    warm = max(args.warmup, 1)
+    # a reference cycle costs 7-12 ms: bound the run to a few minutes whatever --steps says
+    cycles = max(min(args.steps, 3000), 1)
+    warm = max(min(args.warmup, 20), 1)
     if not have_ref():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_replay.so not built"}))
         return
