@@ -9,8 +9,10 @@ cannot hold it; checked through size-independent properties instead --
     (frames are a pure function of the serial, regenerated on the device);
 (2) sampled ids are non-decreasing in ring order (the reference's walk never rewinds)
     and stratified: id_i's prefix interval contains target_i's segment;
-(3) sum_ equals the exact sum of the stored weights (checksum), before and after
-    update_priority, and the updated slots hold the new weights;
+(3) sum_ is the reference's running total, reproduced from the stored weights:
+    float32 sequential sum per add block, accumulated in double
+    (prioritized_replay.h:58-73), minus the popped weights (:84-96), plus the
+    float32 differences of update (:105-118); the updated slots hold the new weights;
 (4) importance weights: max == 1, all in (0, 1], equal to (size*w/sum)^-beta / max within 1e-6;
 (5) eviction brings size back to capacity and zeroes exactly the oldest slots.
 """
@@ -90,7 +92,10 @@ def test_config2_full_size_properties():
 
     st, w0, _ = state()
     assert st["head"] == 0 and st["size"] == n_total
-    assert st["sum"] == float(np.sum(w0.astype(np.float64)))  # (3) exact: all partial sums representable
+    expect_sum = 0.0
+    for s0 in range(0, n_total, blk):  # (3) blockAppend: float block sum in index order, then sum_ += (double) it
+        expect_sum += float(np.cumsum(w0[s0:s0 + blk], dtype=np.float32)[-1])
+    assert st["sum"] == expect_sum
     for it in range(3):
         st_before, w_before, _ = state()
         batch, wt = r.sample(B, "cuda:0")
@@ -99,6 +104,8 @@ def test_config2_full_size_properties():
         st, w1, ev = state()
         # (5) eviction to capacity on the first sample
         if it == 0:
+            expect_sum += -float(np.sum(w_before[:extra].astype(np.float64)))  # blockPop: diff -= w, sum_ += diff
+            assert st["sum"] == expect_sum
             assert st["size"] == cap and st["head"] == extra
             assert (w1[:extra] == 0).all() and (ev[:extra] == 1).all() and (w1[extra:n_total] > 0).all()
         else:
@@ -137,8 +144,13 @@ def test_config2_full_size_properties():
         st2, w2, _ = state()
         neww = torch.pow(newp, alpha).numpy()
         keep = ev[ids] == 0
-        last = {int(s): float(x) for s, x, k in zip(ids, neww, keep) if k}  # last occurrence wins
-        for s, x in last.items():
-            assert w2[s] == np.float32(x)
-        assert st2["sum"] == pytest.approx(float(np.sum(w2.astype(np.float64))), rel=1e-12)
+        cur = w1.copy()
+        diff = 0.0
+        for s, x, k in zip(ids, neww, keep):  # ConcurrentQueue::update, in order, skipping evicted ids
+            if k:
+                diff += float(np.float32(np.float32(x) - cur[s]))
+                cur[s] = np.float32(x)
+        expect_sum += diff
+        assert st2["sum"] == expect_sum
+        np.testing.assert_array_equal(w2, cur)
     r.sync()
