@@ -74,6 +74,14 @@ class ReplayCore {
   void checkLeaf(size_t i, const torch::Tensor& t, bool per_element, int64_t n) const;
   torch::Tensor weightsOf(const torch::Tensor& priority, unsigned* flags) const;
 
+  struct BatchSet {
+    int64_t B = 0;
+    std::vector<torch::Tensor> fields;
+    torch::Tensor weights;
+  };
+  std::vector<BatchSet> pool_;  // batch tensors reused once the caller has released them
+  bool pool_enabled_ = true;
+
   rr_replay* h_ = nullptr;
   int device_ = 0;
   float alpha_ = 1.0f;

@@ -38,6 +38,13 @@ inline void* streamOf(int device) {
   return (void*)c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
 }
 
+// A new tensor object over the same storage, built without the dispatcher.
+torch::Tensor aliasOf(const torch::Tensor& base) {
+  auto impl = c10::make_intrusive<c10::TensorImpl>(c10::Storage(base.storage()), base.key_set(), base.dtype());
+  impl->set_sizes_contiguous(base.sizes());
+  return torch::Tensor(std::move(impl));
+}
+
 uint64_t numelOf(const std::vector<int64_t>& shape) {
   uint64_t n = 1;
   for (auto s : shape) n *= (uint64_t)s;
@@ -56,6 +63,8 @@ ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int pref
   // (fp64 pow rounded once; <= 1e-6 relative).
   const char* e = std::getenv("RELA_B200_DEVICE_POW");
   host_pow_ = !(e && std::atoi(e) != 0);
+  const char* np = std::getenv("RELA_B200_NO_POOL");
+  pool_enabled_ = !(np && std::atoi(np) != 0);
   check(rr_create(&h_, capacity, seed, alpha, beta, prefetch, device_), "PrioritizedReplay");
 }
 
@@ -204,30 +213,61 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
   }
   const int64_t B = batchsize;
   const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
-  // The selection kernels are issued first; the batch tensors are allocated
-  // while they run, then the gather is issued behind them.
-  torch::Tensor weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+  // Batch tensors come from a small pool. The caller never receives the pooled
+  // tensor objects, only fresh aliases of their storages; a set is reused once
+  // every storage is back to a use count of 1, i.e. the caller has dropped the
+  // batch and every view of it -- the steady state of a learner loop that
+  // rebinds `batch` each step. (Handing out the pooled TensorImpl itself would
+  // never come back to a count of 1: its Python wrapper outlives the rebind
+  // while another C++ owner exists.) Otherwise a
+  // new set is allocated -- after the selection kernels have been issued, so
+  // that the allocation overlaps them.
+  BatchSet* set = nullptr;
+  if (pool_enabled_) {
+    for (auto& cand : pool_) {
+      if (cand.B != B) continue;
+      bool idle = cand.weights.storage().use_count() == 1;
+      for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
+      if (idle) {
+        set = &cand;
+        break;
+      }
+    }
+  }
+  BatchSet fresh;
+  const bool reuse = set != nullptr;
+  if (!reuse) {
+    set = &fresh;
+    set->B = B;
+    set->weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+  }
   void* stream = streamOf(device_);
-  check(rr_sample_select(h_, batchsize, weights.data_ptr<float>(), stream), "sample");
+  check(rr_sample_select(h_, batchsize, set->weights.data_ptr<float>(), stream), "sample");
+  if (!reuse) {
+    std::vector<int64_t> shape;
+    for (size_t i = 0; i < schema_.size(); ++i) {
+      const LeafSpec& s = schema_[i];
+      shape.clear();
+      if (!s.time_major) {
+        shape.push_back(B);
+        shape.insert(shape.end(), s.shape.begin(), s.shape.end());
+      } else {
+        shape.push_back(s.shape[0]);
+        shape.push_back(B);
+        shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
+      }
+      set->fields.push_back(torch::empty(shape, torch::TensorOptions().dtype(s.dtype).device(home)));
+    }
+  }
   Leaves out;
   out.reserve(schema_.size());
   std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
-  std::vector<int64_t> shape;
   for (size_t i = 0; i < schema_.size(); ++i) {
-    const LeafSpec& s = schema_[i];
-    shape.clear();
-    if (!s.time_major) {
-      shape.push_back(B);
-      shape.insert(shape.end(), s.shape.begin(), s.shape.end());
-    } else {
-      shape.push_back(s.shape[0]);
-      shape.push_back(B);
-      shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
-    }
-    torch::Tensor t = torch::empty(shape, torch::TensorOptions().dtype(s.dtype).device(home));
-    ptrs[i] = t.data_ptr();
-    out.push_back(Leaf{s.name, std::move(t)});
+    ptrs[i] = set->fields[i].data_ptr();
+    out.push_back(Leaf{schema_[i].name, aliasOf(set->fields[i])});
   }
+  torch::Tensor weights = aliasOf(set->weights);
+  if (!reuse && pool_enabled_ && pool_.size() < 4) pool_.push_back(std::move(fresh));
   check(rr_sample_gather(h_, ptrs.data(), stream), "sample");
   const torch::Device want(device);
   if (want != home && !(want.is_cuda() && !want.has_index())) {

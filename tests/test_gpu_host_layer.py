@@ -77,3 +77,39 @@ def test_device_pow_tolerance():
     np.testing.assert_allclose(w[: len(want)], want, rtol=1e-6, atol=0)
     mism = int((w[: len(want)] != want).sum())
     print("device pow vs torch.pow: %d of %d weights differ by 1 ulp" % (mism, len(want)))
+
+
+def test_batch_pool_never_recycles_live_tensors():
+    """The host layer pools batch tensors; a batch (or a view of it) that the
+    caller still holds must never be overwritten by a later sample."""
+    import torch
+    from rela_b200 import _C
+
+    r = _C.FFPrioritizedReplay(256, 3, 1.0, 1.0, 0)
+    K = 64
+    tr = _C.FFTransition({"s": torch.randint(0, 255, (K, 4, 20, 20), dtype=torch.uint8)}, {"a": torch.arange(K)},
+                         torch.arange(K).float(), torch.zeros(K, dtype=torch.bool), torch.ones(K), {})
+    r.add(tr, torch.rand(K) + 0.1)
+    held, held_w = r.sample(16, "cuda:0")
+    snap = held.obs["s"].clone()
+    snap_a = held.action["a"].clone()
+    view = None
+    ptrs = set()
+    for k in range(12):
+        r.update_priority(torch.rand(16) + 0.1)
+        b, w = r.sample(16, "cuda:0")
+        ptrs.add(b.obs["s"].data_ptr())
+        assert b.obs["s"].data_ptr() != held.obs["s"].data_ptr()
+        assert torch.equal(b.obs["s"].cpu(), tr.obs["s"][b.action["a"].cpu()])
+        if k == 3:
+            view = b.reward[2:5]  # a view keeps the storage alive after `b` is rebound
+            view_snap = view.clone()
+            view_ptr = b.reward.data_ptr()
+        elif view is not None:
+            assert b.reward.data_ptr() != view_ptr
+    torch.cuda.synchronize()
+    assert torch.equal(held.obs["s"], snap) and torch.equal(held.action["a"], snap_a)
+    assert torch.equal(view, view_snap)
+    assert len(ptrs) <= 4, "released batches are recycled"
+    r.update_priority(torch.rand(16) + 0.1)
+    r.sync()
