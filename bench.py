@@ -337,6 +337,15 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; rela_b200 has no CPU path")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    if world > 1:
+        # one slice of the host cores per rank: the cycle is a chain of short kernels, so a
+        # descheduled launch thread shows up directly in the max-over-ranks time
+        try:
+            cpus = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cpus) // world)
+            os.sched_setaffinity(0, set(cpus[local_rank * per:(local_rank + 1) * per]) or set(cpus))
+        except (AttributeError, OSError):
+            pass
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -417,7 +426,8 @@ def run_ours(args):
         cycle_dev(k)
     st0 = get_stats()
     clocks = ClockSampler(local_rank)
-    clocks.start()
+    if rank == 0:  # the line is rank 0's; one nvidia-smi poller per box is enough
+        clocks.start()
     ms = timed(cycle_dev, K)
     st1 = get_stats()
     launches = st1["kernel_launches"] - st0["kernel_launches"]
