@@ -126,6 +126,14 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream);
 int rr_update_priority(rr_replay* r, int n, const float* priority,
                        unsigned flags, void* stream);
 
+/* Staging primitive for device-side sequence assembly (R2D2TransitionBuffer,
+ * rela/r2d2_actor.h:29-87): row i of every packed source
+ * field (src_base[f] + i * row_bytes[f], device) is copied to row dst_rows[i]
+ * of dst_base[f] (device), with the replay's row-copy kernel on `stream`.
+ * dst_rows is a device array of n int32. */
+int rr_scatter_rows(rr_replay* r, int n, int nfields, const uint64_t* row_bytes, const void* const* src_base,
+                    void* const* dst_base, const int32_t* dst_rows, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Capacity sharding over the GPUs of one NVSwitch box (no reference
  * counterpart). One process per GPU. Every shard keeps

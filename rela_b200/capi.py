@@ -17,7 +17,7 @@ SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_select_probe", "rr_stream_fence", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
-    "rr_sample_select", "rr_sample_gather", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
+    "rr_sample_select", "rr_sample_gather", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
 ]
 
 
@@ -74,6 +74,7 @@ def lib():
         L.rr_aggregate_priority.argtypes = [i, i, vp, vp, f, i, vp, vp]
         L.rr_sample_select.argtypes = [vp, i, vp, vp]
         L.rr_sample_gather.argtypes = [vp, vp, vp]
+        L.rr_scatter_rows.argtypes = [vp, i, i, vp, vp, vp, vp, vp]
         L.rr_peer_put.argtypes = [i, vp, C.c_uint64, vp, vp, i, C.c_uint64, vp]
         L.rr_wait_flags.argtypes = [i, vp, i, C.c_uint64, vp, vp]
         L.rr_set_completion.argtypes = [vp, vp, vp, i]

@@ -64,6 +64,18 @@ class ReplayCore {
   int size() const;
   int numAdd() const;
 
+  // ---- device-resident producers (SequenceAssembler)
+  // Freeze the schema from explicit specs (no-op when already set; the specs
+  // must then match).
+  void setSchema(const std::vector<LeafSpec>& specs);
+  // add(vector<DataType>) whose rows already live in HBM: ptrs[f * n + e] is
+  // field f of element e (device pointer); ordered on the current stream.
+  void addDeviceRows(int n, const std::vector<const void*>& ptrs, const torch::Tensor& priority);
+  // row i of src[f] ([n, row] packed, device) -> row dst_rows[i] of dst[f]
+  void scatterRows(int n, const std::vector<uint64_t>& row_bytes, const std::vector<const void*>& src,
+                   const std::vector<void*>& dst, const int32_t* dst_rows_dev);
+  void* stream() const;
+
   void sync();  // waits for the device; throws on a sticky device-side error
   rr_replay* handle() const { return h_; }
   int device() const { return device_; }

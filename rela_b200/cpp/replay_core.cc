@@ -116,6 +116,46 @@ void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_m
   schema_set_ = true;
 }
 
+void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
+  std::lock_guard<std::mutex> lk(schema_m_);
+  if (schema_set_) {
+    bool same = specs.size() == schema_.size();
+    for (size_t i = 0; same && i < specs.size(); ++i)
+      same = specs[i].name == schema_[i].name && specs[i].dtype == schema_[i].dtype &&
+             specs[i].shape == schema_[i].shape && specs[i].chunks == schema_[i].chunks;
+    if (!same) throw std::runtime_error("setSchema: differs from the schema of the first add");
+    return;
+  }
+  std::vector<rr_field> fields(specs.size() ? specs.size() : 1);
+  for (size_t i = 0; i < specs.size(); ++i) {
+    fields[i].name = specs[i].name.c_str();
+    fields[i].row_bytes = specs[i].row_bytes;
+    fields[i].chunks = specs[i].chunks;
+    fields[i].reserved = 0;
+  }
+  check(rr_set_schema(h_, (int)specs.size(), fields.data()), "add (schema)");
+  schema_ = specs;
+  schema_set_ = true;
+}
+
+void* ReplayCore::stream() const { return streamOf(device_); }
+
+void ReplayCore::addDeviceRows(int n, const std::vector<const void*>& ptrs, const torch::Tensor& priority) {
+  unsigned flags = 0;
+  torch::Tensor w = weightsOf(priority, &flags);
+  if (w.size(0) != n || ptrs.size() != schema_.size() * (size_t)n)
+    throw std::runtime_error("addDeviceRows: size mismatch");
+  if (n == 0) return;
+  check(rr_add_rows(h_, n, ptrs.data(), w.data_ptr<float>(), flags | RR_ROWS_DEVICE, streamOf(device_)), "add");
+}
+
+void ReplayCore::scatterRows(int n, const std::vector<uint64_t>& row_bytes, const std::vector<const void*>& src,
+                             const std::vector<void*>& dst, const int32_t* dst_rows_dev) {
+  check(rr_scatter_rows(h_, n, (int)row_bytes.size(), row_bytes.data(), src.data(), dst.data(), dst_rows_dev,
+                        streamOf(device_)),
+        "scatterRows");
+}
+
 void ReplayCore::checkLeaf(size_t i, const torch::Tensor& t, bool per_element, int64_t n) const {
   const LeafSpec& s = schema_[i];
   bool ok = t.defined() && t.scalar_type() == s.dtype;

@@ -36,6 +36,7 @@ struct CopyParams {
   uint32_t bulk_items;  // total bulk items
   uint64_t simt_units;  // total simt units
   const int32_t* ids;   // gather: B sampled slot ids (device); insert: null
+  const int32_t* dst_rows;  // insert: explicit destination row per source row (device), or null = ring order
   int rows;             // B (gather) or n (insert)
   int insert_start;     // insert: first slot
   int slots;            // insert: S

@@ -487,6 +487,39 @@ int rr_wait_flags(int device, const void* flags, int n, uint64_t epoch, int* dev
   return RR_OK;
 }
 
+int rr_scatter_rows(rr_replay* r, int n, int nfields, const uint64_t* row_bytes, const void* const* src_base,
+                    void* const* dst_base, const int32_t* dst_rows, void* stream) {
+  if (r == nullptr || n < 0 || nfields < 0 || nfields > rr::kMaxCopyFields || (nfields > 0 && (!row_bytes || !src_base || !dst_base)) ||
+      dst_rows == nullptr)
+    return fail(RR_ERR_ARG, "rr_scatter_rows: bad argument");
+  if (n == 0 || nfields == 0) return RR_OK;
+  DeviceScope dev_scope(r->device);
+  std::vector<CopyField> cf;
+  for (int fi = 0; fi < nfields; ++fi) {
+    if (row_bytes[fi] == 0) continue;
+    if (row_bytes[fi] >= (1ull << 32)) return fail(RR_ERR_ARG, "rr_scatter_rows: row too large");
+    CopyField c;
+    memset(&c, 0, sizeof(c));
+    c.src = static_cast<const uint8_t*>(src_base[fi]);
+    c.dst = static_cast<uint8_t*>(dst_base[fi]);
+    c.chunks = 1;
+    c.chunk_bytes = (uint32_t)row_bytes[fi];
+    c.src_row_stride = row_bytes[fi];
+    c.dst_row_stride = row_bytes[fi];
+    c.dst_chunk_stride = row_bytes[fi];
+    cf.push_back(c);
+  }
+  CopyPlan plan;
+  int rc = plan_copy(r, false, n, cf, nullptr, 0, &plan);
+  if (rc != RR_OK) return rc;
+  plan.p.dst_rows = dst_rows;
+  plan.p.own_lo = 0;
+  plan.p.own_hi = 0x7fffffff;
+  RR_CUDA(rr::launch_row_copy(plan.p, plan.cfg, static_cast<cudaStream_t>(stream)));
+  r->launches++;
+  return RR_OK;
+}
+
 int rr_shard_range(const rr_replay* r, int* lo, int* hi) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_shard_range: null");
   if (lo) *lo = r->own_lo;

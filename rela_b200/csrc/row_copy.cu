@@ -40,6 +40,8 @@ __device__ __forceinline__ bool row_slot(const CopyParams& p, uint32_t b, uint32
   uint32_t slot;
   if (p.ids != nullptr) {
     slot = (uint32_t)__ldg(p.ids + b);
+  } else if (p.dst_rows != nullptr) {
+    slot = (uint32_t)__ldg(p.dst_rows + b);
   } else {
     slot = (uint32_t)p.insert_start + b;
     if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;

@@ -7,6 +7,8 @@
                                        Actors, thread loops, ModelLocker, Context: unmodified.
   tests/dropin/_build/counting_env.so  a deterministic rela::Env (counting_env.cc), the
                                        stand-in for atari.AtariEnv (no ALE / ROMs here).
+  tests/dropin/_build/seq_fixture.so   reference R2D2TransitionBuffer vs rela_b200::SequenceAssembler
+                                       (seq_fixture.cc), for tests/test_sequence_assembler.py.
   tests/dropin/_build/test_preplay     the reference's rela/tests/test_prioritized_replay.cc,
                                        compiled as is against the drop-in header.
 
@@ -50,6 +52,8 @@ def build(force=False):
         "types.o": os.path.join(REF, "rela", "types.cc"),
         "replay_core.o": os.path.join(cpp, "replay_core.cc"),
         "counting_env.o": os.path.join(HERE, "counting_env.cc"),
+        "seq_fixture.o": os.path.join(HERE, "seq_fixture.cc"),
+        "sequence_assembler.o": os.path.join(cpp, "sequence_assembler.cc"),
         "test_preplay.o": os.path.join(REF, "rela", "tests", "test_prioritized_replay.cc"),
     }
     # the UNMODIFIED reference module (its own replay header), for tools/bench_actors.py --impl reference
@@ -74,6 +78,8 @@ def build(force=False):
     subprocess.run(["g++", "-shared", "-o", o("rela.so"), o("pybind.o"), o("types.o"), o("replay_core.o")] + lib + ld,
                    check=True)
     subprocess.run(["g++", "-shared", "-o", o("counting_env.so"), o("counting_env.o")] + ld, check=True)
+    subprocess.run(["g++", "-shared", "-o", o("seq_fixture.so"), o("seq_fixture.o"), o("sequence_assembler.o"),
+                    o("replay_core.o"), o("types.o")] + lib + ld, check=True)
     subprocess.run(["g++", "-shared", "-o", os.path.join(o("reference"), "rela.so"), o("pybind_ref.o"), o("types.o")] + ld,
                    check=True)
     import nvidia.cuda_runtime as cr
