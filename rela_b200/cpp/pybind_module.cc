@@ -13,6 +13,7 @@
 #include <torch/csrc/DynamicTypes.h>
 #include <torch/extension.h>
 
+#include "rela_b200/sequence_assembler.h"
 #include "rela_b200/types.h"
 
 namespace py = pybind11;
@@ -104,6 +105,23 @@ PYBIND11_MODULE(_C, m) {
            r.add(batch, priority);
          },
          py::call_guard<py::gil_scoped_release>());
+
+  // R2D2 sequence assembly with the windows in HBM (R2D2TransitionBuffer,
+  // rela/r2d2_actor.h:10-187; not bound in the reference, which uses it from C++)
+  py::class_<SequenceAssembler>(m, "SequenceAssembler")
+      .def(py::init([](RNNPrioritizedReplay& r, int batchsize, int multiStep, int seqLen, int burnin, float eta) {
+             return new SequenceAssembler(r.core(), batchsize, multiStep, seqLen, burnin, eta);
+           }),
+           py::keep_alive<1, 2>(), py::arg("replay"), py::arg("batchsize"), py::arg("multi_step"),
+           py::arg("seq_len"), py::arg("burn_in"), py::arg("eta"))
+      .def("push",
+           [](SequenceAssembler& a, const FFTransition& t, const torch::Tensor& priority, const TensorDict& hid) {
+             Leaves h;
+             appendDict(h, "h0", hid);
+             a.push(FFTraits<FFTransition>::leaves(t), priority, h);
+           })
+      .def("can_pop", &SequenceAssembler::canPop)
+      .def("pop_into", &SequenceAssembler::popInto);
 
   py::class_<RNNPrioritizedReplay, std::shared_ptr<RNNPrioritizedReplay>> rnn(m, "RNNPrioritizedReplay");
   bindCommon<RNNPrioritizedReplay>(rnn);
