@@ -91,6 +91,7 @@ def main():
     ap.add_argument("--K", type=int, default=40)
     ap.add_argument("--B", type=int, default=64)
     ap.add_argument("--full-frames", action="store_true")
+    ap.add_argument("--rotate-learner", action="store_true", help="batch k is assembled on rank k % world")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -109,7 +110,7 @@ def main():
         engine = OracleShardEngine(schema, args.capacity, seed, alpha, beta, rank, world)
     rep = ShardedPrioritizedReplay(args.capacity, seed, alpha, beta, names, engine=engine,
                                    device=None if engine else "cuda:%d" % local)
-    ref = Oracle(schema, args.capacity, seed, alpha, beta, 0) if rank == 0 else None
+    ref = Oracle(schema, args.capacity, seed, alpha, beta, 0)  # every rank checks the batches it learns from
     n_checked = 0
     learner = 0
     for op in ops:
@@ -130,23 +131,25 @@ def main():
                 ref.add(rows, torch_pow(prio, alpha))
         elif op[0] == "sample":
             B = op[1]
+            if args.rotate_learner:
+                learner = (learner + 1) % world
             tens, w = rep.sample(B, learner)
             ids = rep.engine.last_ids(B)
             if ref is not None:
                 rc, rrows, rw, rids = ref.sample(B)
                 assert rc == 0
-            if rank == 0:
-                np.testing.assert_array_equal(ids, rids, err_msg="ids differ from the single-buffer oracle")
+            np.testing.assert_array_equal(ids, rids, err_msg="ids differ from the single-buffer oracle")
             if rank == learner:
                 if args.backend == "nccl":
                     torch.cuda.synchronize()
                 got = [t.cpu().numpy() for t in tens]
                 gw = w.cpu().numpy()
-                if learner == 0:
-                    np.testing.assert_allclose(gw, rw, rtol=1e-6, atol=0)
-                    for f, (a, b) in enumerate(zip(got, rrows)):
-                        assert a.shape == b.shape and a.tobytes() == b.tobytes(), "field %d bytes differ" % f
-                    n_checked += 1
+                np.testing.assert_allclose(gw, rw, rtol=1e-6, atol=0)
+                for f, (a, b) in enumerate(zip(got, rrows)):
+                    assert a.shape == b.shape and a.tobytes() == b.tobytes(), "field %d bytes differ" % f
+                n_checked += 1
+            else:
+                assert tens is None and w is None
             assert rep.size() == (ref.size() if ref is not None else rep.size())
         else:
             prio = op[1]
@@ -157,9 +160,12 @@ def main():
         rep.engine.sync()
         st = capi_stats(rep.engine)
         assert st["samples_ordered"] == 0 and st["device_errors"] == 0
-    dist.barrier()
+    total = torch.tensor([n_checked], device=rep.device if args.backend == "nccl" else "cpu")
+    dist.all_reduce(total)
+    n_samples = sum(1 for op in ops if op[0] == "sample")
+    assert int(total.item()) == n_samples, (int(total.item()), n_samples)
     if rank == 0:
-        print("SHARDED_OK world=%d backend=%s samples_checked=%d" % (world, args.backend, n_checked))
+        print("SHARDED_OK world=%d backend=%s samples_checked=%d" % (world, args.backend, n_samples))
     dist.destroy_process_group()
 
 

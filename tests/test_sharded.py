@@ -25,9 +25,9 @@ def _run(world, backend, port, extra=()):
     assert "SHARDED_OK world=%d" % world in out.stdout, out.stdout[-2000:]
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_protocol_gloo(world):
-    _run(world, "gloo", 29640 + world, ("--K", str(12 * world)))
+@pytest.mark.parametrize("world,rotate", [(2, False), (3, False), (2, True)])
+def test_protocol_gloo(world, rotate):
+    _run(world, "gloo", 29640 + world + 10 * rotate, ("--K", str(12 * world)) + (("--rotate-learner",) if rotate else ()))
 
 
 def test_shard_ranges_cover_the_ring():
@@ -51,6 +51,6 @@ def test_sharded_world1_gpu():
 
 @pytest.mark.gpu
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
-@pytest.mark.parametrize("extra", [(), ("--full-frames", "--capacity", "400", "--cycles", "12")])
+@pytest.mark.parametrize("extra", [(), ("--full-frames", "--capacity", "400", "--cycles", "12"), ("--rotate-learner",)])
 def test_sharded_world2_gpu(extra):
     _run(2, "nccl", 29652, extra)
