@@ -87,6 +87,7 @@ constexpr int kMinTileLog2 = 8;
 constexpr int kMaxTileLog2 = 11;
 constexpr int kMaxTiles = 16384;   // tile prefixes held in shared memory (128 KB)
 constexpr int kSelTargets = 32;    // targets per CTA of select_kernel
+constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
 
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
 // PrioritizedReplay (reference rela/prioritized_replay.h:166,343).

@@ -2,6 +2,7 @@
 // mbarrier + 1-D bulk async copies (the TMA engine's non-tensor path,
 // SASS: UBLKCP / SYNCS), 128-bit streaming loads and stores.
 #pragma once
+#include <atomic>
 #include <cstdint>
 #include <cstdlib>
 #include <cuda_runtime.h>
@@ -105,6 +106,25 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
+}
+
+// Host: opt a kernel in to `bytes` of dynamic shared memory. The attribute is
+// per device (context), and several host threads may launch at once, so the
+// high-water mark is kept per device in atomics.
+template <typename Kernel>
+inline cudaError_t ensure_dynamic_smem(Kernel kernel, size_t bytes) {
+  static std::atomic<size_t> configured[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) dev = 63;
+  if (bytes <= 48 * 1024 || bytes <= configured[dev].load(std::memory_order_acquire)) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  size_t cur = configured[dev].load();
+  while (cur < bytes && !configured[dev].compare_exchange_weak(cur, bytes)) {
+  }
+  return cudaSuccess;
 }
 
 // Host: launch with the PDL attribute (RR_PDL=0 disables it).

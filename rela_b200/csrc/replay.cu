@@ -966,6 +966,7 @@ extern "C" {
 int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
     return fail(RR_ERR_ARG, "rr_sample: bad argument");
+  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_sample: batch %d exceeds %d", batch, rr::kMaxBatch);
   if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
   if (r->cur_ids >= 0) {
     // "Error: previous samples' priority has not been updated." (line 204)
@@ -1026,6 +1027,7 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
 
 int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr) return fail(RR_ERR_ARG, "rr_sample_select: bad argument");
+  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_sample: batch %d exceeds %d", batch, rr::kMaxBatch);
   if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
   if (r->cur_ids >= 0 || r->pend_slot >= 0)
     return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");

@@ -270,13 +270,8 @@ cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned
 }
 
 cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(row_copy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         227 * 1024);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  cudaError_t e = ensure_dynamic_smem(row_copy_kernel, 227 * 1024);
+  if (e != cudaSuccess) return e;
   return launch_pdl(row_copy_kernel, dim3(cfg.grid), dim3(cfg.block), cfg.smem, stream, p);
 }
 

@@ -736,12 +736,8 @@ cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
   const size_t nt_pad = (((size_t)a.S_pad >> a.tile_log2) + 3) & ~(size_t)3;
   const size_t smem = std::max(nt_pad * (sizeof(double) + sizeof(float)), (size_t)a.B * sizeof(float)) + 16;
-  static size_t configured = 0;
-  if (smem > 32 * 1024 && smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  cudaError_t e = ensure_dynamic_smem(select_kernel, smem);
+  if (e != cudaSuccess) return e;
   const int grid = (a.B + kSelTargets - 1) / kSelTargets;
   return launch_pdl(select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
 }
@@ -755,12 +751,8 @@ cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const flo
 cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
-  static size_t configured = 0;
-  if (smem > 40 * 1024 && smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  cudaError_t e = ensure_dynamic_smem(update_kernel, smem);
+  if (e != cudaSuccess) return e;
   return launch_pdl(update_kernel, dim3(1), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio, alpha, is_weight);
 }
 

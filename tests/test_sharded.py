@@ -54,3 +54,25 @@ def test_sharded_world1_gpu():
 @pytest.mark.parametrize("extra", [(), ("--full-frames", "--capacity", "400", "--cycles", "12"), ("--rotate-learner",)])
 def test_sharded_world2_gpu(extra):
     _run(2, "nccl", 29652, extra)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_replay_on_a_device_that_is_not_current():
+    """The C ABI makes its device current per call and restores the caller's:
+    a replay on cuda:1 driven from a thread whose current device is cuda:0."""
+    import sys
+
+    sys.path.insert(0, HERE)
+    from harness import CudaReplay, Oracle, apply_trace, compare_records, ff_schema, gen_trace
+
+    torch.cuda.set_device(0)
+    schema = ff_schema(frame=(4, 84, 84))
+    ops = gen_trace(schema, 300, 4, 15, 40, 64)
+    orc = Oracle(schema, 300, 5, 0.6, 0.4, 0)
+    cu = CudaReplay(schema, 300, 5, 0.6, 0.4, 0, device=1)
+    ra = apply_trace(orc, ops, 0.6, False)
+    rb = apply_trace(cu, ops, 0.6, False)
+    assert cu.sync() == 0
+    compare_records(ra, rb, "replay on cuda:1")
+    assert torch.cuda.current_device() == 0
