@@ -396,23 +396,39 @@ def run_ours(args):
     prio_dev = torch.rand((16, B), device=dev, generator=g) + 0.01
     prio_host = (torch.rand((16, B)) + 0.01).pin_memory()
 
-    def cycle_dev(k):
-        capi.check(L.rr_sample(h, B, out_ptrs[k % R], C.c_void_p(out_w[k % R].data_ptr()), sp))
-        capi.check(L.rr_update_priority(h, B, C.c_void_p(prio_dev[k % 16].data_ptr()), capi.RR_PRIO_DEVICE, sp))
+    # The device-resident loop is a learner whose own kernels run on the replay's
+    # stream (rr_get_stream): plain stream order, no event hand-shake, and the
+    # select -> gather -> update kernels chain by programmatic dependent launch.
+    # The same loop from a foreign stream (two event hand-shakes per call) is
+    # reported beside it as value_foreign_stream.
+    own = C.c_void_p()
+    capi.check(L.rr_get_stream(h, C.byref(own)))
+    own_stream = torch.cuda.ExternalStream(own.value, device=dev)
+
+    def make_cycle(stream_ptr):
+        def cycle(k):
+            capi.check(L.rr_sample(h, B, out_ptrs[k % R], C.c_void_p(out_w[k % R].data_ptr()), stream_ptr))
+            capi.check(L.rr_update_priority(h, B, C.c_void_p(prio_dev[k % 16].data_ptr()), capi.RR_PRIO_DEVICE,
+                                            stream_ptr))
+        return cycle
+
+    cycle_dev = make_cycle(own)
+    cycle_foreign = make_cycle(sp)
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(fn, steps):
+    def timed(fn, steps, on=None):
+        on = stream if on is None else on
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
+        e0.record(on)
         for k in range(steps):
             fn(k)
-        capi.check(L.rr_stream_fence(h, sp))
-        e1.record(stream)
+        capi.check(L.rr_stream_fence(h, C.c_void_p(on.cuda_stream)))
+        e1.record(on)
         barrier()
         ms = e0.elapsed_time(e1)
         if dist is not None:
@@ -428,9 +444,10 @@ def run_ours(args):
     clocks = ClockSampler(local_rank)
     if rank == 0:  # the line is rank 0's; one nvidia-smi poller per box is enough
         clocks.start()
-    ms = timed(cycle_dev, K)
+    ms = timed(cycle_dev, K, own_stream)
     st1 = get_stats()
     launches = st1["kernel_launches"] - st0["kernel_launches"]
+    ms_foreign = timed(cycle_foreign, max(1, K // 4))
 
     # ---- roofline: record the id sets of 16 real samples, then re-launch the
     # gather kernel for them back to back (K launches, 8 rotating output
@@ -498,6 +515,10 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / K,
                 "api": "rela_b200.rela.FFPrioritizedReplay (C++ host layer, rela/pybind.cc names): sample(B,'cuda:0') + weights.cpu() + update_priority(pinned cpu tensor)"},
         "gpu_launches": int(launches),
+        "value_foreign_stream": {"value": world * B * max(1, K // 4) / (ms_foreign * 1e-3), "unit": "transitions/s",
+                                 "ms_per_step": ms_foreign / max(1, K // 4),
+                                 "note": "same loop, caller on its own stream: event hand-shake in and out of "
+                                         "every rr_sample / rr_update_priority"},
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,

@@ -192,6 +192,11 @@ int rr_get_stats(rr_replay* r, rr_stats* out);
 /* Make `stream` (caller's cudaStream_t) wait for everything issued so far on
  * the replay's internal stream. Does not block the host. */
 int rr_stream_fence(rr_replay* r, void* stream);
+/* The replay's internal cudaStream_t. A caller that does its own device work
+ * on this stream and passes it as `stream` gets plain stream order and none of
+ * the event hand-shakes: consecutive sample / update kernels then chain by
+ * programmatic dependent launch. */
+int rr_get_stream(rr_replay* r, void** out_stream);
 
 /* Gather-kernel timing for the roofline. While profiling is enabled every
  * rr_sample also keeps a copy of its sampled ids (ring of 16 sets).
@@ -211,6 +216,12 @@ int rr_last_sample_ids(rr_replay* r, int n, int32_t* out_ids_host);
 int rr_debug_state(rr_replay* r, int* head, int* tail, int* size,
                    int* safe_size, double* sum);
 int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host);
+/* The selection kernel's per-tile weight sums and smallest non-zero weights,
+ * as maintained incrementally by add / update / eviction. rebuild != 0 first
+ * recomputes every entry from the weights (tests compare the two bit for bit).
+ * Copies min(cap, tiles) entries; returns the number of tiles (< 0: error). */
+int rr_debug_tiles(rr_replay* r, int rebuild, double* out_sums_host, float* out_mins_host,
+                   int cap, int* out_tile_slots);
 /* clock64 stamps at the phase boundaries of the last selection kernel (16 x u64). */
 int rr_debug_select_probe(rr_replay* r, uint64_t* out16);
 

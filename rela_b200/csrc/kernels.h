@@ -130,12 +130,13 @@ cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream);
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
 
 // add commit (K2 + weights write + sum_, prioritized_replay.h:58-73,188)
-cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const float* prio,
-                          float alpha, int is_weight, cudaStream_t stream);
+cudaError_t launch_commit(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, int S, int start, int n,
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
 
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
-cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
+cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
+                          const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
+                          cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -129,6 +129,7 @@ struct rr_replay {
   int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
+  bool full_build = false;  // $RR_FULL_BUILD: rebuild every tile entry before each selection
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
   int sm_count = 148;
@@ -341,6 +342,19 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   mt_seed(h.mt, (uint32_t)seed);  // rng_.seed(seed), rela/prioritized_replay.h:183
   h.mti = 624;
   RR_CUDA(cudaMemcpyAsync(r->ctl, &h, sizeof(h), cudaMemcpyHostToDevice, r->main));
+  {  // tile entries of the empty buffer: sum 0, min FLT_MAX
+    rr::SelectArgs a;
+    memset(&a, 0, sizeof(a));
+    a.w = r->w;
+    a.l2 = r->l2;
+    a.l2min = r->l2min;
+    a.S_pad = r->S_pad;
+    a.tile_log2 = r->tile_log2;
+    RR_CUDA(cudaMemsetAsync(r->l2, 0, sizeof(double) * nt2, r->main));
+    RR_CUDA(cudaMemsetAsync(r->l2min, 0, sizeof(float) * nt2, r->main));
+    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
+  }
+  r->full_build = env_int("RR_FULL_BUILD", 0) != 0;
   RR_CUDA(cudaStreamSynchronize(r->main));
 
   const int nl = std::max(1, env_int("RR_ADD_LANES", 4));
@@ -764,12 +778,12 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     if (rc == RR_OK) {
       cudaError_t e = cudaStreamWaitEvent(r->main, L.copied, 0);
       if (e == cudaSuccess) {
-        e = rr::launch_commit(r->ctl, r->w, r->S, start, n, prio_dev ? priority : L.dprio, r->alpha,
-                              is_weight, r->main);
+        e = rr::launch_commit(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->S, start, n,
+                              prio_dev ? priority : L.dprio, r->alpha, is_weight, r->main);
         r->launches++;
       }
       if (e == cudaSuccess) e = cudaEventRecord(L.committed, r->main);
-      if (e == cudaSuccess && (rows_dev || prio_dev)) e = cudaStreamWaitEvent(cs, L.committed, 0);
+      if (e == cudaSuccess && (rows_dev || prio_dev) && cs != r->main) e = cudaStreamWaitEvent(cs, L.committed, 0);
       if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "rr_add commit: %s", cudaGetErrorString(e));
     }
     // On failure the slots are still committed (weight 0 keeps them unsampled)
@@ -865,9 +879,14 @@ int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
   a.beta = r->beta;
   a.contract_fma = r->contract_fma;
   a.force_ordered = r->force_ordered;
-  RR_CUDA(rr::launch_build_hierarchy(a, r->main));
+  // The tile entries are kept current by commit / update / eviction; the full
+  // build only runs here as a debugging cross-check ($RR_FULL_BUILD=1).
+  if (r->full_build) {
+    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
+    r->launches++;
+  }
   RR_CUDA(rr::launch_select(a, r->main));
-  r->launches += 2;
+  r->launches++;
   *pop_out = a.pop_n;
   return RR_OK;
 }
@@ -975,8 +994,10 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   // out buffers may have been used on the caller's stream before
-  RR_CUDA(cudaEventRecord(r->evIn, cs));
-  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
+    RR_CUDA(cudaEventRecord(r->evIn, cs));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  }
 
   int rc;
   int slot;
@@ -1003,8 +1024,10 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   r->idbusy[slot] = true;
   r->cur_ids = slot;
   r->cur_B = batch;
-  RR_CUDA(cudaEventRecord(r->evOut, r->main));
-  RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  if (cs != r->main) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
 
   // top the queue up to `prefetch` batches (lines 223-230); they are selected
   // now, i.e. before this batch's updatePriority, like the reference's futures
@@ -1039,8 +1062,10 @@ int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) 
   }
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaEventRecord(r->evIn, cs));
-  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
+    RR_CUDA(cudaEventRecord(r->evIn, cs));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  }
   const int slot = free_idslot(r);
   int rc = select_launch(r, batch, out_weights, slot, &r->pend_pop);
   if (rc != RR_OK) return rc;
@@ -1058,15 +1083,19 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   // the out buffers may have been used on the caller's stream before
-  RR_CUDA(cudaEventRecord(r->evIn, cs));
-  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
+    RR_CUDA(cudaEventRecord(r->evIn, cs));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  }
   int rc = gather_launch(r, batch, out_fields, slot, r->pend_pop);
   if (rc != RR_OK) return rc;
   r->idbusy[slot] = true;
   r->cur_ids = slot;
   r->cur_B = batch;
-  RR_CUDA(cudaEventRecord(r->evOut, r->main));
-  RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  if (cs != r->main) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
   return RR_OK;
 }
 
@@ -1082,8 +1111,10 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   const float* dprio = priority;
   std::unique_lock<std::mutex> lk(r->m_);
   if (prio_dev) {
-    RR_CUDA(cudaEventRecord(r->evIn, cs));
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    if (cs != r->main) {
+      RR_CUDA(cudaEventRecord(r->evIn, cs));
+      RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    }
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
     r->pstage_next = (r->pstage_next + 1) % (int)r->pstage.size();
@@ -1103,10 +1134,10 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     RR_CUDA(cudaEventRecord(st.done, r->main));
     dprio = st.dev;
   }
-  RR_CUDA(rr::launch_update(r->ctl, r->w, r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha, is_weight,
-                            r->main));
+  RR_CUDA(rr::launch_update(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n, dprio,
+                            r->alpha, is_weight, r->main));
   r->launches++;
-  if (prio_dev) {
+  if (prio_dev && cs != r->main) {
     RR_CUDA(cudaEventRecord(r->evOut, r->main));
     RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
   }
@@ -1136,8 +1167,15 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
   DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
+  if (static_cast<cudaStream_t>(stream) == r->main) return RR_OK;
   RR_CUDA(cudaEventRecord(r->evOut, r->main));
   RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
+  return RR_OK;
+}
+
+int rr_get_stream(rr_replay* r, void** out_stream) {
+  if (r == nullptr || out_stream == nullptr) return fail(RR_ERR_ARG, "rr_get_stream: null");
+  *out_stream = r->main;
   return RR_OK;
 }
 
@@ -1273,6 +1311,28 @@ int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {
   if (out_w) RR_CUDA(cudaMemcpy(out_w, r->w, sizeof(float) * (size_t)r->S, cudaMemcpyDeviceToHost));
   if (out_evicted) RR_CUDA(cudaMemcpy(out_evicted, r->evicted, (size_t)r->S, cudaMemcpyDeviceToHost));
   return RR_OK;
+}
+
+int rr_debug_tiles(rr_replay* r, int rebuild, double* out_sums, float* out_mins, int cap, int* out_tile_slots) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_tiles: null");
+  DeviceScope dev_scope(r->device);
+  const int nt = r->S_pad >> r->tile_log2;
+  if (out_tile_slots) *out_tile_slots = 1 << r->tile_log2;
+  if (rebuild) {
+    rr::SelectArgs a;
+    memset(&a, 0, sizeof(a));
+    a.w = r->w;
+    a.l2 = r->l2;
+    a.l2min = r->l2min;
+    a.S_pad = r->S_pad;
+    a.tile_log2 = r->tile_log2;
+    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
+  }
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  const int n = std::min(cap, nt);
+  if (out_sums && n > 0) RR_CUDA(cudaMemcpy(out_sums, r->l2, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+  if (out_mins && n > 0) RR_CUDA(cudaMemcpy(out_mins, r->l2min, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  return nt;
 }
 
 // -------------------------------------------------------------- actor math

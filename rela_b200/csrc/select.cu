@@ -48,9 +48,62 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // ------------------------------------------------------------------ K3 build
-// One CTA of 256 threads per 2048 slots: each thread owns 8 consecutive slots
-// (two 16-byte loads), a warp covers 256 slots. Tiles are 256 << k slots, i.e.
-// 1 << k consecutive warps.
+// Sum (fp64) and smallest non-zero magnitude of 256 consecutive slots held as
+// 8 values per lane. Every producer of a tile entry -- the full build and the
+// incremental retile paths of commit / update / eviction -- goes through this
+// one association, so that a retiled entry is bit-identical to a rebuilt one.
+__device__ __forceinline__ void reduce256(const float4 a, const float4 b, double& s, float& mn) {
+  s = (((double)a.x + (double)a.y) + ((double)a.z + (double)a.w)) +
+      (((double)b.x + (double)b.y) + ((double)b.z + (double)b.w));
+  mn = FLT_MAX;
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (v[k] != 0.0f) mn = fminf(mn, fabsf(v[k]));
+  s = warp_sum(s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+}
+
+// One warp recomputes tile t from the weights in global memory.
+__device__ __forceinline__ void retile_warp(const float* w, double* l2, float* l2min, int t, int tile_log2,
+                                            int lane) {
+  const int nb = 1 << (tile_log2 - 8);
+  double tot = 0.0;
+  float m = FLT_MAX;
+  for (int k = 0; k < nb; ++k) {
+    const float4* src = reinterpret_cast<const float4*>(w + ((size_t)t << tile_log2) + (size_t)k * 256) + lane * 2;
+    const float4 a = src[0], b = src[1];
+    double s;
+    float mn;
+    reduce256(a, b, s, mn);
+    tot += s;
+    m = fminf(m, mn);
+  }
+  if (lane == 0) {
+    l2[t] = tot;
+    l2min[t] = m;
+  }
+}
+
+// The tiles overlapping ring range [start, start + n) (mod S), one warp per
+// tile. The caller has made the new weights of the range visible to the CTA.
+__device__ __forceinline__ void retile_range(const float* w, double* l2, float* l2min, int S, int start, int n,
+                                             int tile_log2, int warp, int nwarps, int lane) {
+  const int n1 = min(n, S - start);
+  for (int seg = 0; seg < 2; ++seg) {
+    const int lo = seg == 0 ? start : 0;
+    const int len = seg == 0 ? n1 : n - n1;
+    if (len <= 0) continue;
+    const int t1 = (lo + len - 1) >> tile_log2;
+    for (int t = (lo >> tile_log2) + warp; t <= t1; t += nwarps) retile_warp(w, l2, l2min, t, tile_log2, lane);
+  }
+}
+
+// Full build: one CTA of 256 threads per 2048 slots, a warp per 256 slots;
+// tiles are 256 << k slots, i.e. 1 << k consecutive warps. Runs once at
+// creation (and on demand for the debug cross-check): afterwards the tile
+// entries are maintained by the kernels that change a weight.
 __global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __restrict__ w,
                                                               double* __restrict__ l2,
                                                               float* __restrict__ l2min, int tile_log2) {
@@ -60,16 +113,9 @@ __global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __res
   pdl_wait();
   const float4* src = reinterpret_cast<const float4*>(w) + (size_t)blockIdx.x * (kBuildSpan / 4) + tid * 2;
   const float4 a = src[0], b = src[1];
-  double s = (((double)a.x + (double)a.y) + ((double)a.z + (double)a.w)) +
-             (((double)b.x + (double)b.y) + ((double)b.z + (double)b.w));
-  float mn = FLT_MAX;
-  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-#pragma unroll
-  for (int k = 0; k < 8; ++k)
-    if (v[k] != 0.0f) mn = fminf(mn, fabsf(v[k]));
-  s = warp_sum(s);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  double s;
+  float mn;
+  reduce256(a, b, s, mn);
   __shared__ double ws[8];
   __shared__ float wm[8];
   if (lane == 0) {
@@ -561,6 +607,8 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       a.evicted[slot] = 1;
       a.w[slot] = 0.0f;
     }
+    __syncthreads();
+    retile_range(a.w, a.l2, a.l2min, a.S, a.head, a.pop_n, a.tile_log2, warp, kWarps, lane);
   }
 
   // importance weights (lines 320-322); wsel was written by other SMs: read through L2
@@ -603,7 +651,8 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
 // ------------------------------------------------------------- add commit
 // weights_[j] = priority^alpha for the block's slots, float block sum in index
 // order, sum_ += (double) blockSum (rela/prioritized_replay.h:58-73,188).
-__global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, int S, int start, int n,
+__global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, double* l2, float* l2min,
+                                                      int tile_log2, int S, int start, int n,
                                                       const float* __restrict__ prio, float alpha,
                                                       int is_weight) {
   __shared__ float buf[1024];
@@ -630,6 +679,8 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, int S,
     __syncthreads();
   }
   if (tid == 0) ctl->sum += (double)sh_sum;
+  // the block's weights are visible to the CTA (barrier above): refresh its tiles
+  retile_range(w, l2, l2min, S, start, n, tile_log2, tid >> 5, 32, tid & 31);
 }
 
 // ------------------------------------------------------ K7 priority update
@@ -640,10 +691,16 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, int S,
 // repeats are always adjacent: occurrence i reads new[i-1], the last one writes.
 // The double accumulation of the float differences is done in parallel when
 // it is provably exact (sum |d| < 2^52 * ulp(min |d|)), else in order.
+//
+// CTA 0 does that bookkeeping. CTAs 1.. keep the tile entries current, one
+// warp per batch element: the warp of the first element of a run that falls
+// into one tile reloads the tile, substitutes the final value of every batch
+// slot in it (computed from the same inputs as CTA 0, so the result does not
+// depend on whether CTA 0's store has landed) and reduces it again.
 __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
                                                       const int32_t* __restrict__ ids, int n,
                                                       const float* __restrict__ prio, float alpha,
-                                                      int is_weight) {
+                                                      int is_weight, double* l2, float* l2min, int tile_log2) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
@@ -655,6 +712,53 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   const int lane = tid & 31, warp = tid >> 5;
   pdl_launch_dependents();
   pdl_wait();
+  if (blockIdx.x > 0) {
+    __shared__ __align__(16) float sub[32][256];
+    for (int i = tid; i < n; i += blockDim.x) {
+      const int id = ids[i];
+      const float p = prio[i];
+      const bool ev = evicted[id] != 0;
+      s_new[i] = is_weight ? p : pow_alpha(p, alpha);
+      s_id[i] = ev ? -1 : id;
+    }
+    __syncthreads();
+    const int i = (blockIdx.x - 1) * 32 + warp;
+    if (i >= n) return;
+    const int id = s_id[i];
+    if (id < 0) return;  // an evicted slot keeps weight 0: its tile does not change
+    const int t = id >> tile_log2;
+    if (i > 0 && s_id[i - 1] >= 0 && (s_id[i - 1] >> tile_log2) == t) return;  // covered by that element's warp
+    const int nb = 1 << (tile_log2 - 8);
+    float* mine = sub[warp];
+    double tot = 0.0;
+    float m = FLT_MAX;
+    for (int k = 0; k < nb; ++k) {
+      const int base = (t << tile_log2) + k * 256;
+      const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
+      reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
+      reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
+      __syncwarp();
+      for (int j = lane; j < n; j += 32) {
+        const int sid = s_id[j];
+        const bool last = !(j + 1 < n && s_id[j + 1] == sid);
+        if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
+      }
+      __syncwarp();
+      const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
+      const float4 b = reinterpret_cast<const float4*>(mine)[lane * 2 + 1];
+      __syncwarp();
+      double s;
+      float mn;
+      reduce256(a, b, s, mn);
+      tot += s;
+      m = fminf(m, mn);
+    }
+    if (lane == 0) {
+      l2[t] = tot;
+      l2min[t] = m;
+    }
+    return;
+  }
   float* s_old = s_diff;  // old weight, replaced by the difference below
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = ids[i];
@@ -742,18 +846,21 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
   return launch_pdl(select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
 }
 
-cudaError_t launch_commit(Ctl* ctl, float* w, int S, int start, int n, const float* prio, float alpha,
-                          int is_weight, cudaStream_t stream) {
-  commit_kernel<<<1, 1024, 0, stream>>>(ctl, w, S, start, n, prio, alpha, is_weight);
+cudaError_t launch_commit(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, int S, int start, int n,
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
+  commit_kernel<<<1, 1024, 0, stream>>>(ctl, w, l2, l2min, tile_log2, S, start, n, prio, alpha, is_weight);
   return cudaGetLastError();
 }
 
-cudaError_t launch_update(Ctl* ctl, float* w, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
+cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
+                          const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
+                          cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel, smem);
   if (e != cudaSuccess) return e;
-  return launch_pdl(update_kernel, dim3(1), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio, alpha, is_weight);
+  const int grid = 1 + (n + 31) / 32;  // CTA 0: sum_ and weights; the others: one warp per element's tile
+  return launch_pdl(update_kernel, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio, alpha,
+                    is_weight, l2, l2min, tile_log2);
 }
 
 }  // namespace rr

@@ -419,7 +419,7 @@ class CudaReplay(_Base):
     the GPU and copied back for comparison."""
 
     def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0, is_weight=True,
-                 device_rows=False, device=0):
+                 device_rows=False, device=0, own_stream=False):
         import torch
         from rela_b200 import capi
 
@@ -440,6 +440,15 @@ class CudaReplay(_Base):
             arr[i].row_bytes = f.row_bytes
             arr[i].chunks = f.chunks
         capi.check(self.lib.rr_set_schema(h, len(schema), arr))
+        self.own = None
+        if own_stream:  # the caller works on the replay's internal stream: no event hand-shake
+            self.own = C.c_void_p()
+            capi.check(self.lib.rr_get_stream(h, C.byref(self.own)))
+
+    def _stream(self):
+        if self.own is not None:
+            return self.own
+        return C.c_void_p(self.torch.cuda.current_stream(self.dev).cuda_stream)
 
     def close(self):
         if getattr(self, "h", None):
@@ -461,7 +470,9 @@ class CudaReplay(_Base):
             keep = [t.from_numpy(np.ascontiguousarray(r).view(np.uint8).reshape(-1)).to(self.dev) for r in rows]
             ptrs = (C.c_void_p * max(1, len(keep)))(*[k.data_ptr() for k in keep])
             flags |= self.capi.RR_ROWS_DEVICE
-            stream = C.c_void_p(t.cuda.current_stream(self.dev).cuda_stream)
+            stream = self._stream()
+            if self.own is not None:
+                t.cuda.current_stream(self.dev).synchronize()  # the uploads above ran on torch's stream
         else:
             ptrs = _ptr_array(rows)
         self.capi.check(self.lib.rr_add(self.h, len(p), ptrs, None, p.ctypes.data, flags, stream))
@@ -482,10 +493,11 @@ class CudaReplay(_Base):
         outs = [t.empty(max(1, f.row_bytes * B), dtype=t.uint8, device=self.dev) for f in self.schema]
         w = t.empty(B, dtype=t.float32, device=self.dev)
         ptrs = (C.c_void_p * max(1, len(outs)))(*[o.data_ptr() for o in outs])
-        stream = C.c_void_p(t.cuda.current_stream(self.dev).cuda_stream)
-        rc = self.lib.rr_sample(self.h, B, ptrs, w.data_ptr(), stream)
+        rc = self.lib.rr_sample(self.h, B, ptrs, w.data_ptr(), self._stream())
         if rc != 0:
             return rc, None, None, None
+        if self.own is not None:
+            self.capi.check(self.lib.rr_sync(self.h))
         ids = np.zeros(B, dtype=np.int32)
         self.capi.check(self.lib.rr_last_sample_ids(self.h, B, ids.ctypes.data))
         rows = None
@@ -521,6 +533,17 @@ class CudaReplay(_Base):
         e = np.zeros(self.S, dtype=np.uint8)
         self.capi.check(self.lib.rr_debug_weights(self.h, w.ctypes.data, e.ctypes.data))
         return w, e
+
+    def tiles(self, rebuild=False):
+        """(sums, mins, slots per tile) of the selection hierarchy; rebuild recomputes it from the weights."""
+        n = self.lib.rr_debug_tiles(self.h, 0, None, None, 0, None)
+        assert n > 0
+        s = np.zeros(n, dtype=np.float64)
+        m = np.zeros(n, dtype=np.float32)
+        ts = C.c_int()
+        rc = self.lib.rr_debug_tiles(self.h, int(rebuild), s.ctypes.data, m.ctypes.data, n, C.addressof(ts))
+        assert rc == n
+        return s, m, ts.value
 
     def stats(self):
         st = self.capi.RRStats()

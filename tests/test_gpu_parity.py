@@ -25,7 +25,23 @@ def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, **cuda_kw):
     np.testing.assert_array_equal(wa[live], wb[live])
     np.testing.assert_array_equal(ea[live], eb[live])
     assert (wb[~live] == 0).all(), "dead slots must hold weight 0"
+    check_tiles(cu, wb)
     return cu
+
+
+def check_tiles(cu, w):
+    """The incrementally maintained tile entries equal a rebuild from the weights, bit for bit,
+    and (mins always, sums when exactly representable) a host recomputation."""
+    s_inc, m_inc, ts = cu.tiles()
+    s_full, m_full, _ = cu.tiles(rebuild=True)
+    np.testing.assert_array_equal(s_inc.view(np.uint64), s_full.view(np.uint64))
+    np.testing.assert_array_equal(m_inc.view(np.uint32), m_full.view(np.uint32))
+    wp = np.zeros(len(s_inc) * ts, dtype=np.float32)
+    wp[: len(w)] = w
+    wt = wp.reshape(len(s_inc), ts)
+    nz = np.where(wt != 0, np.abs(wt), np.float32(np.finfo(np.float32).max))
+    np.testing.assert_array_equal(nz.min(axis=1), m_inc)
+    np.testing.assert_allclose(wt.astype(np.float64).sum(axis=1), s_inc, rtol=1e-12, atol=0)
 
 
 @pytest.mark.parametrize("cap,K,B,alpha,beta,prefetch", [
@@ -121,3 +137,68 @@ def test_batch_not_multiple_of_cta_targets():
     for B in (1, 31, 33, 700):
         ops = gen_trace(schema, 2000, 41 + B, 10, 40, B)
         _run_pair(schema, 2000, 5, 0.6, 0.4, 0, ops)
+
+
+@pytest.mark.parametrize("cap,K,B", [(1, 1, 3), (2, 1, 4), (5, 1, 7), (3, 3, 1)])
+def test_tiny_capacities(cap, K, B):
+    """S = int(1.25 * capacity) is 1, 2, 6, 3 slots: every add wraps, every sample evicts or repeats ids."""
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    ops = gen_trace(schema, cap, 50 + cap, 30, K, B, prefill=min(cap, K), adds_per_cycle=(0, 2))
+    _run_pair(schema, cap, 3, 0.6, 0.4, 0, ops)
+
+
+def test_empty_and_oversized_adds_and_protocol_errors():
+    import ctypes as C
+
+    from rela_b200 import capi
+
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    cu = CudaReplay(schema, 8, 1, 0.6, 0.4, 0)
+    L = cu.lib
+    rng = np.random.default_rng(0)
+    from harness import make_rows
+
+    # sampling an empty buffer: the reference asserts (prioritized_replay.h:297-302)
+    rc, _, _, _ = cu.sample(4)
+    assert rc == capi.RR_ERR_EMPTY
+    # add of zero rows is a no-op
+    cu.add(make_rows(schema, 0, rng), np.zeros(0, np.float32))
+    assert cu.size() == 0 and cu.num_add() == 0
+    # a block larger than the ring can never be appended (the reference would block forever)
+    rows = make_rows(schema, 11, rng)
+    with pytest.raises(capi.ReplayError):
+        cu.add(rows, np.ones(11, np.float32))
+    cu.add(make_rows(schema, 6, rng), np.ones(6, np.float32))
+    rc, _, _, _ = cu.sample(4)
+    assert rc == 0
+    # second sample before update_priority (lines 203-206)
+    rc, _, _, _ = cu.sample(4)
+    assert rc == capi.RR_ERR_STATE and b"not been updated" in L.rr_last_error()
+    # wrong number of priorities (line 237)
+    assert cu.update(np.ones(3, np.float32)) == capi.RR_ERR_ARG
+    assert cu.update(np.ones(4, np.float32)) == 0
+    # update without an outstanding batch
+    assert cu.update(np.ones(4, np.float32)) == capi.RR_ERR_STATE
+    # batch above the documented bound
+    outs = (C.c_void_p * len(schema))()
+    assert L.rr_sample(cu.h, 1 << 20, outs, C.c_void_p(1), None) == capi.RR_ERR_ARG
+    assert cu.sync() == 0
+
+
+def test_reference_test_schema_empty_dicts():
+    """rela/tests/test_prioritized_replay.cc: obs / action / next_obs are EMPTY dicts and
+    reward, terminal, bootstrap are int32 -- the schema is whatever the first add brings."""
+    from harness import Field
+
+    schema = [Field("reward", "int32", ()), Field("terminal", "int32", ()), Field("bootstrap", "int32", ())]
+    ops = gen_trace(schema, 32, 5, 20, 8, 40)
+    _run_pair(schema, 32, 42, 1.0, 1.0, 0, ops)
+
+
+@pytest.mark.parametrize("device_rows", [False, True])
+def test_caller_on_replay_stream(device_rows):
+    """rr_get_stream: a caller that passes the replay's own stream gets plain stream order
+    (no event hand-shakes; the sample / update kernels chain by PDL) and the same results."""
+    schema = ff_schema(frame=(1, 12, 12), n_actions=4)
+    ops = gen_trace(schema, 700, 31, 120, 40, 96)
+    _run_pair(schema, 700, 5, 0.6, 0.4, 0, ops, own_stream=True, device_rows=device_rows)
