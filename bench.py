@@ -466,9 +466,14 @@ def run_ours(args):
     # ---- e2e: public API, priorities from pinned host memory, weights read back
     dev_str = "cuda:%d" % local_rank
 
+    w_pinned = [torch.empty(B, dtype=torch.float32).pin_memory() for _ in range(2)]
+
     def cycle_e2e(k):
         batch, w = replay.sample(B, dev_str)
-        w_host = w.cpu()  # D2H read of the step's result (also the learner's sync point)
+        # D2H read of the step's result into pinned memory (also the learner's sync point)
+        w_host = w_pinned[k & 1]
+        w_host.copy_(w, non_blocking=True)
+        stream.synchronize()
         replay.update_priority(prio_host[k % 16])
         return w_host
 
@@ -513,7 +518,7 @@ def run_ours(args):
         "config": workload_config(args, "1 GPU" if world == 1 else "%d independent capacity shards" % world),
         "e2e": {"value": e2e, "unit": "transitions/s", "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B,
                 "ms_per_step": ms_e2e / K,
-                "api": "rela_b200.rela.FFPrioritizedReplay (C++ host layer, rela/pybind.cc names): sample(B,'cuda:0') + weights.cpu() + update_priority(pinned cpu tensor)"},
+                "api": "rela_b200.rela.FFPrioritizedReplay (C++ host layer, rela/pybind.cc names): sample(B,'cuda:0') + weights -> pinned host copy + stream sync + update_priority(pinned cpu tensor)"},
         "gpu_launches": int(launches),
         "value_foreign_stream": {"value": world * B * max(1, K // 4) / (ms_foreign * 1e-3), "unit": "transitions/s",
                                  "ms_per_step": ms_foreign / max(1, K // 4),

@@ -87,6 +87,7 @@ constexpr int kMinTileLog2 = 8;
 constexpr int kMaxTileLog2 = 11;
 constexpr int kMaxTiles = 16384;   // tile prefixes held in shared memory (128 KB)
 constexpr int kSelTargets = 32;    // targets per CTA of select_kernel
+constexpr int kInlinePrio = 1024;    // largest update whose priorities travel as kernel parameters
 constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
 
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
@@ -137,6 +138,10 @@ cudaError_t launch_commit(Ctl* ctl, float* w, double* l2, float* l2min, int tile
 cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
                           const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
                           cudaStream_t stream);
+// same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
+cudaError_t launch_update_inline(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2,
+                                 const uint8_t* evicted, const int32_t* ids, int n, const float* prio_host,
+                                 float alpha, int is_weight, cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -129,6 +129,7 @@ struct rr_replay {
   int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
+  int inline_prio = rr::kInlinePrio;  // $RR_INLINE_PRIO: largest host-memory update carried in the launch
   bool full_build = false;  // $RR_FULL_BUILD: rebuild every tile entry before each selection
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
@@ -355,6 +356,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   }
   r->full_build = env_int("RR_FULL_BUILD", 0) != 0;
+  r->inline_prio = std::min(rr::kInlinePrio, env_int("RR_INLINE_PRIO", rr::kInlinePrio));
   RR_CUDA(cudaStreamSynchronize(r->main));
 
   const int nl = std::max(1, env_int("RR_ADD_LANES", 4));
@@ -1115,6 +1117,11 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
       RR_CUDA(cudaEventRecord(r->evIn, cs));
       RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
     }
+  } else if (n <= r->inline_prio) {
+    // a learner-sized batch: the priorities travel in the launch parameters
+    RR_CUDA(rr::launch_update_inline(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n,
+                                     priority, r->alpha, is_weight, r->main));
+    dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
     r->pstage_next = (r->pstage_next + 1) % (int)r->pstage.size();
@@ -1134,8 +1141,9 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     RR_CUDA(cudaEventRecord(st.done, r->main));
     dprio = st.dev;
   }
-  RR_CUDA(rr::launch_update(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n, dprio,
-                            r->alpha, is_weight, r->main));
+  if (dprio != nullptr)
+    RR_CUDA(rr::launch_update(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n, dprio,
+                              r->alpha, is_weight, r->main));
   r->launches++;
   if (prio_dev && cs != r->main) {
     RR_CUDA(cudaEventRecord(r->evOut, r->main));

@@ -21,6 +21,7 @@
 // the slot), so physical prefixes need no live-range mask.
 #include <algorithm>
 #include <cfloat>
+#include <cstring>
 #include <cmath>
 
 #include "../../include/rela_b200.h"
@@ -697,9 +698,21 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, double
 // into one tile reloads the tile, substitutes the final value of every batch
 // slot in it (computed from the same inputs as CTA 0, so the result does not
 // depend on whether CTA 0's store has landed) and reduces it again.
+//
+// The new priorities come from device memory or, for a learner-sized batch
+// handed over in host memory, ride in the launch packet itself (PrioInline, a
+// __grid_constant__ parameter read through the constant bank): no staging
+// copy sits between updatePriority and the next sample on the stream.
+struct PrioInline {
+  float v[kInlinePrio];
+};
+__device__ __forceinline__ float prio_at(const float* p, int i) { return p[i]; }
+__device__ __forceinline__ float prio_at(const PrioInline& p, int i) { return p.v[i]; }
+
+template <typename Prio>
 __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
                                                       const int32_t* __restrict__ ids, int n,
-                                                      const float* __restrict__ prio, float alpha,
+                                                      const __grid_constant__ Prio prio, float alpha,
                                                       int is_weight, double* l2, float* l2min, int tile_log2) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
@@ -716,7 +729,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
     __shared__ __align__(16) float sub[32][256];
     for (int i = tid; i < n; i += blockDim.x) {
       const int id = ids[i];
-      const float p = prio[i];
+      const float p = prio_at(prio, i);
       const bool ev = evicted[id] != 0;
       s_new[i] = is_weight ? p : pow_alpha(p, alpha);
       s_id[i] = ev ? -1 : id;
@@ -762,7 +775,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   float* s_old = s_diff;  // old weight, replaced by the difference below
   for (int i = tid; i < n; i += blockDim.x) {
     const int id = ids[i];
-    const float p = prio[i];
+    const float p = prio_at(prio, i);
     const bool ev = evicted[id] != 0;  // both dependent loads are issued together
     const float old = w[id];
     s_new[i] = is_weight ? p : pow_alpha(p, alpha);
@@ -856,11 +869,25 @@ cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile
                           const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
                           cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
-  cudaError_t e = ensure_dynamic_smem(update_kernel, smem);
+  cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
   const int grid = 1 + (n + 31) / 32;  // CTA 0: sum_ and weights; the others: one warp per element's tile
-  return launch_pdl(update_kernel, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio, alpha,
-                    is_weight, l2, l2min, tile_log2);
+  return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio,
+                    alpha, is_weight, l2, l2min, tile_log2);
+}
+
+cudaError_t launch_update_inline(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
+                                 const int32_t* ids, int n, const float* prio_host, float alpha, int is_weight,
+                                 cudaStream_t stream) {
+  if (n > kInlinePrio) return cudaErrorInvalidValue;
+  PrioInline pin;
+  memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
+  const size_t smem = (size_t)n * 12;
+  cudaError_t e = ensure_dynamic_smem(update_kernel<PrioInline>, smem);
+  if (e != cudaSuccess) return e;
+  const int grid = 1 + (n + 31) / 32;
+  return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, pin,
+                    alpha, is_weight, l2, l2min, tile_log2);
 }
 
 }  // namespace rr
