@@ -210,6 +210,18 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields,
                     int reps, double* ms_per_launch, uint64_t* launches,
                     uint64_t* bytes_per_launch);
 
+/* Checkpoint / restore (not in the reference). rr_save
+ * writes the ring counters, the mt19937 state, sum_, the weights, the eviction
+ * flags and the live rows of this replay's slot range to `path` (blocking;
+ * device -> pinned bounce buffer -> file). It needs a quiescent replay: no add
+ * in flight, no sampled batch awaiting its priorities, no prefetched batch.
+ * rr_load restores into a freshly created replay with the same capacity,
+ * alpha, beta, shard and schema; sampling then continues bit-identically to
+ * the run that saved (same ids, same bytes, same weights). A sharded replay
+ * saves / loads one file per rank. */
+int rr_save(rr_replay* r, const char* path);
+int rr_load(rr_replay* r, const char* path);
+
 /* Test/debug introspection (synchronises). ids: the physical slot ids of the
  * batch last returned by rr_sample (the reference's sampledIds_). */
 int rr_last_sample_ids(rr_replay* r, int n, int32_t* out_ids_host);

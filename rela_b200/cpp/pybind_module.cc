@@ -42,6 +42,10 @@ void bindCommon(PyClass& c) {
       .def("sample", &Replay::sample, py::call_guard<py::gil_scoped_release>())
       .def("update_priority", &Replay::updatePriority, py::call_guard<py::gil_scoped_release>())
       .def("sync", [](Replay& r) { r.core().sync(); }, py::call_guard<py::gil_scoped_release>())
+      .def("save", [](Replay& r, const std::string& path) { r.core().save(path); },
+           py::call_guard<py::gil_scoped_release>())
+      .def("load", [](Replay& r, const std::string& path) { r.core().load(path); },
+           py::call_guard<py::gil_scoped_release>())
       .def("handle", [](Replay& r) { return (uintptr_t)r.core().handle(); })
       .def("device", [](Replay& r) { return r.core().device(); })
       .def("schema", [](Replay& r) { return schemaOf(r); });

@@ -70,6 +70,15 @@ class PrioritizedReplay {
     return core_.numAdd();
   }
 
+  // Checkpoint / restore (not in the reference): see ReplayCore::save.
+  void save(const std::string& path) {
+    core_.save(path);
+  }
+
+  void load(const std::string& path) {
+    core_.load(path);
+  }
+
   ReplayCore& core() {
     return core_;
   }

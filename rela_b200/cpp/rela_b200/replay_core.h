@@ -77,6 +77,11 @@ class ReplayCore {
   void* stream() const;
 
   void sync();  // waits for the device; throws on a sticky device-side error
+  // Checkpoint / restore (rr_save / rr_load): a restored replay continues
+  // bit-identically. save() also writes <path>.schema (leaf names, dtypes,
+  // shapes); load() takes the schema from it and needs a freshly created replay.
+  void save(const std::string& path);
+  void load(const std::string& path);
   rr_replay* handle() const { return h_; }
   int device() const { return device_; }
   const std::vector<LeafSpec>& schema() const { return schema_; }

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <fstream>
 #include <stdexcept>
 
 #include <c10/cuda/CUDAFunctions.h>
@@ -75,6 +76,45 @@ ReplayCore::~ReplayCore() {
 int ReplayCore::size() const { return rr_size(h_); }
 int ReplayCore::numAdd() const { return rr_num_add(h_); }
 void ReplayCore::sync() { check(rr_sync(h_), "sync"); }
+// The C ABI checkpoint holds bytes; dtypes and shapes of the leaves are the host
+// layer's business and go into a text sidecar (<path>.schema), one leaf per
+// line: name dtype chunks time_major row_bytes ndim dims...
+void ReplayCore::save(const std::string& path) {
+  if (!schema_set_) throw std::runtime_error("save: nothing has been added yet");
+  check(rr_save(h_, path.c_str()), "save");
+  std::ofstream f(path + ".schema");
+  f << "rela_b200-schema 1 " << schema_.size() << "\n";
+  for (const LeafSpec& s : schema_) {
+    f << s.name << ' ' << (int)s.dtype << ' ' << s.chunks << ' ' << (s.time_major ? 1 : 0) << ' ' << s.row_bytes << ' '
+      << s.shape.size();
+    for (int64_t d : s.shape) f << ' ' << d;
+    f << "\n";
+  }
+  if (!f.good()) throw std::runtime_error("save: cannot write " + path + ".schema");
+}
+
+void ReplayCore::load(const std::string& path) {
+  std::ifstream f(path + ".schema");
+  std::string tag;
+  int version = 0;
+  size_t n = 0;
+  if (!(f >> tag >> version >> n) || tag != "rela_b200-schema" || version != 1 || n > 4096)
+    throw std::runtime_error("load: cannot read " + path + ".schema");
+  std::vector<LeafSpec> specs(n);
+  for (LeafSpec& s : specs) {
+    int dtype = 0, tm = 0;
+    size_t nd = 0;
+    if (!(f >> s.name >> dtype >> s.chunks >> tm >> s.row_bytes >> nd) || nd > 16)
+      throw std::runtime_error("load: corrupt " + path + ".schema");
+    s.dtype = (torch::ScalarType)dtype;
+    s.time_major = tm != 0;
+    s.shape.resize(nd);
+    for (int64_t& d : s.shape)
+      if (!(f >> d)) throw std::runtime_error("load: corrupt " + path + ".schema");
+  }
+  setSchema(specs);  // a replay that already has a schema must have the same one
+  check(rr_load(h_, path.c_str()), "load");
+}
 
 void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_major) {
   std::lock_guard<std::mutex> lk(schema_m_);
