@@ -463,6 +463,29 @@ def run_ours(args):
     capi.check(L.rr_gather_bench(h, R, flat, max(1, K // 16), C.byref(ms_pl), C.byref(n_l), C.byref(bpl)))
     gather_us = ms_pl.value * 1e3
 
+    # the same kernel on a batch 8x larger: how much of the gap to the HBM peak at
+    # batch 512 is the fixed per-launch latency (id load, first-byte latency, store drain)
+    big = None
+    if world == 1 and B <= 1024:
+        B2 = 8 * B
+        outs2 = [[torch.empty(lf.batch_shape(B2), dtype=lf.dtype, device=dev) for lf in schema] for _ in range(2)]
+        ptrs2 = [(C.c_void_p * len(o))(*[t.data_ptr() for t in o]) for o in outs2]
+        w2 = torch.empty(B2, dtype=torch.float32, device=dev)
+        prio2 = torch.rand(B2, device=dev, generator=g) + 0.01
+        torch.cuda.synchronize(dev)
+        capi.check(L.rr_set_profiling(h, 1, B2))
+        for k in range(4):
+            capi.check(L.rr_sample(h, B2, ptrs2[k % 2], C.c_void_p(w2.data_ptr()), own))
+            capi.check(L.rr_update_priority(h, B2, C.c_void_p(prio2.data_ptr()), capi.RR_PRIO_DEVICE, own))
+        capi.check(L.rr_set_profiling(h, 0, B2))
+        flat2 = (C.c_void_p * (2 * nf))(*[t.data_ptr() for o in outs2 for t in o])
+        ms2, n2, b2 = C.c_double(), C.c_uint64(), C.c_uint64()
+        barrier()
+        capi.check(L.rr_gather_bench(h, 2, flat2, max(1, K // 128), C.byref(ms2), C.byref(n2), C.byref(b2)))
+        big = {"batch": B2, "kernel_us": ms2.value * 1e3, "launches_timed": int(n2.value),
+               "bytes_per_launch": 2 * ROW_BYTES * B2}
+        del outs2, ptrs2, flat2
+
     # ---- e2e: public API, priorities from pinned host memory, weights read back
     dev_str = "cuda:%d" % local_rank
 
@@ -536,6 +559,10 @@ def run_ours(args):
                      "step_share": gather_us * 1e-3 / (ms / K)},
         "fill_s": fill_s, "slab_gb": st2["slab_bytes"] / 1e9,
     }
+    if big is not None:
+        big["achieved"] = big["bytes_per_launch"] / (big["kernel_us"] * 1e-6) / 1e9
+        big["frac"] = big["achieved"] / peak
+        line["roofline"]["large_batch"] = big
     if insert is not None:
         insert["frac_of_hbm_peak"] = insert["achieved_gbs"] / peak
         line["insert"] = insert

@@ -197,6 +197,10 @@ int rr_stream_fence(rr_replay* r, void* stream);
  * the event hand-shakes: consecutive sample / update kernels then chain by
  * programmatic dependent launch. */
 int rr_get_stream(rr_replay* r, void** out_stream);
+/* The reverse of rr_stream_fence: the internal stream waits for everything
+ * queued so far on `stream` (inputs produced there for a call that is then
+ * made in own-stream mode). Does not block the host. */
+int rr_stream_wait(rr_replay* r, void* stream);
 
 /* Gather-kernel timing for the roofline. While profiling is enabled every
  * rr_sample also keeps a copy of its sampled ids (ring of 16 sets).

@@ -1182,6 +1182,16 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   return RR_OK;
 }
 
+int rr_stream_wait(rr_replay* r, void* stream) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_wait: null");
+  DeviceScope dev_scope(r->device);
+  std::unique_lock<std::mutex> lk(r->m_);
+  if (static_cast<cudaStream_t>(stream) == r->main) return RR_OK;
+  RR_CUDA(cudaEventRecord(r->evIn, static_cast<cudaStream_t>(stream)));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  return RR_OK;
+}
+
 int rr_get_stream(rr_replay* r, void** out_stream) {
   if (r == nullptr || out_stream == nullptr) return fail(RR_ERR_ARG, "rr_get_stream: null");
   *out_stream = r->main;

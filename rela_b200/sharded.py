@@ -86,6 +86,13 @@ class CapiEngine:
         import os
 
         self.fused_completion = os.environ.get("RELA_B200_SHARD_ALLREDUCE", "0") != "1"
+        # The steady-state step (select, gather, flag wait, priority push, update) runs
+        # on the replay's own stream: plain stream order, no event hand-shake per call.
+        # Only the learner touches torch's stream: once after the batch is complete
+        # (rr_stream_fence) and once before its new priorities are pushed (rr_stream_wait).
+        self._own = C.c_void_p()
+        capi.check(self.L.rr_get_stream(h, C.byref(self._own)))
+        self.own_stream = self.fused_completion and os.environ.get("RELA_B200_SHARD_OWN_STREAM", "1") != "0"
 
     def close(self):
         if getattr(self, "h", None):
@@ -105,6 +112,9 @@ class CapiEngine:
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _step_stream(self):
+        return self._own if (self.own_stream and self.world > 1) else self._stream()
 
     def set_schema(self, leaves):
         self.schema = leaves
@@ -195,7 +205,9 @@ class CapiEngine:
             base = self._flags[learner]
             capi.check(self.L.rr_set_completion(self.h, C.c_void_p(base + 8 * self.rank),
                                                 C.c_void_p(base) if self.rank == learner else None, self.world))
-        capi.check(self.L.rr_sample(self.h, B, ptrs, wptr, self._stream()))
+        capi.check(self.L.rr_sample(self.h, B, ptrs, wptr, self._step_stream()))
+        if self.own_stream and self.world > 1 and self.rank == learner:
+            capi.check(self.L.rr_stream_fence(self.h, self._stream()))  # the batch, for torch's consumers
         if self.world > 1 and not fused:
             # completion: when this returns on the learner's stream, every shard's
             # gather kernel (ordered before its contribution) has finished its stores
@@ -243,17 +255,19 @@ class CapiEngine:
             others = [r for r in range(self.world) if r != learner]
             dst = (C.c_void_p * len(others))(*[self._inbox[r] + 256 for r in others])
             flg = (C.c_void_p * len(others))(*[self._inbox[r] for r in others])
+            if self.own_stream:
+                capi.check(self.L.rr_stream_wait(self.h, self._stream()))  # `weights` was produced on torch's stream
             capi.check(self.L.rr_peer_put(self.index, C.c_void_p(weights.data_ptr()), 4 * n, dst, flg, len(others),
-                                          self._put_epoch, self._stream()))
+                                          self._put_epoch, self._step_stream()))
             return weights.data_ptr()
         mine = self._inbox[self.rank]
         capi.check(self.L.rr_wait_flags(self.index, C.c_void_p(mine), 1, self._put_epoch,
-                                        C.c_void_p(self._err.data_ptr()), self._stream()))
+                                        C.c_void_p(self._err.data_ptr()), self._step_stream()))
         return mine + 256
 
     def update_ptr(self, ptr, n):
         flags = capi.RR_PRIO_DEVICE | capi.RR_PRIO_IS_WEIGHT
-        capi.check(self.L.rr_update_priority(self.h, n, C.c_void_p(ptr), flags, self._stream()))
+        capi.check(self.L.rr_update_priority(self.h, n, C.c_void_p(ptr), flags, self._step_stream()))
 
     def size(self):
         return self.L.rr_size(self.h)
