@@ -118,7 +118,9 @@ inline cudaError_t ensure_dynamic_smem(Kernel kernel, size_t bytes) {
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= 64) dev = 63;
-  if (bytes <= 48 * 1024 || bytes <= configured[dev].load(std::memory_order_acquire)) return cudaSuccess;
+  // No "fits the default 48 KB" shortcut: the default bound on the DYNAMIC part is
+  // 48 KB minus the kernel's static shared memory, so the first launch always opts in.
+  if (bytes <= configured[dev].load(std::memory_order_acquire)) return cudaSuccess;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e != cudaSuccess) return e;
   size_t cur = configured[dev].load();

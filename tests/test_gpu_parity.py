@@ -202,3 +202,14 @@ def test_caller_on_replay_stream(device_rows):
     schema = ff_schema(frame=(1, 12, 12), n_actions=4)
     ops = gen_trace(schema, 700, 31, 120, 40, 96)
     _run_pair(schema, 700, 5, 0.6, 0.4, 0, ops, own_stream=True, device_rows=device_rows)
+
+
+@pytest.mark.parametrize("B", [1500, 4096, 16384])
+def test_large_batches(B):
+    """Batches whose update needs more shared memory than the default per-kernel bound, up to kMaxBatch."""
+    from harness import Field
+
+    schema = [Field("action.a", "int64", ()), Field("reward", "float32", (3,))]
+    cap = 40000
+    ops = gen_trace(schema, cap, 13, 6, 5000, B, prefill=cap - 2000, adds_per_cycle=(1, 2))
+    _run_pair(schema, cap, 21, 0.6, 0.4, 0, ops)
