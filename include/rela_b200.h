@@ -235,9 +235,11 @@ int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host)
 /* The selection kernel's per-tile weight sums and smallest non-zero weights,
  * as maintained incrementally by add / update / eviction. rebuild != 0 first
  * recomputes every entry from the weights (tests compare the two bit for bit).
+ * level 0: the tiles the selection kernel scans; level 1: their 256-slot
+ * leaves (the same thing unless the buffer has more than 4 M slots).
  * Copies min(cap, tiles) entries; returns the number of tiles (< 0: error). */
-int rr_debug_tiles(rr_replay* r, int rebuild, double* out_sums_host, float* out_mins_host,
-                   int cap, int* out_tile_slots);
+int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums_host,
+                   float* out_mins_host, int cap, int* out_tile_slots);
 /* clock64 stamps at the phase boundaries of the last selection kernel (16 x u64). */
 int rr_debug_select_probe(rr_replay* r, uint64_t* out16);
 

@@ -65,7 +65,7 @@ def lib():
         L.rr_last_sample_ids.argtypes = [vp, i, vp]
         L.rr_debug_state.argtypes = [vp, vp, vp, vp, vp, vp]
         L.rr_debug_weights.argtypes = [vp, vp, vp]
-        L.rr_debug_tiles.argtypes = [vp, i, vp, vp, i, vp]
+        L.rr_debug_tiles.argtypes = [vp, i, i, vp, vp, i, vp]
         L.rr_debug_select_probe.argtypes = [vp, vp]
         L.rr_stream_fence.argtypes = [vp, vp]
         L.rr_get_stream.argtypes = [vp, vp]

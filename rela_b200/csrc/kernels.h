@@ -106,12 +106,27 @@ struct Ctl {
   unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel (CTA 0)
 };
 
+// The selection hierarchy over the weights. A tile is 256 << k slots (k =
+// tile_log2 - 8) so that at most kMaxTiles tile sums have to fit the selection
+// kernel's shared memory; for k > 0 the tile is made of 1 << k LEAVES of 256
+// slots whose sums / minima are kept too (in global memory), so that finding a
+// slot and refreshing an entry never touch more than 256 weights.
+struct Tiles {
+  double* l2;      // [S_pad >> tile_log2] tile sums
+  float* l2min;    // [S_pad >> tile_log2] min non-zero weight per tile
+  double* leaf;    // [S_pad >> 8] leaf sums; nullptr when tile_log2 == 8 (the tiles are the leaves)
+  float* leafmin;  // [S_pad >> 8]
+  int tile_log2;
+};
+
 struct SelectArgs {
   Ctl* ctl;
   float* w;             // [S_pad] priority^alpha per slot; dead slots hold 0
   uint8_t* evicted;     // [S]
   double* l2;           // [S_pad >> tile_log2] tile sums
   float* l2min;         // [S_pad >> tile_log2] min non-zero weight per tile
+  double* leaf;         // see Tiles
+  float* leafmin;
   float* wsel;          // [>= B] scratch: weight of each selected slot
   int S, S_pad;
   int tile_log2;
@@ -131,17 +146,15 @@ cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream);
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
 
 // add commit (K2 + weights write + sum_, prioritized_replay.h:58-73,188)
-cudaError_t launch_commit(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, int S, int start, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
+cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int start, int n, const float* prio,
+                          float alpha, int is_weight, cudaStream_t stream);
 
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
-cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
-                          const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
-                          cudaStream_t stream);
+cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
-cudaError_t launch_update_inline(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2,
-                                 const uint8_t* evicted, const int32_t* ids, int n, const float* prio_host,
-                                 float alpha, int is_weight, cudaStream_t stream);
+cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
+                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -145,6 +145,8 @@ struct rr_replay {
   uint8_t* evicted = nullptr;
   double* l2 = nullptr;
   float* l2min = nullptr;
+  double* leaf = nullptr;  // leaf (256-slot) sums / minima, only when tile_log2 > 8 (rr::Tiles)
+  float* leafmin = nullptr;
   rr::Ctl* ctl = nullptr;
 
   // ring counters (rela/prioritized_replay.h:156-164)
@@ -191,6 +193,16 @@ struct rr_replay {
 };
 
 namespace {
+
+rr::Tiles tiles_of(const rr_replay* r) {
+  rr::Tiles t;
+  t.l2 = r->l2;
+  t.l2min = r->l2min;
+  t.leaf = r->leaf;
+  t.leafmin = r->leafmin;
+  t.tile_log2 = r->tile_log2;
+  return t;
+}
 
 using rr::CopyField;
 using rr::CopyLaunch;
@@ -336,6 +348,10 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
   RR_CUDA(cudaMalloc(&r->l2, sizeof(double) * nt2));
   RR_CUDA(cudaMalloc(&r->l2min, sizeof(float) * nt2));
+  if (r->tile_log2 > 8) {
+    RR_CUDA(cudaMalloc(&r->leaf, sizeof(double) * ((size_t)r->S_pad >> 8)));
+    RR_CUDA(cudaMalloc(&r->leafmin, sizeof(float) * ((size_t)r->S_pad >> 8)));
+  }
   RR_CUDA(cudaMalloc(&r->ctl, sizeof(rr::Ctl)));
   RR_CUDA(cudaMemsetAsync(r->w, 0, sizeof(float) * (size_t)r->S_pad, r->main));
   RR_CUDA(cudaMemsetAsync(r->evicted, 0, (size_t)r->S_pad, r->main));
@@ -350,6 +366,8 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     a.w = r->w;
     a.l2 = r->l2;
     a.l2min = r->l2min;
+    a.leaf = r->leaf;
+    a.leafmin = r->leafmin;
     a.S_pad = r->S_pad;
     a.tile_log2 = r->tile_log2;
     RR_CUDA(cudaMemsetAsync(r->l2, 0, sizeof(double) * nt2, r->main));
@@ -389,6 +407,8 @@ int rr_destroy(rr_replay* r) {
   cudaFree(r->wsel);
   cudaFree(r->l2);
   cudaFree(r->l2min);
+  cudaFree(r->leaf);
+  cudaFree(r->leafmin);
   cudaFree(r->ctl);
   for (auto& l : r->lanes) {
     if (l.pinned) cudaFreeHost(l.pinned);
@@ -781,7 +801,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     if (rc == RR_OK) {
       cudaError_t e = cudaStreamWaitEvent(r->main, L.copied, 0);
       if (e == cudaSuccess) {
-        e = rr::launch_commit(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->S, start, n,
+        e = rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n,
                               prio_dev ? priority : L.dprio, r->alpha, is_weight, r->main);
         r->launches++;
       }
@@ -865,6 +885,8 @@ int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
   a.evicted = r->evicted;
   a.l2 = r->l2;
   a.l2min = r->l2min;
+  a.leaf = r->leaf;
+  a.leafmin = r->leafmin;
   a.S = r->S;
   a.S_pad = r->S_pad;
   a.tile_log2 = r->tile_log2;
@@ -1120,7 +1142,7 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     }
   } else if (n <= r->inline_prio) {
     // a learner-sized batch: the priorities travel in the launch parameters
-    RR_CUDA(rr::launch_update_inline(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n,
+    RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n,
                                      priority, r->alpha, is_weight, r->main));
     dprio = nullptr;
   } else {
@@ -1143,7 +1165,7 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     dprio = st.dev;
   }
   if (dprio != nullptr)
-    RR_CUDA(rr::launch_update(r->ctl, r->w, r->l2, r->l2min, r->tile_log2, r->evicted, r->idbuf[r->cur_ids], n, dprio,
+    RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio,
                               r->alpha, is_weight, r->main));
   r->launches++;
   if (prio_dev && cs != r->main) {
@@ -1332,25 +1354,31 @@ int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {
   return RR_OK;
 }
 
-int rr_debug_tiles(rr_replay* r, int rebuild, double* out_sums, float* out_mins, int cap, int* out_tile_slots) {
+int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums, float* out_mins, int cap,
+                   int* out_tile_slots) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_tiles: null");
   DeviceScope dev_scope(r->device);
-  const int nt = r->S_pad >> r->tile_log2;
-  if (out_tile_slots) *out_tile_slots = 1 << r->tile_log2;
+  const bool leaves = level != 0 && r->leaf != nullptr;
+  const int nt = r->S_pad >> (leaves ? 8 : r->tile_log2);
+  if (out_tile_slots) *out_tile_slots = leaves ? 256 : 1 << r->tile_log2;
   if (rebuild) {
     rr::SelectArgs a;
     memset(&a, 0, sizeof(a));
     a.w = r->w;
     a.l2 = r->l2;
     a.l2min = r->l2min;
+    a.leaf = r->leaf;
+    a.leafmin = r->leafmin;
     a.S_pad = r->S_pad;
     a.tile_log2 = r->tile_log2;
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   }
   RR_CUDA(cudaStreamSynchronize(r->main));
   const int n = std::min(cap, nt);
-  if (out_sums && n > 0) RR_CUDA(cudaMemcpy(out_sums, r->l2, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
-  if (out_mins && n > 0) RR_CUDA(cudaMemcpy(out_mins, r->l2min, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  if (out_sums && n > 0)
+    RR_CUDA(cudaMemcpy(out_sums, leaves ? r->leaf : r->l2, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+  if (out_mins && n > 0)
+    RR_CUDA(cudaMemcpy(out_mins, leaves ? r->leafmin : r->l2min, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
   return nt;
 }
 
@@ -1559,6 +1587,8 @@ int rr_load(rr_replay* r, const char* path) {
     a.w = r->w;
     a.l2 = r->l2;
     a.l2min = r->l2min;
+    a.leaf = r->leaf;
+    a.leafmin = r->leafmin;
     a.S_pad = r->S_pad;
     a.tile_log2 = r->tile_log2;
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));

@@ -66,48 +66,62 @@ __device__ __forceinline__ void reduce256(const float4 a, const float4 b, double
   for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
 }
 
-// One warp recomputes tile t from the weights in global memory.
-__device__ __forceinline__ void retile_warp(const float* w, double* l2, float* l2min, int t, int tile_log2,
-                                            int lane) {
-  const int nb = 1 << (tile_log2 - 8);
+// One warp recomputes tile t (and its leaves) from the weights in global memory.
+__device__ __forceinline__ void retile_warp(const float* w, const Tiles& tl, int t, int lane) {
+  const int nb = 1 << (tl.tile_log2 - 8);
   double tot = 0.0;
   float m = FLT_MAX;
   for (int k = 0; k < nb; ++k) {
-    const float4* src = reinterpret_cast<const float4*>(w + ((size_t)t << tile_log2) + (size_t)k * 256) + lane * 2;
+    const float4* src = reinterpret_cast<const float4*>(w + ((size_t)t << tl.tile_log2) + (size_t)k * 256) + lane * 2;
     const float4 a = src[0], b = src[1];
     double s;
     float mn;
     reduce256(a, b, s, mn);
+    if (lane == 0 && tl.leaf != nullptr) {
+      tl.leaf[(size_t)t * nb + k] = s;
+      tl.leafmin[(size_t)t * nb + k] = mn;
+    }
     tot += s;
     m = fminf(m, mn);
   }
   if (lane == 0) {
-    l2[t] = tot;
-    l2min[t] = m;
+    tl.l2[t] = tot;
+    tl.l2min[t] = m;
   }
 }
 
 // The tiles overlapping ring range [start, start + n) (mod S), one warp per
 // tile. The caller has made the new weights of the range visible to the CTA.
-__device__ __forceinline__ void retile_range(const float* w, double* l2, float* l2min, int S, int start, int n,
-                                             int tile_log2, int warp, int nwarps, int lane) {
+__device__ __forceinline__ void retile_range(const float* w, const Tiles& tl, int S, int start, int n, int warp,
+                                             int nwarps, int lane) {
   const int n1 = min(n, S - start);
   for (int seg = 0; seg < 2; ++seg) {
     const int lo = seg == 0 ? start : 0;
     const int len = seg == 0 ? n1 : n - n1;
     if (len <= 0) continue;
-    const int t1 = (lo + len - 1) >> tile_log2;
-    for (int t = (lo >> tile_log2) + warp; t <= t1; t += nwarps) retile_warp(w, l2, l2min, t, tile_log2, lane);
+    const int t1 = (lo + len - 1) >> tl.tile_log2;
+    for (int t = (lo >> tl.tile_log2) + warp; t <= t1; t += nwarps) retile_warp(w, tl, t, lane);
   }
+}
+
+__device__ __host__ __forceinline__ Tiles tiles_of(const SelectArgs& a) {
+  Tiles t;
+  t.l2 = a.l2;
+  t.l2min = a.l2min;
+  t.leaf = a.leaf;
+  t.leafmin = a.leafmin;
+  t.tile_log2 = a.tile_log2;
+  return t;
 }
 
 // Full build: one CTA of 256 threads per 2048 slots, a warp per 256 slots;
 // tiles are 256 << k slots, i.e. 1 << k consecutive warps. Runs once at
 // creation (and on demand for the debug cross-check): afterwards the tile
 // entries are maintained by the kernels that change a weight.
-__global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __restrict__ w,
-                                                              double* __restrict__ l2,
-                                                              float* __restrict__ l2min, int tile_log2) {
+__global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __restrict__ w, const Tiles tl) {
+  double* __restrict__ l2 = tl.l2;
+  float* __restrict__ l2min = tl.l2min;
+  const int tile_log2 = tl.tile_log2;
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   pdl_launch_dependents();
@@ -122,6 +136,10 @@ __global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __res
   if (lane == 0) {
     ws[warp] = s;
     wm[warp] = mn;
+    if (tl.leaf != nullptr) {
+      tl.leaf[(size_t)blockIdx.x * 8 + warp] = s;
+      tl.leafmin[(size_t)blockIdx.x * 8 + warp] = mn;
+    }
   }
   __syncthreads();
   const int wpt = 1 << (tile_log2 - 8);  // warps per tile
@@ -284,7 +302,11 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
   double head_part = 0.0;  // weights in front of head inside head's tile (for the offset O)
   if (warp == kWarps - 1 && a.head > 0) {
     const int last = a.head - 1;
-    for (int k = ((last >> tl) << tl) + lane; k <= last; k += 32) head_part += (double)a.w[k];
+    for (int k = ((last >> 8) << 8) + lane; k <= last; k += 32) head_part += (double)a.w[k];
+    if (tl > 8) {  // whole leaves of head's tile in front of head's leaf
+      const int l0 = (last >> tl) << (tl - 8), l1 = last >> 8;
+      if (l0 + lane < l1) head_part += a.leaf[l0 + lane];
+    }
   }
   mbar_wait(&bar, 0);
   float mn = FLT_MAX;
@@ -389,48 +411,69 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
     __syncthreads();
     if (probing) ctl->probe[3] = clock64();
     // ---- 6. slot inside the tile: one warp per target, two targets per warp.
-    //   Lane l owns tile / 32 consecutive slots (8 for 256-slot tiles: kept in
-    //   registers); a warp scan of the lane totals finds the lane, which then
-    //   walks its own slots.
-    const int c = 1 << (tl - 5);
+    //   Tiles larger than 256 slots first resolve the LEAF: lanes < 2^(tl-8)
+    //   load the tile's leaf sums, a warp scan finds the leaf and the remainder
+    //   inside it. Then lane l owns 8 consecutive slots of the leaf (kept in
+    //   registers); a warp scan of the lane totals finds the lane, which walks
+    //   its own slots.
     constexpr int kPer = kSelTargets / kWarps;
-    double T[kPer];
-    float4 v0[kPer], v1[kPer];
-    const float* wp[kPer];
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {  // all loads of both targets are issued before the first use
-      const int t = warp + k * kWarps;
-      const int tile = t < nT ? s_tile[t] : -1;
-      wp[k] = tile >= 0 ? a.w + ((size_t)tile << tl) + (size_t)lane * c : nullptr;
-      v0[k] = v1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (wp[k] != nullptr) {
-        v0[k] = *reinterpret_cast<const float4*>(wp[k]);
-        v1[k] = *reinterpret_cast<const float4*>(wp[k] + 4);
-      }
-    }
+    const int nb = 1 << (tl - 8);
+    int leaf_t[kPer];
+    double rem_k[kPer];
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
-      T[k] = (((double)v0[k].x + (double)v0[k].y) + ((double)v0[k].z + (double)v0[k].w)) +
-             (((double)v1[k].x + (double)v1[k].y) + ((double)v1[k].z + (double)v1[k].w));
-      if (c > 8 && wp[k] != nullptr) {
-#pragma unroll 4
-        for (int j = 8; j < c; j += 8) {
-          const float4 p = *reinterpret_cast<const float4*>(wp[k] + j);
-          const float4 q = *reinterpret_cast<const float4*>(wp[k] + j + 4);
-          T[k] += (((double)p.x + (double)p.y) + ((double)p.z + (double)p.w)) +
-                  (((double)q.x + (double)q.y) + ((double)q.z + (double)q.w));
+      const int t = warp + k * kWarps;
+      leaf_t[k] = t < nT ? s_tile[t] : -1;
+      rem_k[k] = t < nT ? s_rem[t] : 0.0;
+    }
+    if (nb > 1) {
+      double ls[kPer];
+#pragma unroll
+      for (int k = 0; k < kPer; ++k)  // the loads of both targets are issued together
+        ls[k] = (leaf_t[k] >= 0 && lane < nb) ? a.leaf[(size_t)leaf_t[k] * nb + lane] : 0.0;
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        if (leaf_t[k] < 0) continue;  // warp-uniform
+        double P = ls[k];
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+          const double y = __shfl_up_sync(0xffffffffu, P, o);
+          if (lane >= o) P += y;
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, lane < nb && P >= rem_k[k]);
+        if (hit != 0u) {
+          const int L = __ffs(hit) - 1;
+          rem_k[k] -= __shfl_sync(0xffffffffu, P - ls[k], L);
+          leaf_t[k] = leaf_t[k] * nb + L;
+        } else {
+          leaf_t[k] = -1;
         }
       }
     }
+    double T[kPer];
+    float4 v0[kPer], v1[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {  // all loads of both targets are issued before the first use
+      v0[k] = v1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (leaf_t[k] >= 0) {
+        const float* wp = a.w + ((size_t)leaf_t[k] << 8) + (size_t)lane * 8;
+        v0[k] = *reinterpret_cast<const float4*>(wp);
+        v1[k] = *reinterpret_cast<const float4*>(wp + 4);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k)
+      T[k] = (((double)v0[k].x + (double)v0[k].y) + ((double)v0[k].z + (double)v0[k].w)) +
+             (((double)v1[k].x + (double)v1[k].y) + ((double)v1[k].z + (double)v1[k].w));
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
       const int t = warp + k * kWarps;
       if (t >= nT) continue;  // warp-uniform
-      const int tile = s_tile[t];
+      const int leaf = leaf_t[k];
       int slot = -1;
       float wv = 0.0f;
-      if (tile >= 0) {
-        const double rem = s_rem[t];
+      if (leaf >= 0) {
+        const double rem = rem_k[k];
         double P = T[k];
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -443,31 +486,20 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
           if (lane == L) {
             const double rem_l = rem - (P - T[k]);
             double acc = 0.0;
-            int j = c - 1;
-            if (c == 8) {
-              const float vv[8] = {v0[k].x, v0[k].y, v0[k].z, v0[k].w, v1[k].x, v1[k].y, v1[k].z, v1[k].w};
-              int found = 0;
+            int j = 7;
+            const float vv[8] = {v0[k].x, v0[k].y, v0[k].z, v0[k].w, v1[k].x, v1[k].y, v1[k].z, v1[k].w};
+            int found = 0;
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                acc += (double)vv[q];
-                if (!found && acc >= rem_l) {
-                  found = 1;
-                  j = q;
-                  wv = vv[q];
-                }
+            for (int q = 0; q < 8; ++q) {
+              acc += (double)vv[q];
+              if (!found && acc >= rem_l) {
+                found = 1;
+                j = q;
+                wv = vv[q];
               }
-              if (!found) wv = vv[7];
-            } else {
-              for (int q = 0; q < c; ++q) {
-                acc += (double)wp[k][q];
-                if (acc >= rem_l) {
-                  j = q;
-                  break;
-                }
-              }
-              wv = wp[k][j];
             }
-            slot = (tile << tl) + L * c + j;
+            if (!found) wv = vv[7];
+            slot = (leaf << 8) + L * 8 + j;
           }
           slot = __shfl_sync(0xffffffffu, slot, L);
           wv = __shfl_sync(0xffffffffu, wv, L);
@@ -609,7 +641,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       a.w[slot] = 0.0f;
     }
     __syncthreads();
-    retile_range(a.w, a.l2, a.l2min, a.S, a.head, a.pop_n, a.tile_log2, warp, kWarps, lane);
+    retile_range(a.w, tiles_of(a), a.S, a.head, a.pop_n, warp, kWarps, lane);
   }
 
   // importance weights (lines 320-322); wsel was written by other SMs: read through L2
@@ -652,8 +684,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
 // ------------------------------------------------------------- add commit
 // weights_[j] = priority^alpha for the block's slots, float block sum in index
 // order, sum_ += (double) blockSum (rela/prioritized_replay.h:58-73,188).
-__global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, double* l2, float* l2min,
-                                                      int tile_log2, int S, int start, int n,
+__global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, const Tiles tiles, int S, int start, int n,
                                                       const float* __restrict__ prio, float alpha,
                                                       int is_weight) {
   __shared__ float buf[1024];
@@ -681,7 +712,7 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, double
   }
   if (tid == 0) ctl->sum += (double)sh_sum;
   // the block's weights are visible to the CTA (barrier above): refresh its tiles
-  retile_range(w, l2, l2min, S, start, n, tile_log2, tid >> 5, 32, tid & 31);
+  retile_range(w, tiles, S, start, n, tid >> 5, 32, tid & 31);
 }
 
 // ------------------------------------------------------ K7 priority update
@@ -713,7 +744,8 @@ template <typename Prio>
 __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
                                                       const int32_t* __restrict__ ids, int n,
                                                       const __grid_constant__ Prio prio, float alpha,
-                                                      int is_weight, double* l2, float* l2min, int tile_log2) {
+                                                      int is_weight, const Tiles tiles) {
+  const int tile_log2 = tiles.tile_log2;
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
@@ -743,32 +775,56 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
     if (i > 0 && s_id[i - 1] >= 0 && (s_id[i - 1] >> tile_log2) == t) return;  // covered by that element's warp
     const int nb = 1 << (tile_log2 - 8);
     float* mine = sub[warp];
+    const int tbase = t << tile_log2;
+    // which leaves of the tile hold a batch slot (final values only: last occurrence, not evicted)
+    unsigned touched = 0u;
+    for (int j = lane; j < n; j += 32) {
+      const int sid = s_id[j];
+      if (sid >= tbase && sid < tbase + (1 << tile_log2)) touched |= 1u << ((sid - tbase) >> 8);
+    }
+    touched = __reduce_or_sync(0xffffffffu, touched);
+    // untouched leaves keep their entries: nobody writes them during this kernel
+    double keep_s = 0.0;
+    float keep_m = FLT_MAX;
+    if (nb > 1 && lane < nb && !((touched >> lane) & 1u)) {
+      keep_s = tiles.leaf[(size_t)t * nb + lane];
+      keep_m = tiles.leafmin[(size_t)t * nb + lane];
+    }
     double tot = 0.0;
     float m = FLT_MAX;
     for (int k = 0; k < nb; ++k) {
-      const int base = (t << tile_log2) + k * 256;
-      const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
-      reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
-      reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
-      __syncwarp();
-      for (int j = lane; j < n; j += 32) {
-        const int sid = s_id[j];
-        const bool last = !(j + 1 < n && s_id[j + 1] == sid);
-        if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
-      }
-      __syncwarp();
-      const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
-      const float4 b = reinterpret_cast<const float4*>(mine)[lane * 2 + 1];
-      __syncwarp();
       double s;
       float mn;
-      reduce256(a, b, s, mn);
+      if ((touched >> k) & 1u) {
+        const int base = tbase + k * 256;
+        const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
+        reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
+        reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
+        __syncwarp();
+        for (int j = lane; j < n; j += 32) {
+          const int sid = s_id[j];
+          const bool last = !(j + 1 < n && s_id[j + 1] == sid);
+          if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
+        }
+        __syncwarp();
+        const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
+        const float4 b = reinterpret_cast<const float4*>(mine)[lane * 2 + 1];
+        __syncwarp();
+        reduce256(a, b, s, mn);
+        if (lane == 0 && nb > 1) {
+          tiles.leaf[(size_t)t * nb + k] = s;
+          tiles.leafmin[(size_t)t * nb + k] = mn;
+        }
+      } else {
+        s = __shfl_sync(0xffffffffu, keep_s, k);
+        mn = __shfl_sync(0xffffffffu, keep_m, k);
+      }
       tot += s;
       m = fminf(m, mn);
     }
     if (lane == 0) {
-      l2[t] = tot;
-      l2min[t] = m;
+      tiles.l2[t] = tot;
+      tiles.l2min[t] = m;
     }
     return;
   }
@@ -846,8 +902,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
 
 // ----------------------------------------------------------------- launches
 cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
-  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kBuildSpan), dim3(256), 0, stream, a.w, a.l2, a.l2min,
-                    a.tile_log2);
+  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kBuildSpan), dim3(256), 0, stream, a.w, tiles_of(a));
 }
 
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
@@ -859,26 +914,24 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
   return launch_pdl(select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
 }
 
-cudaError_t launch_commit(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, int S, int start, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
-  commit_kernel<<<1, 1024, 0, stream>>>(ctl, w, l2, l2min, tile_log2, S, start, n, prio, alpha, is_weight);
+cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int start, int n, const float* prio,
+                          float alpha, int is_weight, cudaStream_t stream) {
+  commit_kernel<<<1, 1024, 0, stream>>>(ctl, w, tiles, S, start, n, prio, alpha, is_weight);
   return cudaGetLastError();
 }
 
-cudaError_t launch_update(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
-                          const int32_t* ids, int n, const float* prio, float alpha, int is_weight,
-                          cudaStream_t stream) {
+cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
   const int grid = 1 + (n + 31) / 32;  // CTA 0: sum_ and weights; the others: one warp per element's tile
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio,
-                    alpha, is_weight, l2, l2min, tile_log2);
+                    alpha, is_weight, tiles);
 }
 
-cudaError_t launch_update_inline(Ctl* ctl, float* w, double* l2, float* l2min, int tile_log2, const uint8_t* evicted,
-                                 const int32_t* ids, int n, const float* prio_host, float alpha, int is_weight,
-                                 cudaStream_t stream) {
+cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
+                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream) {
   if (n > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
   memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
@@ -887,7 +940,7 @@ cudaError_t launch_update_inline(Ctl* ctl, float* w, double* l2, float* l2min, i
   if (e != cudaSuccess) return e;
   const int grid = 1 + (n + 31) / 32;
   return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, pin,
-                    alpha, is_weight, l2, l2min, tile_log2);
+                    alpha, is_weight, tiles);
 }
 
 }  // namespace rr

@@ -534,14 +534,15 @@ class CudaReplay(_Base):
         self.capi.check(self.lib.rr_debug_weights(self.h, w.ctypes.data, e.ctypes.data))
         return w, e
 
-    def tiles(self, rebuild=False):
-        """(sums, mins, slots per tile) of the selection hierarchy; rebuild recomputes it from the weights."""
-        n = self.lib.rr_debug_tiles(self.h, 0, None, None, 0, None)
+    def tiles(self, rebuild=False, level=0):
+        """(sums, mins, slots per tile) of the selection hierarchy (level 1: its 256-slot leaves);
+        rebuild recomputes it from the weights."""
+        n = self.lib.rr_debug_tiles(self.h, 0, level, None, None, 0, None)
         assert n > 0
         s = np.zeros(n, dtype=np.float64)
         m = np.zeros(n, dtype=np.float32)
         ts = C.c_int()
-        rc = self.lib.rr_debug_tiles(self.h, int(rebuild), s.ctypes.data, m.ctypes.data, n, C.addressof(ts))
+        rc = self.lib.rr_debug_tiles(self.h, int(rebuild), level, s.ctypes.data, m.ctypes.data, n, C.addressof(ts))
         assert rc == n
         return s, m, ts.value
 

@@ -32,16 +32,18 @@ def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, **cuda_kw):
 def check_tiles(cu, w):
     """The incrementally maintained tile entries equal a rebuild from the weights, bit for bit,
     and (mins always, sums when exactly representable) a host recomputation."""
-    s_inc, m_inc, ts = cu.tiles()
-    s_full, m_full, _ = cu.tiles(rebuild=True)
-    np.testing.assert_array_equal(s_inc.view(np.uint64), s_full.view(np.uint64))
-    np.testing.assert_array_equal(m_inc.view(np.uint32), m_full.view(np.uint32))
-    wp = np.zeros(len(s_inc) * ts, dtype=np.float32)
-    wp[: len(w)] = w
-    wt = wp.reshape(len(s_inc), ts)
-    nz = np.where(wt != 0, np.abs(wt), np.float32(np.finfo(np.float32).max))
-    np.testing.assert_array_equal(nz.min(axis=1), m_inc)
-    np.testing.assert_allclose(wt.astype(np.float64).sum(axis=1), s_inc, rtol=1e-12, atol=0)
+    inc = [cu.tiles(level=lv) for lv in (0, 1)]  # both read before the rebuild overwrites them
+    for lv in (0, 1):
+        s_inc, m_inc, ts = inc[lv]
+        s_full, m_full, _ = cu.tiles(rebuild=True, level=lv)
+        np.testing.assert_array_equal(s_inc.view(np.uint64), s_full.view(np.uint64))
+        np.testing.assert_array_equal(m_inc.view(np.uint32), m_full.view(np.uint32))
+        wp = np.zeros(len(s_inc) * ts, dtype=np.float32)
+        wp[: len(w)] = w
+        wt = wp.reshape(len(s_inc), ts)
+        nz = np.where(wt != 0, np.abs(wt), np.float32(np.finfo(np.float32).max))
+        np.testing.assert_array_equal(nz.min(axis=1), m_inc)
+        np.testing.assert_allclose(wt.astype(np.float64).sum(axis=1), s_inc, rtol=1e-12, atol=0)
 
 
 @pytest.mark.parametrize("cap,K,B,alpha,beta,prefetch", [
