@@ -214,6 +214,23 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields,
                     int reps, double* ms_per_launch, uint64_t* launches,
                     uint64_t* bytes_per_launch);
 
+/* Learner-side fusion at the batch hand-off (not in the reference; SURVEY 8(f)
+ * rank 3). The reference's learner converts the sampled u8 frames right after
+ * sample() with `s.float() / 255` (pyrela/net.py:46,104): a second full pass
+ * over the batch. With a format set, rr_sample / rr_sample_gather write field
+ * `field` as float32 (or bfloat16) = byte / 255 instead of raw bytes --
+ * bit-identical to what the torch expression returns on a CUDA tensor, i.e.
+ * float(byte) * (1.0f / 255.0f) (torch's CUDA kernel multiplies by the
+ * reciprocal of a scalar divisor; the CPU kernel's IEEE quotient can differ
+ * by 1 ulp), then rounded to bf16 -- and out_fields[field] must hold
+ * batch * row_bytes ELEMENTS of that type.
+ * The field's chunk size must be a multiple of 4 bytes. Not available with
+ * prefetch > 0 or on a sharded replay. */
+#define RR_OUT_RAW 0
+#define RR_OUT_F32_DIV255 1
+#define RR_OUT_BF16_DIV255 2
+int rr_set_output_format(rr_replay* r, int field, int format);
+
 /* Checkpoint / restore (not in the reference). rr_save
  * writes the ring counters, the mt19937 state, sum_, the weights, the eviction
  * flags and the live rows of this replay's slot range to `path` (blocking;

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librela_b200.so")
-KERNEL_SOURCES = ["replay.cu", "row_copy.cu", "select.cu", "actor_math.cu"]
+KERNEL_SOURCES = ["replay.cu", "row_copy.cu", "gather_convert.cu", "select.cu", "actor_math.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-Wall", "-shared", "-cudart", "static",

@@ -10,13 +10,14 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "librela_b200.so")
 
+RR_OUT_RAW, RR_OUT_F32_DIV255, RR_OUT_BF16_DIV255 = 0, 1, 2
 RR_OK, RR_ERR_ARG, RR_ERR_CUDA, RR_ERR_STATE, RR_ERR_EMPTY, RR_ERR_NOMEM, RR_ERR_OVERRUN = range(7)
 RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
 
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
-    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence", "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
+    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence", "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
     "rr_sample_select", "rr_sample_gather", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
 ]
 
@@ -72,6 +73,7 @@ def lib():
         L.rr_stream_wait.argtypes = [vp, vp]
         L.rr_save.argtypes = [vp, C.c_char_p]
         L.rr_load.argtypes = [vp, C.c_char_p]
+        L.rr_set_output_format.argtypes = [vp, i, i]
         L.rr_set_profiling.argtypes = [vp, i, i]
         L.rr_gather_bench.argtypes = [vp, i, vp, i, vp, vp, vp]
         L.rr_nstep_return.argtypes = [i, i, f, vp, vp, vp, vp, vp, i, vp]

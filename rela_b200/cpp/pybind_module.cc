@@ -42,6 +42,11 @@ void bindCommon(PyClass& c) {
       .def("sample", &Replay::sample, py::call_guard<py::gil_scoped_release>())
       .def("update_priority", &Replay::updatePriority, py::call_guard<py::gil_scoped_release>())
       .def("sync", [](Replay& r) { r.core().sync(); }, py::call_guard<py::gil_scoped_release>())
+      .def("set_output_format",
+           [](Replay& r, const std::string& leaf, py::object dtype) {
+             r.core().setOutputFormat(leaf, torch::python::detail::py_object_to_dtype(dtype));
+           },
+           py::arg("leaf"), py::arg("dtype"))
       .def("save", [](Replay& r, const std::string& path) { r.core().save(path); },
            py::call_guard<py::gil_scoped_release>())
       .def("load", [](Replay& r, const std::string& path) { r.core().load(path); },

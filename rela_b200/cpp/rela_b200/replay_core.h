@@ -36,6 +36,10 @@ struct LeafSpec {
   uint32_t chunks;             // T: the row is T chunks, gathered time-major
   bool time_major;             // gathered [shape[0], B, shape[1:]...] instead of [B, shape...]
   uint64_t row_bytes;
+  // dtype of the gathered leaf: `dtype`, or float32 / bfloat16 for a u8 leaf
+  // that the gather converts to byte / 255 (setOutputFormat)
+  torch::ScalarType out_dtype = torch::kByte;
+  bool converted = false;
 };
 
 class ReplayCore {
@@ -75,6 +79,13 @@ class ReplayCore {
   void scatterRows(int n, const std::vector<uint64_t>& row_bytes, const std::vector<const void*>& src,
                    const std::vector<void*>& dst, const int32_t* dst_rows_dev);
   void* stream() const;
+
+  // Learner-side fusion (rr_set_output_format): the u8 leaf `name` comes out of
+  // sample() as `dtype` (float32 or bfloat16) = byte / 255, bit-identical to
+  // `leaf.float() / 255` (`.bfloat16()`), without the extra pass over the batch
+  // (pyrela/net.py:46,104). dtype = uint8 switches it off. Needs the schema
+  // (after the first add / load / setSchema).
+  void setOutputFormat(const std::string& name, torch::ScalarType dtype);
 
   void sync();  // waits for the device; throws on a sticky device-side error
   // Checkpoint / restore (rr_save / rr_load): a restored replay continues

@@ -178,6 +178,32 @@ void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
   schema_set_ = true;
 }
 
+void ReplayCore::setOutputFormat(const std::string& name, torch::ScalarType dtype) {
+  std::lock_guard<std::mutex> lk(schema_m_);
+  if (!schema_set_) throw std::runtime_error("set_output_format: the schema is not known yet (add or load first)");
+  for (size_t i = 0; i < schema_.size(); ++i) {
+    LeafSpec& s = schema_[i];
+    if (s.name != name) continue;
+    int fmt;
+    if (dtype == torch::kByte) {
+      fmt = RR_OUT_RAW;
+    } else if (dtype == torch::kFloat32) {
+      fmt = RR_OUT_F32_DIV255;
+    } else if (dtype == torch::kBFloat16) {
+      fmt = RR_OUT_BF16_DIV255;
+    } else {
+      throw std::runtime_error("set_output_format: dtype must be float32, bfloat16 or uint8");
+    }
+    if (s.dtype != torch::kByte) throw std::runtime_error("set_output_format: leaf '" + name + "' is not uint8");
+    check(rr_set_output_format(h_, (int)i, fmt), "set_output_format");
+    s.converted = fmt != RR_OUT_RAW;
+    s.out_dtype = dtype;
+    pool_.clear();  // pooled batch sets have the old dtype
+    return;
+  }
+  throw std::runtime_error("set_output_format: no leaf named '" + name + "'");
+}
+
 void* ReplayCore::stream() const { return streamOf(device_); }
 
 void ReplayCore::addDeviceRows(int n, const std::vector<const void*>& ptrs, const torch::Tensor& priority) {
@@ -336,7 +362,8 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
         shape.push_back(B);
         shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
       }
-      set->fields.push_back(torch::empty(shape, torch::TensorOptions().dtype(s.dtype).device(home)));
+      set->fields.push_back(
+          torch::empty(shape, torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
     }
   }
   Leaves out;

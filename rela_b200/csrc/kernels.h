@@ -106,6 +106,24 @@ struct Ctl {
   unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel (CTA 0)
 };
 
+// ------------------------------------------------- gather with conversion
+// A u8 field gathered as float32 / bfloat16 = byte / 255 (gather_convert.cu).
+struct ConvertField {
+  const uint8_t* src;    // slab
+  void* dst;             // batch tensor, [chunks, B, chunk_bytes] elements of the output type
+  uint64_t row_bytes;
+  uint32_t chunks, chunk_bytes;  // chunk_bytes % 4 == 0
+  int format;            // RR_OUT_F32_DIV255 | RR_OUT_BF16_DIV255
+};
+constexpr int kMaxConvertFields = 4;
+struct ConvertParams {
+  ConvertField f[kMaxConvertFields];
+  int n;
+  int B;
+  const int32_t* ids;
+};
+cudaError_t launch_gather_convert(const ConvertParams& p, int sm_count, cudaStream_t stream);
+
 // The selection hierarchy over the weights. A tile is 256 << k slots (k =
 // tile_log2 - 8) so that at most kMaxTiles tile sums have to fit the selection
 // kernel's shared memory; for k > 0 the tile is made of 1 << k LEAVES of 256

@@ -66,6 +66,7 @@ struct FieldInfo {
   uint32_t chunks;
   uint32_t chunk_bytes;
   uint8_t* slab;
+  int out_format = RR_OUT_RAW;  // rr_set_output_format
 };
 
 // A producer lane: private stream + pinned staging, so that concurrent rr_add
@@ -920,9 +921,21 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
   std::unique_lock<std::mutex> lk(r->m_);
   const int32_t* ids = r->idbuf[idslot];
   std::vector<CopyField> cf;
+  rr::ConvertParams conv;
+  memset(&conv, 0, sizeof(conv));
   for (size_t fi = 0; fi < r->fields.size(); ++fi) {
     const FieldInfo& f = r->fields[fi];
     if (f.row_bytes == 0) continue;
+    if (f.out_format != RR_OUT_RAW) {  // gathered as byte / 255 by the converting kernel
+      rr::ConvertField& cvf = conv.f[conv.n++];
+      cvf.src = f.slab;
+      cvf.dst = out_fields[fi];
+      cvf.row_bytes = f.row_bytes;
+      cvf.chunks = f.chunks;
+      cvf.chunk_bytes = f.chunk_bytes;
+      cvf.format = f.out_format;
+      continue;
+    }
     CopyField c;
     memset(&c, 0, sizeof(c));
     c.src = f.slab;
@@ -936,6 +949,13 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
   }
   CopyPlan plan;
   int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
+  if (rc == RR_OK && conv.n > 0) {
+    conv.B = B;
+    conv.ids = ids;
+    cudaError_t e = rr::launch_gather_convert(conv, r->sm_count, r->main);
+    if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather_convert: %s", cudaGetErrorString(e));
+    r->launches++;
+  }
   if (rc == RR_OK && r->signal_ptr != nullptr) {
     plan.p.done_counter = &r->ctl->gather_done;
     plan.p.signal = r->signal_ptr;
@@ -1439,6 +1459,30 @@ constexpr size_t kCkptBounce = 64u << 20;
 }  // namespace
 
 extern "C" {
+
+int rr_set_output_format(rr_replay* r, int field, int format) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_set_output_format: null");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_set_output_format: rr_set_schema has not been called");
+  if (field < 0 || field >= (int)r->fields.size()) return fail(RR_ERR_ARG, "rr_set_output_format: no field %d", field);
+  if (format != RR_OUT_RAW && format != RR_OUT_F32_DIV255 && format != RR_OUT_BF16_DIV255)
+    return fail(RR_ERR_ARG, "rr_set_output_format: unknown format %d", format);
+  std::unique_lock<std::mutex> lk(r->m_);
+  FieldInfo& f = r->fields[(size_t)field];
+  if (format != RR_OUT_RAW) {
+    if (r->prefetch > 0 || r->shard_world > 1)
+      return fail(RR_ERR_ARG, "rr_set_output_format: not available with prefetch or on a sharded replay");
+    if (f.row_bytes == 0 || (f.chunk_bytes & 3u) != 0)
+      return fail(RR_ERR_ARG, "rr_set_output_format: field '%s' has chunks of %u bytes (need a multiple of 4)",
+                  f.name.c_str(), f.chunk_bytes);
+    int n = 0;
+    for (auto& g : r->fields) n += (&g != &f && g.out_format != RR_OUT_RAW) ? 1 : 0;
+    if (n >= rr::kMaxConvertFields) return fail(RR_ERR_ARG, "rr_set_output_format: at most %d converted fields", rr::kMaxConvertFields);
+  }
+  if (r->cur_ids >= 0 || r->pend_slot >= 0)
+    return fail(RR_ERR_STATE, "rr_set_output_format: a sampled batch is outstanding");
+  f.out_format = format;
+  return RR_OK;
+}
 
 int rr_save(rr_replay* r, const char* path) {
   if (r == nullptr || path == nullptr) return fail(RR_ERR_ARG, "rr_save: null");

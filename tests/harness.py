@@ -488,9 +488,20 @@ class CudaReplay(_Base):
                 ptrs[f * n + i] = r.ctypes.data + i * rb
         self.capi.check(self.lib.rr_add_rows(self.h, n, ptrs, p.ctypes.data, self._flags(), None))
 
+    def set_output_format(self, field_index, fmt):
+        """rr_set_output_format: field gathered as float32 (fmt 1) / bfloat16 (fmt 2) = byte / 255."""
+        rc = self.lib.rr_set_output_format(self.h, field_index, fmt)
+        if rc == 0:
+            self.out_format = dict(getattr(self, "out_format", {}))
+            self.out_format[field_index] = fmt
+        return rc
+
     def sample(self, B, want_rows=True):
         t = self.torch
-        outs = [t.empty(max(1, f.row_bytes * B), dtype=t.uint8, device=self.dev) for f in self.schema]
+        fmt = getattr(self, "out_format", {})
+        width = {0: 1, 1: 4, 2: 2}
+        outs = [t.empty(max(1, f.row_bytes * B * width[fmt.get(i, 0)]), dtype=t.uint8, device=self.dev)
+                for i, f in enumerate(self.schema)]
         w = t.empty(B, dtype=t.float32, device=self.dev)
         ptrs = (C.c_void_p * max(1, len(outs)))(*[o.data_ptr() for o in outs])
         rc = self.lib.rr_sample(self.h, B, ptrs, w.data_ptr(), self._stream())
@@ -503,9 +514,11 @@ class CudaReplay(_Base):
         rows = None
         if want_rows:
             rows = []
-            for f, o in zip(self.schema, outs):
-                a = o.cpu().numpy()[: f.row_bytes * B]
-                rows.append(a.view(f.dtype).reshape(f.batch_shape(B)))
+            for i, (f, o) in enumerate(zip(self.schema, outs)):
+                k = fmt.get(i, 0)
+                a = o.cpu().numpy()[: f.row_bytes * B * width[k]]
+                dt = {0: f.dtype, 1: np.dtype("float32"), 2: np.dtype("uint16")}[k]  # bf16 as raw 16-bit patterns
+                rows.append(a.view(dt).reshape(f.batch_shape(B)))
         return 0, rows, w.cpu().numpy(), ids
 
     def update(self, priority):
