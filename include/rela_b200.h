@@ -113,6 +113,20 @@ int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs,
 int rr_sample(rr_replay* r, int batch, void* const* out_fields,
               float* out_weights, void* stream);
 
+/* Zero-copy prefetch for a host layer that owns the batch buffers (replay
+ * created with prefetch == 0). The reference's sample() returns the oldest
+ * future and launches new ones (prioritized_replay.h:215-230); its futures
+ * assemble into fresh host memory. rr_prefetch_into is one such future: the
+ * batch is selected and gathered NOW -- before the current batch's
+ * updatePriority, like the reference -- into the caller's buffers, and queued.
+ * rr_take_prefetched makes the oldest queued batch the current one (the one
+ * rr_update_priority applies to) and orders its contents on `stream`; no copy.
+ * rr_prefetched returns the queue length. */
+int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields,
+                     float* out_weights, void* stream);
+int rr_take_prefetched(rr_replay* r, void* stream);
+int rr_prefetched(rr_replay* r);
+
 /* rr_sample in two steps, so that a host layer can allocate the batch tensors
  * while the selection kernels already run: rr_sample_select issues the prefix
  * hierarchy, selection, eviction and importance weights (sample_ lines

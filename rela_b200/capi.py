@@ -18,7 +18,7 @@ SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence", "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
-    "rr_sample_select", "rr_sample_gather", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
+    "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
 ]
 
 
@@ -70,6 +70,9 @@ def lib():
         L.rr_debug_select_probe.argtypes = [vp, vp]
         L.rr_stream_fence.argtypes = [vp, vp]
         L.rr_get_stream.argtypes = [vp, vp]
+        L.rr_prefetch_into.argtypes = [vp, i, vp, vp, vp]
+        L.rr_take_prefetched.argtypes = [vp, vp]
+        L.rr_prefetched.argtypes = [vp]
         L.rr_stream_wait.argtypes = [vp, vp]
         L.rr_save.argtypes = [vp, C.c_char_p]
         L.rr_load.argtypes = [vp, C.c_char_p]

@@ -11,6 +11,7 @@
 #pragma once
 
 #include <cstdint>
+#include <deque>
 #include <mutex>
 #include <string>
 #include <tuple>
@@ -108,6 +109,11 @@ class ReplayCore {
     torch::Tensor weights;
   };
   std::vector<BatchSet> pool_;  // batch tensors reused once the caller has released them
+  std::deque<BatchSet> inflight_;  // batches drawn ahead (prefetch), oldest first
+  int prefetch_ = 0;
+  BatchSet acquireSet(int64_t B);
+  std::vector<int64_t> batchShape(const LeafSpec& s, int64_t B) const;
+  std::pair<Leaves, torch::Tensor> samplePrefetched(int batchsize, const std::string& device);
   bool pool_enabled_ = true;
 
   rr_replay* h_ = nullptr;

@@ -66,7 +66,16 @@ ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int pref
   host_pow_ = !(e && std::atoi(e) != 0);
   const char* np = std::getenv("RELA_B200_NO_POOL");
   pool_enabled_ = !(np && std::atoi(np) != 0);
-  check(rr_create(&h_, capacity, seed, alpha, beta, prefetch, device_), "PrioritizedReplay");
+  // prefetch > 0: the futures of the reference (rela/prioritized_replay.h:215-230)
+  // are batches selected and gathered ahead straight into pooled batch tensors
+  // (rr_prefetch_into / rr_take_prefetched): the C ABI replay itself runs without
+  // prefetch and nothing is copied when a batch is handed out.
+  // RELA_B200_ABI_PREFETCH=1 uses the C ABI's own prefetch queue instead
+  // (library-owned buffers + one device-to-device copy per batch).
+  const char* ap = std::getenv("RELA_B200_ABI_PREFETCH");
+  const bool abi_prefetch = ap && std::atoi(ap) != 0;
+  prefetch_ = abi_prefetch ? 0 : std::max(0, prefetch);
+  check(rr_create(&h_, capacity, seed, alpha, beta, abi_prefetch ? prefetch : 0, device_), "PrioritizedReplay");
 }
 
 ReplayCore::~ReplayCore() {
@@ -181,6 +190,7 @@ void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
 void ReplayCore::setOutputFormat(const std::string& name, torch::ScalarType dtype) {
   std::lock_guard<std::mutex> lk(schema_m_);
   if (!schema_set_) throw std::runtime_error("set_output_format: the schema is not known yet (add or load first)");
+  if (!inflight_.empty()) throw std::runtime_error("set_output_format: prefetched batches are pending");
   for (size_t i = 0; i < schema_.size(); ++i) {
     LeafSpec& s = schema_[i];
     if (s.name != name) continue;
@@ -312,11 +322,80 @@ void ReplayCore::addElements(const std::vector<Leaves>& elements, const torch::T
   check(rr_add_rows(h_, (int)n, ptrs.data(), w.data_ptr<float>(), flags, stream), "add");
 }
 
+std::vector<int64_t> ReplayCore::batchShape(const LeafSpec& s, int64_t B) const {
+  std::vector<int64_t> shape;
+  if (!s.time_major) {
+    shape.push_back(B);
+    shape.insert(shape.end(), s.shape.begin(), s.shape.end());
+  } else {
+    shape.push_back(s.shape[0]);
+    shape.push_back(B);
+    shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
+  }
+  return shape;
+}
+
+// A batch set nobody else holds: a pooled one whose storages are back to a use
+// count of 1, else a new one (pooled if there is room).
+ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
+  if (pool_enabled_) {
+    for (auto& cand : pool_) {
+      if (cand.B != B) continue;
+      bool idle = cand.weights.storage().use_count() == 1;
+      for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
+      if (idle) return cand;
+    }
+  }
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  BatchSet set;
+  set.B = B;
+  set.weights = torch::empty({B}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+  for (const LeafSpec& s : schema_)
+    set.fields.push_back(torch::empty(batchShape(s, B),
+                                      torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
+  if (pool_enabled_ && pool_.size() < (size_t)(4 + prefetch_)) pool_.push_back(set);
+  return set;
+}
+
+// sample() with prefetch > 0 (rela/prioritized_replay.h:208-232): hand out the
+// oldest batch drawn ahead (or draw one now if there is none), then draw until
+// `prefetch` batches are queued again -- before this batch's updatePriority,
+// like the reference's futures.
+std::pair<Leaves, torch::Tensor> ReplayCore::samplePrefetched(int batchsize, const std::string& device) {
+  const int64_t B = batchsize;
+  void* stream = streamOf(device_);
+  auto issue = [&]() {
+    BatchSet set = acquireSet(B);  // the copy in inflight_ keeps the set busy (storage use count 2)
+    std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
+    for (size_t i = 0; i < schema_.size(); ++i) ptrs[i] = set.fields[i].data_ptr();
+    check(rr_prefetch_into(h_, batchsize, ptrs.data(), set.weights.data_ptr<float>(), stream), "sample");
+    inflight_.push_back(std::move(set));
+  };
+  if (!inflight_.empty() && inflight_.front().B != B) throw std::runtime_error("sample: batch size differs from the prefetched one");
+  if (inflight_.empty()) issue();
+  check(rr_take_prefetched(h_, stream), "sample");
+  BatchSet set = std::move(inflight_.front());
+  inflight_.pop_front();
+  Leaves out;
+  out.reserve(schema_.size());
+  for (size_t i = 0; i < schema_.size(); ++i) out.push_back(Leaf{schema_[i].name, aliasOf(set.fields[i])});
+  torch::Tensor weights = aliasOf(set.weights);
+  while ((int)inflight_.size() < prefetch_) issue();
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  const torch::Device want(device);
+  if (want != home && !(want.is_cuda() && !want.has_index())) {
+    for (auto& lf : out) lf.t = lf.t.to(want);
+    weights = weights.to(want);
+  }
+  return {std::move(out), std::move(weights)};
+}
+
 std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::string& device) {
   if (!schema_set_) {
     // the reference prints "cannot find enough samples" and asserts (:297-302)
     throw std::runtime_error("sample: the replay buffer is empty");
   }
+  if (prefetch_ > 0) return samplePrefetched(batchsize, device);
   const int64_t B = batchsize;
   const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
   // Batch tensors come from a small pool. The caller never receives the pooled

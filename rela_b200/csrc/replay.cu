@@ -99,6 +99,7 @@ struct Prefetched {
   float* weights = nullptr;
   int idslot = -1;
   int B = 0;
+  bool external = false;  // rr_prefetch_into: the batch already sits in the caller's buffers
 };
 
 // Make the replay's device current for the duration of one C ABI call and put
@@ -1036,6 +1037,8 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     // "Error: previous samples' priority has not been updated." (line 204)
     return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
   }
+  if (!r->queue.empty() && r->queue.front().external)
+    return fail(RR_ERR_STATE, "rr_sample: batches queued by rr_prefetch_into are pending (rr_take_prefetched)");
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   // out buffers may have been used on the caller's stream before
@@ -1092,6 +1095,59 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   }
   return RR_OK;
 }
+
+// Zero-copy prefetch for a host layer that owns the batch buffers.
+int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
+  if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_prefetch_into: bad argument");
+  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_prefetch_into: batch %d exceeds %d", batch, rr::kMaxBatch);
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_prefetch_into: rr_set_schema has not been called");
+  if (r->prefetch > 0) return fail(RR_ERR_STATE, "rr_prefetch_into: the replay was created with its own prefetch");
+  if (r->pend_slot >= 0) return fail(RR_ERR_STATE, "rr_prefetch_into: an rr_sample_select is pending");
+  if (r->queue.size() >= 16) return fail(RR_ERR_STATE, "rr_prefetch_into: 16 batches are already queued");
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  DeviceScope dev_scope(r->device);
+  if (cs != r->main) {  // the buffers may still be in use on the caller's stream
+    RR_CUDA(cudaEventRecord(r->evIn, cs));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  }
+  int slot = free_idslot(r);
+  if (slot < 0) {
+    slot = (int)r->idbuf.size();
+    r->idbuf.push_back(nullptr);
+    r->idcap.push_back(0);
+    r->idbusy.push_back(false);
+  }
+  int rc = sample_into(r, batch, out_fields, out_weights, slot);
+  if (rc != RR_OK) return rc;
+  r->idbusy[slot] = true;
+  Prefetched p;
+  p.B = batch;
+  p.idslot = slot;
+  p.external = true;
+  r->queue.push_back(p);
+  return RR_OK;
+}
+
+int rr_take_prefetched(rr_replay* r, void* stream) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_take_prefetched: null");
+  if (r->cur_ids >= 0) return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
+  if (r->queue.empty() || !r->queue.front().external)
+    return fail(RR_ERR_STATE, "rr_take_prefetched: no batch queued by rr_prefetch_into");
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  DeviceScope dev_scope(r->device);
+  Prefetched p = r->queue.front();
+  r->queue.pop_front();
+  r->cur_ids = p.idslot;
+  r->cur_B = p.B;
+  if (cs != r->main) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
+  return RR_OK;
+}
+
+int rr_prefetched(rr_replay* r) { return r == nullptr ? 0 : (int)r->queue.size(); }
 
 int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr) return fail(RR_ERR_ARG, "rr_sample_select: bad argument");
