@@ -565,6 +565,49 @@ class CudaReplay(_Base):
         return {n: getattr(st, n) for n, _ in st._fields_}
 
 
+class CudaReplayHostPrefetch(CudaReplay):
+    """The C ABI driven the way the C++ host layer drives it for prefetch > 0: the replay itself
+    is created without prefetch; batches are drawn ahead into caller-owned buffers with
+    rr_prefetch_into and handed out with rr_take_prefetched (no copy)."""
+
+    def __init__(self, schema, capacity, seed, alpha, beta, prefetch=0, **kw):
+        super().__init__(schema, capacity, seed, alpha, beta, 0, **kw)
+        self.host_prefetch = prefetch
+        self.pending = []
+
+    def _issue(self, B):
+        t = self.torch
+        outs = [t.empty(max(1, f.row_bytes * B), dtype=t.uint8, device=self.dev) for f in self.schema]
+        w = t.empty(B, dtype=t.float32, device=self.dev)
+        ptrs = (C.c_void_p * max(1, len(outs)))(*[o.data_ptr() for o in outs])
+        rc = self.lib.rr_prefetch_into(self.h, B, ptrs, w.data_ptr(), self._stream())
+        if rc == 0:
+            self.pending.append((outs, w))
+        return rc
+
+    def sample(self, B, want_rows=True):
+        if self.host_prefetch == 0:
+            return super().sample(B, want_rows)
+        if self.lib.rr_prefetched(self.h) == 0:
+            rc = self._issue(B)
+            if rc != 0:
+                return rc, None, None, None
+        rc = self.lib.rr_take_prefetched(self.h, self._stream())
+        if rc != 0:
+            return rc, None, None, None
+        outs, w = self.pending.pop(0)
+        ids = np.zeros(B, dtype=np.int32)
+        self.capi.check(self.lib.rr_last_sample_ids(self.h, B, ids.ctypes.data))
+        rows = None
+        if want_rows:
+            rows = [o.cpu().numpy()[: f.row_bytes * B].view(f.dtype).reshape(f.batch_shape(B))
+                    for f, o in zip(self.schema, outs)]
+        wh = w.cpu().numpy()
+        while self.lib.rr_prefetched(self.h) < self.host_prefetch:
+            self.capi.check(self._issue(B))
+        return 0, rows, wh, ids
+
+
 class CppReplay(CudaReplay):
     """The product through its C++ host layer: rela_b200._C (pybind module with
     rela's class names, rela_b200/cpp/). Priorities are passed RAW: the host

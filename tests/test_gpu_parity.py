@@ -215,3 +215,31 @@ def test_large_batches(B):
     cap = 40000
     ops = gen_trace(schema, cap, 13, 6, 5000, B, prefill=cap - 2000, adds_per_cycle=(1, 2))
     _run_pair(schema, cap, 21, 0.6, 0.4, 0, ops)
+
+
+@pytest.mark.parametrize("prefetch", [1, 2, 3])
+def test_host_managed_prefetch_matches_oracle(prefetch):
+    """rr_prefetch_into / rr_take_prefetched (zero-copy prefetch, as the C++ host layer uses them)
+    give the reference's prefetch semantics: batches are drawn before the pending updatePriority."""
+    from harness import CudaReplayHostPrefetch
+
+    schema = ff_schema(frame=(1, 12, 12), n_actions=4)
+    cap, alpha = 256, 0.6
+    ops = gen_trace(schema, cap, 19, 60, 20, 32)
+    orc = Oracle(schema, cap, 3, alpha, 0.4, prefetch)
+    cu = CudaReplayHostPrefetch(schema, cap, 3, alpha, 0.4, prefetch)
+    ra = apply_trace(orc, ops, alpha, False)
+    rb = apply_trace(cu, ops, alpha, False)
+    assert cu.sync() == 0
+    compare_records(ra, rb, "oracle prefetch=%d vs host-managed prefetch" % prefetch)
+    # protocol errors
+    from rela_b200 import capi
+
+    rc, _, _, _ = cu.sample(32)
+    assert rc == 0
+    assert cu.lib.rr_take_prefetched(cu.h, None) == capi.RR_ERR_STATE  # previous batch not updated
+    outs = (__import__("ctypes").c_void_p * len(schema))()
+    assert cu.lib.rr_sample(cu.h, 32, outs, 1, None) == capi.RR_ERR_STATE
+    assert cu.update(np.ones(32, np.float32)) == 0
+    assert cu.lib.rr_sample(cu.h, 32, outs, 1, None) == capi.RR_ERR_STATE  # queued batches pending
+    assert cu.lib.rr_save(cu.h, b"/tmp/never_written.ckpt") == capi.RR_ERR_STATE
