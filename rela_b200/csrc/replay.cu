@@ -133,6 +133,11 @@ struct rr_replay {
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
   int inline_prio = rr::kInlinePrio;  // $RR_INLINE_PRIO: largest host-memory update carried in the launch
+  // The last operation enqueued on `main` is a gather launched by gather_launch (and nothing
+  // else since): the one situation in which the priority update may run beside its predecessor.
+  // Every other enqueue on `main` clears it (touch_main).
+  bool tail_gather = false;
+  bool late_wait = false;  // $RR_UPDATE_LATE_WAIT=1 (experiment): off by default
   bool full_build = false;  // $RR_FULL_BUILD: rebuild every tile entry before each selection
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
@@ -195,6 +200,8 @@ struct rr_replay {
 };
 
 namespace {
+
+inline void touch_main(rr_replay* r) { r->tail_gather = false; }
 
 rr::Tiles tiles_of(const rr_replay* r) {
   rr::Tiles t;
@@ -265,7 +272,10 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
   if (p.n_bulk > 0) {
     c.block = 128;
     const size_t hdr = rr::kCopyHeaderBytes;
-    const size_t lim = (size_t)227 * 1024 / (size_t)r->g_ctas - 1024;  // 1 KB per-CTA system reserve
+    // 1 KB per-CTA system reserve; a gather also leaves room for one CTA of the priority
+    // update (33.5 KB static + 12 B per element) to run beside it on the same SM
+    const size_t beside = (gather && r->late_wait) ? (size_t)env_int("RR_GATHER_RESERVE_KB", 44) * 1024 : 0;
+    const size_t lim = ((size_t)227 * 1024 - beside) / (size_t)r->g_ctas - 1024;
     if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
     const int want = r->sm_count * r->g_ctas;
     c.grid = (int)std::min<uint64_t>((uint64_t)want, std::max<uint64_t>(items, 1));
@@ -377,6 +387,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   }
   r->full_build = env_int("RR_FULL_BUILD", 0) != 0;
+  r->late_wait = env_int("RR_UPDATE_LATE_WAIT", 0) != 0;
   r->inline_prio = std::min(rr::kInlinePrio, env_int("RR_INLINE_PRIO", rr::kInlinePrio));
   RR_CUDA(cudaStreamSynchronize(r->main));
 
@@ -801,6 +812,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     std::unique_lock<std::mutex> lk(r->m_);
     r->cvTail_.wait(lk, [&] { return r->safeTail_ == start; });
     if (rc == RR_OK) {
+      touch_main(r);
       cudaError_t e = cudaStreamWaitEvent(r->main, L.copied, 0);
       if (e == cudaSuccess) {
         e = rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n,
@@ -908,6 +920,7 @@ int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
   a.force_ordered = r->force_ordered;
   // The tile entries are kept current by commit / update / eviction; the full
   // build only runs here as a debugging cross-check ($RR_FULL_BUILD=1).
+  touch_main(r);
   if (r->full_build) {
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
     r->launches++;
@@ -963,13 +976,16 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
     plan.p.signal_val = ++r->signal_epoch;
     if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) rc = fail(RR_ERR_ARG, "sharded gather needs at least one field");
   }
+  touch_main(r);
   if (rc == RR_OK) rc = launch_plan(r, plan, r->main);
+  bool tail = rc == RR_OK && (plan.p.n_bulk > 0 || plan.p.n_simt > 0) && r->shard_world == 1;
   if (rc == RR_OK && r->signal_ptr != nullptr && r->wait_flags != nullptr) {
     // learner: the batch is complete when every shard has published this epoch
     cudaError_t e = rr::launch_wait_signals(r->wait_flags, r->wait_n, r->signal_epoch, &r->ctl->error,
                                             10ull * 1000 * 1000 * 1000, r->main);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "wait_signals: %s", cudaGetErrorString(e));
     r->launches++;
+    tail = false;
   }
   if (rc == RR_OK && r->profiling) {
     // keep this batch's ids for rr_gather_bench (a copy node here breaks the
@@ -983,7 +999,9 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
       r->hist_n++;
       r->hist_B = B;
     }
+    tail = false;
   }
+  r->tail_gather = tail;
   // blockPop bookkeeping (rela/prioritized_replay.h:94-102): the device side of
   // the eviction already ran in the selection kernel
   if (pop_n > 0) {
@@ -1045,6 +1063,7 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
     RR_CUDA(cudaEventRecord(r->evIn, cs));
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
   }
 
   int rc;
@@ -1058,6 +1077,7 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     Prefetched p = r->queue.front();
     if (p.B != batch) return fail(RR_ERR_ARG, "rr_sample: batch %d differs from the prefetched %d", batch, p.B);
     r->queue.pop_front();
+    touch_main(r);
     for (size_t fi = 0; fi < r->fields.size(); ++fi) {
       if (r->fields[fi].row_bytes == 0) continue;
       RR_CUDA(cudaMemcpyAsync(out_fields[fi], p.fields[fi], r->fields[fi].row_bytes * (size_t)batch,
@@ -1110,6 +1130,7 @@ int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields, float* ou
   if (cs != r->main) {  // the buffers may still be in use on the caller's stream
     RR_CUDA(cudaEventRecord(r->evIn, cs));
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
   }
   int slot = free_idslot(r);
   if (slot < 0) {
@@ -1166,6 +1187,7 @@ int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) 
   if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
     RR_CUDA(cudaEventRecord(r->evIn, cs));
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
   }
   const int slot = free_idslot(r);
   int rc = select_launch(r, batch, out_weights, slot, &r->pend_pop);
@@ -1187,6 +1209,7 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
   if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
     RR_CUDA(cudaEventRecord(r->evIn, cs));
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
   }
   int rc = gather_launch(r, batch, out_fields, slot, r->pend_pop);
   if (rc != RR_OK) return rc;
@@ -1215,11 +1238,16 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     if (cs != r->main) {
       RR_CUDA(cudaEventRecord(r->evIn, cs));
       RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
     }
   } else if (n <= r->inline_prio) {
     // a learner-sized batch: the priorities travel in the launch parameters
+    // host priorities ride in the launch: the kernel consumes nothing its predecessor produces
+    // when that is a gather, and may then run beside it (a caller on the internal stream itself
+    // may have put its own work there, so not for cs == main)
+    const int wait_late = (r->late_wait && r->tail_gather && cs != r->main) ? 1 : 0;
     RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n,
-                                     priority, r->alpha, is_weight, r->main));
+                                     priority, r->alpha, is_weight, wait_late, r->main));
     dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
@@ -1242,8 +1270,9 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   }
   if (dprio != nullptr)
     RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio,
-                              r->alpha, is_weight, r->main));
+                              r->alpha, is_weight, 0, r->main));
   r->launches++;
+  touch_main(r);
   if (prio_dev && cs != r->main) {
     RR_CUDA(cudaEventRecord(r->evOut, r->main));
     RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
@@ -1287,6 +1316,7 @@ int rr_stream_wait(rr_replay* r, void* stream) {
   if (static_cast<cudaStream_t>(stream) == r->main) return RR_OK;
   RR_CUDA(cudaEventRecord(r->evIn, static_cast<cudaStream_t>(stream)));
   RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+    touch_main(r);
   return RR_OK;
 }
 
@@ -1343,6 +1373,7 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
       if (rc != RR_OK) return rc;
     }
   }
+  touch_main(r);
   cudaEvent_t e0, e1;
   RR_CUDA(cudaEventCreate(&e0));
   RR_CUDA(cudaEventCreate(&e1));
@@ -1447,6 +1478,7 @@ int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums, float
     a.leafmin = r->leafmin;
     a.S_pad = r->S_pad;
     a.tile_log2 = r->tile_log2;
+    touch_main(r);
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   }
   RR_CUDA(cudaStreamSynchronize(r->main));

@@ -131,8 +131,11 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       mbar_fence_init();
       if ((uint32_t)tid < mine) it = decode_item(p, first + (uint32_t)tid * step);
     }
-    pdl_launch_dependents();
+    // The trigger comes AFTER the wait: a dependent that starts early (the
+    // priority update, which does not need this kernel's output) may then rely
+    // on everything this kernel waited for -- the selection -- being complete.
     pdl_wait();
+    pdl_launch_dependents();
     if (probe && tid == 0) probe[2] = clock64();
     if (active) {
       uint32_t use = 0;
@@ -164,8 +167,8 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     }
   } else {
     // ---- narrow fields: grid-strided units over the non-bulk warps
-    pdl_launch_dependents();
     pdl_wait();
+    pdl_launch_dependents();
     simt_rows(p);
   }
   if (p.signal == nullptr) return;

@@ -741,10 +741,9 @@ __device__ __forceinline__ float prio_at(const float* p, int i) { return p[i]; }
 __device__ __forceinline__ float prio_at(const PrioInline& p, int i) { return p.v[i]; }
 
 template <typename Prio>
-__global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
-                                                      const int32_t* __restrict__ ids, int n,
-                                                      const __grid_constant__ Prio prio, float alpha,
-                                                      int is_weight, const Tiles tiles) {
+__device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
+                                            const int32_t* __restrict__ ids, int n, const Prio& prio, float alpha,
+                                            int is_weight, const Tiles& tiles) {
   const int tile_log2 = tiles.tile_log2;
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
@@ -755,8 +754,6 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   __shared__ int sh_exact;
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
-  pdl_launch_dependents();
-  pdl_wait();
   if (blockIdx.x > 0) {
     __shared__ __align__(16) float sub[32][256];
     for (int i = tid; i < n; i += blockDim.x) {
@@ -900,6 +897,24 @@ __global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const 
   }
 }
 
+// wait_late: the kernel in front of this one on the stream is the gather of
+// the batch whose priorities are being updated (or of a batch drawn ahead).
+// Nothing here reads what a gather writes, and the gather triggers its
+// dependents only after its own wait for the selection, so the update runs
+// BESIDE the gather and waits for it at its end instead -- its successor, which
+// waits for this grid, then still sees the gather complete. The host sets it
+// only when it knows the predecessor (rr_update_priority).
+template <typename Prio>
+__global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
+                                                      const int32_t* __restrict__ ids, int n,
+                                                      const __grid_constant__ Prio prio, float alpha,
+                                                      int is_weight, const Tiles tiles, int wait_late) {
+  pdl_launch_dependents();
+  if (!wait_late) pdl_wait();
+  update_body<Prio>(ctl, w, evicted, ids, n, prio, alpha, is_weight, tiles);
+  if (wait_late) pdl_wait();
+}
+
 // ----------------------------------------------------------------- launches
 cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
   return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kBuildSpan), dim3(256), 0, stream, a.w, tiles_of(a));
@@ -921,17 +936,18 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
 }
 
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
+                          const float* prio, float alpha, int is_weight, int wait_late, cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
   const int grid = 1 + (n + 31) / 32;  // CTA 0: sum_ and weights; the others: one warp per element's tile
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio,
-                    alpha, is_weight, tiles);
+                    alpha, is_weight, tiles, wait_late);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
-                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream) {
+                                 int n, const float* prio_host, float alpha, int is_weight, int wait_late,
+                                 cudaStream_t stream) {
   if (n > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
   memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
@@ -940,7 +956,7 @@ cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const u
   if (e != cudaSuccess) return e;
   const int grid = 1 + (n + 31) / 32;
   return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, pin,
-                    alpha, is_weight, tiles);
+                    alpha, is_weight, tiles, wait_late);
 }
 
 }  // namespace rr
