@@ -78,6 +78,7 @@ struct Lane {
   cudaEvent_t committed = nullptr;  // commit kernel consumed dprio
   cudaEvent_t in = nullptr;         // marker on the caller's stream (device-resident inputs)
   cudaEvent_t gate = nullptr;       // marker on the internal stream at reservation time
+  cudaEvent_t gate2 = nullptr;      // same marker on the gather stream ($RR_GATHER_STREAM)
   uint8_t* pinned = nullptr;
   size_t pinned_cap = 0;
   float* dprio = nullptr;
@@ -165,6 +166,15 @@ struct rr_replay {
   // streams / events
   cudaStream_t main = nullptr;
   cudaEvent_t evIn = nullptr, evOut = nullptr, evGather = nullptr;
+  // $RR_GATHER_STREAM=1 (experiment; off by default): gathers run on
+  // their own stream `gs`, ordered after their selection by evSel. The control plane (select,
+  // update, commit) stays on `main` and no longer queues behind the HBM-bound gather; whoever
+  // needs a batch waits for the "gather done" event of its id slot (evSlot).
+  bool two_stream = false;
+  cudaStream_t gs = nullptr;
+  cudaEvent_t evSel = nullptr, evJoin = nullptr;
+  std::vector<cudaEvent_t> evSlot;  // per id slot: its gather has finished (recorded on gs)
+  std::vector<bool> slotPending;    // evSlot[i] recorded and not yet waited for by `main`
 
   // producer lanes
   std::mutex laneM_;
@@ -202,6 +212,66 @@ struct rr_replay {
 namespace {
 
 inline void touch_main(rr_replay* r) { r->tail_gather = false; }
+
+// Gathers of this replay go to the gather stream (single-GPU replays only: a sharded gather
+// publishes its completion flag in stream order with the learner's wait kernel).
+inline bool on_gather_stream(const rr_replay* r) {
+  return r->two_stream && r->shard_world == 1 && r->signal_ptr == nullptr;
+}
+
+// `main` waits for everything issued on the gather stream so far.
+int join_gather_stream(rr_replay* r) {
+  if (!r->two_stream) return RR_OK;
+  RR_CUDA(cudaEventRecord(r->evJoin, r->gs));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evJoin, 0));
+  std::fill(r->slotPending.begin(), r->slotPending.end(), false);
+  touch_main(r);
+  return RR_OK;
+}
+
+// Host-side wait for both internal streams (main first: gs may be waiting for a selection).
+int sync_streams(rr_replay* r) {
+  RR_CUDA(cudaStreamSynchronize(r->main));
+  if (r->two_stream) RR_CUDA(cudaStreamSynchronize(r->gs));
+  return RR_OK;
+}
+
+#define RR_SYNC_STREAMS(r)          \
+  do {                              \
+    int src_ = sync_streams(r);     \
+    if (src_ != RR_OK) return src_; \
+  } while (0)
+
+int new_idslot(rr_replay* r) {
+  r->idbuf.push_back(nullptr);
+  r->idcap.push_back(0);
+  r->idbusy.push_back(false);
+  r->slotPending.push_back(false);
+  cudaEvent_t ev = nullptr;
+  if (r->two_stream) RR_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  r->evSlot.push_back(ev);
+  return RR_OK;
+}
+
+// The batch of id slot `slot` becomes visible to the caller's stream `cs`.
+int publish_batch(rr_replay* r, cudaStream_t cs, int slot) {
+  if (on_gather_stream(r) && slot >= 0 && r->slotPending[(size_t)slot]) {
+    // evSlot covers the gather and, through evSel, the selection that wrote the IS weights
+    if (cs == r->main) {
+      RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)slot], 0));
+      r->slotPending[(size_t)slot] = false;
+      touch_main(r);
+    } else {
+      RR_CUDA(cudaStreamWaitEvent(cs, r->evSlot[(size_t)slot], 0));
+    }
+    return RR_OK;
+  }
+  if (cs != r->main) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
+  return RR_OK;
+}
 
 rr::Tiles tiles_of(const rr_replay* r) {
   rr::Tiles t;
@@ -354,6 +424,12 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaEventCreateWithFlags(&r->evIn, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evGather, cudaEventDisableTiming));
+  r->two_stream = env_int("RR_GATHER_STREAM", 0) != 0;
+  if (r->two_stream) {
+    RR_CUDA(cudaStreamCreateWithFlags(&r->gs, cudaStreamNonBlocking));
+    RR_CUDA(cudaEventCreateWithFlags(&r->evSel, cudaEventDisableTiming));
+    RR_CUDA(cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming));
+  }
 
   const size_t nt2 = ((((size_t)r->S_pad >> r->tile_log2) + 3) & ~(size_t)3);  // padded: bulk copies move 16-byte units
   RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
@@ -399,13 +475,15 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     RR_CUDA(cudaEventCreateWithFlags(&l.committed, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.in, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.gate, cudaEventDisableTiming));
+    if (r->two_stream) RR_CUDA(cudaEventCreateWithFlags(&l.gate2, cudaEventDisableTiming));
   }
   r->pstage.resize(4);
   for (auto& s : r->pstage) RR_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   const int nid = prefetch + 2;
-  r->idbuf.assign(nid, nullptr);
-  r->idcap.assign(nid, 0);
-  r->idbusy.assign(nid, false);
+  for (int i = 0; i < nid; ++i) {
+    int rc = new_idslot(r);
+    if (rc != RR_OK) return rc;
+  }
   *out = r;
   return RR_OK;
 }
@@ -431,6 +509,7 @@ int rr_destroy(rr_replay* r) {
     cudaEventDestroy(l.committed);
     cudaEventDestroy(l.in);
     cudaEventDestroy(l.gate);
+    if (l.gate2) cudaEventDestroy(l.gate2);
     cudaStreamDestroy(l.stream);
   }
   for (auto& s : r->pstage) {
@@ -449,6 +528,11 @@ int rr_destroy(rr_replay* r) {
   cudaEventDestroy(r->evIn);
   cudaEventDestroy(r->evOut);
   cudaEventDestroy(r->evGather);
+  for (auto ev : r->evSlot)
+    if (ev) cudaEventDestroy(ev);
+  if (r->evSel) cudaEventDestroy(r->evSel);
+  if (r->evJoin) cudaEventDestroy(r->evJoin);
+  if (r->gs) cudaStreamDestroy(r->gs);
   cudaStreamDestroy(r->main);
   delete r;
   return RR_OK;
@@ -513,6 +597,11 @@ int rr_set_shard(rr_replay* r, int rank, int world) {
 int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world) {
   if (r == nullptr || world < 0 || world > 32) return fail(RR_ERR_ARG, "rr_set_completion: bad argument");
   std::unique_lock<std::mutex> lk(r->m_);
+  if (r->two_stream) {  // from here on the gathers run on `main` again
+    DeviceScope dev_scope(r->device);
+    int jrc = join_gather_stream(r);
+    if (jrc != RR_OK) return jrc;
+  }
   r->signal_ptr = static_cast<unsigned long long*>(signal_ptr);
   r->wait_flags = static_cast<const unsigned long long*>(wait_flags);
   r->wait_n = world;
@@ -684,6 +773,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     // the slots being reused may still be read by gathers already issued on
     // the internal stream: the row copies below are ordered after this marker
     gate_err = cudaEventRecord(L.gate, r->main);
+    if (gate_err == cudaSuccess && r->two_stream) gate_err = cudaEventRecord(L.gate2, r->gs);
   }
   const int end = (start + n) % r->S;
   const int n1 = std::min(n, r->S - start);  // rows before the wrap
@@ -696,6 +786,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     // rows being overwritten may still be read by an in-flight gather
     if (gate_err != cudaSuccess) return fail(RR_ERR_CUDA, "rr_add: %s", cudaGetErrorString(gate_err));
     RR_CUDA(cudaStreamWaitEvent(L.stream, L.gate, 0));
+    if (r->two_stream) RR_CUDA(cudaStreamWaitEvent(L.stream, L.gate2, 0));
     if ((rows_dev || prio_dev)) {
       // order after the producer of the device-resident inputs
       RR_CUDA(cudaEventRecord(L.in, cs));
@@ -921,6 +1012,11 @@ int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
   // The tile entries are kept current by commit / update / eviction; the full
   // build only runs here as a debugging cross-check ($RR_FULL_BUILD=1).
   touch_main(r);
+  if (r->slotPending[(size_t)idslot]) {
+    // the previous gather out of this id buffer (gather stream) must be done reading it
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)idslot], 0));
+    r->slotPending[(size_t)idslot] = false;
+  }
   if (r->full_build) {
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
     r->launches++;
@@ -963,10 +1059,18 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
   }
   CopyPlan plan;
   int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
+  const bool use_gs = on_gather_stream(r);
+  cudaStream_t gstream = use_gs ? r->gs : r->main;
+  if (rc == RR_OK && use_gs) {
+    // the gather follows ITS selection (the last thing on `main`), not main's later work
+    cudaError_t e = cudaEventRecord(r->evSel, r->main);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(r->gs, r->evSel, 0);
+    if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
+  }
   if (rc == RR_OK && conv.n > 0) {
     conv.B = B;
     conv.ids = ids;
-    cudaError_t e = rr::launch_gather_convert(conv, r->sm_count, r->main);
+    cudaError_t e = rr::launch_gather_convert(conv, r->sm_count, gstream);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather_convert: %s", cudaGetErrorString(e));
     r->launches++;
   }
@@ -977,8 +1081,13 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
     if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) rc = fail(RR_ERR_ARG, "sharded gather needs at least one field");
   }
   touch_main(r);
-  if (rc == RR_OK) rc = launch_plan(r, plan, r->main);
-  bool tail = rc == RR_OK && (plan.p.n_bulk > 0 || plan.p.n_simt > 0) && r->shard_world == 1;
+  if (rc == RR_OK) rc = launch_plan(r, plan, gstream);
+  if (rc == RR_OK && use_gs) {
+    cudaError_t e = cudaEventRecord(r->evSlot[(size_t)idslot], r->gs);
+    if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
+    r->slotPending[(size_t)idslot] = true;
+  }
+  bool tail = rc == RR_OK && !use_gs && (plan.p.n_bulk > 0 || plan.p.n_simt > 0) && r->shard_world == 1;
   if (rc == RR_OK && r->signal_ptr != nullptr && r->wait_flags != nullptr) {
     // learner: the batch is complete when every shard has published this epoch
     cudaError_t e = rr::launch_wait_signals(r->wait_flags, r->wait_n, r->signal_epoch, &r->ctl->error,
@@ -1078,6 +1187,10 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     if (p.B != batch) return fail(RR_ERR_ARG, "rr_sample: batch %d differs from the prefetched %d", batch, p.B);
     r->queue.pop_front();
     touch_main(r);
+    if (r->slotPending[(size_t)p.idslot]) {  // its gather ran on the gather stream
+      RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)p.idslot], 0));
+      r->slotPending[(size_t)p.idslot] = false;
+    }
     for (size_t fi = 0; fi < r->fields.size(); ++fi) {
       if (r->fields[fi].row_bytes == 0) continue;
       RR_CUDA(cudaMemcpyAsync(out_fields[fi], p.fields[fi], r->fields[fi].row_bytes * (size_t)batch,
@@ -1092,10 +1205,8 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   r->idbusy[slot] = true;
   r->cur_ids = slot;
   r->cur_B = batch;
-  if (cs != r->main) {
-    RR_CUDA(cudaEventRecord(r->evOut, r->main));
-    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
-  }
+  rc = publish_batch(r, cs, slot);
+  if (rc != RR_OK) return rc;
 
   // top the queue up to `prefetch` batches (lines 223-230); they are selected
   // now, i.e. before this batch's updatePriority, like the reference's futures
@@ -1135,9 +1246,8 @@ int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields, float* ou
   int slot = free_idslot(r);
   if (slot < 0) {
     slot = (int)r->idbuf.size();
-    r->idbuf.push_back(nullptr);
-    r->idcap.push_back(0);
-    r->idbusy.push_back(false);
+    int nrc = new_idslot(r);
+    if (nrc != RR_OK) return nrc;
   }
   int rc = sample_into(r, batch, out_fields, out_weights, slot);
   if (rc != RR_OK) return rc;
@@ -1161,11 +1271,7 @@ int rr_take_prefetched(rr_replay* r, void* stream) {
   r->queue.pop_front();
   r->cur_ids = p.idslot;
   r->cur_B = p.B;
-  if (cs != r->main) {
-    RR_CUDA(cudaEventRecord(r->evOut, r->main));
-    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
-  }
-  return RR_OK;
+  return publish_batch(r, cs, p.idslot);
 }
 
 int rr_prefetched(rr_replay* r) { return r == nullptr ? 0 : (int)r->queue.size(); }
@@ -1216,11 +1322,7 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
   r->idbusy[slot] = true;
   r->cur_ids = slot;
   r->cur_B = batch;
-  if (cs != r->main) {
-    RR_CUDA(cudaEventRecord(r->evOut, r->main));
-    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
-  }
-  return RR_OK;
+  return publish_batch(r, cs, slot);
 }
 
 int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flags, void* stream) {
@@ -1287,7 +1389,10 @@ int rr_sync(rr_replay* r) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_sync: null");
   DeviceScope dev_scope(r->device);
   for (auto& l : r->lanes) RR_CUDA(cudaStreamSynchronize(l.stream));
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  {
+    int src = sync_streams(r);
+    if (src != RR_OK) return src;
+  }
   int err = 0;
   RR_CUDA(cudaMemcpy(&err, &r->ctl->error, sizeof(int), cudaMemcpyDeviceToHost));
   if (err != 0) {
@@ -1303,9 +1408,13 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
   DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
-  if (static_cast<cudaStream_t>(stream) == r->main) return RR_OK;
+  if (static_cast<cudaStream_t>(stream) == r->main) return join_gather_stream(r);
   RR_CUDA(cudaEventRecord(r->evOut, r->main));
   RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
+  if (r->two_stream) {
+    RR_CUDA(cudaEventRecord(r->evJoin, r->gs));
+    RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evJoin, 0));
+  }
   return RR_OK;
 }
 
@@ -1329,7 +1438,7 @@ int rr_get_stream(rr_replay* r, void** out_stream) {
 int rr_set_profiling(rr_replay* r, int enabled, int max_batch) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_set_profiling: null");
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   if (enabled && r->hist_cap < max_batch) {
     for (auto* hp : r->hist) RR_CUDA(cudaFree(hp));
     r->hist.assign(16, nullptr);
@@ -1373,6 +1482,10 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
       if (rc != RR_OK) return rc;
     }
   }
+  {
+    int jrc = join_gather_stream(r);
+    if (jrc != RR_OK) return jrc;
+  }
   touch_main(r);
   cudaEvent_t e0, e1;
   RR_CUDA(cudaEventCreate(&e0));
@@ -1406,7 +1519,7 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
 int rr_get_stats(rr_replay* r, rr_stats* out) {
   if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_get_stats: null");
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   rr::Ctl h;
   RR_CUDA(cudaMemcpy(&h, r->ctl, sizeof(h), cudaMemcpyDeviceToHost));
   out->kernel_launches = r->launches.load();
@@ -1424,7 +1537,7 @@ int rr_last_sample_ids(rr_replay* r, int n, int32_t* out) {
   if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_last_sample_ids: null");
   if (r->cur_ids < 0 || n != r->cur_B) return fail(RR_ERR_STATE, "rr_last_sample_ids: no batch of %d outstanding", n);
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   RR_CUDA(cudaMemcpy(out, r->idbuf[r->cur_ids], sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost));
   return RR_OK;
 }
@@ -1439,7 +1552,7 @@ int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size
     if (size) *size = r->size_;
     if (safe_size) *safe_size = r->safeSize_;
   }
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   if (sum) RR_CUDA(cudaMemcpy(sum, &r->ctl->sum, sizeof(double), cudaMemcpyDeviceToHost));
   return RR_OK;
 }
@@ -1447,7 +1560,7 @@ int rr_debug_state(rr_replay* r, int* head, int* tail, int* size, int* safe_size
 int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
   if (r == nullptr || out16 == nullptr) return fail(RR_ERR_ARG, "rr_debug_select_probe: null");
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   RR_CUDA(cudaMemcpy(out16, r->ctl->probe, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
   return RR_OK;
 }
@@ -1455,7 +1568,7 @@ int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
 int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_weights: null");
   DeviceScope dev_scope(r->device);
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   if (out_w) RR_CUDA(cudaMemcpy(out_w, r->w, sizeof(float) * (size_t)r->S, cudaMemcpyDeviceToHost));
   if (out_evicted) RR_CUDA(cudaMemcpy(out_evicted, r->evicted, (size_t)r->S, cudaMemcpyDeviceToHost));
   return RR_OK;
@@ -1481,7 +1594,7 @@ int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums, float
     touch_main(r);
     RR_CUDA(rr::launch_build_hierarchy(a, r->main));
   }
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   const int n = std::min(cap, nt);
   if (out_sums && n > 0)
     RR_CUDA(cudaMemcpy(out_sums, leaves ? r->leaf : r->l2, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
@@ -1581,7 +1694,7 @@ int rr_save(rr_replay* r, const char* path) {
   if (r->cur_ids >= 0 || r->pend_slot >= 0)
     return fail(RR_ERR_STATE, "rr_save: a sampled batch is outstanding (update its priorities first)");
   if (!r->queue.empty()) return fail(RR_ERR_STATE, "rr_save: %d prefetched batches are pending", (int)r->queue.size());
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   rr::Ctl ctl;
   RR_CUDA(cudaMemcpy(&ctl, r->ctl, sizeof(ctl), cudaMemcpyDeviceToHost));
   if (ctl.error != 0) return fail(RR_ERR_STATE, "rr_save: the replay holds a device-side error (%d)", ctl.error);
@@ -1679,7 +1792,7 @@ int rr_load(rr_replay* r, const char* path) {
       return fail(RR_ERR_ARG, "rr_load: field '%s' (%llu B x %u) does not match the schema's '%s' (%llu B x %u)", name.c_str(),
                   (unsigned long long)rb, chunks, f.name.c_str(), (unsigned long long)f.row_bytes, f.chunks);
   }
-  RR_CUDA(cudaStreamSynchronize(r->main));
+  RR_SYNC_STREAMS(r);
   {
     std::vector<float> w((size_t)r->S);
     std::vector<uint8_t> ev((size_t)r->S);
