@@ -16,6 +16,8 @@ O=gpurun_out
   timeout 300 python tools/bench_gather_stream.py $((1 << 20)) 512 2 5000
   timeout 300 python tools/bench_gather_stream.py $((1 << 21)) 512 2 5000
   timeout 300 python tools/bench_gather_stream.py $((1 << 21)) 512 3 5000
+  echo "== 3b. config 4: actor-side math, reference leg on this host + device leg"
+  timeout 300 python tools/bench_actor_math.py --iters 3000
   echo "== 4. bench line, default and under the switch (e2e with prefetch 2 is the number to compare)"
   timeout 600 python bench.py > $O/r2a_bench_default.json
   tail -c 400 $O/r2a_bench_default.json; echo
