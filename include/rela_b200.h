@@ -23,9 +23,17 @@
  * reference's blockAppend protocol, prioritized_replay.h:43-78, including its
  * blocking when all S slots are in flight). rr_sample and rr_update_priority
  * must come from one thread at a time (the reference holds mSampler_).
- * All device work is issued on one internal stream in the order the calls
- * commit; rr_sample / rr_update_priority hand-shake with the caller's stream
- * by events and never block the host.
+ * The control plane (selection, priority update, add commit) is issued on one
+ * internal stream in the order the calls commit; gathers of batches drawn
+ * ahead run on two internal gather streams beside it. rr_sample /
+ * rr_update_priority hand-shake with the caller's stream by events and never
+ * block the host.
+ *
+ * Device-side errors (a selection that runs past the last element -- the
+ * reference's assert at prioritized_replay.h:297-302 -- or a shard that never
+ * signals) are sticky: the kernel mirrors the code into host-visible memory and
+ * every later rr_sample* / rr_prefetch* / rr_take_prefetched /
+ * rr_update_priority fails with it until rr_sync has reported and cleared it.
  */
 #ifndef RELA_B200_H_
 #define RELA_B200_H_
@@ -128,10 +136,11 @@ int rr_take_prefetched(rr_replay* r, void* stream);
 int rr_prefetched(rr_replay* r);
 
 /* rr_sample in two steps, so that a host layer can allocate the batch tensors
- * while the selection kernels already run: rr_sample_select issues the prefix
- * hierarchy, selection, eviction and importance weights (sample_ lines
- * 258-325); rr_sample_gather issues makeBatch (line 326) into out_fields and
- * orders the results on `stream`. rr_sample == select + gather. */
+ * while the selection kernel already runs: rr_sample_select issues the
+ * selection, eviction and raw importance weights (sample_ lines 258-321);
+ * rr_sample_gather issues makeBatch (line 326) into out_fields, normalises the
+ * importance weights into out_weights (line 322) in the same kernel and orders
+ * the results on `stream`. rr_sample == select + gather. */
 int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream);
 int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream);
 
@@ -149,51 +158,104 @@ int rr_scatter_rows(rr_replay* r, int n, int nfields, const uint64_t* row_bytes,
                     void* const* dst_base, const int32_t* dst_rows, void* stream);
 
 /* ---------------------------------------------------------------------------
- * Capacity sharding over the GPUs of one NVSwitch box (no reference
- * counterpart). One process per GPU. Every shard keeps
- * the FULL control state (weights, evicted flags, prefix hierarchy, sum_, RNG:
- * 4 B per slot) and applies every add / sample / update in the same order, so
- * all shards select the same ids -- bit-identical to the single-buffer
- * reference -- with no collective in the sampling path. Only the payload slabs
- * are partitioned: shard `rank` stores slots [rank * ceil(S / world), ...).
- *   rr_add*  receives the whole block; rows of other shards are skipped.
- *   rr_sample gathers only the rows this shard owns, straight into
- *            out_fields, which on non-learner shards are peer-mapped pointers
- *            (rr_ipc_open) into the learner GPU's batch tensors: NVLink stores.
- * Call rr_set_shard before rr_set_schema. prefetch must be 0. */
+ * One replay striped over the GPUs of one NVSwitch box (no reference
+ * counterpart). One process per GPU, SPMD: every shard
+ * keeps the FULL control state (weights, evicted flags, prefix hierarchy,
+ * sum_, RNG: ~4.1 B per slot) and applies every add / sample / update in the
+ * same order, so all shards select the same ids -- bit-identical to the
+ * single-buffer reference -- with no collective in the sampling path. Only the
+ * payload slabs are partitioned: shard `rank` stores slots
+ * [rank * ceil(S / world), ...). Call rr_set_shard before rr_set_schema. The
+ * host side of the protocol is rela_b200/cpp/sharded_core.cc. */
 int rr_set_shard(rr_replay* r, int rank, int world);
 int rr_shard_range(const rr_replay* r, int* lo, int* hi);
+/* Device base pointers of the field slabs (for rr_ipc_export): out[nfields]. */
+int rr_slab_ptrs(rr_replay* r, void** out, int cap);
 
-/* Completion of a sharded batch without a collective: after this call every
- * rr_sample's gather kernel ends by publishing a sample counter ("epoch", the
- * same on all shards because all shards run all samples) at `signal_ptr` -- this
- * shard's 8-byte flag in the LEARNER's memory (peer-mapped on the other shards)
- * -- with a system-scope release after its stores. On the learner, pass
- * `wait_flags` = the base of the `world` flags: its rr_sample then appends a
- * one-warp kernel that acquires all of them, so the batch is complete, in
- * stream order, when rr_sample's results are. wait_flags == NULL elsewhere;
- * signal_ptr == NULL switches the mechanism off. */
-int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world);
+/* Where the rows of a batch drawn from a striped replay go. The batch of
+ * `batch_total` rows is split evenly over n_learners learner GPUs: rows
+ * [l * B, (l + 1) * B), B = batch_total / n_learners, belong to learner l and
+ * are stored by whichever shard owns their slot straight into THAT learner's
+ * batch tensors (bulk stores over NVLink). n_learners == 1: one learner gets
+ * the whole batch; n_learners == world: every GPU draws its share of one
+ * stratified batch of world * B (a data-parallel learner; equivalent to ONE
+ * reference replay sampling world * B and splitting the batch). */
+typedef struct rr_route {
+  int n_learners;
+  const void* dst_tab;       /* DEVICE array uint64[n_learners * nfields]: base of field f of
+                                learner l's batch tensors (local or peer-mapped pointers)      */
+  void* const* signal_ptrs;  /* host array [n_signals]: this shard's 8-byte completion flag in
+                                each rank's memory (peer-mapped); published (st.release.sys)
+                                with the selection epoch after this shard's stores           */
+  int n_signals;
+  const void* wait_flags;    /* device array of wait_n flags in THIS rank's memory, one per
+                                shard, or NULL if this rank does not consume the batch        */
+  int wait_n;
+  int my_learner;            /* this rank's index among the learners, -1 if none             */
+  float* out_weights;        /* this learner's B importance weights (device), or NULL        */
+  int on_demand;             /* != 0: the batch is taken right away (no prefetch): its gather
+                                stays on the internal stream behind its selection             */
+} rr_route;
 
-/* One-sided exchange of small messages between shards (the learner's new
- * priorities -> every other shard) without a collective. rr_peer_put copies
- * `bytes` from `src` (device) into n peer-mapped buffers and then publishes
- * `epoch` at each peer's 8-byte flag (system-scope release), on `stream`.
- * rr_wait_flags enqueues a one-warp kernel on `stream` that acquires until
- * flags[0..n) >= epoch (10 s timeout -> *device_error = RR_ERR_CUDA;
- * device_error is a DEVICE pointer). */
+/* rr_prefetch_into for a shard of a striped replay: select batch_total ids
+ * (identically on every shard), gather the rows this shard owns to their
+ * learners, queue the batch. rr_take_prefetched then makes it current and, on a
+ * learner, appends a one-warp kernel to `stream` that acquires the wait_n
+ * flags: the batch is complete, in stream order, when that kernel is. Every
+ * rank passes wait_flags (rr_add_sharded_rows waits on them before it reuses
+ * slots a queued gather may still read); only learners wait when they take. */
+int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* route, void* stream);
+
+/* Collective add into a striped replay. Step 1 reserves the block of n_total
+ * slots (identically on every shard) and moves THIS rank's rows -- rows
+ * [row0, row0 + n_local) of the block, device memory, field_base[f] packed --
+ * straight into the slabs of the shards that own their slots (slab_tab: DEVICE
+ * array uint64[world * nfields] of peer-mapped slab bases, rank-major).
+ * RR_ERR_STATE when the ring is full (the reference blocks there; an SPMD
+ * caller must sample first). Step 2, after the ranks have exchanged their
+ * weights (rr_exchange, ordered after step 1 so that a shard that sees the
+ * weights also sees the rows): weights_all = priority^alpha (or raw priorities
+ * without RR_PRIO_IS_WEIGHT) of the whole block, device memory. */
+int rr_add_sharded_rows(rr_replay* r, int n_total, int row0, int n_local, const void* const* field_base,
+                        const void* slab_tab, void* stream);
+int rr_add_sharded_commit(rr_replay* r, const float* weights_all, unsigned flags);
+
+/* All-gather of small messages between shards through peer memory, one launch
+ * on the replay's internal stream (ordered after `stream`): copy `bytes` from
+ * `src` (device) into n peer-mapped buffers, publish `epoch` at the n flags
+ * (st.release.sys), then acquire until wait_flags[0..n_wait) (this rank's
+ * memory) have all reached `epoch` (10 s timeout -> sticky device error). A
+ * rank with nothing to contribute passes bytes == 0, n == 0 and only waits. */
+int rr_exchange(rr_replay* r, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs,
+                int n, uint64_t epoch, const void* wait_flags, int n_wait, void* stream);
+
+/* Lower-level one-sided primitives (used by tests): rr_peer_put copies `bytes`
+ * from `src` (device) into n peer-mapped buffers and then publishes `epoch` at
+ * each peer's 8-byte flag, on `stream`. rr_wait_flags enqueues a one-warp
+ * kernel on `stream` that acquires until flags[0..n) >= epoch (10 s timeout ->
+ * *device_error = RR_ERR_CUDA; device_error is a DEVICE pointer). */
 int rr_peer_put(int device, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs, int n,
                 uint64_t epoch, void* stream);
 int rr_wait_flags(int device, const void* flags, int n, uint64_t epoch, int* device_error, void* stream);
 
-/* Peer-memory plumbing for the learner's batch buffers: cudaMalloc'ed on the
- * learner GPU, exported as a 64-byte CUDA IPC handle, opened by the other
- * shards' processes with peer access over NVLink. */
+/* Peer-memory plumbing: cudaMalloc'ed buffers exported as 64-byte CUDA IPC
+ * handles and opened by the other shards' processes with peer access. */
 int rr_device_alloc(int device, uint64_t bytes, void** out_ptr); /* zero-filled */
 int rr_device_free(int device, void* ptr);
 int rr_ipc_export(int device, const void* ptr, void* handle64_out);
 int rr_ipc_open(int device, const void* handle64, void** out_ptr);
 int rr_ipc_close(int device, void* ptr);
+
+/* Rendezvous of the shard processes of one box, used at set-up time only (IPC
+ * handle exchange): a POSIX shared-memory segment named after `name`, created
+ * by rank 0. Up to 16 ranks, up to 64 KB per rank and all-gather. */
+typedef struct rr_group rr_group;
+int rr_group_create(rr_group** out, const char* name, int rank, int world);
+int rr_group_allgather(rr_group* g, const void* mine, uint64_t bytes, void* all_out);
+int rr_group_barrier(rr_group* g);
+int rr_group_rank(const rr_group* g);
+int rr_group_world(const rr_group* g);
+int rr_group_destroy(rr_group* g);
 
 int rr_size(const rr_replay* r);    /* safeSize_ (prioritized_replay.h:247) */
 int rr_num_add(const rr_replay* r); /* numAdd_   (prioritized_replay.h:251) */
@@ -222,11 +284,13 @@ int rr_stream_wait(rr_replay* r, void* stream);
  * back to back on the internal stream, `reps` times over all sets, rotating
  * over n_out_sets output batches (out_fields[o * nfields + f], device), and
  * times the whole region with one CUDA-event pair: ms_per_launch is the
- * kernel's average duration without per-launch event overhead. */
+ * kernel's average duration without per-launch event overhead. streams == 1:
+ * back to back on the internal stream; streams == 2: alternating over the two
+ * gather streams, the way the gathers of batches drawn ahead are issued. */
 int rr_set_profiling(rr_replay* r, int enabled, int max_batch);
 int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields,
-                    int reps, double* ms_per_launch, uint64_t* launches,
-                    uint64_t* bytes_per_launch);
+                    int reps, int streams, double* ms_per_launch,
+                    uint64_t* launches, uint64_t* bytes_per_launch);
 
 /* Learner-side fusion at the batch hand-off (not in the reference; SURVEY 8(f)
  * rank 3). The reference's learner converts the sampled u8 frames right after
@@ -248,14 +312,21 @@ int rr_set_output_format(rr_replay* r, int field, int format);
 /* Checkpoint / restore (not in the reference). rr_save
  * writes the ring counters, the mt19937 state, sum_, the weights, the eviction
  * flags and the live rows of this replay's slot range to `path` (blocking;
- * device -> pinned bounce buffer -> file). It needs a quiescent replay: no add
- * in flight, no sampled batch awaiting its priorities, no prefetched batch.
+ * device -> pinned bounce buffer -> <path>.tmp, fsync, rename). No add may be
+ * in flight and no sampled batch may await its priorities; batches drawn
+ * AHEAD (prefetch) are saved with their ids, weights and gathered rows.
  * rr_load restores into a freshly created replay with the same capacity,
  * alpha, beta, shard and schema; sampling then continues bit-identically to
- * the run that saved (same ids, same bytes, same weights). A sharded replay
- * saves / loads one file per rank. */
+ * the run that saved (same ids, same bytes, same weights), prefetched batches
+ * included: they return to the queue in library-owned buffers. A host layer
+ * that owns its batch buffers (rr_prefetch_into) claims entry k with
+ * rr_restore_prefetched (copied into its buffers; rr_prefetched_batch(k) is the
+ * entry's batch size). A sharded replay saves / loads one file per rank and
+ * must have no batch queued. */
 int rr_save(rr_replay* r, const char* path);
 int rr_load(rr_replay* r, const char* path);
+int rr_restore_prefetched(rr_replay* r, int k, void* const* out_fields, float* out_weights, void* stream);
+int rr_prefetched_batch(rr_replay* r, int k);
 
 /* Test/debug introspection (synchronises). ids: the physical slot ids of the
  * batch last returned by rr_sample (the reference's sampledIds_). */
@@ -266,8 +337,8 @@ int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host)
 /* The selection kernel's per-tile weight sums and smallest non-zero weights,
  * as maintained incrementally by add / update / eviction. rebuild != 0 first
  * recomputes every entry from the weights (tests compare the two bit for bit).
- * level 0: the tiles the selection kernel scans; level 1: their 256-slot
- * leaves (the same thing unless the buffer has more than 4 M slots).
+ * level 0: the groups the selection kernel scans (16,384 slots); level 1:
+ * their 256-slot leaves.
  * Copies min(cap, tiles) entries; returns the number of tiles (< 0: error). */
 int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums_host,
                    float* out_mins_host, int cap, int* out_tile_slots);

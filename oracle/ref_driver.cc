@@ -223,8 +223,17 @@ void ref_ff_weights(void* hv, float* out_w, unsigned char* out_evicted) {
 // Timed sample+update loop run entirely in C++ (no ctypes overhead): `cycles`
 // iterations of sample(B,"cpu") + updatePriority(prio_pool[c % pool]).
 // Returns seconds.
+double ref_ff_cycle_loop_dev(void* hv, int B, int cycles, const float* prio_pool, int pool, const char* device);
 double ref_ff_cycle_loop(void* hv, int B, int cycles, const float* prio_pool, int pool) {
+  return ref_ff_cycle_loop_dev(hv, B, cycles, prio_pool, pool, "cpu");
+}
+
+// Same with the `device` argument of sample() given by the caller: "cuda:0" makes the reference
+// copy the assembled batch to the learner GPU (types.cc:34-43, pageable host memory), the
+// like-for-like "batch on the learner device" number.
+double ref_ff_cycle_loop_dev(void* hv, int B, int cycles, const float* prio_pool, int pool, const char* device) {
   auto* h = static_cast<FFHandle*>(hv);
+  const std::string dev(device);
   std::vector<torch::Tensor> prios;
   for (int p = 0; p < pool; ++p) {
     prios.push_back(torch::from_blob(const_cast<float*>(prio_pool) + (size_t)p * B, {B}, torch::kFloat32).clone());
@@ -233,7 +242,8 @@ double ref_ff_cycle_loop(void* hv, int B, int cycles, const float* prio_pool, in
   for (int c = 0; c < cycles; ++c) {
     FFTransition batch;
     torch::Tensor w;
-    std::tie(batch, w) = h->replay->sample(B, "cpu");
+    std::tie(batch, w) = h->replay->sample(B, dev);
+    if (dev != "cpu") w = w.cpu();  // the learner's read of the step's result; waits for the copies
     h->replay->updatePriority(prios[c % pool]);
   }
   auto t1 = std::chrono::steady_clock::now();

@@ -12,10 +12,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librela_b200.so")
-KERNEL_SOURCES = ["replay.cu", "row_copy.cu", "gather_convert.cu", "select.cu", "actor_math.cu"]
+KERNEL_SOURCES = ["replay.cu", "row_copy.cu", "gather_convert.cu", "select.cu", "actor_math.cu", "group.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC,-Wall", "-shared", "-cudart", "static",
+    "-Xcompiler", "-fPIC,-Wall", "-shared", "-cudart", "static", "-lrt",
 ]
 
 
@@ -64,7 +64,7 @@ def _torch_flags():
 
 CPP = os.path.join(HERE, "cpp")
 SHIM = os.path.join(HERE, "_C.so")
-SHIM_SOURCES = ["replay_core.cc", "sequence_assembler.cc", "pybind_module.cc"]
+SHIM_SOURCES = ["replay_core.cc", "sharded_core.cc", "sequence_assembler.cc", "pybind_module.cc"]
 
 
 def build_shim(force=False):

@@ -17,8 +17,15 @@ RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
-    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence", "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority", "rr_aggregate_priority",
-    "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_set_completion", "rr_set_shard", "rr_shard_range", "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
+    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence",
+    "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
+    "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority",
+    "rr_aggregate_priority", "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_prefetch_routed",
+    "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_exchange",
+    "rr_set_shard", "rr_shard_range", "rr_slab_ptrs", "rr_add_sharded_rows", "rr_add_sharded_commit",
+    "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
+    "rr_group_create", "rr_group_allgather", "rr_group_barrier", "rr_group_rank", "rr_group_world",
+    "rr_group_destroy",
 ]
 
 
@@ -31,6 +38,12 @@ class RRStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "kernel_launches", "samples", "samples_exact", "samples_ordered", "pops", "device_errors",
         "slab_bytes", "h2d_bytes")]
+
+
+class RRRoute(C.Structure):
+    _fields_ = [("n_learners", C.c_int), ("dst_tab", C.c_void_p), ("signal_ptrs", C.POINTER(C.c_void_p)),
+                ("n_signals", C.c_int), ("wait_flags", C.c_void_p), ("wait_n", C.c_int),
+                ("my_learner", C.c_int), ("out_weights", C.c_void_p), ("on_demand", C.c_int)]
 
 
 class ReplayError(RuntimeError):
@@ -78,7 +91,7 @@ def lib():
         L.rr_load.argtypes = [vp, C.c_char_p]
         L.rr_set_output_format.argtypes = [vp, i, i]
         L.rr_set_profiling.argtypes = [vp, i, i]
-        L.rr_gather_bench.argtypes = [vp, i, vp, i, vp, vp, vp]
+        L.rr_gather_bench.argtypes = [vp, i, vp, i, i, vp, vp, vp]
         L.rr_nstep_return.argtypes = [i, i, f, vp, vp, vp, vp, vp, i, vp]
         L.rr_td_priority.argtypes = [i, vp, vp, vp, vp, f, vp, vp]
         L.rr_aggregate_priority.argtypes = [i, i, vp, vp, f, i, vp, vp]
@@ -87,7 +100,19 @@ def lib():
         L.rr_scatter_rows.argtypes = [vp, i, i, vp, vp, vp, vp, vp]
         L.rr_peer_put.argtypes = [i, vp, C.c_uint64, vp, vp, i, C.c_uint64, vp]
         L.rr_wait_flags.argtypes = [i, vp, i, C.c_uint64, vp, vp]
-        L.rr_set_completion.argtypes = [vp, vp, vp, i]
+        L.rr_exchange.argtypes = [vp, vp, C.c_uint64, vp, vp, i, C.c_uint64, vp, i, vp]
+        L.rr_prefetch_routed.argtypes = [vp, i, C.POINTER(RRRoute), vp]
+        L.rr_slab_ptrs.argtypes = [vp, vp, i]
+        L.rr_add_sharded_rows.argtypes = [vp, i, i, i, vp, vp, vp]
+        L.rr_add_sharded_commit.argtypes = [vp, vp, u]
+        L.rr_restore_prefetched.argtypes = [vp, i, vp, vp, vp]
+        L.rr_prefetched_batch.argtypes = [vp, i]
+        L.rr_group_create.argtypes = [C.POINTER(vp), C.c_char_p, i, i]
+        L.rr_group_allgather.argtypes = [vp, vp, C.c_uint64, vp]
+        L.rr_group_barrier.argtypes = [vp]
+        L.rr_group_rank.argtypes = [vp]
+        L.rr_group_world.argtypes = [vp]
+        L.rr_group_destroy.argtypes = [vp]
         L.rr_set_shard.argtypes = [vp, i, i]
         L.rr_shard_range.argtypes = [vp, vp, vp]
         L.rr_device_alloc.argtypes = [i, C.c_uint64, C.POINTER(vp)]

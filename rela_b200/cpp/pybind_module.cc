@@ -7,12 +7,19 @@
 //     .size() .num_add() .sample(batchsize, device) .update_priority(priority)
 //                                                  pybind.cc:37-59
 // Additions (the reference binds no producer side; its actors call add from
-// C++): .add(...), .sync(), .handle(), .schema(), and a `device` keyword.
+// C++): .add(...), .sync(), .handle(), .schema(), a `device` keyword, and the
+// keywords of a replay striped over several GPUs (shard_rank, shard_world,
+// learner, group: ShardConfig in rela_b200/replay_core.h). The actor-side
+// arithmetic kernels are module functions: nstep_return, td_priority,
+// aggregate_priority.
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 #include <torch/csrc/DynamicTypes.h>
 #include <torch/extension.h>
 
+#include <c10/cuda/CUDAStream.h>
+
+#include "rela_b200.h"
 #include "rela_b200/sequence_assembler.h"
 #include "rela_b200/types.h"
 
@@ -37,6 +44,18 @@ void bindCommon(PyClass& c) {
         py::arg("beta"), py::arg("prefetch"))
       .def(py::init<int, int, float, float, int, int>(), py::arg("capacity"), py::arg("seed"), py::arg("alpha"),
            py::arg("beta"), py::arg("prefetch"), py::arg("device"))
+      .def(py::init([](int capacity, int seed, float alpha, float beta, int prefetch, int device, int shard_rank,
+                       int shard_world, int learner, const std::string& group) {
+             ShardConfig sc;
+             sc.rank = shard_rank;
+             sc.world = shard_world;
+             sc.learner = learner;
+             sc.group = group;
+             return std::make_shared<Replay>(capacity, seed, alpha, beta, prefetch, device, sc);
+           }),
+           py::arg("capacity"), py::arg("seed"), py::arg("alpha"), py::arg("beta"), py::arg("prefetch"),
+           py::arg("device"), py::arg("shard_rank"), py::arg("shard_world"), py::arg("learner") = -1,
+           py::arg("group") = "rela_b200")
       .def("size", &Replay::size)
       .def("num_add", &Replay::numAdd)
       .def("sample", &Replay::sample, py::call_guard<py::gil_scoped_release>())
@@ -58,8 +77,77 @@ void bindCommon(PyClass& c) {
 
 }  // namespace
 
+namespace {
+
+void* currentStream(const torch::Tensor& t) {
+  return (void*)c10::cuda::getCurrentCUDAStream(t.device().index()).stream();
+}
+
+void checkActor(int rc, const char* where) {
+  if (rc != RR_OK) throwLast(rc, where);
+}
+
+// MultiStepTransitionBuffer::popTransition arithmetic (rela/dqn_actor.h:58-106): reward float32
+// [n + 1, K], terminal bool / uint8 [n + 1, K] on CUDA -> (return [K], bootstrap [K], terminal [K] bool)
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> nstepReturn(const torch::Tensor& reward,
+                                                                    const torch::Tensor& terminal, double gamma,
+                                                                    bool contract_fma) {
+  if (!reward.is_cuda() || reward.scalar_type() != torch::kFloat32 || reward.dim() != 2 || !terminal.is_cuda() ||
+      terminal.sizes() != reward.sizes())
+    throw std::runtime_error("nstep_return: reward float32 [n + 1, K] and terminal [n + 1, K] on CUDA");
+  const torch::Tensor r = reward.contiguous();
+  torch::Tensor t = terminal.contiguous();
+  if (t.scalar_type() == torch::kBool) t = t.view(torch::kUInt8);
+  if (t.scalar_type() != torch::kUInt8) throw std::runtime_error("nstep_return: terminal must be bool or uint8");
+  const int64_t K = r.size(1);
+  torch::Tensor out_r = torch::empty({K}, r.options());
+  torch::Tensor out_b = torch::empty({K}, r.options());
+  torch::Tensor out_t = torch::empty({K}, t.options());
+  checkActor(rr_nstep_return((int)r.size(0) - 1, (int)K, (float)gamma, r.data_ptr<float>(), t.data_ptr<uint8_t>(),
+                             out_r.data_ptr<float>(), out_b.data_ptr<float>(), out_t.data_ptr<uint8_t>(),
+                             contract_fma ? 1 : 0, currentStream(r)),
+             "nstep_return");
+  return std::make_tuple(out_r, out_b, out_t.view(torch::kBool));
+}
+
+// |reward + bootstrap * gamma^n * q_next - q_sa| (pyrela/apex.py:44-45,77-78)
+torch::Tensor tdPriority(const torch::Tensor& reward, const torch::Tensor& bootstrap, const torch::Tensor& q_next,
+                         const torch::Tensor& q_sa, double gamma_n) {
+  const torch::Tensor a = reward.contiguous(), b = bootstrap.contiguous(), c = q_next.contiguous(),
+                      d = q_sa.contiguous();
+  for (const torch::Tensor* t : {&a, &b, &c, &d})
+    if (!t->is_cuda() || t->scalar_type() != torch::kFloat32 || t->numel() != a.numel())
+      throw std::runtime_error("td_priority: four float32 CUDA tensors of one size");
+  torch::Tensor out = torch::empty({a.numel()}, a.options());
+  checkActor(rr_td_priority((int)a.numel(), a.data_ptr<float>(), b.data_ptr<float>(), c.data_ptr<float>(),
+                            d.data_ptr<float>(), (float)gamma_n, out.data_ptr<float>(), currentStream(a)),
+             "td_priority");
+  return out;
+}
+
+// eta * max + (1 - eta) * mean per sequence (pyrela/r2d2.py:103-120)
+torch::Tensor aggregatePriority(const torch::Tensor& priority, const torch::Tensor& seq_len, double eta, int burn_in) {
+  if (!priority.is_cuda() || priority.scalar_type() != torch::kFloat32 || priority.dim() != 2 || !seq_len.is_cuda() ||
+      seq_len.scalar_type() != torch::kFloat32 || seq_len.numel() != priority.size(0))
+    throw std::runtime_error("aggregate_priority: priority float32 [nseq, L] and seq_len float32 [nseq] on CUDA");
+  const torch::Tensor p = priority.contiguous(), l = seq_len.contiguous();
+  torch::Tensor out = torch::empty({p.size(0)}, p.options());
+  checkActor(rr_aggregate_priority((int)p.size(0), (int)p.size(1), p.data_ptr<float>(), l.data_ptr<float>(),
+                                   (float)eta, burn_in, out.data_ptr<float>(), currentStream(p)),
+             "aggregate_priority");
+  return out;
+}
+
+}  // namespace
+
 PYBIND11_MODULE(_C, m) {
   m.doc() = "rela_b200: B200-native prioritized replay behind rela's replay API";
+  m.def("nstep_return", &nstepReturn, py::arg("reward"), py::arg("terminal"), py::arg("gamma"),
+        py::arg("contract_fma") = true);
+  m.def("td_priority", &tdPriority, py::arg("reward"), py::arg("bootstrap"), py::arg("q_next"), py::arg("q_sa"),
+        py::arg("gamma_n"));
+  m.def("aggregate_priority", &aggregatePriority, py::arg("priority"), py::arg("seq_len"), py::arg("eta"),
+        py::arg("burn_in"));
 
   py::class_<FFTransition, std::shared_ptr<FFTransition>>(m, "FFTransition")
       .def(py::init<>())

@@ -40,6 +40,11 @@ class PrioritizedReplay {
       : core_(capacity, seed, alpha, beta, prefetch, device) {
   }
 
+  // one shard of a replay striped over several GPUs (ShardConfig, rela_b200/replay_core.h)
+  PrioritizedReplay(int capacity, int seed, float alpha, float beta, int prefetch, int device, const ShardConfig& shard)
+      : core_(capacity, seed, alpha, beta, prefetch, device, shard) {
+  }
+
   // Elements one by one (R2D2Actor::postStep, rela/r2d2_actor.h:301).
   void add(const std::vector<DataType>& sample, const torch::Tensor& priority) {
     std::vector<Leaves> elements;

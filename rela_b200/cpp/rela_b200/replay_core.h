@@ -10,8 +10,10 @@
 // tensors that rr_sample fills and supplies the caller's CUDA stream.
 #pragma once
 
+#include <atomic>
 #include <cstdint>
 #include <deque>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <tuple>
@@ -43,12 +45,37 @@ struct LeafSpec {
   bool converted = false;
 };
 
+// One replay striped over the GPUs of one box (no
+// reference counterpart). One process per GPU, SPMD: every rank constructs the
+// replay with the same arguments (`capacity` is the TOTAL capacity) and calls
+// add / sample / update_priority collectively, in the same order.
+//   add(batch, priority)        every rank contributes n rows (same n); the
+//                               block is the ranks' rows in rank order
+//   sample(B, device)           learners = -1: every rank is a learner and
+//                               receives B rows: rows [rank * B, (rank + 1) * B)
+//                               of ONE stratified batch of world * B drawn from
+//                               the whole buffer -- what one reference replay
+//                               returns for sample(world * B), split over the
+//                               ranks. learners = r: rank r receives all B rows,
+//                               the other ranks get empty tensors.
+//   update_priority(priority)   each learner passes the priorities of its rows
+// With $RELA_B200_SHARDED=1 the plain constructor reads the configuration from
+// the torchrun environment (RANK, WORLD_SIZE, LOCAL_RANK, MASTER_PORT;
+// $RELA_B200_LEARNER = "all" | rank), so that unmodified callers of the
+// reference API (pyrela/main.py:138-144, rela/pybind.cc:37-47) get a striped replay.
+struct ShardConfig {
+  int rank = 0, world = 1;
+  int learner = -1;    // -1: every rank is a learner (data-parallel); else the one learner's rank
+  std::string group;   // rendezvous name shared by the ranks of this replay (rr_group_create)
+};
+
 class ReplayCore {
  public:
   // PrioritizedReplay(capacity, seed, alpha, beta, prefetch)
   // (rela/prioritized_replay.h:176-184). The slabs live on CUDA device
   // `device`; -1 = $RELA_B200_DEVICE, else the current device.
   ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device = -1);
+  ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device, const ShardConfig& shard);
   ~ReplayCore();
   ReplayCore(const ReplayCore&) = delete;
   ReplayCore& operator=(const ReplayCore&) = delete;
@@ -97,6 +124,9 @@ class ReplayCore {
   rr_replay* handle() const { return h_; }
   int device() const { return device_; }
   const std::vector<LeafSpec>& schema() const { return schema_; }
+  struct Sharded;  // state of the striped-replay protocol (sharded_core.cc)
+  int shardRank() const { return shard_.rank; }
+  int shardWorld() const { return shard_.world; }
 
  private:
   void ensureSchema(const Leaves& first, bool per_element, bool time_major);
@@ -114,16 +144,30 @@ class ReplayCore {
   BatchSet acquireSet(int64_t B);
   std::vector<int64_t> batchShape(const LeafSpec& s, int64_t B) const;
   std::pair<Leaves, torch::Tensor> samplePrefetched(int batchsize, const std::string& device);
-  bool pool_enabled_ = true;
+  std::pair<Leaves, torch::Tensor> handOut(const BatchSet& set, const std::string& device) const;
+  void init(int capacity, int seed, float alpha, float beta, int prefetch, int device);
+  void applySchema(const std::vector<LeafSpec>& specs);
+  std::string shardFile(const std::string& path) const;
+  // sharded_core.cc
+  void startSharded();
+  void stopSharded();
+  void shareSlabs();
+  void shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w, unsigned flags);
+  std::pair<Leaves, torch::Tensor> shardedSample(int batchsize, const std::string& device);
+  void shardedUpdate(const torch::Tensor& w, unsigned flags);
+  torch::Tensor raisedForShards(const torch::Tensor& w, unsigned flags) const;
 
   rr_replay* h_ = nullptr;
   int device_ = 0;
   float alpha_ = 1.0f;
   bool host_pow_ = true;
-  std::once_flag schema_once_;
   std::vector<LeafSpec> schema_;
-  bool schema_set_ = false;
+  std::atomic<bool> schema_set_{false};  // written under schema_m_ (release), read without it (acquire)
   mutable std::mutex schema_m_;
+
+  // striped replay (ShardConfig): the SPMD protocol lives in sharded_core.cc
+  ShardConfig shard_;
+  std::shared_ptr<Sharded> sharded_;  // shared_ptr: the type is complete only in sharded_core.cc
 };
 
 [[noreturn]] void throwLast(int code, const char* where);

@@ -27,6 +27,8 @@
 
 #include <vector>
 
+#include <ATen/cuda/CUDAEvent.h>
+
 #include "rela_b200/replay_core.h"
 
 namespace rela_b200 {
@@ -37,8 +39,13 @@ class SequenceAssembler {
 
   // One step of the K envs. `step`: the FFTransition leaves without next_obs
   // (obs.*, action.*, reward, terminal, bootstrap), each [K, ...] on the host;
-  // `priority`: per-step priority [K] float32 on the host; `hid`: the hidden
-  // state BEFORE this step, leaves "h0.<name>" of shape [layers, K, hid].
+  // `priority`: per-step priority [K] float32; `hid`: the hidden state BEFORE
+  // this step, leaves "h0.<name>" of shape [layers, K, hid].
+  // A HOST priority tensor (what the reference's actor passes after `.cpu()`,
+  // r2d2_actor.h:331-341) keeps the per-step values on the host and mixes them
+  // there in float, like the reference. A CUDA priority tensor keeps them in a
+  // device window and the eta-mix runs on the device (rr_aggregate_priority):
+  // nothing of the priority path touches the host. One assembler uses one mode.
   void push(const Leaves& step, const torch::Tensor& priority, const Leaves& hid);
 
   bool canPop() const { return can_pop_; }
@@ -81,6 +88,12 @@ class SequenceAssembler {
   std::vector<std::vector<uint8_t>> terminal_;     // [K][T] host copy of the terminal flags
   torch::Tensor dst_rows_host_, dst_rows_dev_;     // scatter destinations of one step
   torch::Tensor seq_len_host_, seq_len_dev_;       // [2K] float: seq_len of the sequences of one pop
+  // the pinned staging buffers above are rewritten every step / pop: each remembers the copy
+  // that last read it and the host waits for that copy before writing again
+  at::cuda::CUDAEvent rows_copied_, len_copied_;
+  int prio_mode_ = -1;                             // 0: host priorities, 1: device priorities
+  torch::Tensor prio_window_;                      // [K, seqLen + multiStep] float32, device (mode 1)
+  torch::Tensor env_offset_;                       // [K] int64, device: (i + 1) * burnin
   std::vector<std::pair<int, int>> elem_src_;      // schema leaf -> (0 field | 1 hidden | 2 seq_len, index)
   std::vector<torch::Tensor> keep_;                // spill windows alive until the add has been issued
 };

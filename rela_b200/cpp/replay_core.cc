@@ -54,8 +54,42 @@ uint64_t numelOf(const std::vector<int64_t>& shape) {
 
 }  // namespace
 
+ShardConfig shardConfigFromEnv() {
+  ShardConfig c;
+  const char* on = std::getenv("RELA_B200_SHARDED");
+  if (!(on && std::atoi(on) != 0)) return c;
+  auto geti = [](const char* n, int d) {
+    const char* v = std::getenv(n);
+    return (v && *v) ? std::atoi(v) : d;
+  };
+  c.world = geti("WORLD_SIZE", 1);
+  c.rank = geti("RANK", 0);
+  const char* l = std::getenv("RELA_B200_LEARNER");
+  c.learner = (l && *l && std::string(l) != "all") ? std::atoi(l) : -1;
+  const char* g = std::getenv("RELA_B200_GROUP");
+  const char* port = std::getenv("MASTER_PORT");
+  c.group = g ? g : (std::string("job") + (port ? port : "0"));
+  return c;
+}
+
 ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device)
-    : alpha_(alpha) {
+    : alpha_(alpha), shard_(shardConfigFromEnv()) {
+  init(capacity, seed, alpha, beta, prefetch, device);
+}
+
+ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int prefetch, int device,
+                       const ShardConfig& shard)
+    : alpha_(alpha), shard_(shard) {
+  init(capacity, seed, alpha, beta, prefetch, device);
+}
+
+void ReplayCore::init(int capacity, int seed, float alpha, float beta, int prefetch, int device) {
+  if (shard_.world > 1 && device < 0 && std::getenv("RELA_B200_DEVICE") == nullptr) {
+    // one process per GPU: LOCAL_RANK (several ranks may share a GPU on a smaller box)
+    const char* lr = std::getenv("LOCAL_RANK");
+    const int n = torch::cuda::is_available() ? (int)c10::cuda::device_count() : 1;
+    device = ((lr && *lr) ? std::atoi(lr) : shard_.rank) % std::max(1, n);
+  }
   device_ = pickDevice(device);
   // Host priorities are raised with the function the reference calls
   // (torch::pow on the CPU, rela/prioritized_replay.h:188,239), which makes the
@@ -64,21 +98,18 @@ ReplayCore::ReplayCore(int capacity, int seed, float alpha, float beta, int pref
   // (fp64 pow rounded once; <= 1e-6 relative).
   const char* e = std::getenv("RELA_B200_DEVICE_POW");
   host_pow_ = !(e && std::atoi(e) != 0);
-  const char* np = std::getenv("RELA_B200_NO_POOL");
-  pool_enabled_ = !(np && std::atoi(np) != 0);
   // prefetch > 0: the futures of the reference (rela/prioritized_replay.h:215-230)
   // are batches selected and gathered ahead straight into pooled batch tensors
   // (rr_prefetch_into / rr_take_prefetched): the C ABI replay itself runs without
   // prefetch and nothing is copied when a batch is handed out.
-  // RELA_B200_ABI_PREFETCH=1 uses the C ABI's own prefetch queue instead
-  // (library-owned buffers + one device-to-device copy per batch).
-  const char* ap = std::getenv("RELA_B200_ABI_PREFETCH");
-  const bool abi_prefetch = ap && std::atoi(ap) != 0;
-  prefetch_ = abi_prefetch ? 0 : std::max(0, prefetch);
-  check(rr_create(&h_, capacity, seed, alpha, beta, abi_prefetch ? prefetch : 0, device_), "PrioritizedReplay");
+  prefetch_ = std::max(0, prefetch);
+  check(rr_create(&h_, capacity, seed, alpha, beta, 0, device_), "PrioritizedReplay");
+  if (shard_.world > 1) startSharded();
 }
 
 ReplayCore::~ReplayCore() {
+  inflight_.clear();
+  stopSharded();
   if (h_ != nullptr) rr_destroy(h_);
 }
 
@@ -89,17 +120,25 @@ void ReplayCore::sync() { check(rr_sync(h_), "sync"); }
 // layer's business and go into a text sidecar (<path>.schema), one leaf per
 // line: name dtype chunks time_major row_bytes ndim dims...
 void ReplayCore::save(const std::string& path) {
-  if (!schema_set_) throw std::runtime_error("save: nothing has been added yet");
-  check(rr_save(h_, path.c_str()), "save");
-  std::ofstream f(path + ".schema");
-  f << "rela_b200-schema 1 " << schema_.size() << "\n";
-  for (const LeafSpec& s : schema_) {
-    f << s.name << ' ' << (int)s.dtype << ' ' << s.chunks << ' ' << (s.time_major ? 1 : 0) << ' ' << s.row_bytes << ' '
-      << s.shape.size();
-    for (int64_t d : s.shape) f << ' ' << d;
-    f << "\n";
+  if (!schema_set_.load(std::memory_order_acquire)) throw std::runtime_error("save: nothing has been added yet");
+  const std::string file = shard_.world > 1 ? shardFile(path) : path;
+  check(rr_save(h_, file.c_str()), "save");  // batches drawn ahead (inflight_) are saved with it
+  if (shard_.rank != 0) return;
+  const std::string tmp = path + ".schema.tmp";
+  {
+    std::ofstream f(tmp);
+    f << "rela_b200-schema 1 " << schema_.size() << "\n";
+    for (const LeafSpec& s : schema_) {
+      f << s.name << ' ' << (int)s.dtype << ' ' << s.chunks << ' ' << (s.time_major ? 1 : 0) << ' ' << s.row_bytes << ' '
+        << s.shape.size();
+      for (int64_t d : s.shape) f << ' ' << d;
+      f << "\n";
+    }
+    f.flush();
+    if (!f.good()) throw std::runtime_error("save: cannot write " + tmp);
   }
-  if (!f.good()) throw std::runtime_error("save: cannot write " + path + ".schema");
+  if (std::rename(tmp.c_str(), (path + ".schema").c_str()) != 0)
+    throw std::runtime_error("save: cannot rename " + tmp);
 }
 
 void ReplayCore::load(const std::string& path) {
@@ -122,12 +161,42 @@ void ReplayCore::load(const std::string& path) {
       if (!(f >> d)) throw std::runtime_error("load: corrupt " + path + ".schema");
   }
   setSchema(specs);  // a replay that already has a schema must have the same one
-  check(rr_load(h_, path.c_str()), "load");
+  const std::string file = shard_.world > 1 ? shardFile(path) : path;
+  check(rr_load(h_, file.c_str()), "load");
+  // batches the saved run had drawn ahead: claim them into pooled batch tensors, oldest first
+  const int queued = rr_prefetched(h_);
+  void* stream = streamOf(device_);
+  for (int k = 0; k < queued; ++k) {
+    BatchSet set = acquireSet(rr_prefetched_batch(h_, k));
+    std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
+    for (size_t i = 0; i < schema_.size(); ++i) ptrs[i] = set.fields[i].data_ptr();
+    check(rr_restore_prefetched(h_, k, ptrs.data(), set.weights.data_ptr<float>(), stream), "load");
+    inflight_.push_back(std::move(set));
+  }
+}
+
+std::string ReplayCore::shardFile(const std::string& path) const {
+  return path + ".shard" + std::to_string(shard_.rank) + "of" + std::to_string(shard_.world);
+}
+
+void ReplayCore::applySchema(const std::vector<LeafSpec>& specs) {  // schema_m_ held
+  std::vector<rr_field> fields(specs.size() ? specs.size() : 1);
+  for (size_t i = 0; i < specs.size(); ++i) {
+    fields[i].name = specs[i].name.c_str();
+    fields[i].row_bytes = specs[i].row_bytes;
+    fields[i].chunks = specs[i].chunks;
+    fields[i].reserved = 0;
+  }
+  if (shard_.world > 1) check(rr_set_shard(h_, shard_.rank, shard_.world), "add (shard)");
+  check(rr_set_schema(h_, (int)specs.size(), fields.data()), "add (schema)");
+  schema_ = specs;
+  if (shard_.world > 1) shareSlabs();
+  schema_set_.store(true, std::memory_order_release);
 }
 
 void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_major) {
   std::lock_guard<std::mutex> lk(schema_m_);
-  if (schema_set_) return;
+  if (schema_set_.load(std::memory_order_acquire)) return;
   std::vector<LeafSpec> specs;
   for (const Leaf& lf : first) {
     if (!lf.t.defined()) throw std::runtime_error("add: leaf '" + lf.name + "' is undefined");
@@ -153,21 +222,12 @@ void ReplayCore::ensureSchema(const Leaves& first, bool per_element, bool time_m
     if (s.chunks == 0) s.chunks = 1;
     specs.push_back(std::move(s));
   }
-  std::vector<rr_field> fields(specs.size() ? specs.size() : 1);
-  for (size_t i = 0; i < specs.size(); ++i) {
-    fields[i].name = specs[i].name.c_str();
-    fields[i].row_bytes = specs[i].row_bytes;
-    fields[i].chunks = specs[i].chunks;
-    fields[i].reserved = 0;
-  }
-  check(rr_set_schema(h_, (int)specs.size(), fields.data()), "add (schema)");
-  schema_ = std::move(specs);
-  schema_set_ = true;
+  applySchema(specs);
 }
 
 void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
   std::lock_guard<std::mutex> lk(schema_m_);
-  if (schema_set_) {
+  if (schema_set_.load(std::memory_order_acquire)) {
     bool same = specs.size() == schema_.size();
     for (size_t i = 0; same && i < specs.size(); ++i)
       same = specs[i].name == schema_[i].name && specs[i].dtype == schema_[i].dtype &&
@@ -175,21 +235,12 @@ void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
     if (!same) throw std::runtime_error("setSchema: differs from the schema of the first add");
     return;
   }
-  std::vector<rr_field> fields(specs.size() ? specs.size() : 1);
-  for (size_t i = 0; i < specs.size(); ++i) {
-    fields[i].name = specs[i].name.c_str();
-    fields[i].row_bytes = specs[i].row_bytes;
-    fields[i].chunks = specs[i].chunks;
-    fields[i].reserved = 0;
-  }
-  check(rr_set_schema(h_, (int)specs.size(), fields.data()), "add (schema)");
-  schema_ = specs;
-  schema_set_ = true;
+  applySchema(specs);
 }
 
 void ReplayCore::setOutputFormat(const std::string& name, torch::ScalarType dtype) {
   std::lock_guard<std::mutex> lk(schema_m_);
-  if (!schema_set_) throw std::runtime_error("set_output_format: the schema is not known yet (add or load first)");
+  if (!schema_set_.load(std::memory_order_acquire)) throw std::runtime_error("set_output_format: the schema is not known yet (add or load first)");
   if (!inflight_.empty()) throw std::runtime_error("set_output_format: prefetched batches are pending");
   for (size_t i = 0; i < schema_.size(); ++i) {
     LeafSpec& s = schema_[i];
@@ -264,7 +315,7 @@ void ReplayCore::addBatch(const Leaves& batch, const torch::Tensor& priority) {
   unsigned flags = 0;
   torch::Tensor w = weightsOf(priority, &flags);
   const int64_t n = w.size(0);
-  if (!schema_set_) ensureSchema(batch, false, false);
+  if (!schema_set_.load(std::memory_order_acquire)) ensureSchema(batch, false, false);
   if (batch.size() != schema_.size()) throw std::runtime_error("add: number of leaves differs from the schema");
   std::vector<torch::Tensor> keep(batch.size());
   std::vector<const void*> ptrs(batch.size() ? batch.size() : 1, nullptr);
@@ -273,6 +324,10 @@ void ReplayCore::addBatch(const Leaves& batch, const torch::Tensor& priority) {
     checkLeaf(i, batch[i].t, false, n);
     keep[i] = batch[i].t.contiguous();
     (keep[i].is_cuda() ? any_cuda : any_cpu) = true;
+  }
+  if (shard_.world > 1) {
+    shardedAdd(keep, w, flags);
+    return;
   }
   if (any_cuda && any_cpu) {
     for (auto& t : keep)
@@ -296,7 +351,7 @@ void ReplayCore::addElements(const std::vector<Leaves>& elements, const torch::T
   const int64_t n = w.size(0);
   if ((int64_t)elements.size() != n) throw std::runtime_error("add: priority length differs from the elements");
   if (n == 0) return;
-  if (!schema_set_) ensureSchema(elements[0], true, time_major);
+  if (!schema_set_.load(std::memory_order_acquire)) ensureSchema(elements[0], true, time_major);
   const size_t nf = schema_.size();
   std::vector<torch::Tensor> keep;
   keep.reserve(nf * (size_t)n);
@@ -309,6 +364,18 @@ void ReplayCore::addElements(const std::vector<Leaves>& elements, const torch::T
       keep.push_back(elements[e][f].t.contiguous());
       (keep.back().is_cuda() ? any_cuda : any_cpu) = true;
     }
+  }
+  if (shard_.world > 1) {
+    // a striped replay moves packed blocks: stack the elements field by field
+    std::vector<torch::Tensor> packed(nf);
+    for (size_t f = 0; f < nf; ++f) {
+      std::vector<torch::Tensor> col;
+      col.reserve((size_t)n);
+      for (int64_t e = 0; e < n; ++e) col.push_back(keep[(size_t)e * nf + f].reshape(schema_[f].shape));
+      packed[f] = torch::stack(col, 0);
+    }
+    shardedAdd(packed, w, flags);
+    return;
   }
   if (any_cuda && any_cpu) {
     for (auto& t : keep)
@@ -338,13 +405,11 @@ std::vector<int64_t> ReplayCore::batchShape(const LeafSpec& s, int64_t B) const 
 // A batch set nobody else holds: a pooled one whose storages are back to a use
 // count of 1, else a new one (pooled if there is room).
 ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
-  if (pool_enabled_) {
-    for (auto& cand : pool_) {
-      if (cand.B != B) continue;
-      bool idle = cand.weights.storage().use_count() == 1;
-      for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
-      if (idle) return cand;
-    }
+  for (auto& cand : pool_) {
+    if (cand.B != B) continue;
+    bool idle = cand.weights.storage().use_count() == 1;
+    for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
+    if (idle) return cand;
   }
   const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
   BatchSet set;
@@ -353,8 +418,30 @@ ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
   for (const LeafSpec& s : schema_)
     set.fields.push_back(torch::empty(batchShape(s, B),
                                       torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
-  if (pool_enabled_ && pool_.size() < (size_t)(4 + prefetch_)) pool_.push_back(set);
+  if (pool_.size() < (size_t)(4 + prefetch_)) pool_.push_back(set);
   return set;
+}
+
+// sample() with prefetch > 0 (rela/prioritized_replay.h:208-232): hand out the
+// oldest batch drawn ahead (or draw one now if there is none), then draw until
+// `prefetch` batches are queued again -- before this batch's updatePriority,
+// like the reference's futures.
+// What the caller receives: fresh tensor objects over the storages of a batch set, on the
+// device the caller named (the reference assembles on the host and copies to `device`,
+// rela/types.cc:34-43; here the batch is assembled in HBM and moved only if the learner asked
+// for another device).
+std::pair<Leaves, torch::Tensor> ReplayCore::handOut(const BatchSet& set, const std::string& device) const {
+  Leaves out;
+  out.reserve(schema_.size());
+  for (size_t i = 0; i < schema_.size(); ++i) out.push_back(Leaf{schema_[i].name, aliasOf(set.fields[i])});
+  torch::Tensor weights = aliasOf(set.weights);
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  const torch::Device want(device);
+  if (want != home && !(want.is_cuda() && !want.has_index())) {
+    for (auto& lf : out) lf.t = lf.t.to(want);
+    weights = weights.to(want);
+  }
+  return {std::move(out), std::move(weights)};
 }
 
 // sample() with prefetch > 0 (rela/prioritized_replay.h:208-232): hand out the
@@ -376,47 +463,36 @@ std::pair<Leaves, torch::Tensor> ReplayCore::samplePrefetched(int batchsize, con
   check(rr_take_prefetched(h_, stream), "sample");
   BatchSet set = std::move(inflight_.front());
   inflight_.pop_front();
-  Leaves out;
-  out.reserve(schema_.size());
-  for (size_t i = 0; i < schema_.size(); ++i) out.push_back(Leaf{schema_[i].name, aliasOf(set.fields[i])});
-  torch::Tensor weights = aliasOf(set.weights);
+  auto out = handOut(set, device);
   while ((int)inflight_.size() < prefetch_) issue();
-  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
-  const torch::Device want(device);
-  if (want != home && !(want.is_cuda() && !want.has_index())) {
-    for (auto& lf : out) lf.t = lf.t.to(want);
-    weights = weights.to(want);
-  }
-  return {std::move(out), std::move(weights)};
+  return out;
 }
 
 std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::string& device) {
-  if (!schema_set_) {
+  if (!schema_set_.load(std::memory_order_acquire)) {
     // the reference prints "cannot find enough samples" and asserts (:297-302)
     throw std::runtime_error("sample: the replay buffer is empty");
   }
-  if (prefetch_ > 0) return samplePrefetched(batchsize, device);
-  const int64_t B = batchsize;
-  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
+  if (shard_.world > 1) return shardedSample(batchsize, device);
+  if (prefetch_ > 0 || !inflight_.empty()) return samplePrefetched(batchsize, device);
   // Batch tensors come from a small pool. The caller never receives the pooled
   // tensor objects, only fresh aliases of their storages; a set is reused once
   // every storage is back to a use count of 1, i.e. the caller has dropped the
   // batch and every view of it -- the steady state of a learner loop that
   // rebinds `batch` each step. (Handing out the pooled TensorImpl itself would
   // never come back to a count of 1: its Python wrapper outlives the rebind
-  // while another C++ owner exists.) Otherwise a
-  // new set is allocated -- after the selection kernels have been issued, so
-  // that the allocation overlaps them.
+  // while another C++ owner exists.) A new set is allocated after the selection
+  // kernel has been issued, so that the allocation overlaps it.
+  const int64_t B = batchsize;
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)device_);
   BatchSet* set = nullptr;
-  if (pool_enabled_) {
-    for (auto& cand : pool_) {
-      if (cand.B != B) continue;
-      bool idle = cand.weights.storage().use_count() == 1;
-      for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
-      if (idle) {
-        set = &cand;
-        break;
-      }
+  for (auto& cand : pool_) {
+    if (cand.B != B) continue;
+    bool idle = cand.weights.storage().use_count() == 1;
+    for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
+    if (idle) {
+      set = &cand;
+      break;
     }
   }
   BatchSet fresh;
@@ -429,46 +505,25 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
   void* stream = streamOf(device_);
   check(rr_sample_select(h_, batchsize, set->weights.data_ptr<float>(), stream), "sample");
   if (!reuse) {
-    std::vector<int64_t> shape;
-    for (size_t i = 0; i < schema_.size(); ++i) {
-      const LeafSpec& s = schema_[i];
-      shape.clear();
-      if (!s.time_major) {
-        shape.push_back(B);
-        shape.insert(shape.end(), s.shape.begin(), s.shape.end());
-      } else {
-        shape.push_back(s.shape[0]);
-        shape.push_back(B);
-        shape.insert(shape.end(), s.shape.begin() + 1, s.shape.end());
-      }
-      set->fields.push_back(
-          torch::empty(shape, torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
-    }
+    for (const LeafSpec& s : schema_)
+      set->fields.push_back(torch::empty(batchShape(s, B),
+                                         torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
   }
-  Leaves out;
-  out.reserve(schema_.size());
   std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
-  for (size_t i = 0; i < schema_.size(); ++i) {
-    ptrs[i] = set->fields[i].data_ptr();
-    out.push_back(Leaf{schema_[i].name, aliasOf(set->fields[i])});
-  }
-  torch::Tensor weights = aliasOf(set->weights);
-  if (!reuse && pool_enabled_ && pool_.size() < 4) pool_.push_back(std::move(fresh));
+  for (size_t i = 0; i < schema_.size(); ++i) ptrs[i] = set->fields[i].data_ptr();
   check(rr_sample_gather(h_, ptrs.data(), stream), "sample");
-  const torch::Device want(device);
-  if (want != home && !(want.is_cuda() && !want.has_index())) {
-    // the reference assembles on the host and copies to `device`
-    // (rela/types.cc:34-43); here the batch is assembled in HBM and moved only
-    // if the learner asked for another device
-    for (auto& lf : out) lf.t = lf.t.to(want);
-    weights = weights.to(want);
-  }
-  return {std::move(out), std::move(weights)};
+  auto out = handOut(*set, device);
+  if (!reuse && pool_.size() < 4) pool_.push_back(std::move(fresh));
+  return out;
 }
 
 void ReplayCore::updatePriority(const torch::Tensor& priority) {
   unsigned flags = 0;
   torch::Tensor w = weightsOf(priority, &flags);
+  if (shard_.world > 1) {
+    shardedUpdate(w, flags);
+    return;
+  }
   check(rr_update_priority(h_, (int)w.size(0), w.data_ptr<float>(), flags, streamOf(device_)),
         "update_priority");
 }

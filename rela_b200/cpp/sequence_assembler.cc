@@ -7,6 +7,8 @@
 
 #include <c10/cuda/CUDAStream.h>
 
+#include "rela_b200.h"
+
 namespace rela_b200 {
 
 namespace {
@@ -124,9 +126,17 @@ void SequenceAssembler::push(const Leaves& step, const torch::Tensor& priority, 
   if (!ready_) setup(step, hid);
   if (priority.dim() != 1 || priority.size(0) != K_ || priority.scalar_type() != torch::kFloat32)
     throw std::runtime_error("SequenceAssembler::push: priority must be float32 [K]");  // assert at :32
-  const torch::Tensor prio = priority.contiguous().cpu();
-  const float* pa = prio.data_ptr<float>();
+  const int mode = priority.is_cuda() ? 1 : 0;
+  if (prio_mode_ < 0) prio_mode_ = mode;
+  if (mode != prio_mode_) throw std::runtime_error("SequenceAssembler::push: host and device priorities mixed");
   const torch::Device home(torch::kCUDA, (c10::DeviceIndex)replay_.device());
+  const torch::Tensor prio = mode == 0 ? priority.contiguous() : torch::Tensor();
+  const float* pa = mode == 0 ? prio.data_ptr<float>() : nullptr;
+  if (mode == 1 && !prio_window_.defined()) {
+    prio_window_ = torch::zeros({K_, seqLen_ + multiStep_}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+    env_offset_ = (torch::arange(K_, torch::TensorOptions().dtype(torch::kInt64).device(home)) + 1) * burnin_;
+  }
+  bool pinned_src = false;  // a pinned source is copied asynchronously: the caller may reuse it after push()
 
   // upload this step's rows once (one H2D copy per leaf) ...
   const uint8_t* term_host = nullptr;
@@ -143,17 +153,21 @@ void SequenceAssembler::push(const Leaves& step, const torch::Tensor& priority, 
     }
     if (f.row_bytes == 0) continue;
     torch::Tensor flat = src.view(torch::kUInt8).reshape({K_, (int64_t)f.row_bytes});
+    pinned_src = pinned_src || (!src.is_cuda() && src.is_pinned());
     f.upload.copy_(flat, /*non_blocking=*/true);
   }
   if (term_host == nullptr) throw std::runtime_error("SequenceAssembler::push: no 'terminal' leaf");
 
   // ... and decide, per env, where it goes (the reference's push loop, :35-86)
+  rows_copied_.synchronize();  // the previous step's copy out of this pinned buffer
   int32_t* dst = dst_rows_host_.data_ptr<int32_t>();
+  std::vector<int> finished;
   for (int i = 0; i < K_; ++i) {
     if (next_idx_[i] == 0) {
       // fresh sequence: its h0 is the hidden state of this step (:38-39), burn-in rows are padding (:44-47)
       for (size_t h = 0; h < hidden_.size(); ++h) {
         torch::Tensor row = hid[h].t.select(1, i).contiguous().view(torch::kUInt8).reshape({(int64_t)hidden_[h].row_bytes});
+        pinned_src = pinned_src || (!row.is_cuda() && row.is_pinned());
         hidden_[h].cur.select(0, i).copy_(row, true);
       }
       zeroRows(i, 0, burnin_);
@@ -165,20 +179,34 @@ void SequenceAssembler::push(const Leaves& step, const torch::Tensor& priority, 
     if (idx == seqLen_) {  // becomes the h0 of the next window (:65-68)
       for (size_t h = 0; h < hidden_.size(); ++h) {
         torch::Tensor row = hid[h].t.select(1, i).contiguous().view(torch::kUInt8).reshape({(int64_t)hidden_[h].row_bytes});
+        pinned_src = pinned_src || (!row.is_cuda() && row.is_pinned());
         hidden_[h].next.select(0, i).copy_(row, true);
       }
     }
     dst[i] = i * T_ + idx;
     terminal_[i][idx] = term_host[i];
-    seq_priority_[i][idx - burnin_] = pa[i];
+    if (mode == 0) seq_priority_[i][idx - burnin_] = pa[i];
     ++next_idx_[i];
     if (!term_host[i] && next_idx_[i] < T_) continue;
     // sequence finished: remember its length, pad the rest (:78-85)
     len_[i] = next_idx_[i];
-    for (int t = next_idx_[i]; t < T_; ++t) seq_priority_[i][t - burnin_] = 0.0f;
+    if (mode == 0) {
+      for (int t = next_idx_[i]; t < T_; ++t) seq_priority_[i][t - burnin_] = 0.0f;
+    } else {
+      finished.push_back(i);
+    }
     can_pop_ = true;
   }
   dst_rows_dev_.copy_(dst_rows_host_, true);
+  rows_copied_.record(c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)replay_.device()));
+  if (mode == 1) {
+    // this step's priorities into the device window: column idx - burnin of row i, i.e. flat index
+    // (i * T + idx) - (i + 1) * burnin; then the padding behind finished sequences
+    torch::Tensor p = priority.to(home).to(torch::kFloat32).contiguous();
+    prio_window_.view({-1}).index_copy_(0, dst_rows_dev_.to(torch::kInt64) - env_offset_, p);
+    for (int i : finished)
+      if (next_idx_[i] < T_) prio_window_.select(0, i).narrow(0, next_idx_[i] - burnin_, T_ - next_idx_[i]).zero_();
+  }
   std::vector<uint64_t> rb;
   std::vector<const void*> src;
   std::vector<void*> dstp;
@@ -196,6 +224,7 @@ void SequenceAssembler::push(const Leaves& step, const torch::Tensor& priority, 
       next_idx_[i] = T_;
     }
   }
+  if (pinned_src) c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)replay_.device()).synchronize();
 }
 
 int SequenceAssembler::popInto() {
@@ -204,9 +233,12 @@ int SequenceAssembler::popInto() {
     int env;
     bool second;
     float len;
-    std::vector<float> prio;             // [seqLen]
+    std::vector<float> prio;             // [seqLen] (host priorities)
+    torch::Tensor prio_dev;              // [seqLen] (device priorities)
     std::vector<torch::Tensor> spill;    // per field, second sequences only
   };
+  const bool dev_prio = prio_mode_ == 1;
+  const torch::Device home(torch::kCUDA, (c10::DeviceIndex)replay_.device());
   std::vector<Emit> emits;
   std::vector<int> carry;  // envs whose window continues
   const int c = burnin_ + multiStep_;
@@ -214,7 +246,9 @@ int SequenceAssembler::popInto() {
   for (int i = 0; i < K_; ++i) {
     if (len_[i] == 0) continue;
     const int L = std::min(len_[i], burnin_ + seqLen_);  // :107
-    Emit m{i, false, (float)L, std::vector<float>(seq_priority_[i].begin(), seq_priority_[i].begin() + seqLen_), {}};
+    Emit m{i, false, (float)L, std::vector<float>(seq_priority_[i].begin(), seq_priority_[i].begin() + seqLen_),
+           torch::Tensor(), {}};
+    if (dev_prio) m.prio_dev = prio_window_.select(0, i).narrow(0, 0, seqLen_).clone();
     emits.push_back(std::move(m));
     if (terminal_[i][L - 1]) {
       next_idx_[i] = 0;  // episode ended: fresh start (:118-121)
@@ -229,7 +263,11 @@ int SequenceAssembler::popInto() {
       if (len2 != -1) {
         // the carried steps already end the episode: emit them at once as a
         // second, padded sequence (:146-162); built from the window as it is now
-        Emit e{i, true, (float)len2, std::vector<float>(carried.begin(), carried.begin() + seqLen_), {}};
+        Emit e{i, true, (float)len2, std::vector<float>(carried.begin(), carried.begin() + seqLen_), torch::Tensor(), {}};
+        if (dev_prio) {
+          e.prio_dev = torch::zeros({seqLen_}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+          e.prio_dev.narrow(0, 0, multiStep_).copy_(prio_window_.select(0, i).narrow(0, seqLen_, multiStep_));
+        }
         for (Field& f : fields_) {
           torch::Tensor sp = deviceBytes(T_, f.row_bytes, replay_.device());
           if (f.name == "terminal") sp.fill_(1);  // padLike
@@ -243,6 +281,8 @@ int SequenceAssembler::popInto() {
         carry.push_back(i);
         for (int j = 0; j < c; ++j) terminal_[i][j] = terminal_[i][seqLen_ + j];
         for (int j = 0; j < multiStep_; ++j) seq_priority_[i][j] = carried[j];
+        if (dev_prio)
+          prio_window_.select(0, i).narrow(0, 0, multiStep_).copy_(prio_window_.select(0, i).narrow(0, seqLen_, multiStep_).clone());
         next_idx_[i] = c;
       }
     }
@@ -256,10 +296,12 @@ int SequenceAssembler::popInto() {
   std::vector<const void*> ptrs(nf * (size_t)n, nullptr);
   torch::Tensor prio = torch::empty({n}, torch::kFloat32);
   float* pp = prio.data_ptr<float>();
+  len_copied_.synchronize();  // the previous pop's copy out of this pinned buffer
   float* sl = seq_len_host_.data_ptr<float>();
   for (int e = 0; e < n; ++e) {
     const Emit& m = emits[e];
     sl[e] = m.len;
+    if (dev_prio) continue;
     // eta * max + (1 - eta) * mean over the sequence (pyrela/r2d2.py:103-120); len counts the burn-in
     float sum = 0.0f, mx = 0.0f;
     for (int j = 0; j < seqLen_; ++j) {
@@ -270,6 +312,19 @@ int SequenceAssembler::popInto() {
     pp[e] = eta_ * mx + (1.0f - eta_) * (sum / (m.len - (float)burnin_));
   }
   seq_len_dev_.narrow(0, 0, n).copy_(seq_len_host_.narrow(0, 0, n), true);
+  len_copied_.record(c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)replay_.device()));
+  if (dev_prio) {
+    // the same mix on the device, one warp per sequence (K9, rela_b200/csrc/actor_math.cu)
+    std::vector<torch::Tensor> rows;
+    rows.reserve((size_t)n);
+    for (const Emit& m : emits) rows.push_back(m.prio_dev);
+    torch::Tensor per_step = torch::stack(rows, 0).contiguous();
+    prio = torch::empty({n}, torch::TensorOptions().dtype(torch::kFloat32).device(home));
+    const int rc = rr_aggregate_priority(n, seqLen_, per_step.data_ptr<float>(), seq_len_dev_.data_ptr<float>(), eta_,
+                                         burnin_, prio.data_ptr<float>(), replay_.stream());
+    if (rc != RR_OK) throwLast(rc, "SequenceAssembler::popInto");
+    keep_.push_back(per_step);
+  }
   for (int e = 0; e < n; ++e) {
     const Emit& m = emits[e];
     for (size_t f = 0; f < nf; ++f) {

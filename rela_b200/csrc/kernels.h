@@ -13,6 +13,7 @@ namespace rr {
 //   INSERT (K1): src row = producer batch row b, dst = slab[(start + b) % S]
 //                (reference rela/prioritized_replay.h:61-66)
 constexpr int kMaxCopyFields = 24;
+constexpr int kMaxPeers = 8;       // GPUs of one NVSwitch box
 
 struct CopyField {
   const uint8_t* src;        // gather: slab base; insert: producer base (or null with row_ptrs)
@@ -27,6 +28,7 @@ struct CopyField {
   uint32_t piece_bytes;      // bulk path: bytes per piece (last piece may be shorter)
   uint32_t vec;              // simt path: bytes per unit (1,2,4,8,16)
   uint32_t begin;            // first item (bulk) / unit (simt) of this field in the flat index
+  uint32_t tab;              // multi-destination gather: this field's column in CopyParams::dst_tab
 };
 
 struct CopyParams {
@@ -48,12 +50,27 @@ struct CopyParams {
   int stages;           // smem ring depth
   uint32_t stage_bytes; // smem bytes per stage (>= max piece_bytes)
   unsigned long long* probe;  // debug: 8 timestamps per CTA (tools/gather_probe.cu), else null
-  // Completion signal (sharded gather): when `signal` is set, the last CTA to
-  // finish its stores publishes `signal_val` there with a system-scope release.
-  // `signal` may be a peer-mapped pointer into the learner GPU's memory.
+  // Multi-destination gather (one striped replay, several learner GPUs): batch
+  // row b belongs to learner b / rows_per_dst and lands in THAT learner's batch
+  // tensor, whose base for field column f is dst_tab[learner * tab_cols + f]
+  // (device array of pointers, local or peer-mapped). Null: one destination
+  // (CopyField::dst).
+  const uint64_t* dst_tab;
+  int tab_cols;
+  int rows_per_dst;
+  // Completion signals (sharded gather): when n_signals > 0, the last CTA to
+  // finish its stores publishes `signal_val` at every signal[i] with a
+  // system-scope release. The pointers may be peer-mapped (the learners' memory).
   unsigned int* done_counter;
-  unsigned long long* signal;
+  unsigned long long* signal[kMaxPeers];
+  int n_signals;
   unsigned long long signal_val;
+  // Importance weights (select.cu, SelectArgs::israw): out[i] = raw[i] / max for
+  // i < norm_n, by the narrow-field warps (rela/prioritized_replay.h:322).
+  const float* norm_raw;
+  const unsigned long long* norm_max;
+  float* norm_out;
+  int norm_n;
 };
 
 // shared-memory header of row_copy_kernel: barriers + per-stage piece records
@@ -71,35 +88,44 @@ cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStre
 // Learner side of the sharded gather: one warp spins (acquire, system scope)
 // until flags[0..n) have all reached `val`; raises *error after timeout_ns.
 cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned long long val, int* error,
-                                unsigned long long timeout_ns, cudaStream_t stream);
+                                int* host_error, unsigned long long timeout_ns, cudaStream_t stream);
 
 cudaError_t launch_peer_put(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
                             unsigned long long val, cudaStream_t stream);
+// put + wait in one launch (the all-gather of priorities between the shards of a striped replay)
+cudaError_t launch_exchange(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
+                            unsigned long long val, const unsigned long long* wait_flags, int n_wait, int* error,
+                            int* host_error, unsigned long long timeout_ns, cudaStream_t stream);
 
 // ------------------------------------------------------------- selection
-// Two-level prefix structure over the S_pad weights: tiles of (1 << tile_log2)
-// slots (256 ... 2048, chosen so that there are at most kMaxTiles tiles) whose
-// sums are rebuilt per sample by build_hierarchy_kernel, scanned in shared
-// memory by every CTA of select_kernel, and searched per target; the slot
-// inside the tile is found by one warp reading the tile's weights.
-constexpr int kBuildSpan = 2048;   // slots per CTA of build_hierarchy_kernel; S_pad is a multiple
-constexpr int kMinTileLog2 = 8;
-constexpr int kMaxTileLog2 = 11;
-constexpr int kMaxTiles = 16384;   // tile prefixes held in shared memory (128 KB)
-constexpr int kSelTargets = 32;    // targets per CTA of select_kernel
-constexpr int kInlinePrio = 1024;    // largest update whose priorities travel as kernel parameters
+// Three-level prefix structure over the S_pad weights, all of it maintained
+// incrementally by the kernels that change a weight:
+//   leaf   256 consecutive slots          (fp64 sum, smallest non-zero weight)
+//   group  1 << group_log2 leaves (64)    (same pair, over its leaves)
+// select_kernel scans the group sums in shared memory (at most kMaxGroups of
+// them: 1.3 KB at 2^21 transitions), then walks group -> leaf -> slot with one
+// warp per target and two dependent L2 reads.
+constexpr int kBuildSpan = 2048;   // slots per CTA of build_leaves_kernel; S_pad is a multiple
+constexpr int kLeafLog2 = 8;
+constexpr int kMaxGroupLog2 = 6;   // 64 leaves = 16,384 slots per group
+constexpr int kMaxGroups = 2048;   // group prefixes held in shared memory (24 KB): 33.5 M slots
+constexpr int kSelThreads = 256;
+constexpr int kSelTargets = 8;     // targets per CTA of select_kernel: one per warp
+constexpr int kInlinePrio = 1024;  // largest update whose priorities travel as kernel parameters
 constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
 
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
-// PrioritizedReplay (reference rela/prioritized_replay.h:166,343).
+// PrioritizedReplay (reference rela/prioritized_replay.h:166,343). The RNG
+// state is double-buffered: selection k reads mt[k & 1] and writes the state
+// after its B draws to mt[(k + 1) & 1], so no CTA of one selection can see a
+// half-written state and nobody has to finish "last".
 struct Ctl {
-  uint32_t mt[624];                // first: 16-byte aligned source of a bulk copy
+  uint32_t mt[2][624];             // first: 16-byte aligned sources of a bulk copy (2496 B each)
   double sum;
-  int mti;
-  int error;                       // sticky RR_ERR_* raised by a kernel
-  unsigned int done_ctas;          // select_kernel: CTAs that finished their targets
+  int mti[2];
+  int error;                       // sticky RR_ERR_* raised by a kernel (mirrored to a mapped host word)
+  unsigned int done_ctas;          // select_kernel with an eviction: CTAs that finished their targets
   unsigned int gather_done;        // row_copy_kernel: CTAs that finished their stores (completion signal)
-  int sel_fail;                    // select_kernel: a target ran past the buffer
   unsigned long long n_exact;      // samples selected by the parallel search
   unsigned long long n_ordered;    // samples that needed the ordered walk
   unsigned long long n_popped;
@@ -124,43 +150,45 @@ struct ConvertParams {
 };
 cudaError_t launch_gather_convert(const ConvertParams& p, int sm_count, cudaStream_t stream);
 
-// The selection hierarchy over the weights. A tile is 256 << k slots (k =
-// tile_log2 - 8) so that at most kMaxTiles tile sums have to fit the selection
-// kernel's shared memory; for k > 0 the tile is made of 1 << k LEAVES of 256
-// slots whose sums / minima are kept too (in global memory), so that finding a
-// slot and refreshing an entry never touch more than 256 weights.
+// The selection hierarchy over the weights (see "selection" above).
 struct Tiles {
-  double* l2;      // [S_pad >> tile_log2] tile sums
-  float* l2min;    // [S_pad >> tile_log2] min non-zero weight per tile
-  double* leaf;    // [S_pad >> 8] leaf sums; nullptr when tile_log2 == 8 (the tiles are the leaves)
-  float* leafmin;  // [S_pad >> 8]
-  int tile_log2;
+  double* leaf;    // [S_pad >> 8] leaf sums
+  float* leafmin;  // [S_pad >> 8] smallest non-zero weight per leaf (FLT_MAX: none)
+  double* grp;     // [ng padded to 4] group sums
+  float* grpmin;   // [ng padded to 4]
+  int group_log2;  // leaves per group = 1 << group_log2 (<= kMaxGroupLog2)
+  int ng;          // groups = S_pad >> (8 + group_log2) <= kMaxGroups
 };
 
 struct SelectArgs {
   Ctl* ctl;
   float* w;             // [S_pad] priority^alpha per slot; dead slots hold 0
   uint8_t* evicted;     // [S]
-  double* l2;           // [S_pad >> tile_log2] tile sums
-  float* l2min;         // [S_pad >> tile_log2] min non-zero weight per tile
-  double* leaf;         // see Tiles
-  float* leafmin;
-  float* wsel;          // [>= B] scratch: weight of each selected slot
+  Tiles t;
   int S, S_pad;
-  int tile_log2;
   int head;             // ring head at selection time
   int size;             // safeSize_: elements the walk may visit
   int size_is;          // size_ re-read before the pop (prioritized_replay.h:312)
   int pop_n;            // elements to evict after selection
   int B;
   int32_t* ids;         // out [B]
-  float* is_weights;    // out [B] (caller memory)
+  // Importance weights (prioritized_replay.h:320-322) leave this kernel RAW,
+  // (size * w / sum) ^ -beta per target, together with their maximum; the
+  // division by the maximum is done by the gather that follows (row_copy.cu),
+  // so no CTA has to wait for the others. The maximum is kept as
+  // (epoch << 32 | float bits) under a 64-bit atomicMax: a later selection's
+  // values always win over an earlier one's, so the word never needs a reset.
+  float* israw;               // out [B]
+  unsigned long long* ismax;  // in/out
+  uint32_t epoch;             // > the epoch of every earlier selection that used `ismax`
+  int rng_par;                // which Ctl::mt / mti this selection reads
   float beta;
   int contract_fma;
   int force_ordered;    // test hook: always take the ordered walk
+  int* host_err;        // mapped pinned host word mirroring Ctl::error (device pointer)
 };
 
-cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream);
+cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cudaStream_t stream);
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
 
 // add commit (K2 + weights write + sum_, prioritized_replay.h:58-73,188)
@@ -168,13 +196,11 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
                           float alpha, int is_weight, cudaStream_t stream);
 
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
-// wait_late: see update_kernel (select.cu); 0 is always correct
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, int wait_late, cudaStream_t stream);
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
-                                 int n, const float* prio_host, float alpha, int is_weight, int wait_late,
-                                 cudaStream_t stream);
+                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cerrno>
+#include <unistd.h>
 #include <cstring>
 #include <deque>
 #include <mutex>
@@ -78,7 +79,6 @@ struct Lane {
   cudaEvent_t committed = nullptr;  // commit kernel consumed dprio
   cudaEvent_t in = nullptr;         // marker on the caller's stream (device-resident inputs)
   cudaEvent_t gate = nullptr;       // marker on the internal stream at reservation time
-  cudaEvent_t gate2 = nullptr;      // same marker on the gather stream ($RR_GATHER_STREAM)
   uint8_t* pinned = nullptr;
   size_t pinned_cap = 0;
   float* dprio = nullptr;
@@ -101,6 +101,13 @@ struct Prefetched {
   int idslot = -1;
   int B = 0;
   bool external = false;  // rr_prefetch_into: the batch already sits in the caller's buffers
+  // a learner of a striped replay (rr_prefetch_routed): the batch is complete once
+  // wait_flags[0..wait_n) have all reached `epoch`
+  const unsigned long long* wait_flags = nullptr;
+  int wait_n = 0;
+  bool take_waits = false;  // this rank consumes the batch (a learner)
+  unsigned long long epoch = 0;
+  bool restored = false;  // put back by rr_load for a host layer that owns its batch buffers (rr_restore_prefetched)
 };
 
 // Make the replay's device current for the duration of one C ABI call and put
@@ -127,19 +134,12 @@ uint32_t pow2_divisor(uint64_t v, uint32_t cap) {
 
 struct rr_replay {
   // configuration
-  int tile_log2 = 8;
-  float* wsel = nullptr;
-  int wsel_cap = 0;
+  int group_log2 = rr::kMaxGroupLog2, ng = 0;
   int capacity = 0, S = 0, S_pad = 0, seed = 0, prefetch = 0, device = 0;
   float alpha = 0, beta = 0;
   int contract_fma = 1, force_ordered = 0;
-  int inline_prio = rr::kInlinePrio;  // $RR_INLINE_PRIO: largest host-memory update carried in the launch
-  // The last operation enqueued on `main` is a gather launched by gather_launch (and nothing
-  // else since): the one situation in which the priority update may run beside its predecessor.
-  // Every other enqueue on `main` clears it (touch_main).
-  bool tail_gather = false;
-  bool late_wait = false;  // $RR_UPDATE_LATE_WAIT=1 (experiment): off by default
-  bool full_build = false;  // $RR_FULL_BUILD: rebuild every tile entry before each selection
+  uint32_t epoch = 0;  // selections launched so far (SelectArgs::epoch)
+  int rng_par = 0;     // Ctl::mt / mti buffer the next selection reads
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
   int sm_count = 148;
@@ -151,11 +151,13 @@ struct rr_replay {
   // device state
   float* w = nullptr;
   uint8_t* evicted = nullptr;
-  double* l2 = nullptr;
-  float* l2min = nullptr;
-  double* leaf = nullptr;  // leaf (256-slot) sums / minima, only when tile_log2 > 8 (rr::Tiles)
+  double* leaf = nullptr;  // rr::Tiles: leaf (256-slot) and group sums / minima
   float* leafmin = nullptr;
+  double* grp = nullptr;
+  float* grpmin = nullptr;
   rr::Ctl* ctl = nullptr;
+  int* host_err = nullptr;      // mapped pinned mirror of Ctl::error: readable without a sync
+  int* host_err_dev = nullptr;  // its device address
 
   // ring counters (rela/prioritized_replay.h:156-164)
   mutable std::mutex m_;
@@ -165,15 +167,19 @@ struct rr_replay {
 
   // streams / events
   cudaStream_t main = nullptr;
-  cudaEvent_t evIn = nullptr, evOut = nullptr, evGather = nullptr;
-  // $RR_GATHER_STREAM=1 (experiment; off by default): gathers run on
-  // their own stream `gs`, ordered after their selection by evSel. The control plane (select,
-  // update, commit) stays on `main` and no longer queues behind the HBM-bound gather; whoever
-  // needs a batch waits for the "gather done" event of its id slot (evSlot).
-  bool two_stream = false;
-  cudaStream_t gs = nullptr;
+  cudaEvent_t evIn = nullptr, evOut = nullptr;
+  // Gathers of batches drawn AHEAD (rr_prefetch_into, the prefetch queue) run on the gather
+  // streams gs[0], gs[1] (alternating), ordered after their selection by evSel: the control plane
+  // (select, update, commit) stays on `main` and does not queue behind the HBM-bound gathers,
+  // whose kernels leave enough shared memory for the control-plane kernels to run beside them
+  // (kGatherReserve), and consecutive gathers overlap ramp and drain. Whoever needs such a
+  // batch waits for the "gather done" event of its id slot (evSlot). A batch drawn on demand
+  // (rr_sample without prefetch) is needed at once: its gather stays on `main`, chained to its
+  // selection by programmatic dependent launch.
+  cudaStream_t gs[2] = {nullptr, nullptr};
+  int gs_next = 0;
   cudaEvent_t evSel = nullptr, evJoin = nullptr;
-  std::vector<cudaEvent_t> evSlot;  // per id slot: its gather has finished (recorded on gs)
+  std::vector<cudaEvent_t> evSlot;  // per id slot: its gather has finished (recorded on a gather stream)
   std::vector<bool> slotPending;    // evSlot[i] recorded and not yet waited for by `main`
 
   // producer lanes
@@ -181,18 +187,18 @@ struct rr_replay {
   std::condition_variable laneCv_;
   std::vector<Lane> lanes;
 
-  // sampled ids: ring of device buffers; cur = batch handed to the learner
+  // sampled ids: ring of device buffers; cur = batch handed to the learner. One allocation per
+  // slot: [ismax u64 | pad][ids int32 x cap][israw float x cap] (SelectArgs)
   std::vector<int32_t*> idbuf;
+  std::vector<float*> israw;
+  std::vector<unsigned long long*> ismax;
+  std::vector<void*> idalloc;
   std::vector<int> idcap;
   std::vector<bool> idbusy;
   int cur_ids = -1, cur_B = 0;
   float* pend_w = nullptr;
-  // completion signal of the sharded gather (rr_set_completion)
-  unsigned long long* signal_ptr = nullptr;
-  const unsigned long long* wait_flags = nullptr;
-  int wait_n = 0;
-  unsigned long long signal_epoch = 0;
   int pend_slot = -1, pend_B = 0, pend_pop = 0;  // rr_sample_select done, rr_sample_gather pending
+  int pend_add_start = -1, pend_add_n = 0;       // rr_add_sharded_rows done, rr_add_sharded_commit pending
   std::deque<Prefetched> queue;
   std::vector<Prefetched> pool;
 
@@ -211,28 +217,20 @@ struct rr_replay {
 
 namespace {
 
-inline void touch_main(rr_replay* r) { r->tail_gather = false; }
-
-// Gathers of this replay go to the gather stream (single-GPU replays only: a sharded gather
-// publishes its completion flag in stream order with the learner's wait kernel).
-inline bool on_gather_stream(const rr_replay* r) {
-  return r->two_stream && r->shard_world == 1 && r->signal_ptr == nullptr;
-}
-
-// `main` waits for everything issued on the gather stream so far.
-int join_gather_stream(rr_replay* r) {
-  if (!r->two_stream) return RR_OK;
-  RR_CUDA(cudaEventRecord(r->evJoin, r->gs));
-  RR_CUDA(cudaStreamWaitEvent(r->main, r->evJoin, 0));
+// `main` waits for everything issued on the gather streams so far.
+int join_gather_streams(rr_replay* r) {
+  for (cudaStream_t g : r->gs) {
+    RR_CUDA(cudaEventRecord(r->evJoin, g));
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evJoin, 0));
+  }
   std::fill(r->slotPending.begin(), r->slotPending.end(), false);
-  touch_main(r);
   return RR_OK;
 }
 
-// Host-side wait for both internal streams (main first: gs may be waiting for a selection).
+// Host-side wait for all internal streams (main first: a gather stream may be waiting for a selection).
 int sync_streams(rr_replay* r) {
   RR_CUDA(cudaStreamSynchronize(r->main));
-  if (r->two_stream) RR_CUDA(cudaStreamSynchronize(r->gs));
+  for (cudaStream_t g : r->gs) RR_CUDA(cudaStreamSynchronize(g));
   return RR_OK;
 }
 
@@ -242,28 +240,37 @@ int sync_streams(rr_replay* r) {
     if (src_ != RR_OK) return src_; \
   } while (0)
 
+// A kernel has raised the sticky device error (select_kernel: the prefix walk overran, the
+// reference's assert(false) at prioritized_replay.h:297-302; wait_signals_kernel: a shard never
+// signalled). The kernels mirror Ctl::error into a mapped pinned word, so this is one host load.
+int check_device_error(rr_replay* r, const char* where) {
+  const int err = *reinterpret_cast<volatile int*>(r->host_err);
+  if (err == 0) return RR_OK;
+  return fail(err, "%s: device-side error %d (%s); rr_sync clears it", where, err,
+              err == RR_ERR_OVERRUN ? "an earlier selection ran past the last element, the reference asserts here"
+                                    : "a shard never published its completion flag");
+}
+
 int new_idslot(rr_replay* r) {
   r->idbuf.push_back(nullptr);
+  r->israw.push_back(nullptr);
+  r->ismax.push_back(nullptr);
+  r->idalloc.push_back(nullptr);
   r->idcap.push_back(0);
   r->idbusy.push_back(false);
   r->slotPending.push_back(false);
   cudaEvent_t ev = nullptr;
-  if (r->two_stream) RR_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  RR_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   r->evSlot.push_back(ev);
   return RR_OK;
 }
 
 // The batch of id slot `slot` becomes visible to the caller's stream `cs`.
 int publish_batch(rr_replay* r, cudaStream_t cs, int slot) {
-  if (on_gather_stream(r) && slot >= 0 && r->slotPending[(size_t)slot]) {
-    // evSlot covers the gather and, through evSel, the selection that wrote the IS weights
-    if (cs == r->main) {
-      RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)slot], 0));
-      r->slotPending[(size_t)slot] = false;
-      touch_main(r);
-    } else {
-      RR_CUDA(cudaStreamWaitEvent(cs, r->evSlot[(size_t)slot], 0));
-    }
+  if (slot >= 0 && r->slotPending[(size_t)slot]) {
+    // its gather ran on a gather stream: evSlot covers it and, through evSel, its selection
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evSlot[(size_t)slot], 0));
+    if (cs == r->main) r->slotPending[(size_t)slot] = false;
     return RR_OK;
   }
   if (cs != r->main) {
@@ -275,13 +282,19 @@ int publish_batch(rr_replay* r, cudaStream_t cs, int slot) {
 
 rr::Tiles tiles_of(const rr_replay* r) {
   rr::Tiles t;
-  t.l2 = r->l2;
-  t.l2min = r->l2min;
   t.leaf = r->leaf;
   t.leafmin = r->leafmin;
-  t.tile_log2 = r->tile_log2;
+  t.grp = r->grp;
+  t.grpmin = r->grpmin;
+  t.group_log2 = r->group_log2;
+  t.ng = r->ng;
   return t;
 }
+
+// Shared memory a gather leaves free on every SM so that one CTA each of select_kernel
+// (~3.5 KB static + 12 B per group) and update_kernel (~10 KB static + 12 B per element) can be
+// resident beside its CTA -- otherwise the control plane would queue behind every gather.
+constexpr size_t kGatherReserve = 32 * 1024;
 
 using rr::CopyField;
 using rr::CopyLaunch;
@@ -344,7 +357,7 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
     const size_t hdr = rr::kCopyHeaderBytes;
     // 1 KB per-CTA system reserve; a gather also leaves room for one CTA of the priority
     // update (33.5 KB static + 12 B per element) to run beside it on the same SM
-    const size_t beside = (gather && r->late_wait) ? (size_t)env_int("RR_GATHER_RESERVE_KB", 44) * 1024 : 0;
+    const size_t beside = gather ? kGatherReserve : 0;
     const size_t lim = ((size_t)227 * 1024 - beside) / (size_t)r->g_ctas - 1024;
     if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
     const int want = r->sm_count * r->g_ctas;
@@ -366,8 +379,16 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
   return RR_OK;
 }
 
+// `main` is ordered after everything queued so far on the caller's stream
+int order_after_caller_(rr_replay* r, cudaStream_t cs) {
+  if (cs == r->main) return RR_OK;
+  RR_CUDA(cudaEventRecord(r->evIn, cs));
+  RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
+  return RR_OK;
+}
+
 int launch_plan(rr_replay* r, const CopyPlan& plan, cudaStream_t s) {
-  if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) return RR_OK;
+  if (plan.p.n_bulk == 0 && plan.p.n_simt == 0 && plan.p.norm_n == 0) return RR_OK;
   RR_CUDA(rr::launch_row_copy(plan.p, plan.cfg, s));
   r->launches++;
   return RR_OK;
@@ -380,6 +401,10 @@ extern "C" {
 
 const char* rr_last_error(void) {
   return g_err.c_str();
+}
+
+void rr_set_last_error_(const char* text) {  // for the other translation units of the library
+  g_err = text ? text : "";
 }
 
 int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, int prefetch, int device) {
@@ -395,13 +420,17 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   rr_replay* r = new rr_replay();
   r->capacity = capacity;
   r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
-  r->S_pad = ((r->S + rr::kBuildSpan - 1) / rr::kBuildSpan) * rr::kBuildSpan;
-  r->tile_log2 = std::min(rr::kMaxTileLog2, std::max(rr::kMinTileLog2, env_int("RR_TILE_LOG2", rr::kMinTileLog2)));
-  while ((r->S_pad >> r->tile_log2) > rr::kMaxTiles && r->tile_log2 < rr::kMaxTileLog2) ++r->tile_log2;
-  if ((r->S_pad >> r->tile_log2) > rr::kMaxTiles) {
+  // leaves per group: 64; $RR_GROUP_LOG2 (test hook) forces smaller groups so that small
+  // buffers exercise the multi-group paths
+  r->group_log2 = std::min(rr::kMaxGroupLog2, std::max(0, env_int("RR_GROUP_LOG2", rr::kMaxGroupLog2)));
+  const int span = std::max(rr::kBuildSpan, 1 << (rr::kLeafLog2 + r->group_log2));  // S_pad: whole groups
+  r->S_pad = (int)((((int64_t)r->S + span - 1) / span) * span);
+  r->ng = r->S_pad >> (rr::kLeafLog2 + r->group_log2);
+  if (r->ng > rr::kMaxGroups) {
+    const int ng = r->ng, gl = r->group_log2;
     delete r;
-    return fail(RR_ERR_ARG, "rr_create: capacity %d exceeds the %d slots one replay can index", capacity,
-                rr::kMaxTiles << rr::kMaxTileLog2);
+    return fail(RR_ERR_ARG, "rr_create: capacity %d needs %d groups of %d slots; one replay indexes %d", capacity, ng,
+                1 << (rr::kLeafLog2 + gl), rr::kMaxGroups);
   }
   r->own_lo = 0;
   r->own_hi = r->S;
@@ -423,48 +452,32 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaStreamCreateWithFlags(&r->main, cudaStreamNonBlocking));
   RR_CUDA(cudaEventCreateWithFlags(&r->evIn, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
-  RR_CUDA(cudaEventCreateWithFlags(&r->evGather, cudaEventDisableTiming));
-  r->two_stream = env_int("RR_GATHER_STREAM", 0) != 0;
-  if (r->two_stream) {
-    RR_CUDA(cudaStreamCreateWithFlags(&r->gs, cudaStreamNonBlocking));
-    RR_CUDA(cudaEventCreateWithFlags(&r->evSel, cudaEventDisableTiming));
-    RR_CUDA(cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming));
-  }
+  for (cudaStream_t& g : r->gs) RR_CUDA(cudaStreamCreateWithFlags(&g, cudaStreamNonBlocking));
+  RR_CUDA(cudaEventCreateWithFlags(&r->evSel, cudaEventDisableTiming));
+  RR_CUDA(cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming));
 
-  const size_t nt2 = ((((size_t)r->S_pad >> r->tile_log2) + 3) & ~(size_t)3);  // padded: bulk copies move 16-byte units
+  const size_t ng_pad = ((size_t)r->ng + 3) & ~(size_t)3;  // padded: bulk copies move 16-byte units
   RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
   RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
-  RR_CUDA(cudaMalloc(&r->l2, sizeof(double) * nt2));
-  RR_CUDA(cudaMalloc(&r->l2min, sizeof(float) * nt2));
-  if (r->tile_log2 > 8) {
-    RR_CUDA(cudaMalloc(&r->leaf, sizeof(double) * ((size_t)r->S_pad >> 8)));
-    RR_CUDA(cudaMalloc(&r->leafmin, sizeof(float) * ((size_t)r->S_pad >> 8)));
-  }
+  RR_CUDA(cudaMalloc(&r->leaf, sizeof(double) * ((size_t)r->S_pad >> rr::kLeafLog2)));
+  RR_CUDA(cudaMalloc(&r->leafmin, sizeof(float) * ((size_t)r->S_pad >> rr::kLeafLog2)));
+  RR_CUDA(cudaMalloc(&r->grp, sizeof(double) * ng_pad));
+  RR_CUDA(cudaMalloc(&r->grpmin, sizeof(float) * ng_pad));
   RR_CUDA(cudaMalloc(&r->ctl, sizeof(rr::Ctl)));
+  RR_CUDA(cudaHostAlloc(&r->host_err, sizeof(int), cudaHostAllocMapped));
+  *r->host_err = 0;
+  RR_CUDA(cudaHostGetDevicePointer(&r->host_err_dev, r->host_err, 0));
   RR_CUDA(cudaMemsetAsync(r->w, 0, sizeof(float) * (size_t)r->S_pad, r->main));
   RR_CUDA(cudaMemsetAsync(r->evicted, 0, (size_t)r->S_pad, r->main));
+  RR_CUDA(cudaMemsetAsync(r->grp, 0, sizeof(double) * ng_pad, r->main));
+  RR_CUDA(cudaMemsetAsync(r->grpmin, 0, sizeof(float) * ng_pad, r->main));
   rr::Ctl h;
   memset(&h, 0, sizeof(h));
-  mt_seed(h.mt, (uint32_t)seed);  // rng_.seed(seed), rela/prioritized_replay.h:183
-  h.mti = 624;
+  mt_seed(h.mt[0], (uint32_t)seed);  // rng_.seed(seed), rela/prioritized_replay.h:183
+  h.mti[0] = 624;
   RR_CUDA(cudaMemcpyAsync(r->ctl, &h, sizeof(h), cudaMemcpyHostToDevice, r->main));
-  {  // tile entries of the empty buffer: sum 0, min FLT_MAX
-    rr::SelectArgs a;
-    memset(&a, 0, sizeof(a));
-    a.w = r->w;
-    a.l2 = r->l2;
-    a.l2min = r->l2min;
-    a.leaf = r->leaf;
-    a.leafmin = r->leafmin;
-    a.S_pad = r->S_pad;
-    a.tile_log2 = r->tile_log2;
-    RR_CUDA(cudaMemsetAsync(r->l2, 0, sizeof(double) * nt2, r->main));
-    RR_CUDA(cudaMemsetAsync(r->l2min, 0, sizeof(float) * nt2, r->main));
-    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
-  }
-  r->full_build = env_int("RR_FULL_BUILD", 0) != 0;
-  r->late_wait = env_int("RR_UPDATE_LATE_WAIT", 0) != 0;
-  r->inline_prio = std::min(rr::kInlinePrio, env_int("RR_INLINE_PRIO", rr::kInlinePrio));
+  // entries of the empty buffer: sum 0, min FLT_MAX
+  RR_CUDA(rr::launch_build_hierarchy(r->w, tiles_of(r), r->S_pad, r->main));
   RR_CUDA(cudaStreamSynchronize(r->main));
 
   const int nl = std::max(1, env_int("RR_ADD_LANES", 4));
@@ -475,7 +488,6 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     RR_CUDA(cudaEventCreateWithFlags(&l.committed, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.in, cudaEventDisableTiming));
     RR_CUDA(cudaEventCreateWithFlags(&l.gate, cudaEventDisableTiming));
-    if (r->two_stream) RR_CUDA(cudaEventCreateWithFlags(&l.gate2, cudaEventDisableTiming));
   }
   r->pstage.resize(4);
   for (auto& s : r->pstage) RR_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
@@ -495,12 +507,12 @@ int rr_destroy(rr_replay* r) {
   for (auto& f : r->fields) cudaFree(f.slab);
   cudaFree(r->w);
   cudaFree(r->evicted);
-  cudaFree(r->wsel);
-  cudaFree(r->l2);
-  cudaFree(r->l2min);
   cudaFree(r->leaf);
   cudaFree(r->leafmin);
+  cudaFree(r->grp);
+  cudaFree(r->grpmin);
   cudaFree(r->ctl);
+  if (r->host_err) cudaFreeHost(r->host_err);
   for (auto& l : r->lanes) {
     if (l.pinned) cudaFreeHost(l.pinned);
     cudaFree(l.dprio);
@@ -509,7 +521,6 @@ int rr_destroy(rr_replay* r) {
     cudaEventDestroy(l.committed);
     cudaEventDestroy(l.in);
     cudaEventDestroy(l.gate);
-    if (l.gate2) cudaEventDestroy(l.gate2);
     cudaStreamDestroy(l.stream);
   }
   for (auto& s : r->pstage) {
@@ -517,8 +528,9 @@ int rr_destroy(rr_replay* r) {
     cudaFree(s.dev);
     cudaEventDestroy(s.done);
   }
-  for (auto* p : r->idbuf) cudaFree(p);
+  for (auto* p : r->idalloc) cudaFree(p);
   auto free_pre = [](Prefetched& p) {
+    if (p.external) return;  // the caller's buffers
     for (auto* f : p.fields) cudaFree(f);
     cudaFree(p.weights);
   };
@@ -527,12 +539,12 @@ int rr_destroy(rr_replay* r) {
   for (auto* hp : r->hist) cudaFree(hp);
   cudaEventDestroy(r->evIn);
   cudaEventDestroy(r->evOut);
-  cudaEventDestroy(r->evGather);
   for (auto ev : r->evSlot)
     if (ev) cudaEventDestroy(ev);
   if (r->evSel) cudaEventDestroy(r->evSel);
   if (r->evJoin) cudaEventDestroy(r->evJoin);
-  if (r->gs) cudaStreamDestroy(r->gs);
+  for (cudaStream_t g : r->gs)
+    if (g) cudaStreamDestroy(g);
   cudaStreamDestroy(r->main);
   delete r;
   return RR_OK;
@@ -594,20 +606,6 @@ int rr_set_shard(rr_replay* r, int rank, int world) {
   return RR_OK;
 }
 
-int rr_set_completion(rr_replay* r, void* signal_ptr, const void* wait_flags, int world) {
-  if (r == nullptr || world < 0 || world > 32) return fail(RR_ERR_ARG, "rr_set_completion: bad argument");
-  std::unique_lock<std::mutex> lk(r->m_);
-  if (r->two_stream) {  // from here on the gathers run on `main` again
-    DeviceScope dev_scope(r->device);
-    int jrc = join_gather_stream(r);
-    if (jrc != RR_OK) return jrc;
-  }
-  r->signal_ptr = static_cast<unsigned long long*>(signal_ptr);
-  r->wait_flags = static_cast<const unsigned long long*>(wait_flags);
-  r->wait_n = world;
-  return RR_OK;
-}
-
 int rr_peer_put(int device, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs, int n,
                 uint64_t epoch, void* stream) {
   if (src == nullptr || n < 0 || n > 16 || bytes >= (1ull << 32) || (n > 0 && (!dst_ptrs || !flag_ptrs)))
@@ -621,8 +619,25 @@ int rr_peer_put(int device, const void* src, uint64_t bytes, void* const* dst_pt
 int rr_wait_flags(int device, const void* flags, int n, uint64_t epoch, int* device_error, void* stream) {
   if (flags == nullptr || n < 1 || n > 32 || device_error == nullptr) return fail(RR_ERR_ARG, "rr_wait_flags: bad argument");
   DeviceScope dev_scope(device);
-  RR_CUDA(rr::launch_wait_signals(static_cast<const unsigned long long*>(flags), n, epoch, device_error,
+  RR_CUDA(rr::launch_wait_signals(static_cast<const unsigned long long*>(flags), n, epoch, device_error, nullptr,
                                   10ull * 1000 * 1000 * 1000, static_cast<cudaStream_t>(stream)));
+  return RR_OK;
+}
+
+int rr_exchange(rr_replay* r, const void* src, uint64_t bytes, void* const* dst_ptrs, void* const* flag_ptrs, int n,
+                uint64_t epoch, const void* wait_flags, int n_wait, void* stream) {
+  if (r == nullptr || n < 0 || n > rr::kMaxPeers || n_wait < 0 || n_wait > 32 || bytes >= (1ull << 32) ||
+      (bytes > 0 && src == nullptr) || (n > 0 && (!dst_ptrs || !flag_ptrs)) || (n_wait > 0 && !wait_flags))
+    return fail(RR_ERR_ARG, "rr_exchange: bad argument");
+  DeviceScope dev_scope(r->device);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  std::unique_lock<std::mutex> lk(r->m_);
+  int rc = order_after_caller_(r, cs);  // `src` was produced there
+  if (rc != RR_OK) return rc;
+  RR_CUDA(rr::launch_exchange(src, (uint32_t)bytes, dst_ptrs, flag_ptrs, n, epoch,
+                              static_cast<const unsigned long long*>(wait_flags), n_wait, &r->ctl->error,
+                              r->host_err_dev, 10ull * 1000 * 1000 * 1000, r->main));
+  r->launches++;
   return RR_OK;
 }
 
@@ -656,6 +671,13 @@ int rr_scatter_rows(rr_replay* r, int n, int nfields, const uint64_t* row_bytes,
   plan.p.own_hi = 0x7fffffff;
   RR_CUDA(rr::launch_row_copy(plan.p, plan.cfg, static_cast<cudaStream_t>(stream)));
   r->launches++;
+  return RR_OK;
+}
+
+int rr_slab_ptrs(rr_replay* r, void** out, int cap) {
+  if (r == nullptr || out == nullptr) return fail(RR_ERR_ARG, "rr_slab_ptrs: null");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_slab_ptrs: rr_set_schema has not been called");
+  for (int i = 0; i < cap && i < (int)r->fields.size(); ++i) out[i] = r->fields[(size_t)i].slab;
   return RR_OK;
 }
 
@@ -764,6 +786,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
   // -- reserve [start, start + n) (rela/prioritized_replay.h:46-55); blocks while full
   int start;
   cudaError_t gate_err;
+  std::vector<cudaEvent_t> pending_gathers;
   {
     std::unique_lock<std::mutex> lk(r->m_);
     r->cvSize_.wait(lk, [&] { return r->size_ + n <= r->S; });
@@ -773,7 +796,9 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     // the slots being reused may still be read by gathers already issued on
     // the internal stream: the row copies below are ordered after this marker
     gate_err = cudaEventRecord(L.gate, r->main);
-    if (gate_err == cudaSuccess && r->two_stream) gate_err = cudaEventRecord(L.gate2, r->gs);
+    // ... or by gathers of batches drawn ahead, which run on the gather streams
+    for (size_t i = 0; i < r->evSlot.size(); ++i)
+      if (r->slotPending[i]) pending_gathers.push_back(r->evSlot[i]);
   }
   const int end = (start + n) % r->S;
   const int n1 = std::min(n, r->S - start);  // rows before the wrap
@@ -786,7 +811,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     // rows being overwritten may still be read by an in-flight gather
     if (gate_err != cudaSuccess) return fail(RR_ERR_CUDA, "rr_add: %s", cudaGetErrorString(gate_err));
     RR_CUDA(cudaStreamWaitEvent(L.stream, L.gate, 0));
-    if (r->two_stream) RR_CUDA(cudaStreamWaitEvent(L.stream, L.gate2, 0));
+    for (cudaEvent_t ev : pending_gathers) RR_CUDA(cudaStreamWaitEvent(L.stream, ev, 0));
     if ((rows_dev || prio_dev)) {
       // order after the producer of the device-resident inputs
       RR_CUDA(cudaEventRecord(L.in, cs));
@@ -903,7 +928,6 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
     std::unique_lock<std::mutex> lk(r->m_);
     r->cvTail_.wait(lk, [&] { return r->safeTail_ == start; });
     if (rc == RR_OK) {
-      touch_main(r);
       cudaError_t e = cudaStreamWaitEvent(r->main, L.copied, 0);
       if (e == cudaSuccess) {
         e = rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n,
@@ -942,6 +966,89 @@ int rr_add_rows(rr_replay* r, int n, const void* const* row_ptrs, const float* p
   return add_impl(r, n, nullptr, nullptr, row_ptrs, priority, flags, static_cast<cudaStream_t>(stream));
 }
 
+// Collective add into a striped replay, step 1: reserve the block of n_total slots (the same
+// on every shard) and move THIS rank's rows -- rows [row0, row0 + n_local) of the block, device
+// memory -- straight into the slabs of the shards that own their slots (peer-mapped bases in
+// slab_tab), on the internal stream after `stream`. The weights of the whole block are
+// committed by rr_add_sharded_commit once the ranks have exchanged them.
+int rr_add_sharded_rows(rr_replay* r, int n_total, int row0, int n_local, const void* const* field_base,
+                        const void* slab_tab, void* stream) {
+  if (r == nullptr || n_total < 0 || row0 < 0 || n_local < 0 || row0 + n_local > n_total || slab_tab == nullptr ||
+      (n_local > 0 && !r->fields.empty() && field_base == nullptr))
+    return fail(RR_ERR_ARG, "rr_add_sharded_rows: bad argument");
+  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_add: rr_set_schema has not been called");
+  if (r->pend_add_start >= 0) return fail(RR_ERR_STATE, "rr_add_sharded_rows: the previous block has not been committed");
+  if (n_total == 0) return RR_OK;
+  DeviceScope dev_scope(r->device);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  std::unique_lock<std::mutex> lk(r->m_);
+  // the reference blocks here until a sample evicts (prioritized_replay.h:47); in an SPMD program the
+  // same thread would have to sample, so a full ring is reported instead
+  if (r->size_ + n_total > r->S)
+    return fail(RR_ERR_STATE, "add: ring is full (%d + %d > %d slots); sample first", r->size_, n_total, r->S);
+  const int start = r->tail_;
+  r->tail_ = (r->tail_ + n_total) % r->S;
+  r->size_ += n_total;
+  int rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
+  // slots being reused may still be read by gathers of batches drawn ahead, on ANY shard: wait for
+  // every shard's completion flag of every queued batch
+  for (const Prefetched& q : r->queue) {
+    if (q.wait_n == 0) continue;
+    RR_CUDA(rr::launch_wait_signals(q.wait_flags, q.wait_n, q.epoch, &r->ctl->error, r->host_err_dev,
+                                    10ull * 1000 * 1000 * 1000, r->main));
+    r->launches++;
+  }
+  if (n_local > 0 && !r->fields.empty()) {
+    std::vector<CopyField> cf;
+    for (size_t fi = 0; fi < r->fields.size(); ++fi) {
+      const FieldInfo& f = r->fields[fi];
+      if (f.row_bytes == 0) continue;
+      CopyField c;
+      memset(&c, 0, sizeof(c));
+      c.src = static_cast<const uint8_t*>(field_base[fi]);
+      c.src_row_stride = f.row_bytes;
+      c.tab = (uint32_t)fi;
+      c.chunks = 1;
+      c.chunk_bytes = (uint32_t)f.row_bytes;
+      c.dst_row_stride = f.row_bytes;
+      c.dst_chunk_stride = f.row_bytes;
+      cf.push_back(c);
+    }
+    CopyPlan plan;
+    rc = plan_copy(r, false, n_local, cf, nullptr, (start + row0) % r->S, &plan);
+    if (rc != RR_OK) return rc;
+    plan.p.own_lo = 0;  // every slot has an owner: nothing is skipped
+    plan.p.own_hi = r->S;
+    plan.p.dst_tab = static_cast<const uint64_t*>(slab_tab);
+    plan.p.tab_cols = (int)r->fields.size();
+    plan.p.rows_per_dst = (r->S + r->shard_world - 1) / r->shard_world;  // slots per shard (rr_set_shard)
+    rc = launch_plan(r, plan, r->main);
+    if (rc != RR_OK) return rc;
+  }
+  r->pend_add_start = start;
+  r->pend_add_n = n_total;
+  return RR_OK;
+}
+
+// Step 2: weights_[j] for the whole block (device memory, n_total floats in block order),
+// sum_ and the hierarchy, identically on every shard; the block becomes sampleable.
+int rr_add_sharded_commit(rr_replay* r, const float* weights_all, unsigned flags) {
+  if (r == nullptr || weights_all == nullptr) return fail(RR_ERR_ARG, "rr_add_sharded_commit: bad argument");
+  if (r->pend_add_start < 0) return fail(RR_ERR_STATE, "rr_add_sharded_commit: no block is pending");
+  DeviceScope dev_scope(r->device);
+  std::unique_lock<std::mutex> lk(r->m_);
+  const int start = r->pend_add_start, n = r->pend_add_n;
+  r->pend_add_start = -1;
+  RR_CUDA(rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n, weights_all, r->alpha,
+                            (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0, r->main));
+  r->launches++;
+  r->safeTail_ = (start + n) % r->S;
+  r->safeSize_ += n;
+  r->numAdd_ += n;
+  return RR_OK;
+}
+
 }  // extern "C"
 
 // ============================================================== sample / update
@@ -949,11 +1056,19 @@ namespace {
 
 int ensure_idbuf(rr_replay* r, int slot, int B) {
   if (r->idcap[slot] < B) {
-    RR_CUDA(cudaFree(r->idbuf[slot]));
-    r->idbuf[slot] = nullptr;
-    int cap = std::max(B, 1024);
-    RR_CUDA(cudaMalloc(&r->idbuf[slot], sizeof(int32_t) * (size_t)cap));
-    r->idcap[slot] = cap;
+    RR_SYNC_STREAMS(r);  // an earlier gather may still read the old buffer
+    RR_CUDA(cudaFree(r->idalloc[slot]));
+    r->idalloc[slot] = nullptr;
+    r->idcap[slot] = 0;
+    const size_t cap = (size_t)std::max(B, 1024);
+    uint8_t* base = nullptr;
+    RR_CUDA(cudaMalloc(&base, 16 + cap * (sizeof(int32_t) + sizeof(float))));
+    RR_CUDA(cudaMemsetAsync(base, 0, 16, r->main));
+    r->idalloc[slot] = base;
+    r->ismax[slot] = reinterpret_cast<unsigned long long*>(base);
+    r->idbuf[slot] = reinterpret_cast<int32_t*>(base + 16);
+    r->israw[slot] = reinterpret_cast<float*>(base + 16 + cap * sizeof(int32_t));
+    r->idcap[slot] = (int)cap;
   }
   return RR_OK;
 }
@@ -961,41 +1076,45 @@ int ensure_idbuf(rr_replay* r, int slot, int B) {
 int free_idslot(rr_replay* r) {
   for (size_t i = 0; i < r->idbusy.size(); ++i)
     if (!r->idbusy[i]) return (int)i;
-  return -1;
+  const int slot = (int)r->idbuf.size();
+  return new_idslot(r) == RR_OK ? slot : -1;
 }
 
-// sample_ (rela/prioritized_replay.h:258-328) in two stream-ordered steps on
-// the internal stream: (1) prefix hierarchy + selection + eviction + IS
-// weights, (2) makeBatch = the gather. The caller's stream has already been
-// ordered before `main` (evIn). The host-side blockPop bookkeeping is applied
-// in step 2: until the gather has been issued, a concurrent add must not be
-// able to reserve (and overwrite) the evicted slots the gather still reads.
-int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
+// Where the rows of a batch go when the replay is one shard of a striped buffer (rr_route).
+struct Route {
+  int n_learners = 1;
+  const uint64_t* dst_tab = nullptr;
+  unsigned long long* signals[rr::kMaxPeers] = {};
+  int n_signals = 0;
+  int my_learner = -1;
+};
+
+// sample_ (rela/prioritized_replay.h:258-328) in two stream-ordered steps: (1) selection +
+// eviction + raw importance weights on the internal stream, (2) makeBatch = the gather (which
+// also normalises the importance weights), on the internal stream or, for a batch drawn ahead,
+// on a gather stream. The caller's stream has already been ordered before `main` (evIn). The
+// host-side blockPop bookkeeping is applied in step 2: until the gather has been issued, a
+// concurrent add must not be able to reserve (and overwrite) the evicted slots the gather
+// still reads.
+int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   int rc = ensure_idbuf(r, idslot, B);
   if (rc != RR_OK) return rc;
-  if (r->wsel_cap < B) {
-    RR_CUDA(cudaStreamSynchronize(r->main));
-    RR_CUDA(cudaFree(r->wsel));
-    r->wsel = nullptr;
-    const int cap = std::max(B, 1024);
-    RR_CUDA(cudaMalloc(&r->wsel, sizeof(float) * (size_t)cap));
-    r->wsel_cap = cap;
-  }
   std::unique_lock<std::mutex> lk(r->m_);
   if (r->safeSize_ == 0) return fail(RR_ERR_EMPTY, "rr_sample: buffer is empty");
+  if (r->epoch == 0xfffffffeu) {  // the epoch tags of SelectArgs::ismax wrap: start over from a clean slate
+    RR_SYNC_STREAMS(r);
+    for (size_t i = 0; i < r->ismax.size(); ++i)
+      if (r->ismax[i]) RR_CUDA(cudaMemset(r->ismax[i], 0, sizeof(unsigned long long)));
+    r->epoch = 0;
+  }
   rr::SelectArgs a;
   memset(&a, 0, sizeof(a));
   a.ctl = r->ctl;
   a.w = r->w;
   a.evicted = r->evicted;
-  a.l2 = r->l2;
-  a.l2min = r->l2min;
-  a.leaf = r->leaf;
-  a.leafmin = r->leafmin;
+  a.t = tiles_of(r);
   a.S = r->S;
   a.S_pad = r->S_pad;
-  a.tile_log2 = r->tile_log2;
-  a.wsel = r->wsel;
   a.head = r->head_;
   a.size = r->safeSize_;
   a.size_is = r->size_;  // storage_.size(), re-read at line 312: includes in-flight appends
@@ -1005,34 +1124,35 @@ int select_launch(rr_replay* r, int B, float* out_w, int idslot, int* pop_out) {
                 r->safeSize_);
   a.B = B;
   a.ids = r->idbuf[idslot];
-  a.is_weights = out_w;
+  a.israw = r->israw[idslot];
+  a.ismax = r->ismax[idslot];
+  a.epoch = ++r->epoch;
+  a.rng_par = r->rng_par;
   a.beta = r->beta;
   a.contract_fma = r->contract_fma;
   a.force_ordered = r->force_ordered;
-  // The tile entries are kept current by commit / update / eviction; the full
-  // build only runs here as a debugging cross-check ($RR_FULL_BUILD=1).
-  touch_main(r);
+  a.host_err = r->host_err_dev;
   if (r->slotPending[(size_t)idslot]) {
     // the previous gather out of this id buffer (gather stream) must be done reading it
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)idslot], 0));
     r->slotPending[(size_t)idslot] = false;
   }
-  if (r->full_build) {
-    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
-    r->launches++;
-  }
   RR_CUDA(rr::launch_select(a, r->main));
+  r->rng_par ^= 1;
   r->launches++;
   *pop_out = a.pop_n;
   return RR_OK;
 }
 
-int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int pop_n) {
+// out_w: this caller's importance weights (B floats, or B / n_learners with a route); may be null.
+int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot, int pop_n, bool ahead,
+                  const Route* route) {
   std::unique_lock<std::mutex> lk(r->m_);
   const int32_t* ids = r->idbuf[idslot];
   std::vector<CopyField> cf;
   rr::ConvertParams conv;
   memset(&conv, 0, sizeof(conv));
+  const int rows_per_dst = route ? B / route->n_learners : B;
   for (size_t fi = 0; fi < r->fields.size(); ++fi) {
     const FieldInfo& f = r->fields[fi];
     if (f.row_bytes == 0) continue;
@@ -1049,22 +1169,43 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
     CopyField c;
     memset(&c, 0, sizeof(c));
     c.src = f.slab;
-    c.dst = static_cast<uint8_t*>(out_fields[fi]);
+    c.dst = route ? nullptr : static_cast<uint8_t*>(out_fields[fi]);
+    c.tab = (uint32_t)fi;
     c.src_row_stride = f.row_bytes;
     c.dst_row_stride = f.chunk_bytes;
-    c.dst_chunk_stride = (uint64_t)B * f.chunk_bytes;
+    c.dst_chunk_stride = (uint64_t)rows_per_dst * f.chunk_bytes;
     c.chunk_bytes = f.chunk_bytes;
     c.chunks = f.chunks;
     cf.push_back(c);
   }
   CopyPlan plan;
   int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
-  const bool use_gs = on_gather_stream(r);
-  cudaStream_t gstream = use_gs ? r->gs : r->main;
-  if (rc == RR_OK && use_gs) {
+  if (rc == RR_OK && route) {
+    if (conv.n > 0) rc = fail(RR_ERR_ARG, "converted fields are not available on a sharded replay");
+    plan.p.dst_tab = route->dst_tab;
+    plan.p.tab_cols = (int)r->fields.size();
+    plan.p.rows_per_dst = rows_per_dst;
+    plan.p.done_counter = &r->ctl->gather_done;
+    plan.p.n_signals = route->n_signals;
+    for (int i = 0; i < route->n_signals; ++i) plan.p.signal[i] = route->signals[i];
+    plan.p.signal_val = r->epoch;  // the same on every shard: all shards run all selections
+  }
+  if (rc == RR_OK && out_w != nullptr) {
+    const int l = route ? route->my_learner : 0;
+    if (l >= 0) {
+      plan.p.norm_raw = r->israw[idslot] + (size_t)l * rows_per_dst;
+      plan.p.norm_max = r->ismax[idslot];
+      plan.p.norm_out = out_w;
+      plan.p.norm_n = rows_per_dst;
+    }
+  }
+  cudaStream_t gstream = r->main;
+  if (rc == RR_OK && ahead) {
     // the gather follows ITS selection (the last thing on `main`), not main's later work
+    gstream = r->gs[r->gs_next];
+    r->gs_next ^= 1;
     cudaError_t e = cudaEventRecord(r->evSel, r->main);
-    if (e == cudaSuccess) e = cudaStreamWaitEvent(r->gs, r->evSel, 0);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(gstream, r->evSel, 0);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
   }
   if (rc == RR_OK && conv.n > 0) {
@@ -1074,27 +1215,11 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather_convert: %s", cudaGetErrorString(e));
     r->launches++;
   }
-  if (rc == RR_OK && r->signal_ptr != nullptr) {
-    plan.p.done_counter = &r->ctl->gather_done;
-    plan.p.signal = r->signal_ptr;
-    plan.p.signal_val = ++r->signal_epoch;
-    if (plan.p.n_bulk == 0 && plan.p.n_simt == 0) rc = fail(RR_ERR_ARG, "sharded gather needs at least one field");
-  }
-  touch_main(r);
   if (rc == RR_OK) rc = launch_plan(r, plan, gstream);
-  if (rc == RR_OK && use_gs) {
-    cudaError_t e = cudaEventRecord(r->evSlot[(size_t)idslot], r->gs);
+  if (rc == RR_OK && ahead) {
+    cudaError_t e = cudaEventRecord(r->evSlot[(size_t)idslot], gstream);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
     r->slotPending[(size_t)idslot] = true;
-  }
-  bool tail = rc == RR_OK && !use_gs && (plan.p.n_bulk > 0 || plan.p.n_simt > 0) && r->shard_world == 1;
-  if (rc == RR_OK && r->signal_ptr != nullptr && r->wait_flags != nullptr) {
-    // learner: the batch is complete when every shard has published this epoch
-    cudaError_t e = rr::launch_wait_signals(r->wait_flags, r->wait_n, r->signal_epoch, &r->ctl->error,
-                                            10ull * 1000 * 1000 * 1000, r->main);
-    if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "wait_signals: %s", cudaGetErrorString(e));
-    r->launches++;
-    tail = false;
   }
   if (rc == RR_OK && r->profiling) {
     // keep this batch's ids for rr_gather_bench (a copy node here breaks the
@@ -1108,9 +1233,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
       r->hist_n++;
       r->hist_B = B;
     }
-    tail = false;
   }
-  r->tail_gather = tail;
   // blockPop bookkeeping (rela/prioritized_replay.h:94-102): the device side of
   // the eviction already ran in the selection kernel
   if (pop_n > 0) {
@@ -1124,11 +1247,12 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, int idslot, int 
   return rc;
 }
 
-int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot) {
+int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot, bool ahead,
+                const Route* route = nullptr) {
   int pop_n = 0;
-  int rc = select_launch(r, B, out_w, idslot, &pop_n);
+  int rc = select_launch(r, B, idslot, &pop_n);
   if (rc != RR_OK) return rc;
-  return gather_launch(r, B, out_fields, idslot, pop_n);
+  return gather_launch(r, B, out_fields, out_w, idslot, pop_n, ahead, route);
 }
 
 int acquire_prefetch_buffers(rr_replay* r, int B, Prefetched* out) {
@@ -1143,12 +1267,19 @@ int acquire_prefetch_buffers(rr_replay* r, int B, Prefetched* out) {
   p.B = B;
   for (auto& f : r->fields) {
     uint8_t* d = nullptr;
-    if (f.row_bytes > 0) RR_CUDA(cudaMalloc(&d, f.row_bytes * (size_t)B));
+    const size_t width = f.out_format == RR_OUT_F32_DIV255 ? 4 : f.out_format == RR_OUT_BF16_DIV255 ? 2 : 1;
+    if (f.row_bytes > 0) RR_CUDA(cudaMalloc(&d, f.row_bytes * (size_t)B * width));
     p.fields.push_back(d);
   }
   RR_CUDA(cudaMalloc(&p.weights, sizeof(float) * (size_t)B));
   *out = p;
   return RR_OK;
+}
+
+int sample_checks(rr_replay* r, int batch, const char* who) {
+  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "%s: batch %d exceeds %d", who, batch, rr::kMaxBatch);
+  if (!r->schema_set) return fail(RR_ERR_STATE, "%s: rr_set_schema has not been called", who);
+  return check_device_error(r, who);
 }
 
 }  // namespace
@@ -1158,8 +1289,9 @@ extern "C" {
 int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
     return fail(RR_ERR_ARG, "rr_sample: bad argument");
-  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_sample: batch %d exceeds %d", batch, rr::kMaxBatch);
-  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
+  int rc = sample_checks(r, batch, "rr_sample");
+  if (rc != RR_OK) return rc;
+  if (r->shard_world > 1) return fail(RR_ERR_STATE, "rr_sample: a sharded replay samples through rr_prefetch_routed");
   if (r->cur_ids >= 0) {
     // "Error: previous samples' priority has not been updated." (line 204)
     return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
@@ -1168,26 +1300,21 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     return fail(RR_ERR_STATE, "rr_sample: batches queued by rr_prefetch_into are pending (rr_take_prefetched)");
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
-  // out buffers may have been used on the caller's stream before
-  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
-    RR_CUDA(cudaEventRecord(r->evIn, cs));
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
-  }
+  rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
 
-  int rc;
   int slot;
   if (r->prefetch == 0 || r->queue.empty()) {
     slot = free_idslot(r);
-    rc = sample_into(r, batch, out_fields, out_weights, slot);
+    if (slot < 0) return RR_ERR_CUDA;
+    rc = sample_into(r, batch, out_fields, out_weights, slot, false);
     if (rc != RR_OK) return rc;
   } else {
     // futures_.front().get() (line 220): the batch selected earlier
     Prefetched p = r->queue.front();
     if (p.B != batch) return fail(RR_ERR_ARG, "rr_sample: batch %d differs from the prefetched %d", batch, p.B);
     r->queue.pop_front();
-    touch_main(r);
-    if (r->slotPending[(size_t)p.idslot]) {  // its gather ran on the gather stream
+    if (r->slotPending[(size_t)p.idslot]) {  // its gather ran on a gather stream
       RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)p.idslot], 0));
       r->slotPending[(size_t)p.idslot] = false;
     }
@@ -1215,8 +1342,9 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
     rc = acquire_prefetch_buffers(r, batch, &p);
     if (rc != RR_OK) return rc;
     p.idslot = free_idslot(r);
+    if (p.idslot < 0) return RR_ERR_CUDA;
     std::vector<void*> ptrs(p.fields.begin(), p.fields.end());
-    rc = sample_into(r, batch, ptrs.data(), p.weights, p.idslot);
+    rc = sample_into(r, batch, ptrs.data(), p.weights, p.idslot, true);
     if (rc != RR_OK) {
       r->pool.push_back(p);
       return rc;
@@ -1227,76 +1355,118 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
   return RR_OK;
 }
 
-// Zero-copy prefetch for a host layer that owns the batch buffers.
-int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
-  if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
-    return fail(RR_ERR_ARG, "rr_prefetch_into: bad argument");
-  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_prefetch_into: batch %d exceeds %d", batch, rr::kMaxBatch);
-  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_prefetch_into: rr_set_schema has not been called");
+namespace {
+int prefetch_impl(rr_replay* r, int batch, void* const* out_fields, float* out_weights, const Route* route,
+                  const unsigned long long* wait_flags, int wait_n, bool take_waits, bool ahead, cudaStream_t cs) {
   if (r->prefetch > 0) return fail(RR_ERR_STATE, "rr_prefetch_into: the replay was created with its own prefetch");
   if (r->pend_slot >= 0) return fail(RR_ERR_STATE, "rr_prefetch_into: an rr_sample_select is pending");
   if (r->queue.size() >= 16) return fail(RR_ERR_STATE, "rr_prefetch_into: 16 batches are already queued");
-  cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
-  if (cs != r->main) {  // the buffers may still be in use on the caller's stream
-    RR_CUDA(cudaEventRecord(r->evIn, cs));
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
-  }
-  int slot = free_idslot(r);
-  if (slot < 0) {
-    slot = (int)r->idbuf.size();
-    int nrc = new_idslot(r);
-    if (nrc != RR_OK) return nrc;
-  }
-  int rc = sample_into(r, batch, out_fields, out_weights, slot);
+  int rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
+  const int slot = free_idslot(r);
+  if (slot < 0) return RR_ERR_CUDA;
+  rc = sample_into(r, batch, out_fields, out_weights, slot, ahead, route);
   if (rc != RR_OK) return rc;
   r->idbusy[slot] = true;
   Prefetched p;
   p.B = batch;
   p.idslot = slot;
   p.external = true;
+  if (out_fields != nullptr)  // not owned: rr_save reads the queued batch through them
+    for (size_t fi = 0; fi < r->fields.size(); ++fi) p.fields.push_back(static_cast<uint8_t*>(out_fields[fi]));
+  p.weights = out_weights;
+  p.wait_flags = wait_flags;
+  p.wait_n = wait_n;
+  p.take_waits = take_waits;
+  p.epoch = r->epoch;
   r->queue.push_back(p);
   return RR_OK;
+}
+}  // namespace
+
+// Zero-copy prefetch for a host layer that owns the batch buffers.
+int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields, float* out_weights, void* stream) {
+  if (r == nullptr || batch <= 0 || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_prefetch_into: bad argument");
+  int rc = sample_checks(r, batch, "rr_prefetch_into");
+  if (rc != RR_OK) return rc;
+  if (r->shard_world > 1) return fail(RR_ERR_STATE, "rr_prefetch_into: a sharded replay samples through rr_prefetch_routed");
+  return prefetch_impl(r, batch, out_fields, out_weights, nullptr, nullptr, 0, false, true,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* rt, void* stream) {
+  if (r == nullptr || rt == nullptr || batch_total <= 0 || rt->n_learners < 1 || rt->n_learners > rr::kMaxPeers ||
+      rt->n_signals < 0 || rt->n_signals > rr::kMaxPeers || rt->dst_tab == nullptr ||
+      (rt->n_signals > 0 && rt->signal_ptrs == nullptr) || rt->my_learner >= rt->n_learners)
+    return fail(RR_ERR_ARG, "rr_prefetch_routed: bad argument");
+  if (batch_total % rt->n_learners != 0)
+    return fail(RR_ERR_ARG, "rr_prefetch_routed: batch %d does not split over %d learners", batch_total, rt->n_learners);
+  int rc = sample_checks(r, batch_total, "rr_prefetch_routed");
+  if (rc != RR_OK) return rc;
+  if (r->fields.empty()) return fail(RR_ERR_ARG, "rr_prefetch_routed: the schema has no field");
+  Route route;
+  route.n_learners = rt->n_learners;
+  route.dst_tab = static_cast<const uint64_t*>(rt->dst_tab);
+  route.n_signals = rt->n_signals;
+  for (int i = 0; i < rt->n_signals; ++i) route.signals[i] = static_cast<unsigned long long*>(rt->signal_ptrs[i]);
+  route.my_learner = rt->my_learner;
+  return prefetch_impl(r, batch_total, nullptr, rt->my_learner >= 0 ? rt->out_weights : nullptr, &route,
+                       static_cast<const unsigned long long*>(rt->wait_flags), rt->wait_flags ? rt->wait_n : 0,
+                       rt->my_learner >= 0, rt->on_demand == 0, static_cast<cudaStream_t>(stream));
 }
 
 int rr_take_prefetched(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_take_prefetched: null");
   if (r->cur_ids >= 0) return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
+  if (!r->queue.empty() && r->queue.front().restored)
+    return fail(RR_ERR_STATE, "rr_take_prefetched: the batch restored by rr_load has not been claimed (rr_restore_prefetched)");
   if (r->queue.empty() || !r->queue.front().external)
     return fail(RR_ERR_STATE, "rr_take_prefetched: no batch queued by rr_prefetch_into");
+  int rc = check_device_error(r, "rr_take_prefetched");
+  if (rc != RR_OK) return rc;
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   Prefetched p = r->queue.front();
   r->queue.pop_front();
   r->cur_ids = p.idslot;
   r->cur_B = p.B;
-  return publish_batch(r, cs, p.idslot);
+  rc = publish_batch(r, cs, p.idslot);
+  if (rc == RR_OK && p.wait_n > 0 && p.take_waits) {
+    // a learner of a striped replay: the batch is complete when every shard has published its epoch
+    RR_CUDA(rr::launch_wait_signals(p.wait_flags, p.wait_n, p.epoch, &r->ctl->error, r->host_err_dev,
+                                    10ull * 1000 * 1000 * 1000, cs));
+    r->launches++;
+    // ... and everything the replay does from here on (the update's exchange, adds that reuse
+    // slots) comes after every shard's gather of this batch
+    rc = order_after_caller_(r, cs);
+  }
+  return rc;
 }
 
 int rr_prefetched(rr_replay* r) { return r == nullptr ? 0 : (int)r->queue.size(); }
 
 int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr) return fail(RR_ERR_ARG, "rr_sample_select: bad argument");
-  if (batch > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_sample: batch %d exceeds %d", batch, rr::kMaxBatch);
-  if (!r->schema_set) return fail(RR_ERR_STATE, "rr_sample: rr_set_schema has not been called");
+  int rc = sample_checks(r, batch, "rr_sample");
+  if (rc != RR_OK) return rc;
+  if (r->shard_world > 1) return fail(RR_ERR_STATE, "rr_sample: a sharded replay samples through rr_prefetch_routed");
   if (r->cur_ids >= 0 || r->pend_slot >= 0)
     return fail(RR_ERR_STATE, "rr_sample: previous samples' priority has not been updated");
   r->pend_B = batch;
+  r->pend_w = out_weights;
   if (r->prefetch > 0) {  // batches come out of the prefetch queue: everything happens in rr_sample_gather
     r->pend_slot = 1 << 30;
-    r->pend_w = out_weights;
     return RR_OK;
   }
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
-  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
-    RR_CUDA(cudaEventRecord(r->evIn, cs));
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
-  }
+  rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
   const int slot = free_idslot(r);
-  int rc = select_launch(r, batch, out_weights, slot, &r->pend_pop);
+  if (slot < 0) return RR_ERR_CUDA;
+  rc = select_launch(r, batch, slot, &r->pend_pop);
   if (rc != RR_OK) return rc;
   r->pend_slot = slot;
   return RR_OK;
@@ -1312,12 +1482,9 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   // the out buffers may have been used on the caller's stream before
-  if (cs != r->main) {  // a caller working on the replay's own stream (rr_get_stream) needs no hand-shake
-    RR_CUDA(cudaEventRecord(r->evIn, cs));
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
-  }
-  int rc = gather_launch(r, batch, out_fields, slot, r->pend_pop);
+  int rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
+  rc = gather_launch(r, batch, out_fields, r->pend_w, slot, r->pend_pop, false, nullptr);
   if (rc != RR_OK) return rc;
   r->idbusy[slot] = true;
   r->cur_ids = slot;
@@ -1330,6 +1497,8 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   if (r->cur_ids < 0) return fail(RR_ERR_STATE, "rr_update_priority: no sampled batch is outstanding");
   if (n != r->cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
     return fail(RR_ERR_ARG, "rr_update_priority: %d priorities for a batch of %d", n, r->cur_B);
+  int erc = check_device_error(r, "rr_update_priority");
+  if (erc != RR_OK) return erc;
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
   const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
@@ -1337,19 +1506,12 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   const float* dprio = priority;
   std::unique_lock<std::mutex> lk(r->m_);
   if (prio_dev) {
-    if (cs != r->main) {
-      RR_CUDA(cudaEventRecord(r->evIn, cs));
-      RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
-    }
-  } else if (n <= r->inline_prio) {
-    // a learner-sized batch: the priorities travel in the launch parameters
-    // host priorities ride in the launch: the kernel consumes nothing its predecessor produces
-    // when that is a gather, and may then run beside it (a caller on the internal stream itself
-    // may have put its own work there, so not for cs == main)
-    const int wait_late = (r->late_wait && r->tail_gather && cs != r->main) ? 1 : 0;
-    RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n,
-                                     priority, r->alpha, is_weight, wait_late, r->main));
+    int rc = order_after_caller_(r, cs);
+    if (rc != RR_OK) return rc;
+  } else if (n <= rr::kInlinePrio) {
+    // a learner-sized batch handed over in host memory: the priorities travel in the launch parameters
+    RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, priority,
+                                     r->alpha, is_weight, r->main));
     dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
@@ -1371,10 +1533,9 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
     dprio = st.dev;
   }
   if (dprio != nullptr)
-    RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio,
-                              r->alpha, is_weight, 0, r->main));
+    RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha,
+                              is_weight, r->main));
   r->launches++;
-  touch_main(r);
   if (prio_dev && cs != r->main) {
     RR_CUDA(cudaEventRecord(r->evOut, r->main));
     RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
@@ -1398,6 +1559,7 @@ int rr_sync(rr_replay* r) {
   if (err != 0) {
     int zero = 0;
     RR_CUDA(cudaMemcpy(&r->ctl->error, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    *reinterpret_cast<volatile int*>(r->host_err) = 0;
     return fail(err, "device-side error %d (%s)", err,
                 err == RR_ERR_OVERRUN ? "prefix walk overran the buffer, reference asserts here" : "?");
   }
@@ -1408,11 +1570,11 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
   DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
-  if (static_cast<cudaStream_t>(stream) == r->main) return join_gather_stream(r);
+  if (static_cast<cudaStream_t>(stream) == r->main) return join_gather_streams(r);
   RR_CUDA(cudaEventRecord(r->evOut, r->main));
   RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
-  if (r->two_stream) {
-    RR_CUDA(cudaEventRecord(r->evJoin, r->gs));
+  for (cudaStream_t g : r->gs) {
+    RR_CUDA(cudaEventRecord(r->evJoin, g));
     RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evJoin, 0));
   }
   return RR_OK;
@@ -1425,7 +1587,6 @@ int rr_stream_wait(rr_replay* r, void* stream) {
   if (static_cast<cudaStream_t>(stream) == r->main) return RR_OK;
   RR_CUDA(cudaEventRecord(r->evIn, static_cast<cudaStream_t>(stream)));
   RR_CUDA(cudaStreamWaitEvent(r->main, r->evIn, 0));
-    touch_main(r);
   return RR_OK;
 }
 
@@ -1450,8 +1611,8 @@ int rr_set_profiling(rr_replay* r, int enabled, int max_batch) {
   return RR_OK;
 }
 
-int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int reps, double* ms_per_launch,
-                    uint64_t* launches, uint64_t* bytes_per_launch) {
+int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int reps, int streams,
+                    double* ms_per_launch, uint64_t* launches, uint64_t* bytes_per_launch) {
   if (r == nullptr || out_fields == nullptr || n_out_sets <= 0 || reps <= 0)
     return fail(RR_ERR_ARG, "rr_gather_bench: bad argument");
   const int nsets = (int)std::min(r->hist_n, r->hist.size());
@@ -1483,10 +1644,14 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
     }
   }
   {
-    int jrc = join_gather_stream(r);
+    int jrc = join_gather_streams(r);
     if (jrc != RR_OK) return jrc;
   }
-  touch_main(r);
+  // streams == 1: back to back on the internal stream (each launch waits for its predecessor);
+  // streams == 2: alternating over the two gather streams, the way the gathers of batches drawn
+  // ahead are issued (consecutive launches overlap ramp and drain)
+  const int ns = streams == 2 ? 2 : 1;
+  cudaStream_t lanes[2] = {ns == 2 ? r->gs[0] : r->main, ns == 2 ? r->gs[1] : r->main};
   cudaEvent_t e0, e1;
   RR_CUDA(cudaEventCreate(&e0));
   RR_CUDA(cudaEventCreate(&e1));
@@ -1496,11 +1661,17 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
     if (rc != RR_OK) return rc;
   }
   RR_CUDA(cudaEventRecord(e0, r->main));
+  if (ns == 2)
+    for (cudaStream_t g : r->gs) RR_CUDA(cudaStreamWaitEvent(g, e0, 0));
   for (int rep = 0; rep < reps; ++rep) {
     for (int k = 0; k < nsets; ++k, ++n) {
-      int rc = launch_plan(r, plans[(size_t)k * n_out_sets + (n % (uint64_t)n_out_sets)], r->main);
+      int rc = launch_plan(r, plans[(size_t)k * n_out_sets + (n % (uint64_t)n_out_sets)], lanes[n & 1]);
       if (rc != RR_OK) return rc;
     }
+  }
+  if (ns == 2) {
+    int jrc = join_gather_streams(r);
+    if (jrc != RR_OK) return jrc;
   }
   RR_CUDA(cudaEventRecord(e1, r->main));
   RR_CUDA(cudaEventSynchronize(e1));
@@ -1578,28 +1749,17 @@ int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums, float
                    int* out_tile_slots) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_tiles: null");
   DeviceScope dev_scope(r->device);
-  const bool leaves = level != 0 && r->leaf != nullptr;
-  const int nt = r->S_pad >> (leaves ? 8 : r->tile_log2);
-  if (out_tile_slots) *out_tile_slots = leaves ? 256 : 1 << r->tile_log2;
-  if (rebuild) {
-    rr::SelectArgs a;
-    memset(&a, 0, sizeof(a));
-    a.w = r->w;
-    a.l2 = r->l2;
-    a.l2min = r->l2min;
-    a.leaf = r->leaf;
-    a.leafmin = r->leafmin;
-    a.S_pad = r->S_pad;
-    a.tile_log2 = r->tile_log2;
-    touch_main(r);
-    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
-  }
+  const bool leaves = level != 0;
+  const int shift = rr::kLeafLog2 + (leaves ? 0 : r->group_log2);
+  const int nt = r->S_pad >> shift;
+  if (out_tile_slots) *out_tile_slots = 1 << shift;
+  if (rebuild) RR_CUDA(rr::launch_build_hierarchy(r->w, tiles_of(r), r->S_pad, r->main));
   RR_SYNC_STREAMS(r);
   const int n = std::min(cap, nt);
   if (out_sums && n > 0)
-    RR_CUDA(cudaMemcpy(out_sums, leaves ? r->leaf : r->l2, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+    RR_CUDA(cudaMemcpy(out_sums, leaves ? r->leaf : r->grp, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
   if (out_mins && n > 0)
-    RR_CUDA(cudaMemcpy(out_mins, leaves ? r->leafmin : r->l2min, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    RR_CUDA(cudaMemcpy(out_mins, leaves ? r->leafmin : r->grpmin, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
   return nt;
 }
 
@@ -1611,7 +1771,7 @@ int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums, float
 
 namespace {
 
-constexpr char kCkptMagic[8] = {'R', 'R', 'C', 'K', 'P', 'T', '0', '1'};
+constexpr char kCkptMagic[8] = {'R', 'R', 'C', 'K', 'P', 'T', '0', '2'};
 constexpr char kCkptTail[8] = {'R', 'R', 'C', 'K', 'E', 'N', 'D', '.'};
 
 struct CkptHeader {
@@ -1619,6 +1779,7 @@ struct CkptHeader {
   uint32_t header_bytes, nfields;
   int32_t capacity, S, shard_rank, shard_world;
   int32_t head, tail, size, mti;
+  int32_t n_queued, reserved;
   float alpha, beta;
   int64_t num_add;
   double sum;
@@ -1693,15 +1854,20 @@ int rr_save(rr_replay* r, const char* path) {
   if (r->size_ != r->safeSize_) return fail(RR_ERR_STATE, "rr_save: %d rows are still being appended", r->size_ - r->safeSize_);
   if (r->cur_ids >= 0 || r->pend_slot >= 0)
     return fail(RR_ERR_STATE, "rr_save: a sampled batch is outstanding (update its priorities first)");
-  if (!r->queue.empty()) return fail(RR_ERR_STATE, "rr_save: %d prefetched batches are pending", (int)r->queue.size());
+  if (!r->queue.empty() && r->shard_world > 1)
+    return fail(RR_ERR_STATE, "rr_save: %d batches drawn ahead are pending on a sharded replay", (int)r->queue.size());
   RR_SYNC_STREAMS(r);
+  std::fill(r->slotPending.begin(), r->slotPending.end(), false);  // every gather has finished
   rr::Ctl ctl;
   RR_CUDA(cudaMemcpy(&ctl, r->ctl, sizeof(ctl), cudaMemcpyDeviceToHost));
   if (ctl.error != 0) return fail(RR_ERR_STATE, "rr_save: the replay holds a device-side error (%d)", ctl.error);
 
+  // write <path>.tmp, flush it to the disk, then rename: a crash mid-save leaves the previous
+  // checkpoint intact
+  const std::string tmp = std::string(path) + ".tmp";
   FileGuard fg;
-  fg.f = fopen(path, "wb");
-  if (!fg.f) return fail(RR_ERR_ARG, "rr_save: cannot open %s: %s", path, strerror(errno));
+  fg.f = fopen(tmp.c_str(), "wb");
+  if (!fg.f) return fail(RR_ERR_ARG, "rr_save: cannot open %s: %s", tmp.c_str(), strerror(errno));
   auto put = [&](const void* p, size_t n) { return n == 0 || fwrite(p, 1, n, fg.f) == n; };
   CkptHeader h;
   memset(&h, 0, sizeof(h));
@@ -1715,12 +1881,13 @@ int rr_save(rr_replay* r, const char* path) {
   h.head = r->head_;
   h.tail = r->tail_;
   h.size = r->size_;
-  h.mti = ctl.mti;
+  h.mti = ctl.mti[r->rng_par];
   h.alpha = r->alpha;
   h.beta = r->beta;
   h.num_add = r->numAdd_.load();
   h.sum = ctl.sum;
-  memcpy(h.mt, ctl.mt, sizeof(h.mt));
+  h.n_queued = (int32_t)r->queue.size();
+  memcpy(h.mt, ctl.mt[r->rng_par], sizeof(h.mt));
   bool ok = put(&h, sizeof(h));
   for (auto& f : r->fields) {
     const uint32_t len = (uint32_t)f.name.size();
@@ -1735,24 +1902,53 @@ int rr_save(rr_replay* r, const char* path) {
   }
   PinnedGuard pg;
   RR_CUDA(cudaHostAlloc(&pg.p, kCkptBounce, cudaHostAllocDefault));
+  auto put_device = [&](const uint8_t* src, size_t left) -> int {
+    while (left > 0 && ok) {
+      const size_t n = std::min(left, kCkptBounce);
+      RR_CUDA(cudaMemcpy(pg.p, src, n, cudaMemcpyDeviceToHost));
+      ok = put(pg.p, n);
+      src += n;
+      left -= n;
+    }
+    return RR_OK;
+  };
   int rg[2][2];
   const int nrg = live_ranges(r, h.head, h.size, rg);
   for (auto& f : r->fields) {
     if (f.row_bytes == 0) continue;
     for (int k = 0; k < nrg && ok; ++k) {
-      const uint8_t* src = f.slab + (size_t)(rg[k][0] - r->own_lo) * f.row_bytes;
-      size_t left = (size_t)(rg[k][1] - rg[k][0]) * f.row_bytes;
-      while (left > 0 && ok) {
-        const size_t n = std::min(left, kCkptBounce);
-        RR_CUDA(cudaMemcpy(pg.p, src, n, cudaMemcpyDeviceToHost));
-        ok = put(pg.p, n);
-        src += n;
-        left -= n;
-      }
+      int rc = put_device(f.slab + (size_t)(rg[k][0] - r->own_lo) * f.row_bytes,
+                          (size_t)(rg[k][1] - rg[k][0]) * f.row_bytes);
+      if (rc != RR_OK) return rc;
     }
   }
-  ok = ok && put(kCkptTail, 8) && fflush(fg.f) == 0;
-  if (!ok) return fail(RR_ERR_ARG, "rr_save: write to %s failed: %s", path, strerror(errno));
+  // batches drawn ahead (the reference's futures, prioritized_replay.h:215-230): their sampled
+  // ids, importance weights and gathered rows, oldest first, so that a restored run hands out the
+  // very batches the saved run would have (a slot may have been overwritten since it was gathered)
+  for (const Prefetched& q : r->queue) {
+    if (!ok) break;
+    const int32_t B = q.B;
+    ok = put(&B, 4);
+    int rc = put_device(reinterpret_cast<const uint8_t*>(r->idbuf[q.idslot]), sizeof(int32_t) * (size_t)B);
+    if (rc == RR_OK) rc = put_device(reinterpret_cast<const uint8_t*>(q.weights), sizeof(float) * (size_t)B);
+    for (size_t fi = 0; fi < r->fields.size() && rc == RR_OK; ++fi) {
+      const FieldInfo& f = r->fields[fi];
+      const uint32_t width = f.out_format == RR_OUT_F32_DIV255 ? 4 : f.out_format == RR_OUT_BF16_DIV255 ? 2 : 1;
+      if (f.row_bytes > 0) rc = put_device(q.fields[fi], f.row_bytes * (size_t)B * width);
+    }
+    if (rc != RR_OK) return rc;
+  }
+  ok = ok && put(kCkptTail, 8) && fflush(fg.f) == 0 && fsync(fileno(fg.f)) == 0;
+  if (ok) {
+    ok = fclose(fg.f) == 0;
+    fg.f = nullptr;
+  }
+  if (ok) ok = rename(tmp.c_str(), path) == 0;
+  if (!ok) {
+    const int err = errno;
+    remove(tmp.c_str());
+    return fail(RR_ERR_ARG, "rr_save: write to %s failed: %s", path, strerror(err));
+  }
   return RR_OK;
 }
 
@@ -1776,7 +1972,8 @@ int rr_load(rr_replay* r, const char* path) {
   if (h.alpha != r->alpha || h.beta != r->beta)
     return fail(RR_ERR_ARG, "rr_load: checkpoint alpha/beta %g/%g, this replay %g/%g", h.alpha, h.beta, r->alpha, r->beta);
   if (h.nfields != r->fields.size()) return fail(RR_ERR_ARG, "rr_load: %u fields in the checkpoint, %zu in the schema", h.nfields, r->fields.size());
-  if (h.size < 0 || h.size > h.S || h.head < 0 || h.head >= h.S || h.tail != (h.head + h.size) % h.S || h.mti < 0 || h.mti > 624)
+  if (h.size < 0 || h.size > h.S || h.head < 0 || h.head >= h.S || h.tail != (h.head + h.size) % h.S || h.mti < 0 ||
+      h.mti > 624 || h.n_queued < 0 || h.n_queued > 16)
     return fail(RR_ERR_ARG, "rr_load: corrupt ring counters");
   for (auto& f : r->fields) {
     uint32_t len = 0, chunks = 0;
@@ -1802,48 +1999,96 @@ int rr_load(rr_replay* r, const char* path) {
   }
   PinnedGuard pg;
   RR_CUDA(cudaHostAlloc(&pg.p, kCkptBounce, cudaHostAllocDefault));
+  auto get_device = [&](uint8_t* dst, size_t left) -> int {
+    while (left > 0) {
+      const size_t n = std::min(left, kCkptBounce);
+      if (!get(pg.p, n)) return fail(RR_ERR_ARG, "rr_load: truncated checkpoint");
+      RR_CUDA(cudaMemcpy(dst, pg.p, n, cudaMemcpyHostToDevice));
+      dst += n;
+      left -= n;
+    }
+    return RR_OK;
+  };
   int rg[2][2];
   const int nrg = live_ranges(r, h.head, h.size, rg);
   for (auto& f : r->fields) {
     if (f.row_bytes == 0) continue;
     for (int k = 0; k < nrg; ++k) {
-      uint8_t* dst = f.slab + (size_t)(rg[k][0] - r->own_lo) * f.row_bytes;
-      size_t left = (size_t)(rg[k][1] - rg[k][0]) * f.row_bytes;
-      while (left > 0) {
-        const size_t n = std::min(left, kCkptBounce);
-        if (!get(pg.p, n)) return fail(RR_ERR_ARG, "rr_load: truncated checkpoint");
-        RR_CUDA(cudaMemcpy(dst, pg.p, n, cudaMemcpyHostToDevice));
-        dst += n;
-        left -= n;
-      }
+      int rc = get_device(f.slab + (size_t)(rg[k][0] - r->own_lo) * f.row_bytes,
+                          (size_t)(rg[k][1] - rg[k][0]) * f.row_bytes);
+      if (rc != RR_OK) return rc;
     }
+  }
+  // batches that had been drawn ahead: back into the queue, in library-owned buffers; a host
+  // layer that manages the prefetch itself moves them into its own (rr_restore_prefetched)
+  for (int k = 0; k < h.n_queued; ++k) {
+    int32_t B = 0;
+    if (!get(&B, 4) || B <= 0 || B > rr::kMaxBatch) return fail(RR_ERR_ARG, "rr_load: corrupt queued batch");
+    Prefetched q;
+    int rc = acquire_prefetch_buffers(r, B, &q);
+    if (rc != RR_OK) return rc;
+    q.idslot = free_idslot(r);
+    if (q.idslot < 0) return RR_ERR_CUDA;
+    rc = ensure_idbuf(r, q.idslot, B);
+    if (rc == RR_OK) rc = get_device(reinterpret_cast<uint8_t*>(r->idbuf[q.idslot]), sizeof(int32_t) * (size_t)B);
+    if (rc == RR_OK) rc = get_device(reinterpret_cast<uint8_t*>(q.weights), sizeof(float) * (size_t)B);
+    for (size_t fi = 0; fi < r->fields.size() && rc == RR_OK; ++fi) {
+      const FieldInfo& f = r->fields[fi];
+      const uint32_t width = f.out_format == RR_OUT_F32_DIV255 ? 4 : f.out_format == RR_OUT_BF16_DIV255 ? 2 : 1;
+      if (f.row_bytes > 0) rc = get_device(q.fields[fi], f.row_bytes * (size_t)B * width);
+    }
+    if (rc != RR_OK) return rc;
+    r->idbusy[q.idslot] = true;
+    q.restored = r->prefetch == 0;  // not the library's own queue: waits for rr_restore_prefetched
+    r->queue.push_back(q);
   }
   char tail[8];
   if (!get(tail, 8) || memcmp(tail, kCkptTail, 8) != 0) return fail(RR_ERR_ARG, "rr_load: truncated checkpoint");
   rr::Ctl ctl;
   RR_CUDA(cudaMemcpy(&ctl, r->ctl, sizeof(ctl), cudaMemcpyDeviceToHost));
-  memcpy(ctl.mt, h.mt, sizeof(h.mt));
-  ctl.mti = h.mti;
+  memcpy(ctl.mt[r->rng_par], h.mt, sizeof(h.mt));
+  ctl.mti[r->rng_par] = h.mti;
   ctl.sum = h.sum;
   RR_CUDA(cudaMemcpy(r->ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice));
-  {  // tile entries of the restored weights
-    rr::SelectArgs a;
-    memset(&a, 0, sizeof(a));
-    a.w = r->w;
-    a.l2 = r->l2;
-    a.l2min = r->l2min;
-    a.leaf = r->leaf;
-    a.leafmin = r->leafmin;
-    a.S_pad = r->S_pad;
-    a.tile_log2 = r->tile_log2;
-    RR_CUDA(rr::launch_build_hierarchy(a, r->main));
-    RR_CUDA(cudaStreamSynchronize(r->main));
-  }
+  // hierarchy entries of the restored weights
+  RR_CUDA(rr::launch_build_hierarchy(r->w, tiles_of(r), r->S_pad, r->main));
+  RR_CUDA(cudaStreamSynchronize(r->main));
   r->head_ = h.head;
   r->tail_ = r->safeTail_ = h.tail;
   r->size_ = r->safeSize_ = h.size;
   r->numAdd_.store((int)h.num_add);
   return RR_OK;
+}
+
+int rr_restore_prefetched(rr_replay* r, int k, void* const* out_fields, float* out_weights, void* stream) {
+  if (r == nullptr || out_weights == nullptr || (!r->fields.empty() && out_fields == nullptr))
+    return fail(RR_ERR_ARG, "rr_restore_prefetched: bad argument");
+  if (k < 0 || k >= (int)r->queue.size() || !r->queue[(size_t)k].restored)
+    return fail(RR_ERR_STATE, "rr_restore_prefetched: queue entry %d was not restored by rr_load", k);
+  DeviceScope dev_scope(r->device);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  Prefetched& q = r->queue[(size_t)k];
+  for (size_t fi = 0; fi < r->fields.size(); ++fi) {
+    const FieldInfo& f = r->fields[fi];
+    if (f.row_bytes == 0) continue;
+    const uint32_t width = f.out_format == RR_OUT_F32_DIV255 ? 4 : f.out_format == RR_OUT_BF16_DIV255 ? 2 : 1;
+    RR_CUDA(cudaMemcpyAsync(out_fields[fi], q.fields[fi], f.row_bytes * (size_t)q.B * width, cudaMemcpyDeviceToDevice, cs));
+  }
+  RR_CUDA(cudaMemcpyAsync(out_weights, q.weights, sizeof(float) * (size_t)q.B, cudaMemcpyDeviceToDevice, cs));
+  RR_CUDA(cudaStreamSynchronize(cs));
+  for (auto* f : q.fields) cudaFree(f);
+  cudaFree(q.weights);
+  q.fields.clear();
+  for (size_t fi = 0; fi < r->fields.size(); ++fi) q.fields.push_back(static_cast<uint8_t*>(out_fields[fi]));
+  q.weights = out_weights;
+  q.restored = false;
+  q.external = true;
+  return RR_OK;
+}
+
+int rr_prefetched_batch(rr_replay* r, int k) {
+  if (r == nullptr || k < 0 || k >= (int)r->queue.size()) return 0;
+  return r->queue[(size_t)k].B;
 }
 
 // -------------------------------------------------------------- actor math

@@ -46,14 +46,25 @@ __device__ __forceinline__ bool row_slot(const CopyParams& p, uint32_t b, uint32
     slot = (uint32_t)p.insert_start + b;
     if (slot >= (uint32_t)p.slots) slot -= (uint32_t)p.slots;
   }
-  *local = slot - (uint32_t)p.own_lo;
+  *local = slot - (uint32_t)p.own_lo;  // sharded insert (dst_tab): own_lo == 0, i.e. the ring slot itself
   return slot >= (uint32_t)p.own_lo && slot < (uint32_t)p.own_hi;
 }
 
 __device__ __forceinline__ uint8_t* row_dst(const CopyParams& p, const CopyField& f, uint32_t b, uint32_t t,
                                             uint32_t off, uint32_t local) {
   if (p.ids != nullptr) {  // gather: batch [t, b, :]
+    if (p.dst_tab != nullptr) {  // ... of the learner that owns batch row b
+      const uint32_t learner = b / (uint32_t)p.rows_per_dst;
+      const uint32_t bl = b - learner * (uint32_t)p.rows_per_dst;
+      uint8_t* base = reinterpret_cast<uint8_t*>(__ldg(p.dst_tab + (size_t)learner * p.tab_cols + f.tab));
+      return base + (uint64_t)t * f.dst_chunk_stride + (uint64_t)bl * f.dst_row_stride + off;
+    }
     return f.dst + (uint64_t)t * f.dst_chunk_stride + (uint64_t)b * f.dst_row_stride + off;
+  }
+  if (p.dst_tab != nullptr) {  // insert into a striped replay: the slab of the shard that owns the slot
+    const uint32_t owner = local / (uint32_t)p.rows_per_dst;
+    uint8_t* base = reinterpret_cast<uint8_t*>(__ldg(p.dst_tab + (size_t)owner * p.tab_cols + f.tab));
+    return base + (uint64_t)(local - owner * (uint32_t)p.rows_per_dst) * f.dst_row_stride + (uint64_t)t * f.chunk_bytes + off;
   }
   return f.dst + (uint64_t)local * f.dst_row_stride + (uint64_t)t * f.chunk_bytes + off;  // insert: slab row
 }
@@ -159,7 +170,7 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       // the stores only have to be done READING shared memory before the CTA
       // exits; kernel completion makes them visible. With a completion signal
       // they must be complete before the flag is published.
-      if (p.signal != nullptr) bulk_wait_all<0>(); else bulk_wait_read<0>();
+      if (p.n_signals > 0) bulk_wait_all<0>(); else bulk_wait_read<0>();
       if (probe && tid == 0) {
         probe[6] = clock64();
         probe[7] = globaltimer_ns();
@@ -171,22 +182,26 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     pdl_launch_dependents();
     simt_rows(p);
   }
-  if (p.signal == nullptr) return;
+  if (p.n_signals == 0) return;
   // ---- completion: the last CTA publishes the epoch (st.release.sys) after
   // every CTA's stores have been fenced at system scope
+  __shared__ int sh_last;
   __syncthreads();
   if (tid == 0) {
     __threadfence_system();
-    if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
+    sh_last = atomicAdd(p.done_counter, 1u) == gridDim.x - 1;
+    if (sh_last) {
       atomicExch(p.done_counter, 0u);
       __threadfence_system();
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.signal), "l"(p.signal_val) : "memory");
     }
   }
+  __syncthreads();
+  if (sh_last && tid < p.n_signals)
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.signal[tid]), "l"(p.signal_val) : "memory");
 }
 
 __global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsigned long long val, int* error,
-                                    unsigned long long timeout_ns) {
+                                    int* host_error, unsigned long long timeout_ns) {
   const int lane = threadIdx.x;
   if (lane >= n) return;
   const unsigned long long t0 = globaltimer_ns();
@@ -196,6 +211,10 @@ __global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsi
     if (v >= val) break;
     if (globaltimer_ns() - t0 > timeout_ns) {
       *error = 2;  // RR_ERR_CUDA: a shard never signalled
+      if (host_error != nullptr) {
+        *reinterpret_cast<volatile int*>(host_error) = 2;
+        __threadfence_system();
+      }
       break;
     }
     __nanosleep(100);
@@ -227,6 +246,60 @@ __global__ void __launch_bounds__(256) peer_put_kernel(const uint8_t* __restrict
   if (tid < n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flag[tid]), "l"(val) : "memory");
 }
 
+// peer_put + wait in one launch: push this rank's contribution to every rank's inbox (its own
+// included), publish `val` at this rank's flag in each of them, then acquire until the flags of
+// all n_wait contributors in MY inbox have reached `val`. The all-gather of new priorities /
+// block weights between the shards of a striped replay, without a collective library.
+__global__ void __launch_bounds__(256) exchange_kernel(const uint8_t* __restrict__ src, uint32_t bytes, PeerList peers,
+                                                       int n, unsigned long long val,
+                                                       const unsigned long long* wait_flags, int n_wait, int* error,
+                                                       int* host_error, unsigned long long timeout_ns) {
+  const int tid = threadIdx.x;
+  if (bytes > 0) {
+    for (int p = 0; p < n; ++p) {
+      uint8_t* dst = static_cast<uint8_t*>(peers.dst[p]);
+      if ((bytes & 15u) == 0 && ((uintptr_t)src & 15u) == 0 && ((uintptr_t)dst & 15u) == 0) {
+        for (uint32_t i = tid * 16u; i < bytes; i += blockDim.x * 16u)
+          *reinterpret_cast<uint4*>(dst + i) = *reinterpret_cast<const uint4*>(src + i);
+      } else {
+        for (uint32_t i = tid; i < bytes; i += blockDim.x) dst[i] = src[i];
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flag[tid]), "l"(val) : "memory");
+  if (tid < n_wait) {
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+      unsigned long long v;
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(wait_flags + tid) : "memory");
+      if (v >= val) break;
+      if (globaltimer_ns() - t0 > timeout_ns) {
+        *error = 2;  // RR_ERR_CUDA: a shard never published
+        if (host_error != nullptr) {
+          *reinterpret_cast<volatile int*>(host_error) = 2;
+          __threadfence_system();
+        }
+        break;
+      }
+      __nanosleep(100);
+    }
+  }
+}
+
+cudaError_t launch_exchange(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
+                            unsigned long long val, const unsigned long long* wait_flags, int n_wait, int* error,
+                            int* host_error, unsigned long long timeout_ns, cudaStream_t stream) {
+  PeerList pl;
+  for (int i = 0; i < n; ++i) {
+    pl.dst[i] = dst[i];
+    pl.flag[i] = static_cast<unsigned long long*>(flags[i]);
+  }
+  return launch_pdl(exchange_kernel, dim3(1), dim3(256), 0, stream, static_cast<const uint8_t*>(src), bytes, pl, n, val,
+                    wait_flags, n_wait, error, host_error, timeout_ns);
+}
+
 cudaError_t launch_peer_put(const void* src, uint32_t bytes, void* const* dst, void* const* flags, int n,
                             unsigned long long val, cudaStream_t stream) {
   PeerList pl;
@@ -241,11 +314,16 @@ cudaError_t launch_peer_put(const void* src, uint32_t bytes, void* const* dst, v
 namespace {
 __device__ __forceinline__ void simt_rows(const CopyParams& p) {
   const int tid = threadIdx.x;
-  if (p.n_simt == 0) return;
   const uint32_t lane_base = (p.n_bulk > 0) ? 32u : 0u;
   const uint64_t per_cta = blockDim.x - lane_base;
   uint64_t u = (uint64_t)blockIdx.x * per_cta + (tid - lane_base);
   const uint64_t stride = (uint64_t)gridDim.x * per_cta;
+  if (p.norm_n > 0) {
+    // importance weights: raw / max (the max's low word; the high word is the selection's epoch)
+    const float mx = __uint_as_float((uint32_t)__ldcg(p.norm_max));
+    for (uint64_t i = u; i < (uint64_t)p.norm_n; i += stride) p.norm_out[i] = __fdiv_rn(__ldcg(p.norm_raw + i), mx);
+  }
+  if (p.n_simt == 0) return;
   for (; u < p.simt_units; u += stride) {
     int fi = 0;
 #pragma unroll 1
@@ -267,13 +345,14 @@ __device__ __forceinline__ void simt_rows(const CopyParams& p) {
 }  // namespace
 
 cudaError_t launch_wait_signals(const unsigned long long* flags, int n, unsigned long long val, int* error,
-                                unsigned long long timeout_ns, cudaStream_t stream) {
-  wait_signals_kernel<<<1, 32, 0, stream>>>(flags, n, val, error, timeout_ns);
+                                int* host_error, unsigned long long timeout_ns, cudaStream_t stream) {
+  wait_signals_kernel<<<1, 32, 0, stream>>>(flags, n, val, error, host_error, timeout_ns);
   return cudaGetLastError();
 }
 
 cudaError_t launch_row_copy(const CopyParams& p, const CopyLaunch& cfg, cudaStream_t stream) {
-  cudaError_t e = ensure_dynamic_smem(row_copy_kernel, 227 * 1024);
+  // the kernel has a few bytes of static shared memory: opt in to what this launch needs, not to the 227 KB maximum
+  cudaError_t e = ensure_dynamic_smem(row_copy_kernel, cfg.smem);
   if (e != cudaSuccess) return e;
   return launch_pdl(row_copy_kernel, dim3(cfg.grid), dim3(cfg.block), cfg.smem, stream, p);
 }

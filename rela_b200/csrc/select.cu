@@ -10,9 +10,10 @@
 // representable in double, that walk returns the same indices as ANY
 // association of the same additions. A sufficient, cheaply checkable condition:
 // all weights are multiples of u = ulp(smallest non-zero weight) and the total
-// is < 2^52 * u. Then every value this file computes (tile sums, prefixes,
-// differences of prefixes) is a multiple of u below 2^53 * u, hence exact in
-// fp64, and the two-level search below is bit-identical to the sequential walk. When the condition fails (weights spanning > 29 binades
+// is < 2^52 * u. Then every value this file computes (leaf sums, group sums,
+// prefixes, differences of prefixes) is a multiple of u below 2^53 * u, hence
+// exact in fp64, and the three-level search below is bit-identical to the
+// sequential walk. When the condition fails (weights spanning > 29 binades
 // relative to the total) the kernel takes the ordered walk instead, which is
 // the reference's loop verbatim, and counts it in Ctl::n_ordered.
 //
@@ -32,8 +33,6 @@ namespace rr {
 
 namespace {
 
-constexpr int kSelThreads = 512;
-
 __device__ __forceinline__ float pow_alpha(float p, float alpha) {
   // K2: priority ^ alpha. alpha == 1 is the identity (ATen copies in that
   // case). Otherwise evaluate in fp64 and round once: correctly rounded
@@ -48,11 +47,27 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// inclusive warp scan
+__device__ __forceinline__ double warp_scan(double v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double y = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += y;
+  }
+  return v;
+}
+
 // ------------------------------------------------------------------ K3 build
 // Sum (fp64) and smallest non-zero magnitude of 256 consecutive slots held as
-// 8 values per lane. Every producer of a tile entry -- the full build and the
-// incremental retile paths of commit / update / eviction -- goes through this
-// one association, so that a retiled entry is bit-identical to a rebuilt one.
+// 8 values per lane. Every producer of a leaf entry -- the full build and the
+// incremental paths of commit / update / eviction -- goes through this one
+// association, so that a maintained entry is bit-identical to a rebuilt one.
 __device__ __forceinline__ void reduce256(const float4 a, const float4 b, double& s, float& mn) {
   s = (((double)a.x + (double)a.y) + ((double)a.z + (double)a.w)) +
       (((double)b.x + (double)b.y) + ((double)b.z + (double)b.w));
@@ -62,98 +77,80 @@ __device__ __forceinline__ void reduce256(const float4 a, const float4 b, double
   for (int k = 0; k < 8; ++k)
     if (v[k] != 0.0f) mn = fminf(mn, fabsf(v[k]));
   s = warp_sum(s);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  mn = warp_min(mn);
 }
 
-// One warp recomputes tile t (and its leaves) from the weights in global memory.
-__device__ __forceinline__ void retile_warp(const float* w, const Tiles& tl, int t, int lane) {
-  const int nb = 1 << (tl.tile_log2 - 8);
-  double tot = 0.0;
-  float m = FLT_MAX;
-  for (int k = 0; k < nb; ++k) {
-    const float4* src = reinterpret_cast<const float4*>(w + ((size_t)t << tl.tile_log2) + (size_t)k * 256) + lane * 2;
-    const float4 a = src[0], b = src[1];
-    double s;
-    float mn;
-    reduce256(a, b, s, mn);
-    if (lane == 0 && tl.leaf != nullptr) {
-      tl.leaf[(size_t)t * nb + k] = s;
-      tl.leafmin[(size_t)t * nb + k] = mn;
-    }
-    tot += s;
-    m = fminf(m, mn);
-  }
+// Same for a group entry: lane l holds the (sum, min) of leaves l and l + 32 of
+// the group (0 / FLT_MAX beyond the group's last leaf).
+__device__ __forceinline__ void reduce_group(double s0, double s1, float m0, float m1, double& s, float& mn) {
+  s = warp_sum(s0 + s1);
+  mn = warp_min(fminf(m0, m1));
+}
+
+// One warp recomputes leaf `lf` from the weights in global memory.
+__device__ __forceinline__ void retile_leaf(const float* w, const Tiles& tl, int lf, int lane) {
+  const float4* src = reinterpret_cast<const float4*>(w + ((size_t)lf << kLeafLog2)) + lane * 2;
+  const float4 a = src[0], b = src[1];
+  double s;
+  float mn;
+  reduce256(a, b, s, mn);
   if (lane == 0) {
-    tl.l2[t] = tot;
-    tl.l2min[t] = m;
+    tl.leaf[lf] = s;
+    tl.leafmin[lf] = mn;
   }
 }
 
-// The tiles overlapping ring range [start, start + n) (mod S), one warp per
-// tile. The caller has made the new weights of the range visible to the CTA.
-__device__ __forceinline__ void retile_range(const float* w, const Tiles& tl, int S, int start, int n, int warp,
-                                             int nwarps, int lane) {
+// One warp recomputes group g from its leaf entries in global memory.
+__device__ __forceinline__ void regroup(const Tiles& tl, int g, int lane) {
+  const int L = 1 << tl.group_log2;
+  const size_t lb = (size_t)g << tl.group_log2;
+  const double s0 = lane < L ? tl.leaf[lb + lane] : 0.0;
+  const double s1 = lane + 32 < L ? tl.leaf[lb + 32 + lane] : 0.0;
+  const float m0 = lane < L ? tl.leafmin[lb + lane] : FLT_MAX;
+  const float m1 = lane + 32 < L ? tl.leafmin[lb + 32 + lane] : FLT_MAX;
+  double s;
+  float mn;
+  reduce_group(s0, s1, m0, m1, s, mn);
+  if (lane == 0) {
+    tl.grp[g] = s;
+    tl.grpmin[g] = mn;
+  }
+}
+
+// The leaves (shift = 8) or groups (shift = 8 + group_log2) overlapping ring
+// range [start, start + n) (mod S), one warp per entry. The caller has made the
+// inputs (weights, resp. leaf entries) of the range visible to the CTA.
+template <bool kGroups>
+__device__ __forceinline__ void refresh_range(const float* w, const Tiles& tl, int S, int start, int n, int warp,
+                                              int nwarps, int lane) {
+  const int shift = kGroups ? kLeafLog2 + tl.group_log2 : kLeafLog2;
   const int n1 = min(n, S - start);
   for (int seg = 0; seg < 2; ++seg) {
     const int lo = seg == 0 ? start : 0;
     const int len = seg == 0 ? n1 : n - n1;
     if (len <= 0) continue;
-    const int t1 = (lo + len - 1) >> tl.tile_log2;
-    for (int t = (lo >> tl.tile_log2) + warp; t <= t1; t += nwarps) retile_warp(w, tl, t, lane);
+    const int t1 = (lo + len - 1) >> shift;
+    for (int t = (lo >> shift) + warp; t <= t1; t += nwarps) {
+      if (kGroups) regroup(tl, t, lane); else retile_leaf(w, tl, t, lane);
+    }
   }
 }
 
-__device__ __host__ __forceinline__ Tiles tiles_of(const SelectArgs& a) {
-  Tiles t;
-  t.l2 = a.l2;
-  t.l2min = a.l2min;
-  t.leaf = a.leaf;
-  t.leafmin = a.leafmin;
-  t.tile_log2 = a.tile_log2;
-  return t;
-}
-
-// Full build: one CTA of 256 threads per 2048 slots, a warp per 256 slots;
-// tiles are 256 << k slots, i.e. 1 << k consecutive warps. Runs once at
-// creation (and on demand for the debug cross-check): afterwards the tile
-// entries are maintained by the kernels that change a weight.
-__global__ void __launch_bounds__(256) build_hierarchy_kernel(const float* __restrict__ w, const Tiles tl) {
-  double* __restrict__ l2 = tl.l2;
-  float* __restrict__ l2min = tl.l2min;
-  const int tile_log2 = tl.tile_log2;
-  const int tid = threadIdx.x;
-  const int lane = tid & 31, warp = tid >> 5;
+// Full build: one CTA of 256 threads per 2048 slots, a warp per leaf; then one
+// warp per group. Runs at creation and after a checkpoint load (and on demand
+// for the debug cross-check): afterwards the entries are maintained by the
+// kernels that change a weight.
+__global__ void __launch_bounds__(256) build_leaves_kernel(const float* __restrict__ w, const Tiles tl) {
   pdl_launch_dependents();
   pdl_wait();
-  const float4* src = reinterpret_cast<const float4*>(w) + (size_t)blockIdx.x * (kBuildSpan / 4) + tid * 2;
-  const float4 a = src[0], b = src[1];
-  double s;
-  float mn;
-  reduce256(a, b, s, mn);
-  __shared__ double ws[8];
-  __shared__ float wm[8];
-  if (lane == 0) {
-    ws[warp] = s;
-    wm[warp] = mn;
-    if (tl.leaf != nullptr) {
-      tl.leaf[(size_t)blockIdx.x * 8 + warp] = s;
-      tl.leafmin[(size_t)blockIdx.x * 8 + warp] = mn;
-    }
-  }
-  __syncthreads();
-  const int wpt = 1 << (tile_log2 - 8);  // warps per tile
-  const int tiles = 8 / wpt;             // tiles per CTA
-  if (tid < tiles) {
-    double tot = 0.0;
-    float m = FLT_MAX;
-    for (int k = 0; k < wpt; ++k) {
-      tot += ws[tid * wpt + k];
-      m = fminf(m, wm[tid * wpt + k]);
-    }
-    l2[(size_t)blockIdx.x * tiles + tid] = tot;
-    l2min[(size_t)blockIdx.x * tiles + tid] = m;
-  }
+  retile_leaf(w, tl, (int)blockIdx.x * (kBuildSpan >> kLeafLog2) + (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31));
+}
+
+__global__ void __launch_bounds__(256) build_groups_kernel(const Tiles tl) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int g = (int)blockIdx.x * 8 + (int)(threadIdx.x >> 5);
+  if (g < tl.ng) regroup(tl, g, (int)(threadIdx.x & 31));
 }
 
 // ------------------------------------------------------------ mt19937 (K4)
@@ -232,49 +229,76 @@ __device__ void gen_targets(uint32_t* mt, int mti, int B, int d_lo, int d_hi, fl
   *mti_out = (mti + B - 1) % 624 + 1;
 }
 
+
+// Raw importance weight of one selected element (rela/prioritized_replay.h:320-321):
+// weights = w / sum; weights = pow(size * weights, -beta), in float like ATen,
+// the pow evaluated in fp64 and rounded once.
+__device__ __forceinline__ float is_raw(float wv, float sumf, int size_is, float beta) {
+  float v = __fdiv_rn(wv, sumf);
+  v = __fmul_rn((float)size_is, v);
+  return (float)pow((double)v, (double)(-beta));
+}
+
+__device__ __forceinline__ void publish_max(unsigned long long* ismax, uint32_t epoch, float v) {
+  // v >= +0 (or +inf): the float order is the order of the bit patterns. NaN is skipped like fmaxf does.
+  if (v == v) atomicMax(ismax, ((unsigned long long)epoch << 32) | (unsigned long long)__float_as_uint(v));
+}
+
+__device__ __forceinline__ void raise_error(const SelectArgs& a, int code) {
+  a.ctl->error = code;  // reference: assert(false) at lines 297-302
+  if (a.host_err != nullptr) {
+    *reinterpret_cast<volatile int*>(a.host_err) = code;
+    __threadfence_system();
+  }
+}
+
 }  // namespace
 
 // -------------------------------------------------------------- K4/K5 select
-// Grid: one CTA of 512 threads per 32 targets. Every CTA pulls the tile sums
-// (at most 16 K doubles, L2-resident) into shared memory with one bulk async
-// copy, scans them, and regenerates the mt19937 stream for its own targets, so
-// the CTAs never wait for each other; the CTA that finishes last (ticket in
-// Ctl::done_ctas) evicts, turns the selected weights into importance weights
-// (block-wide max) and writes the RNG state back.
+// Grid: one CTA of 256 threads per 8 targets, one warp per target. Every CTA
+// pulls the group sums and minima (1.3 KB + 0.6 KB at 2^21 transitions; at most
+// 24 KB) and the mt19937 state into shared memory with three bulk async copies,
+// scans the group sums, regenerates the mt19937 stream for its own targets, and
+// then each warp walks group -> leaf -> slot for its target: 64 leaf sums, then
+// 256 weights, both read coalesced from L2. The CTAs never wait for each other:
+//   * importance weights leave RAW with an atomic max (SelectArgs::israw);
+//   * the RNG state is double-buffered, CTA 0 writes the successor state;
+//   * only a call that has to evict (pop_n > 0) elects a last CTA (ticket in
+//     Ctl::done_ctas) to pop after every CTA's marks, like the reference.
 //
 // All prefix arithmetic is in fp64 on the weights themselves. Under the
 // exactness condition (every weight a multiple of u = ulp(min non-zero weight),
 // total < 2^52 u) every partial sum formed here is a multiple of u below
 // 2^53 u, hence exact and independent of the association. Conversely, if any
-// addition anywhere (tile sums included) had to round, its result is >= 2^53 u
-// and so is the total: the single test `total < 2^52 u` detects every inexact
-// case, and those take the ordered walk.
+// addition anywhere (leaf and group sums included) had to round, its result is
+// >= 2^53 u and so is the total: the single test `total < 2^52 u` detects every
+// inexact case, and those take the ordered walk.
 //
-// Dynamic shared memory: tile prefixes (8 B x tiles) | tile minima (4 B x tiles);
-// the first region is reused for the targets of the ordered walk and for the
-// importance weights.
-__global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs a) {
+// Dynamic shared memory: group prefixes (8 B x groups) | group minima (4 B x groups).
+__global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
-  const int tl = a.tile_log2;
-  const int nt = a.S_pad >> tl;
-  const int nt_pad = (nt + 3) & ~3;
-  double* p2d = reinterpret_cast<double*>(sm_raw);
-  float* tmin = reinterpret_cast<float*>(sm_raw + (size_t)nt_pad * sizeof(double));
+  const Tiles& tl = a.t;
+  const int ng = tl.ng;
+  const int ng_pad = (ng + 3) & ~3;
+  const int gl = tl.group_log2;
+  const int span_log2 = kLeafLog2 + gl;  // slots per group
+  double* gpre = reinterpret_cast<double*>(sm_raw);
+  float* gmin = reinterpret_cast<float*>(sm_raw + (size_t)ng_pad * sizeof(double));
   __shared__ __align__(16) uint32_t mt[624];
   __shared__ __align__(8) uint64_t bar;
   __shared__ double red_d[kSelThreads / 32];
   __shared__ float red_f[kSelThreads / 32];
   __shared__ float s_target[kSelTargets];
-  __shared__ int s_tile[kSelTargets];
+  __shared__ int s_grp[kSelTargets];
   __shared__ int s_wrapped[kSelTargets];
   __shared__ double s_rem[kSelTargets];
   __shared__ double sh_offset;
-  __shared__ float sh_max;
   __shared__ int sh_last, sh_mti;
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kSelThreads / 32;
+  static_assert(kWarps == kSelTargets, "one warp per target");
   Ctl* ctl = a.ctl;
   const int i0 = (int)blockIdx.x * kSelTargets;
   const int nT = min(kSelTargets, a.B - i0);
@@ -288,39 +312,32 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
   __syncthreads();
   pdl_wait();
   if (probing) ctl->probe[0] = clock64();
-  // ---- 1. everything that depends on nothing but the kernel arguments:
-  //         tile sums, tile minima and the RNG state by bulk copies (TMA)
+  // ---- 1. group sums, group minima and the RNG state by bulk copies (TMA)
   if (tid == 0) {
-    const uint32_t b2 = (uint32_t)nt_pad * 8u, bm = (uint32_t)nt_pad * 4u, br = 624u * 4u;
+    const uint32_t b2 = (uint32_t)ng_pad * 8u, bm = (uint32_t)ng_pad * 4u, br = 624u * 4u;
     mbar_expect_tx(&bar, b2 + bm + br);
-    bulk_g2s(p2d, a.l2, b2, &bar);
-    bulk_g2s(tmin, a.l2min, bm, &bar);
-    bulk_g2s(mt, ctl->mt, br, &bar);
+    bulk_g2s(gpre, tl.grp, b2, &bar);
+    bulk_g2s(gmin, tl.grpmin, bm, &bar);
+    bulk_g2s(mt, ctl->mt[a.rng_par], br, &bar);
   }
   const double sum_d = ctl->sum;
-  const int mti0 = ctl->mti;
-  double head_part = 0.0;  // weights in front of head inside head's tile (for the offset O)
+  const int mti0 = ctl->mti[a.rng_par];
+  // mass in front of head inside head's group: the slots of head's leaf and the
+  // whole leaves of head's group that precede it (for the offset O below)
+  double head_part = 0.0;
   if (warp == kWarps - 1 && a.head > 0) {
     const int last = a.head - 1;
-    for (int k = ((last >> 8) << 8) + lane; k <= last; k += 32) head_part += (double)a.w[k];
-    if (tl > 8) {  // whole leaves of head's tile in front of head's leaf
-      const int l0 = (last >> tl) << (tl - 8), l1 = last >> 8;
-      if (l0 + lane < l1) head_part += a.leaf[l0 + lane];
-    }
+    for (int k = ((last >> kLeafLog2) << kLeafLog2) + lane; k <= last; k += 32) head_part += (double)a.w[k];
+    const int l1 = last >> kLeafLog2, l0 = (l1 >> gl) << gl;
+    for (int k = l0 + lane; k < l1; k += 32) head_part += tl.leaf[k];
   }
   mbar_wait(&bar, 0);
   float mn = FLT_MAX;
-  for (int i = tid; i < nt; i += kSelThreads) mn = fminf(mn, tmin[i]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  for (int i = tid; i < ng; i += kSelThreads) mn = fminf(mn, gmin[i]);
+  mn = warp_min(mn);
   if (lane == 0) red_f[warp] = mn;
   __syncthreads();
-  {
-    float m = lane < kWarps ? red_f[lane] : FLT_MAX;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    mn = m;  // every warp now holds the global min non-zero weight
-  }
+  mn = warp_min(lane < kWarps ? red_f[lane] : FLT_MAX);  // every warp now holds the global min non-zero weight
   int ue = -149;
   if (mn != FLT_MAX) {
     int e;
@@ -335,40 +352,29 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
   gen_targets(mt, mti0, a.B, i0, i0 + nT, sumf, a.contract_fma, s_target, &sh_mti);
   if (probing) ctl->probe[1] = clock64();
 
-  // ---- 3. inclusive prefix of the tile sums: contiguous chunk per thread (odd
-  //         length: conflict-free 8-byte accesses), block scan of the chunk
-  //         totals, second pass adds the chunk offset
-  const int per = ((nt + kSelThreads - 1) / kSelThreads) | 1;
-  const int c0 = min(tid * per, nt), c1 = min(c0 + per, nt);
+  // ---- 3. inclusive prefix of the group sums: contiguous chunk per thread (odd
+  //         length: conflict-free 8-byte accesses), block scan of the chunk totals
+  const int per = ((ng + kSelThreads - 1) / kSelThreads) | 1;
+  const int c0 = min(tid * per, ng), c1 = min(c0 + per, ng);
   double run = 0.0;
   for (int i = c0; i < c1; ++i) {
-    run += p2d[i];
-    p2d[i] = run;
+    run += gpre[i];
+    gpre[i] = run;
   }
-  double x = run;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const double y = __shfl_up_sync(0xffffffffu, x, o);
-    if (lane >= o) x += y;
-  }
+  const double x = warp_scan(run, lane);
   if (lane == 31) red_d[warp] = x;
   __syncthreads();
   if (warp == 0) {
-    double t = lane < kWarps ? red_d[lane] : 0.0;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const double y = __shfl_up_sync(0xffffffffu, t, o);
-      if (lane >= o) t += y;
-    }
+    const double t = warp_scan(lane < kWarps ? red_d[lane] : 0.0, lane);
     if (lane < kWarps) red_d[lane] = t;
   }
   __syncthreads();
   {
     const double off = (warp > 0 ? red_d[warp - 1] : 0.0) + (x - run);
-    for (int i = c0; i < c1; ++i) p2d[i] += off;
+    for (int i = c0; i < c1; ++i) gpre[i] += off;
   }
   __syncthreads();
-  const double total = p2d[nt - 1];
+  const double total = gpre[ng - 1];
   const bool exact = (total < ldexp(1.0, ue + 52)) && !a.force_ordered;  // false for NaN / Inf totals too
   if (probing) ctl->probe[2] = clock64();
 
@@ -378,13 +384,13 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       double part = 0.0;
       if (a.head > 0) {
         part = warp_sum(head_part);
-        const int t = (a.head - 1) >> tl;
-        if (t > 0) part += p2d[t - 1];
+        const int g = (a.head - 1) >> span_log2;
+        if (g > 0) part += gpre[g - 1];
       }
       if (lane == 0) sh_offset = part;
     }
     __syncthreads();
-    // ---- 5. tile of each target. Both cases reduce to "first physical slot
+    // ---- 5. group of each target. Both cases reduce to "first physical slot
     //   whose prefix reaches a key":
     //   unwrapped part [head, S):  P(s) - O >= t'   <=>  P(s) >= t' + O
     //   wrapped part   [0, head):  M1 + P(s) >= t'  <=>  P(s) >= t' - M1
@@ -399,95 +405,62 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       if (tf > 0.0f) tq = fmax(ldexp(ceil(ldexp((double)tf, -ue)), ue), unit);  // exact: power-of-two scalings
       const int wrapped = !(m1 >= tq);
       const double key = wrapped ? tq - m1 : tq + off;
-      int lo = 0, hi = nt;  // first tile whose inclusive prefix reaches the key
+      int lo = 0, hi = ng;  // first group whose inclusive prefix reaches the key
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (p2d[mid] >= key) hi = mid; else lo = mid + 1;
+        if (gpre[mid] >= key) hi = mid; else lo = mid + 1;
       }
-      s_tile[tid] = lo < nt ? lo : -1;
-      s_rem[tid] = lo < nt ? key - (lo > 0 ? p2d[lo - 1] : 0.0) : 0.0;  // u <= rem <= tile sum
+      s_grp[tid] = lo < ng ? lo : -1;
+      s_rem[tid] = lo < ng ? key - (lo > 0 ? gpre[lo - 1] : 0.0) : 0.0;  // u <= rem <= group sum
       s_wrapped[tid] = wrapped;
     }
     __syncthreads();
     if (probing) ctl->probe[3] = clock64();
-    // ---- 6. slot inside the tile: one warp per target, two targets per warp.
-    //   Tiles larger than 256 slots first resolve the LEAF: lanes < 2^(tl-8)
-    //   load the tile's leaf sums, a warp scan finds the leaf and the remainder
-    //   inside it. Then lane l owns 8 consecutive slots of the leaf (kept in
-    //   registers); a warp scan of the lane totals finds the lane, which walks
-    //   its own slots.
-    constexpr int kPer = kSelTargets / kWarps;
-    const int nb = 1 << (tl - 8);
-    int leaf_t[kPer];
-    double rem_k[kPer];
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int t = warp + k * kWarps;
-      leaf_t[k] = t < nT ? s_tile[t] : -1;
-      rem_k[k] = t < nT ? s_rem[t] : 0.0;
-    }
-    if (nb > 1) {
-      double ls[kPer];
-#pragma unroll
-      for (int k = 0; k < kPer; ++k)  // the loads of both targets are issued together
-        ls[k] = (leaf_t[k] >= 0 && lane < nb) ? a.leaf[(size_t)leaf_t[k] * nb + lane] : 0.0;
-#pragma unroll
-      for (int k = 0; k < kPer; ++k) {
-        if (leaf_t[k] < 0) continue;  // warp-uniform
-        double P = ls[k];
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-          const double y = __shfl_up_sync(0xffffffffu, P, o);
-          if (lane >= o) P += y;
-        }
-        const unsigned hit = __ballot_sync(0xffffffffu, lane < nb && P >= rem_k[k]);
-        if (hit != 0u) {
-          const int L = __ffs(hit) - 1;
-          rem_k[k] -= __shfl_sync(0xffffffffu, P - ls[k], L);
-          leaf_t[k] = leaf_t[k] * nb + L;
-        } else {
-          leaf_t[k] = -1;
+    // ---- 6. one warp per target: leaf inside the group (lane l holds the sums of
+    //   leaves l and l + 32, two warp scans), then the slot inside the leaf (lane l
+    //   owns 8 consecutive slots kept in registers; a warp scan of the lane totals
+    //   finds the lane, which walks its own slots).
+    const int t = warp;
+    if (t < nT) {  // warp-uniform
+      const int g = s_grp[t];
+      double rem = s_rem[t];
+      int leaf = -1;
+      if (g >= 0) {
+        const int L = 1 << gl;
+        const size_t lb = (size_t)g << gl;
+        const double x0 = lane < L ? tl.leaf[lb + lane] : 0.0;
+        const double x1 = lane + 32 < L ? tl.leaf[lb + 32 + lane] : 0.0;
+        const double P0 = warp_scan(x0, lane);
+        const double P1 = warp_scan(x1, lane) + __shfl_sync(0xffffffffu, P0, 31);
+        const unsigned h0 = __ballot_sync(0xffffffffu, lane < L && P0 >= rem);
+        const unsigned h1 = __ballot_sync(0xffffffffu, lane + 32 < L && P1 >= rem);
+        if (h0 != 0u) {
+          const int Lh = __ffs(h0) - 1;
+          rem -= __shfl_sync(0xffffffffu, P0 - x0, Lh);
+          leaf = (int)lb + Lh;
+        } else if (h1 != 0u) {
+          const int Lh = __ffs(h1) - 1;
+          rem -= __shfl_sync(0xffffffffu, P1 - x1, Lh);
+          leaf = (int)lb + 32 + Lh;
         }
       }
-    }
-    double T[kPer];
-    float4 v0[kPer], v1[kPer];
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {  // all loads of both targets are issued before the first use
-      v0[k] = v1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (leaf_t[k] >= 0) {
-        const float* wp = a.w + ((size_t)leaf_t[k] << 8) + (size_t)lane * 8;
-        v0[k] = *reinterpret_cast<const float4*>(wp);
-        v1[k] = *reinterpret_cast<const float4*>(wp + 4);
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < kPer; ++k)
-      T[k] = (((double)v0[k].x + (double)v0[k].y) + ((double)v0[k].z + (double)v0[k].w)) +
-             (((double)v1[k].x + (double)v1[k].y) + ((double)v1[k].z + (double)v1[k].w));
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int t = warp + k * kWarps;
-      if (t >= nT) continue;  // warp-uniform
-      const int leaf = leaf_t[k];
       int slot = -1;
       float wv = 0.0f;
       if (leaf >= 0) {
-        const double rem = rem_k[k];
-        double P = T[k];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const double y = __shfl_up_sync(0xffffffffu, P, o);
-          if (lane >= o) P += y;
-        }
+        const float* wp = a.w + ((size_t)leaf << kLeafLog2) + (size_t)lane * 8;
+        const float4 v0 = *reinterpret_cast<const float4*>(wp);
+        const float4 v1 = *reinterpret_cast<const float4*>(wp + 4);
+        const double T = (((double)v0.x + (double)v0.y) + ((double)v0.z + (double)v0.w)) +
+                         (((double)v1.x + (double)v1.y) + ((double)v1.z + (double)v1.w));
+        const double P = warp_scan(T, lane);
         const unsigned hit = __ballot_sync(0xffffffffu, P >= rem);
         if (hit != 0u) {
-          const int L = __ffs(hit) - 1;
-          if (lane == L) {
-            const double rem_l = rem - (P - T[k]);
+          const int Lh = __ffs(hit) - 1;
+          if (lane == Lh) {
+            const double rem_l = rem - (P - T);
             double acc = 0.0;
             int j = 7;
-            const float vv[8] = {v0[k].x, v0[k].y, v0[k].z, v0[k].w, v1[k].x, v1[k].y, v1[k].z, v1[k].w};
+            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
             int found = 0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
@@ -499,10 +472,10 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
               }
             }
             if (!found) wv = vv[7];
-            slot = (leaf << 8) + L * 8 + j;
+            slot = (leaf << kLeafLog2) + Lh * 8 + j;
           }
-          slot = __shfl_sync(0xffffffffu, slot, L);
-          wv = __shfl_sync(0xffffffffu, wv, L);
+          slot = __shfl_sync(0xffffffffu, slot, Lh);
+          wv = __shfl_sync(0xffffffffu, wv, Lh);
         }
       }
       if (lane == 0) {
@@ -510,13 +483,15 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
         int logical = -1;
         if (slot >= 0) logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
         if (slot < 0 || slot >= a.S || logical >= a.size) {
-          ctl->sel_fail = 1;  // reference: assert(false) at lines 297-302
+          raise_error(a, RR_ERR_OVERRUN);
           slot = a.head;
           wv = a.w[slot];
           logical = 0;
         }
         a.ids[i0 + t] = slot;
-        a.wsel[i0 + t] = wv;
+        const float v = is_raw(wv, sumf, a.size_is, a.beta);
+        a.israw[i0 + t] = v;
+        publish_max(a.ismax, a.epoch, v);
         // getElementAndMark (line 126). A slot that this call also evicts ends
         // up evicted (the pop comes after the marks): leave it to the eviction.
         if (logical >= a.pop_n) a.evicted[slot] = 0;
@@ -524,14 +499,16 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
     }
   } else if (blockIdx.x == 0) {
     // ordered walk: the reference's loop (lines 274-308) for ALL targets, staged
-    // kSelThreads weights at a time and consumed by one thread in order
-    float* targets = reinterpret_cast<float*>(sm_raw);
+    // kSelThreads weights at a time and consumed by one thread in order. The
+    // targets live in a.israw (global); entry i is replaced by the selected weight
+    // once target i has been served and by the raw importance weight at the end.
+    volatile float* targets = a.israw;
     __shared__ float chunk[kSelThreads];
     __shared__ int sh_next_i, sh_id;
     __shared__ double sh_acc;
     __shared__ float sh_w;
     __syncthreads();
-    for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[i];
+    for (int i = tid; i < 624; i += kSelThreads) mt[i] = ctl->mt[a.rng_par][i];
     if (tid == 0) {
       sh_next_i = 0;
       sh_acc = 0.0;
@@ -539,7 +516,9 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       sh_id = 0;
     }
     __syncthreads();
-    gen_targets(mt, mti0, a.B, 0, a.B, sumf, a.contract_fma, targets, &sh_mti);
+    gen_targets(mt, mti0, a.B, 0, a.B, sumf, a.contract_fma, a.israw, &sh_mti);
+    __threadfence_block();
+    __syncthreads();
     const int size = a.size;
     for (int base = 0; base <= size; base += kSelThreads) {
       const int idx = base + tid;
@@ -560,7 +539,7 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
           const double target = (double)targets[i];
           if (acc > 0.0 && acc >= target) {
             a.ids[i] = id;
-            a.wsel[i] = w;
+            targets[i] = w;
             ++i;
             continue;
           }
@@ -580,22 +559,40 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
       if (sh_next_i >= a.B) break;
     }
     if (tid == 0 && sh_next_i < a.B) {
-      ctl->sel_fail = 1;
+      raise_error(a, RR_ERR_OVERRUN);
       for (int i = sh_next_i; i < a.B; ++i) {
         a.ids[i] = a.head;
-        a.wsel[i] = a.w[a.head];
+        targets[i] = a.w[a.head];
       }
     }
+    __threadfence_block();
     __syncthreads();
     for (int i = tid; i < a.B; i += kSelThreads) {
       const int slot = a.ids[i];
       const int logical = slot >= a.head ? slot - a.head : slot + a.S - a.head;
       if (logical >= a.pop_n) a.evicted[slot] = 0;
+      const float v = is_raw(targets[i], sumf, a.size_is, a.beta);
+      targets[i] = v;
+      publish_max(a.ismax, a.epoch, v);
     }
   }
   if (probing) ctl->probe[4] = clock64();
 
-  // ---- 7. the last CTA to get here finishes the call
+  // ---- 7. RNG state after the B draws and the counters: CTA 0 (every CTA ran
+  //         the same twists, so every CTA holds the successor state)
+  if (blockIdx.x == 0) {
+    __syncthreads();
+    for (int i = tid; i < 624; i += kSelThreads) ctl->mt[a.rng_par ^ 1][i] = mt[i];
+    if (tid == 0) {
+      ctl->mti[a.rng_par ^ 1] = sh_mti;
+      if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
+      ctl->probe[5] = clock64();
+    }
+  }
+  if (a.pop_n <= 0) return;
+
+  // ---- 8. eviction (blockPop, lines 84-103) after every CTA's marks, like the
+  //         reference: the last CTA to get here pops
   __syncthreads();
   if (tid == 0) {
     __threadfence();
@@ -605,77 +602,44 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
   if (!sh_last) return;
   __threadfence();
   if (tid == 0) ctl->probe[6] = clock64();
-
-  // eviction (blockPop, lines 84-103): after the marks like the reference
-  if (a.pop_n > 0) {
-    if (exact) {
-      double part = 0.0;  // exact in any order under the exactness condition
-      for (int j = tid; j < a.pop_n; j += kSelThreads) {
-        int slot = a.head + j;
-        if (slot >= a.S) slot -= a.S;
-        part += (double)a.w[slot];
-      }
-      part = warp_sum(part);
-      if (lane == 0) red_d[warp] = part;
-      __syncthreads();
-      if (tid == 0) {
-        double tot = 0.0;
-        for (int k = 0; k < kWarps; ++k) tot += red_d[k];
-        // diff = -(w_0 + w_1 + ...) exactly, then sum_ += diff (line 96)
-        ctl->sum = sum_d + -tot;
-      }
-    } else if (tid == 0) {
-      double diff = 0.0;
-      for (int j = 0; j < a.pop_n; ++j) {
-        int slot = a.head + j;
-        if (slot >= a.S) slot -= a.S;
-        diff -= (double)a.w[slot];
-      }
-      ctl->sum = sum_d + diff;
-    }
-    __syncthreads();
+  if (exact) {
+    double part = 0.0;  // exact in any order under the exactness condition
     for (int j = tid; j < a.pop_n; j += kSelThreads) {
       int slot = a.head + j;
       if (slot >= a.S) slot -= a.S;
-      a.evicted[slot] = 1;
-      a.w[slot] = 0.0f;
+      part += (double)__ldcg(a.w + slot);
     }
+    part = warp_sum(part);
+    if (lane == 0) red_d[warp] = part;
     __syncthreads();
-    retile_range(a.w, tiles_of(a), a.S, a.head, a.pop_n, warp, kWarps, lane);
-  }
-
-  // importance weights (lines 320-322); wsel was written by other SMs: read through L2
-  float* wbuf = reinterpret_cast<float*>(sm_raw);  // the tile prefixes are no longer needed
-  __syncthreads();
-  float mx = -INFINITY;
-  for (int i = tid; i < a.B; i += kSelThreads) {
-    float v = __fdiv_rn(__ldcg(a.wsel + i), sumf);
-    v = __fmul_rn((float)a.size_is, v);
-    v = (float)pow((double)v, (double)(-a.beta));
-    wbuf[i] = v;
-    mx = fmaxf(mx, v);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if (lane == 0) red_f[warp] = mx;
-  __syncthreads();
-  if (warp == 0) {
-    float m = lane < kWarps ? red_f[lane] : -INFINITY;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) sh_max = m;
+    if (tid == 0) {
+      double tot = 0.0;
+      for (int k = 0; k < kWarps; ++k) tot += red_d[k];
+      // diff = -(w_0 + w_1 + ...) exactly, then sum_ += diff (line 96)
+      ctl->sum = sum_d + -tot;
+    }
+  } else if (tid == 0) {
+    double diff = 0.0;
+    for (int j = 0; j < a.pop_n; ++j) {
+      int slot = a.head + j;
+      if (slot >= a.S) slot -= a.S;
+      diff -= (double)__ldcg(a.w + slot);
+    }
+    ctl->sum = sum_d + diff;
   }
   __syncthreads();
-  for (int i = tid; i < a.B; i += kSelThreads) a.is_weights[i] = __fdiv_rn(wbuf[i], sh_max);
-
-  // RNG state after the B draws, counters
-  for (int i = tid; i < 624; i += kSelThreads) ctl->mt[i] = mt[i];
+  for (int j = tid; j < a.pop_n; j += kSelThreads) {
+    int slot = a.head + j;
+    if (slot >= a.S) slot -= a.S;
+    a.evicted[slot] = 1;
+    a.w[slot] = 0.0f;
+  }
+  __syncthreads();
+  refresh_range<false>(a.w, tl, a.S, a.head, a.pop_n, warp, kWarps, lane);
+  __syncthreads();
+  refresh_range<true>(a.w, tl, a.S, a.head, a.pop_n, warp, kWarps, lane);
   if (tid == 0) {
-    ctl->mti = sh_mti;
-    if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
     ctl->n_popped += (unsigned long long)a.pop_n;
-    if (*reinterpret_cast<volatile int*>(&ctl->sel_fail)) ctl->error = RR_ERR_OVERRUN;
-    ctl->sel_fail = 0;
     ctl->done_ctas = 0u;
     ctl->probe[7] = clock64();
   }
@@ -687,32 +651,45 @@ __global__ void __launch_bounds__(kSelThreads, 1) select_kernel(const SelectArgs
 __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, const Tiles tiles, int S, int start, int n,
                                                       const float* __restrict__ prio, float alpha,
                                                       int is_weight) {
-  __shared__ float buf[1024];
+  __shared__ __align__(16) float buf[1024];
   __shared__ float sh_sum;
   const int tid = threadIdx.x;
   if (tid == 0) sh_sum = 0.0f;
   for (int base = 0; base < n; base += 1024) {
     const int i = base + tid;
+    float v = 0.0f;
     if (i < n) {
-      float p = prio[i];
-      float v = is_weight ? p : pow_alpha(p, alpha);
+      const float p = prio[i];
+      v = is_weight ? p : pow_alpha(p, alpha);
       int slot = start + i;
       if (slot >= S) slot -= S;
       w[slot] = v;
-      buf[tid] = v;
     }
+    buf[tid] = v;
     __syncthreads();
     if (tid == 0) {
+      // the reference's sum is a serial float sum in index order (line 63): one
+      // dependent add per element, the operands fetched four at a time
       float s = sh_sum;
       const int m = min(1024, n - base);
-      for (int k = 0; k < m; ++k) s = __fadd_rn(s, buf[k]);
+      int k = 0;
+      for (; k + 4 <= m; k += 4) {
+        const float4 q = *reinterpret_cast<const float4*>(buf + k);
+        s = __fadd_rn(s, q.x);
+        s = __fadd_rn(s, q.y);
+        s = __fadd_rn(s, q.z);
+        s = __fadd_rn(s, q.w);
+      }
+      for (; k < m; ++k) s = __fadd_rn(s, buf[k]);
       sh_sum = s;
     }
     __syncthreads();
   }
   if (tid == 0) ctl->sum += (double)sh_sum;
-  // the block's weights are visible to the CTA (barrier above): refresh its tiles
-  retile_range(w, tiles, S, start, n, tid >> 5, 32, tid & 31);
+  // the block's weights are visible to the CTA (barrier above): refresh its leaves, then its groups
+  refresh_range<false>(w, tiles, S, start, n, tid >> 5, 32, tid & 31);
+  __syncthreads();
+  refresh_range<true>(w, tiles, S, start, n, tid >> 5, 32, tid & 31);
 }
 
 // ------------------------------------------------------ K7 priority update
@@ -724,16 +701,22 @@ __global__ void __launch_bounds__(1024) commit_kernel(Ctl* ctl, float* w, const 
 // The double accumulation of the float differences is done in parallel when
 // it is provably exact (sum |d| < 2^52 * ulp(min |d|)), else in order.
 //
-// CTA 0 does that bookkeeping. CTAs 1.. keep the tile entries current, one
-// warp per batch element: the warp of the first element of a run that falls
-// into one tile reloads the tile, substitutes the final value of every batch
-// slot in it (computed from the same inputs as CTA 0, so the result does not
-// depend on whether CTA 0's store has landed) and reduces it again.
+// CTA 0 does that bookkeeping. CTAs 1.. keep the hierarchy current, one CTA per
+// touched GROUP: its warps reload the leaves of the group that hold a batch
+// slot, substitute the final value of every batch slot (computed from the same
+// inputs as CTA 0, so the result does not depend on whether CTA 0's store has
+// landed), reduce them again, and after a CTA barrier one warp re-reduces the
+// group from its 64 leaf entries. Nothing waits across CTAs.
+// Candidate c = blockIdx.x - 1 is group c when there are at most n groups
+// (by_group), else the group of batch element c, handled by the CTA of the
+// first element that falls into it.
 //
 // The new priorities come from device memory or, for a learner-sized batch
 // handed over in host memory, ride in the launch packet itself (PrioInline, a
 // __grid_constant__ parameter read through the constant bank): no staging
 // copy sits between updatePriority and the next sample on the stream.
+constexpr int kUpdThreads = 256;
+
 struct PrioInline {
   float v[kInlinePrio];
 };
@@ -743,90 +726,125 @@ __device__ __forceinline__ float prio_at(const PrioInline& p, int i) { return p.
 template <typename Prio>
 __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
                                             const int32_t* __restrict__ ids, int n, const Prio& prio, float alpha,
-                                            int is_weight, const Tiles& tiles) {
-  const int tile_log2 = tiles.tile_log2;
+                                            int is_weight, const Tiles& tiles, int by_group) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
   float* s_diff = s_new + n;
-  __shared__ double r_sum[32], r_abs[32];
-  __shared__ float r_min[32];
+  __shared__ double r_sum[kUpdThreads / 32], r_abs[kUpdThreads / 32];
+  __shared__ float r_min[kUpdThreads / 32];
   __shared__ int sh_exact;
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kUpdThreads / 32;
   if (blockIdx.x > 0) {
-    __shared__ __align__(16) float sub[32][256];
-    for (int i = tid; i < n; i += blockDim.x) {
+    __shared__ __align__(16) float sub[kWarps][256];
+    __shared__ double s_ls[64];
+    __shared__ float s_lm[64];
+    __shared__ unsigned long long s_mask;
+    __shared__ int s_lo, s_hi;
+    for (int i = tid; i < n; i += kUpdThreads) {
       const int id = ids[i];
       const float p = prio_at(prio, i);
       const bool ev = evicted[id] != 0;
       s_new[i] = is_weight ? p : pow_alpha(p, alpha);
       s_id[i] = ev ? -1 : id;
     }
+    if (tid == 0) {
+      s_mask = 0ull;
+      s_lo = n;
+      s_hi = -1;
+    }
     __syncthreads();
-    const int i = (blockIdx.x - 1) * 32 + warp;
-    if (i >= n) return;
-    const int id = s_id[i];
-    if (id < 0) return;  // an evicted slot keeps weight 0: its tile does not change
-    const int t = id >> tile_log2;
-    if (i > 0 && s_id[i - 1] >= 0 && (s_id[i - 1] >> tile_log2) == t) return;  // covered by that element's warp
-    const int nb = 1 << (tile_log2 - 8);
-    float* mine = sub[warp];
-    const int tbase = t << tile_log2;
-    // which leaves of the tile hold a batch slot (final values only: last occurrence, not evicted)
-    unsigned touched = 0u;
-    for (int j = lane; j < n; j += 32) {
-      const int sid = s_id[j];
-      if (sid >= tbase && sid < tbase + (1 << tile_log2)) touched |= 1u << ((sid - tbase) >> 8);
+    const int gl = tiles.group_log2;
+    const int span_log2 = kLeafLog2 + gl;
+    const int c = (int)blockIdx.x - 1;
+    int g;
+    if (by_group) {
+      g = c;
+    } else {
+      const int id = s_id[c];
+      if (id < 0) return;  // an evicted slot keeps weight 0: nothing changes (CTA-uniform)
+      g = id >> span_log2;
+      int dup = 0;  // an earlier element of the batch in the same group: that element's CTA covers it
+      for (int j = tid; j < c; j += kUpdThreads) {
+        const int sid = s_id[j];
+        if (sid >= 0 && (sid >> span_log2) == g) dup = 1;
+      }
+      if (__syncthreads_or(dup)) return;
     }
-    touched = __reduce_or_sync(0xffffffffu, touched);
+    // leaves of the group that hold a batch slot (final values only: not evicted),
+    // and the index range of the batch that falls into the group
+    {
+      unsigned long long m = 0ull;
+      int lo = n, hi = -1;
+      for (int j = tid; j < n; j += kUpdThreads) {
+        const int sid = s_id[j];
+        if (sid >= 0 && (sid >> span_log2) == g) {
+          m |= 1ull << ((sid >> kLeafLog2) & ((1 << gl) - 1));
+          lo = min(lo, j);
+          hi = max(hi, j);
+        }
+      }
+      if (m != 0ull) {
+        atomicOr(&s_mask, m);
+        atomicMin(&s_lo, lo);
+        atomicMax(&s_hi, hi);
+      }
+    }
+    __syncthreads();
+    const unsigned long long mask = s_mask;
+    if (mask == 0ull) return;
+    const int jlo = s_lo, jhi = s_hi;
+    const int L = 1 << gl;
+    const size_t lb = (size_t)g << gl;
     // untouched leaves keep their entries: nobody writes them during this kernel
-    double keep_s = 0.0;
-    float keep_m = FLT_MAX;
-    if (nb > 1 && lane < nb && !((touched >> lane) & 1u)) {
-      keep_s = tiles.leaf[(size_t)t * nb + lane];
-      keep_m = tiles.leafmin[(size_t)t * nb + lane];
+    if (tid < L && !((mask >> tid) & 1ull)) {
+      s_ls[tid] = tiles.leaf[lb + tid];
+      s_lm[tid] = tiles.leafmin[lb + tid];
     }
-    double tot = 0.0;
-    float m = FLT_MAX;
-    for (int k = 0; k < nb; ++k) {
+    float* mine = sub[warp];
+    for (int k = warp; k < L; k += kWarps) {
+      if (!((mask >> k) & 1ull)) continue;  // warp-uniform
+      const int base = (int)(lb + k) << kLeafLog2;
+      const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
+      reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
+      reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
+      __syncwarp();
+      for (int j = jlo + lane; j <= jhi; j += 32) {
+        const int sid = s_id[j];
+        const bool last = !(j + 1 < n && s_id[j + 1] == sid);
+        if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
+      }
+      __syncwarp();
+      const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
+      const float4 b = reinterpret_cast<const float4*>(mine)[lane * 2 + 1];
+      __syncwarp();
       double s;
       float mn;
-      if ((touched >> k) & 1u) {
-        const int base = tbase + k * 256;
-        const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
-        reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
-        reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
-        __syncwarp();
-        for (int j = lane; j < n; j += 32) {
-          const int sid = s_id[j];
-          const bool last = !(j + 1 < n && s_id[j + 1] == sid);
-          if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
-        }
-        __syncwarp();
-        const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
-        const float4 b = reinterpret_cast<const float4*>(mine)[lane * 2 + 1];
-        __syncwarp();
-        reduce256(a, b, s, mn);
-        if (lane == 0 && nb > 1) {
-          tiles.leaf[(size_t)t * nb + k] = s;
-          tiles.leafmin[(size_t)t * nb + k] = mn;
-        }
-      } else {
-        s = __shfl_sync(0xffffffffu, keep_s, k);
-        mn = __shfl_sync(0xffffffffu, keep_m, k);
+      reduce256(a, b, s, mn);
+      if (lane == 0) {
+        tiles.leaf[lb + k] = s;
+        tiles.leafmin[lb + k] = mn;
+        s_ls[k] = s;
+        s_lm[k] = mn;
       }
-      tot += s;
-      m = fminf(m, mn);
     }
-    if (lane == 0) {
-      tiles.l2[t] = tot;
-      tiles.l2min[t] = m;
+    __syncthreads();
+    if (warp == 0) {
+      double s;
+      float mn;
+      reduce_group(lane < L ? s_ls[lane] : 0.0, lane + 32 < L ? s_ls[lane + 32] : 0.0,
+                   lane < L ? s_lm[lane] : FLT_MAX, lane + 32 < L ? s_lm[lane + 32] : FLT_MAX, s, mn);
+      if (lane == 0) {
+        tiles.grp[g] = s;
+        tiles.grpmin[g] = mn;
+      }
     }
     return;
   }
   float* s_old = s_diff;  // old weight, replaced by the difference below
-  for (int i = tid; i < n; i += blockDim.x) {
+  for (int i = tid; i < n; i += kUpdThreads) {
     const int id = ids[i];
     const float p = prio_at(prio, i);
     const bool ev = evicted[id] != 0;  // both dependent loads are issued together
@@ -838,7 +856,7 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
   __syncthreads();
   double sum = 0.0, asum = 0.0;
   float mn = FLT_MAX;
-  for (int i = tid; i < n; i += blockDim.x) {
+  for (int i = tid; i < n; i += kUpdThreads) {
     const int id = s_id[i];
     float d = 0.0f;
     if (id >= 0) {
@@ -852,15 +870,14 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
     s_diff[i] = d;  // same thread read s_old[i] above
   }
   __syncthreads();  // all reads of the old weights are done
-  for (int i = tid; i < n; i += blockDim.x) {
+  for (int i = tid; i < n; i += kUpdThreads) {
     const int id = s_id[i];
     const bool last = !(i + 1 < n && s_id[i + 1] == id);
     if (id >= 0 && last) w[id] = s_new[i];
   }
   sum = warp_sum(sum);
   asum = warp_sum(asum);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  mn = warp_min(mn);
   if (lane == 0) {
     r_sum[warp] = sum;
     r_abs[warp] = asum;
@@ -868,14 +885,12 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
   }
   __syncthreads();
   if (warp == 0) {
-    const int nw = blockDim.x >> 5;
-    double a = lane < nw ? r_sum[lane] : 0.0;
-    double b = lane < nw ? r_abs[lane] : 0.0;
-    float m = lane < nw ? r_min[lane] : FLT_MAX;
+    double a = lane < kWarps ? r_sum[lane] : 0.0;
+    double b = lane < kWarps ? r_abs[lane] : 0.0;
+    float m = lane < kWarps ? r_min[lane] : FLT_MAX;
     a = warp_sum(a);
     b = warp_sum(b);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    m = warp_min(m);
     if (lane == 0) {
       int exact = 1;
       if (m != FLT_MAX) {
@@ -897,32 +912,26 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
   }
 }
 
-// wait_late: the kernel in front of this one on the stream is the gather of
-// the batch whose priorities are being updated (or of a batch drawn ahead).
-// Nothing here reads what a gather writes, and the gather triggers its
-// dependents only after its own wait for the selection, so the update runs
-// BESIDE the gather and waits for it at its end instead -- its successor, which
-// waits for this grid, then still sees the gather complete. The host sets it
-// only when it knows the predecessor (rr_update_priority).
 template <typename Prio>
-__global__ void __launch_bounds__(1024) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
-                                                      const int32_t* __restrict__ ids, int n,
-                                                      const __grid_constant__ Prio prio, float alpha,
-                                                      int is_weight, const Tiles tiles, int wait_late) {
+__global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
+                                                             const int32_t* __restrict__ ids, int n,
+                                                             const __grid_constant__ Prio prio, float alpha,
+                                                             int is_weight, const Tiles tiles, int by_group) {
   pdl_launch_dependents();
-  if (!wait_late) pdl_wait();
-  update_body<Prio>(ctl, w, evicted, ids, n, prio, alpha, is_weight, tiles);
-  if (wait_late) pdl_wait();
+  pdl_wait();
+  update_body<Prio>(ctl, w, evicted, ids, n, prio, alpha, is_weight, tiles, by_group);
 }
 
 // ----------------------------------------------------------------- launches
-cudaError_t launch_build_hierarchy(const SelectArgs& a, cudaStream_t stream) {
-  return launch_pdl(build_hierarchy_kernel, dim3(a.S_pad / kBuildSpan), dim3(256), 0, stream, a.w, tiles_of(a));
+cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cudaStream_t stream) {
+  cudaError_t e = launch_pdl(build_leaves_kernel, dim3(S_pad / kBuildSpan), dim3(256), 0, stream, w, t);
+  if (e != cudaSuccess) return e;
+  return launch_pdl(build_groups_kernel, dim3((t.ng + 7) / 8), dim3(256), 0, stream, t);
 }
 
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
-  const size_t nt_pad = (((size_t)a.S_pad >> a.tile_log2) + 3) & ~(size_t)3;
-  const size_t smem = std::max(nt_pad * (sizeof(double) + sizeof(float)), (size_t)a.B * sizeof(float)) + 16;
+  const size_t ng_pad = ((size_t)a.t.ng + 3) & ~(size_t)3;
+  const size_t smem = ng_pad * (sizeof(double) + sizeof(float)) + 16;
   cudaError_t e = ensure_dynamic_smem(select_kernel, smem);
   if (e != cudaSuccess) return e;
   const int grid = (a.B + kSelTargets - 1) / kSelTargets;
@@ -935,28 +944,36 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
   return cudaGetLastError();
 }
 
+namespace {
+inline int update_grid(const Tiles& tiles, int n, int* by_group) {
+  *by_group = tiles.ng <= n ? 1 : 0;
+  return 1 + (*by_group ? tiles.ng : n);  // CTA 0: sum_ and weights; the others: one per candidate group
+}
+}  // namespace
+
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, int wait_late, cudaStream_t stream) {
+                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
-  const int grid = 1 + (n + 31) / 32;  // CTA 0: sum_ and weights; the others: one warp per element's tile
-  return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, prio,
-                    alpha, is_weight, tiles, wait_late);
+  int by_group;
+  const int grid = update_grid(tiles, n, &by_group);
+  return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
+                    prio, alpha, is_weight, tiles, by_group);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
-                                 int n, const float* prio_host, float alpha, int is_weight, int wait_late,
-                                 cudaStream_t stream) {
+                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream) {
   if (n > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
   memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<PrioInline>, smem);
   if (e != cudaSuccess) return e;
-  const int grid = 1 + (n + 31) / 32;
-  return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(1024), smem, stream, ctl, w, evicted, ids, n, pin,
-                    alpha, is_weight, tiles, wait_late);
+  int by_group;
+  const int grid = update_grid(tiles, n, &by_group);
+  return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
+                    pin, alpha, is_weight, tiles, by_group);
 }
 
 }  // namespace rr

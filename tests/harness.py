@@ -240,6 +240,8 @@ def ref_lib():
             getattr(lib, f"ref_{kind}_cycle_loop").restype = C.c_double
             getattr(lib, f"ref_{kind}_cycle_loop").argtypes = [C.c_void_p, C.c_int, C.c_int,
                                                                C.c_void_p, C.c_int]
+        lib.ref_ff_cycle_loop_dev.restype = C.c_double
+        lib.ref_ff_cycle_loop_dev.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_char_p]
         lib.ref_ff_state.argtypes = [C.c_void_p] * 6
         lib.ref_ff_weights.argtypes = [C.c_void_p] * 3
         lib.ref_nstep_pop.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
@@ -321,9 +323,12 @@ class RefReplay(_Base):
         self.lib.ref_ff_weights(self.h, w.ctypes.data, e.ctypes.data)
         return w, e
 
-    def cycle_loop(self, B, cycles, prio_pool):
+    def cycle_loop(self, B, cycles, prio_pool, device="cpu"):
         pool = np.ascontiguousarray(prio_pool, dtype=np.float32)
         assert pool.ndim == 2 and pool.shape[1] == B
+        if device != "cpu":
+            assert self.kind == "ff"
+            return self.lib.ref_ff_cycle_loop_dev(self.h, B, cycles, pool.ctypes.data, pool.shape[0], device.encode())
         return getattr(self.lib, f"ref_{self.kind}_cycle_loop")(self.h, B, cycles, pool.ctypes.data,
                                                                 pool.shape[0])
 

@@ -1,182 +1,130 @@
-"""Worker of the sharded-replay tests (one process per rank).
+"""Worker of the striped-replay tests: one process per rank, several ranks may share one GPU.
 
-  torchrun --nproc-per-node N tests/sharded_worker.py --backend nccl   GPU: CapiEngine
-  torchrun --nproc-per-node N tests/sharded_worker.py --backend gloo   CPU: protocol only
+  RANK=r WORLD_SIZE=N python tests/sharded_worker.py --group NAME [--learner -1|r] [--prefetch P] ...
 
-Every rank replays the same scripted trace. Each add block of K rows is split
-rank-major over the ranks (rank r contributes rows [r*K/N, (r+1)*K/N)), which
-is exactly how ShardedPrioritizedReplay concatenates them, so ONE single-buffer
-oracle fed the unsplit blocks must produce the same ids, bytes and weights.
-With gloo the device engine is replaced by OracleShardEngine below (the
-oracle as the replicated control plane, payload kept only for owned slots):
-that run checks the SPMD protocol -- block order, ownership ranges, broadcast
-roots -- not the kernels.
+Every rank replays the same scripted trace through the C++ host layer
+(rela_b200._C.FFPrioritizedReplay with shard_rank / shard_world, i.e.
+rela_b200/cpp/sharded_core.cc). Each add block of K rows is split rank-major over
+the ranks (rank r contributes rows [r*K/N, (r+1)*K/N)), which is how the striped
+replay orders a collective block, so ONE single-buffer oracle fed the unsplit
+blocks must produce the same ids, bytes and weights:
+
+  learner = -1   every rank samples B rows: rows [r*B, (r+1)*B) of the oracle's
+                 batch of N*B; every rank passes the priorities of its rows
+  learner = r    rank r receives the oracle's whole batch of B
 """
 import argparse
+import ctypes as C
 import os
 import sys
 
 import numpy as np
 import torch
-import torch.distributed as dist
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 sys.path.insert(0, HERE)
 
 from harness import Oracle, ff_schema, gen_trace, torch_pow  # noqa: E402
-from rela_b200.sharded import Leaf, ShardedPrioritizedReplay, shard_range  # noqa: E402
 
 
-class OracleShardEngine:
-    """CPU stand-in for CapiEngine used ONLY by the gloo protocol test."""
-
-    def __init__(self, schema, capacity, seed, alpha, beta, rank, world):
-        self.fields = schema
-        self.orc = Oracle(schema, capacity, seed, alpha, beta, 0)
-        self.S = int(1.25 * capacity)
-        self.lo, self.hi = shard_range(self.S, rank, world)
-        self.rank, self.world = rank, world
-        self.device = torch.device("cpu")
-        self.schema = None
-        self.tail = 0
-        self._ids = None
-
-    def set_schema(self, leaves):
-        self.schema = leaves
-
-    def add_block(self, n, tensors, weights):
-        slots = (self.tail + np.arange(n)) % self.S
-        mine = (slots >= self.lo) & (slots < self.hi)
-        rows = []
-        for t in tensors:
-            a = t.numpy().copy()
-            a[~mine] = 0  # payload of other shards is not stored here
-            rows.append(a)
-        self.orc.add(rows, weights.numpy())
-        self.tail = (self.tail + n) % self.S
-
-    def sample(self, B, learner):
-        rc, rows, w, ids = self.orc.sample(B)
-        assert rc == 0
-        self._ids = ids
-        mine = (ids >= self.lo) & (ids < self.hi)
-        out = []
-        for a in rows:
-            a = a.copy()
-            a[~mine] = 0
-            t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).astype(np.int32))
-            dist.reduce(t, dst=learner, op=dist.ReduceOp.SUM)  # exactly one shard contributes each row
-            out.append(torch.from_numpy(t.numpy().astype(np.uint8).view(a.dtype).reshape(a.shape)))
-        return (out, torch.from_numpy(w)) if self.rank == learner else (None, None)
-
-    def update(self, weights):
-        assert self.orc.update(weights.numpy()) == 0
-
-    def size(self):
-        return self.orc.size()
-
-    def num_add(self):
-        return self.orc.num_add()
-
-    def last_ids(self, B):
-        return self._ids
+def record(_C, schema, tensors):
+    groups = {"obs": {}, "action": {}, "next_obs": {}}
+    scalars = {}
+    for f, t in zip(schema, tensors):
+        grp, _, key = f.name.partition(".")
+        if key:
+            groups[grp][key] = t
+        else:
+            scalars[f.name] = t
+    return _C.FFTransition(groups["obs"], groups["action"], scalars["reward"], scalars["terminal"],
+                           scalars["bootstrap"], groups["next_obs"])
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--backend", default="nccl")
+    ap.add_argument("--group", required=True)
+    ap.add_argument("--learner", type=int, default=-1)
+    ap.add_argument("--prefetch", type=int, default=0)
     ap.add_argument("--capacity", type=int, default=600)
     ap.add_argument("--cycles", type=int, default=40)
-    ap.add_argument("--K", type=int, default=40)
-    ap.add_argument("--B", type=int, default=64)
+    ap.add_argument("--K", type=int, default=24)
+    ap.add_argument("--B", type=int, default=32)
     ap.add_argument("--full-frames", action="store_true")
-    ap.add_argument("--rotate-learner", action="store_true", help="batch k is assembled on rank k % world")
-    args = ap.parse_args()
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.backend == "nccl":
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    else:
-        dist.init_process_group("gloo")
-    alpha, beta, seed = 0.6, 0.4, 7
-    schema = ff_schema() if args.full_frames else ff_schema(frame=(4, 12, 12), n_actions=6)
-    assert args.K % world == 0
-    ops = gen_trace(schema, args.capacity, 3, args.cycles, args.K, args.B)
-    names = [f.name for f in schema]
-    engine = None
-    if args.backend == "gloo":
-        engine = OracleShardEngine(schema, args.capacity, seed, alpha, beta, rank, world)
-    rep = ShardedPrioritizedReplay(args.capacity, seed, alpha, beta, names, engine=engine,
-                                   device=None if engine else "cuda:%d" % local)
-    ref = Oracle(schema, args.capacity, seed, alpha, beta, 0)  # every rank checks the batches it learns from
-    n_checked = 0
-    learner = 0
+    ap.add_argument("--device-rows", action="store_true")
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    from rela_b200 import _C, capi
+
+    ndev = torch.cuda.device_count()
+    dev_index = rank % ndev
+    torch.cuda.set_device(dev_index)
+    dev = torch.device("cuda", dev_index)
+    schema = ff_schema() if a.full_frames else ff_schema(frame=(2, 12, 12), n_actions=5)
+    alpha, beta, seed = 0.6, 0.4, 11
+    n_learn = world if a.learner < 0 else 1
+    Btot = a.B * n_learn
+    assert a.K % world == 0
+    ops = gen_trace(schema, a.capacity, 5, a.cycles, a.K, Btot)
+    orc = Oracle(schema, a.capacity, seed, alpha, beta, a.prefetch)
+    rep = _C.FFPrioritizedReplay(a.capacity, seed, alpha, beta, a.prefetch, dev_index, rank, world, a.learner, a.group)
+    L = capi.lib()
+    h = C.c_void_p(rep.handle())
+    my_learner = rank if a.learner < 0 else (0 if rank == a.learner else -1)
+    n_samples = 0
     for op in ops:
         if op[0] == "add":
             rows, prio = op[1], op[2]
-            n = len(prio)
-            per = n // world
-            if n % world:  # the trace's short prefill block: pad by giving the remainder to nobody
-                rows = [r[: per * world] for r in rows]
-                prio = prio[: per * world]
-                n = per * world
-                if n == 0:
-                    continue
-            sl = slice(rank * per, (rank + 1) * per)
-            rep.add([torch.from_numpy(np.ascontiguousarray(r[sl])) for r in rows],
-                    torch.from_numpy(np.ascontiguousarray(prio[sl])))
-            if ref is not None:
-                ref.add(rows, torch_pow(prio, alpha))
+            orc.add(rows, torch_pow(prio, alpha))
+            n = len(prio) // world
+            lo = rank * n
+            tens = [torch.from_numpy(np.ascontiguousarray(r[lo:lo + n])) for r in rows]
+            if a.device_rows:
+                tens = [t.to(dev) for t in tens]
+            rep.add(record(_C, schema, tens), torch.from_numpy(np.ascontiguousarray(prio[lo:lo + n])))
+            assert rep.size() == orc.size() and rep.num_add() == orc.num_add()
         elif op[0] == "sample":
-            B = op[1]
-            if args.rotate_learner:
-                learner = (learner + 1) % world
-            tens, w = rep.sample(B, learner)
-            ids = rep.engine.last_ids(B)
-            if ref is not None:
-                rc, rrows, rw, rids = ref.sample(B)
-                assert rc == 0
-            np.testing.assert_array_equal(ids, rids, err_msg="ids differ from the single-buffer oracle")
-            if rank == learner:
-                if args.backend == "nccl":
-                    torch.cuda.synchronize()
-                got = [t.cpu().numpy() for t in tens]
-                gw = w.cpu().numpy()
-                np.testing.assert_allclose(gw, rw, rtol=1e-6, atol=0)
-                for f, (a, b) in enumerate(zip(got, rrows)):
-                    assert a.shape == b.shape and a.tobytes() == b.tobytes(), "field %d bytes differ" % f
-                n_checked += 1
+            rc, want_rows, want_w, want_ids = orc.sample(Btot)
+            assert rc == 0
+            batch, w = rep.sample(a.B, "cuda:%d" % dev_index)
+            ids = np.zeros(Btot, dtype=np.int32)
+            capi.check(L.rr_last_sample_ids(h, Btot, ids.ctypes.data))
+            np.testing.assert_array_equal(ids, want_ids, err_msg="rank %d sample %d: ids" % (rank, n_samples))
+            assert rep.size() == orc.size()
+            if my_learner >= 0:
+                sl = slice(my_learner * a.B, (my_learner + 1) * a.B)
+                torch.cuda.synchronize(dev)
+                np.testing.assert_allclose(w.cpu().numpy(), want_w[sl], rtol=1e-6, atol=0,
+                                           err_msg="rank %d sample %d: IS weights" % (rank, n_samples))
+                attr = {"obs": batch.obs, "action": batch.action, "next_obs": batch.next_obs}
+                for f, wr in zip(schema, want_rows):
+                    grp, _, key = f.name.partition(".")
+                    x = attr[grp][key] if key else getattr(batch, f.name)
+                    got = x.cpu().numpy()
+                    assert got.shape == wr[sl].shape, (f.name, got.shape, wr[sl].shape)
+                    assert got.tobytes() == wr[sl].tobytes(), "rank %d sample %d: field %s bytes differ" % (
+                        rank, n_samples, f.name)
             else:
-                assert tens is None and w is None
-            assert rep.size() == (ref.size() if ref is not None else rep.size())
+                assert w is None or w.numel() == 0
+            n_samples += 1
         else:
             prio = op[1]
-            rep.update_priority(torch.from_numpy(prio) if rank == learner else None)
-            if ref is not None:
-                assert ref.update(torch_pow(prio, alpha)) == 0
-    if args.backend == "nccl":
-        rep.engine.sync()
-        st = capi_stats(rep.engine)
-        assert st["samples_ordered"] == 0 and st["device_errors"] == 0
-    total = torch.tensor([n_checked], device=rep.device if args.backend == "nccl" else "cpu")
-    dist.all_reduce(total)
-    n_samples = sum(1 for op in ops if op[0] == "sample")
-    assert int(total.item()) == n_samples, (int(total.item()), n_samples)
-    if rank == 0:
-        print("SHARDED_OK world=%d backend=%s samples_checked=%d" % (world, args.backend, n_samples))
-    dist.destroy_process_group()
-
-
-def capi_stats(engine):
-    import ctypes as C
-
-    from rela_b200 import capi
-
-    st = capi.RRStats()
-    capi.check(engine.L.rr_get_stats(engine.h, C.byref(st)))
-    return {n: getattr(st, n) for n, _ in st._fields_}
+            orc.update(torch_pow(prio, alpha))
+            if my_learner >= 0:
+                mine = prio[my_learner * a.B:(my_learner + 1) * a.B]
+            else:
+                mine = np.zeros(0, np.float32)
+            rep.update_priority(torch.from_numpy(np.ascontiguousarray(mine)))
+    rep.sync()
+    # the replicated control state equals the single buffer's
+    v = [C.c_int() for _ in range(4)]
+    s = C.c_double()
+    capi.check(L.rr_debug_state(h, *[C.addressof(x) for x in v], C.addressof(s)))
+    st = orc.state()
+    assert (v[0].value, v[1].value, v[2].value, v[3].value) == (st["head"], st["tail"], st["size"], st["safe_size"])
+    assert s.value == st["sum"], (s.value, st["sum"])
+    del rep
+    print("SHARDED_OK rank=%d world=%d samples=%d" % (rank, world, n_samples), flush=True)
 
 
 if __name__ == "__main__":

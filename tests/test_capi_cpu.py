@@ -41,7 +41,7 @@ def test_no_cpu_fallback():
     assert b"no CPU path" in lib.rr_last_error()
     import rela_b200
 
-    with pytest.raises(capi.ReplayError):
+    with pytest.raises(RuntimeError, match="no CPU path"):
         rela_b200.FFPrioritizedReplay(128, 1, 0.6, 0.4, 0)
 
 

@@ -120,3 +120,73 @@ def test_python_layer_save_load(tmp_path):
         assert torch.equal(ba.reward, bb.reward) and torch.equal(ba.next_obs["s"], bb.next_obs["s"])
         a.update_priority(prio)
         b.update_priority(prio)
+
+
+@pytest.mark.parametrize("prefetch", [1, 2])
+def test_save_load_with_batches_drawn_ahead(tmp_path, prefetch):
+    """prefetch > 0 (the reference's main.py default is 1): after the first sample() there are
+    always batches drawn ahead. They are saved with the checkpoint -- ids, weights, gathered rows --
+    and a restored replay hands out the very batches the uninterrupted run does, also when the
+    slots they came from have been overwritten since."""
+    import torch
+
+    import rela_b200.rela as rela
+
+    def transition(n, g, serial):
+        obs = {"s": torch.randint(0, 256, (n, 2, 8, 8), dtype=torch.uint8, generator=g)}
+        act = {"a": torch.arange(serial, serial + n, dtype=torch.int64)}
+        nxt = {"s": torch.randint(0, 256, (n, 2, 8, 8), dtype=torch.uint8, generator=g)}
+        return rela.FFTransition(obs, act, torch.randn(n, generator=g), torch.zeros(n, dtype=torch.bool),
+                                 torch.ones(n), nxt)
+
+    g = torch.Generator().manual_seed(5)
+    a = rela.FFPrioritizedReplay(100, 3, 0.6, 0.4, prefetch)
+    serial = 0
+    for _ in range(7):
+        a.add(transition(16, g, serial), torch.rand(16, generator=g) + 0.01)
+        serial += 16
+    for _ in range(3):
+        a.sample(32, "cuda:0")
+        a.update_priority(torch.rand(32, generator=g) + 0.01)
+        a.add(transition(16, g, serial), torch.rand(16, generator=g) + 0.01)  # overwrites evicted slots
+        serial += 16
+    path = str(tmp_path / "pf.ckpt")
+    a.save(path)   # `prefetch` batches are queued at this point
+    b = rela.FFPrioritizedReplay(100, 777, 0.6, 0.4, prefetch)
+    b.load(path)
+    assert b.size() == a.size() and b.num_add() == a.num_add()
+    for k in range(6):
+        ba, wa = a.sample(32, "cuda:0")
+        bb, wb = b.sample(32, "cuda:0")
+        assert torch.equal(wa, wb), k
+        assert torch.equal(ba.action["a"], bb.action["a"]), k
+        assert torch.equal(ba.obs["s"], bb.obs["s"]) and torch.equal(ba.next_obs["s"], bb.next_obs["s"])
+        assert torch.equal(ba.reward, bb.reward)
+        prio = torch.rand(32, generator=g) + 0.01
+        a.update_priority(prio)
+        b.update_priority(prio)
+        if k % 2 == 0:
+            t = transition(16, g, serial)
+            p = torch.rand(16, generator=g) + 0.01
+            a.add(t, p)
+            b.add(t, p)
+            serial += 16
+    a.sync()
+    b.sync()
+
+
+def test_save_is_atomic(tmp_path):
+    """rr_save writes <path>.tmp and renames: an existing checkpoint survives a failed save."""
+    from rela_b200 import capi
+
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    a = CudaReplay(schema, 64, 1, 0.6, 0.4, 0)
+    apply_trace(a, gen_trace(schema, 64, 3, 6, 8, 16), 0.6, False)
+    path = tmp_path / "r.ckpt"
+    capi.check(a.lib.rr_save(a.h, str(path).encode()))
+    good = path.read_bytes()
+    assert not (tmp_path / "r.ckpt.tmp").exists()
+    # a save that cannot create its temporary file fails and leaves the checkpoint alone
+    (tmp_path / "r.ckpt.tmp").mkdir()
+    assert a.lib.rr_save(a.h, str(path).encode()) == capi.RR_ERR_ARG
+    assert path.read_bytes() == good

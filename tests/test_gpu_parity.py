@@ -30,8 +30,9 @@ def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, **cuda_kw):
 
 
 def check_tiles(cu, w):
-    """The incrementally maintained tile entries equal a rebuild from the weights, bit for bit,
-    and (mins always, sums when exactly representable) a host recomputation."""
+    """The incrementally maintained hierarchy entries (level 0: groups, level 1: leaves) equal a
+    rebuild from the weights, bit for bit, and (mins always, sums when exactly representable) a
+    host recomputation."""
     inc = [cu.tiles(level=lv) for lv in (0, 1)]  # both read before the rebuild overwrites them
     for lv in (0, 1):
         s_inc, m_inc, ts = inc[lv]
@@ -114,24 +115,101 @@ def test_rnn_full_size_rows():
     _run_pair(schema, 24, 3, 0.9, 0.6, 0, ops)
 
 
-@pytest.mark.parametrize("tile_log2", [9, 10, 11])
-def test_larger_prefix_tiles(monkeypatch, tile_log2):
-    """Replays above 4 M slots use tiles of 512 ... 2048 slots (at most 16 K tile
-    prefixes fit in shared memory); force them at a small capacity."""
-    monkeypatch.setenv("RR_TILE_LOG2", str(tile_log2))
+@pytest.mark.parametrize("group_log2,B", [(0, 200), (1, 200), (3, 64), (5, 700)])
+def test_small_groups_many_groups(monkeypatch, group_log2, B):
+    """The group level of the hierarchy at a small capacity: groups of 1 ... 32 leaves give 44 ... 2
+    groups for 11,250 slots, so the scan over group sums, the head offset inside a group, the
+    per-group maintenance of update_kernel (both candidate modes: fewer groups than batch elements
+    and more) and the group refresh of commit / eviction all see many groups."""
+    monkeypatch.setenv("RR_GROUP_LOG2", str(group_log2))
     schema = ff_schema(frame=(1, 4, 4), n_actions=2)
-    ops = gen_trace(schema, 9000, 31 + tile_log2, 40, 80, 200, zero_frac=0.05)
+    ops = gen_trace(schema, 9000, 31 + group_log2, 40, 80, B, zero_frac=0.05)
     cu = _run_pair(schema, 9000, 5, 0.6, 0.4, 0, ops)
     assert cu.stats()["samples_ordered"] == 0
 
 
-def test_six_million_slots_natural_tile_size():
-    """capacity 6 M -> 7.5 M slots -> 512-slot tiles chosen by rr_create; selection
-    only (tiny rows), a few cycles (the oracle walks 6 M weights per sample)."""
+def test_more_groups_than_batch_elements(monkeypatch):
+    """ng > B: update_kernel's candidates are batch elements, not groups."""
+    monkeypatch.setenv("RR_GROUP_LOG2", "0")
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    ops = gen_trace(schema, 20000, 91, 30, 400, 24, zero_frac=0.02)
+    _run_pair(schema, 20000, 5, 0.6, 0.4, 0, ops)
+
+
+def test_headline_capacity_selection_differential():
+    """BASELINE.json configs[1] geometry -- capacity 2^21, 2,621,440 slots = 160 groups of 64
+    leaves, batch 512 -- with tiny rows, so that the ORACLE holds it too: every sampled id is
+    compared, not only properties (the oracle walks 2 M weights per sample: a few cycles)."""
+    schema = [f for f in ff_schema(frame=(1, 1, 1), n_actions=1) if f.name in ("action.a", "reward")]
+    cap = 1 << 21
+    ops = gen_trace(schema, cap, 77, 6, 100_000, 512, prefill=cap, adds_per_cycle=(1, 1))
+    cu = _run_pair(schema, cap, 9, 0.6, 0.4, 0, ops)
+    st = cu.stats()
+    assert st["samples_ordered"] == 0 and st["pops"] > 0
+
+
+def test_six_million_slots():
+    """capacity 6 M -> 7.5 M slots -> 458 groups; selection only (tiny rows), a few cycles."""
     schema = [f for f in ff_schema(frame=(1, 1, 1), n_actions=1) if f.name in ("action.a", "reward")]
     cap = 6_000_000
     ops = gen_trace(schema, cap, 77, 4, 200_000, 512, prefill=cap, adds_per_cycle=(1, 1))
     _run_pair(schema, cap, 9, 0.6, 0.4, 0, ops)
+
+
+def test_selection_overrun_is_reported_at_the_next_call():
+    """The reference asserts when the walk runs past the last element
+    (prioritized_replay.h:297-302). Here the kernel raises a sticky error that the NEXT
+    rr_sample / rr_update_priority returns without any synchronisation, until rr_sync clears it.
+    Provoked through the public API: all priorities zero -> sum_ == 0 -> no slot reaches any target."""
+    from harness import make_rows
+    from rela_b200 import capi
+
+    schema = ff_schema(frame=(1, 4, 4), n_actions=2)
+    cu = CudaReplay(schema, 64, 1, 0.6, 0.4, 0)
+    rng = np.random.default_rng(0)
+    cu.add(make_rows(schema, 32, rng), np.zeros(32, np.float32))
+    rc, _, _, _ = cu.sample(8)   # launches; the overrun is raised on the device
+    assert rc == 0
+    import torch
+
+    torch.cuda.synchronize()
+    assert cu.update(np.ones(8, np.float32)) == capi.RR_ERR_OVERRUN
+    assert b"reference asserts" in cu.lib.rr_last_error()
+    rc, _, _, _ = cu.sample(8)
+    assert rc == capi.RR_ERR_OVERRUN or rc == capi.RR_ERR_STATE
+    assert cu.sync() == capi.RR_ERR_OVERRUN   # reported and cleared
+    assert cu.sync() == 0
+
+
+@pytest.mark.parametrize("prefetch", [1, 2, 3])
+def test_pipelined_full_frames(prefetch):
+    """Batches drawn ahead gather on the two gather streams while the control plane (selection,
+    update, commit) runs beside them: full 4x84x84 rows so that the gather really is the long
+    kernel, adds between samples so that evicted rows are re-reserved while earlier gathers may
+    still be queued."""
+    from harness import CudaReplayHostPrefetch
+
+    schema = ff_schema()
+    cap, alpha = 600, 0.6
+    ops = gen_trace(schema, cap, 19 + prefetch, 80, 60, 128, adds_per_cycle=(0, 3))
+    orc = Oracle(schema, cap, 3, alpha, 0.4, prefetch)
+    cu = CudaReplayHostPrefetch(schema, cap, 3, alpha, 0.4, prefetch)
+    ra = apply_trace(orc, ops, alpha, False)
+    rb = apply_trace(cu, ops, alpha, False)
+    assert cu.sync() == 0
+    compare_records(ra, rb, "oracle prefetch=%d vs pipelined" % prefetch)
+    assert orc.state() == cu.state()
+
+
+@pytest.mark.parametrize("prefetch", [1, 2])
+@pytest.mark.parametrize("own_stream", [False, True])
+def test_library_prefetch_queue(prefetch, own_stream):
+    """rr_create(prefetch > 0): the library's own queue (device-to-device hand-out), from a
+    foreign stream and from the replay's own stream."""
+    schema = ff_schema(frame=(4, 12, 12), n_actions=6)
+    cap, alpha = 256, 0.6
+    ops = gen_trace(schema, cap, 3, 80, 20, 32)
+    _run_pair(schema, cap, 7, alpha, 0.4, prefetch, ops, own_stream=own_stream)
 
 
 def test_batch_not_multiple_of_cta_targets():
@@ -242,4 +320,4 @@ def test_host_managed_prefetch_matches_oracle(prefetch):
     assert cu.lib.rr_sample(cu.h, 32, outs, 1, None) == capi.RR_ERR_STATE
     assert cu.update(np.ones(32, np.float32)) == 0
     assert cu.lib.rr_sample(cu.h, 32, outs, 1, None) == capi.RR_ERR_STATE  # queued batches pending
-    assert cu.lib.rr_save(cu.h, b"/tmp/never_written.ckpt") == capi.RR_ERR_STATE
+    # a checkpoint may be taken with batches drawn ahead (they are saved with it): tests/test_gpu_checkpoint.py

@@ -110,3 +110,32 @@ def _same(ba, bb, T, B):
     assert torch.equal(ba.action["a"], bb.action["a"])
     assert torch.equal(ba.reward, bb.reward) and torch.equal(ba.terminal, bb.terminal)
     assert torch.equal(ba.bootstrap, bb.bootstrap) and torch.equal(ba.seq_len, bb.seq_len)
+
+
+@pytest.mark.parametrize("seq_len,burn_in,multi_step,p_term", [(8, 0, 2, 0.07), (6, 0, 3, 0.15)])
+def test_device_priorities_mix_on_the_device(seq_len, burn_in, multi_step, p_term):
+    """Per-step priorities handed over as CUDA tensors stay in a device window and the eta-mix is
+    computed by the K9 kernel (rr_aggregate_priority) inside popInto: same sequences, same
+    priorities (exact here: multiples of 1/64, eta 0.5, alpha 1), same samples as the reference."""
+    if BUILD not in sys.path:
+        sys.path.insert(0, BUILD)
+    import rela
+    import seq_fixture
+
+    K, n_steps, eta, B = 6, 160, 0.5, 32
+    T = burn_in + seq_len + multi_step
+    steps = _steps(K, n_steps, 300 + seq_len, p_term)
+    steps_dev = [s[:5] + (s[5].cuda(),) + s[6:] for s in steps]
+    ref = rela.RNNPrioritizedReplay(4096, 3, 1.0, 0.6, 0)
+    dev = rela.RNNPrioritizedReplay(4096, 3, 1.0, 0.6, 0)
+    n_ref = seq_fixture.feed_reference(ref, K, multi_step, seq_len, burn_in, eta, steps)
+    n_dev = seq_fixture.feed_assembler(dev, K, multi_step, seq_len, burn_in, eta, steps_dev)
+    assert n_ref == n_dev and n_ref > 5
+    for _ in range(6):
+        ba, wa = ref.sample(B, "cuda:0")
+        bb, wb = dev.sample(B, "cuda:0")
+        _same(ba, bb, T, B)
+        assert torch.allclose(wa, wb, rtol=1e-6, atol=0)
+        p = torch.rand(B) + 0.1
+        ref.update_priority(p)
+        dev.update_priority(p)

@@ -1,10 +1,15 @@
-"""Capacity-sharded replay: N ranks must reproduce ONE
+"""One replay striped over N shard processes: N ranks must reproduce ONE
 single-buffer oracle bit for bit.
 
-CPU (`gloo`, world_size 2): the SPMD protocol of rela_b200/sharded.py with the
-device engine replaced by an oracle-backed stand-in (tests/sharded_worker.py).
-GPU (`nccl`): the real engine; world 1 on any box, world 2 when two GPUs are
-visible (gpurun --gpus 2): rows travel over NVLink into the learner's batch."""
+CPU: the rendezvous the shards set themselves up with (rr_group_*: shared memory, several
+processes, stale segments) and the shard ranges.
+GPU: the real thing through the C++ host layer (rela_b200/cpp/sharded_core.cc). The ranks are
+plain processes; with fewer GPUs than ranks several ranks share a device (peer memory is then
+the same device's memory, mapped through CUDA IPC), so the whole protocol -- routed gathers
+into the learners' batch tensors, completion flags, the all-gather of priorities, the
+owner-routed inserts -- runs and is compared byte for byte on a ONE-GPU box too."""
+import ctypes as C
+import multiprocessing as mp
 import os
 import subprocess
 import sys
@@ -16,44 +21,140 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 WORKER = os.path.join(HERE, "sharded_worker.py")
 
 
-def _run(world, backend, port, extra=()):
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
-           "--master-addr", "127.0.0.1", "--master-port", str(port), WORKER, "--backend", backend, *extra]
-    env = dict(os.environ, OMP_NUM_THREADS="1")
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
-    assert out.returncode == 0, (out.stdout[-2000:], out.stderr[-4000:])
-    assert "SHARDED_OK world=%d" % world in out.stdout, out.stdout[-2000:]
+def _group_worker(rank, world, name, rounds, q):
+    sys.path.insert(0, os.path.dirname(HERE))
+    from rela_b200 import capi
+
+    L = capi.lib()
+    g = C.c_void_p()
+    rc = L.rr_group_create(C.byref(g), name.encode(), rank, world)
+    assert rc == 0, (rc, L.rr_last_error())
+    assert L.rr_group_rank(g) == rank and L.rr_group_world(g) == world
+    for it in range(rounds):
+        mine = (C.c_uint8 * 64)(*[(rank * 7 + it + k) % 256 for k in range(64)])
+        allb = (C.c_uint8 * (64 * world))()
+        assert L.rr_group_allgather(g, mine, 64, allb) == 0
+        for r in range(world):
+            assert list(allb[r * 64:(r + 1) * 64]) == [(r * 7 + it + k) % 256 for k in range(64)], (rank, it, r)
+    assert L.rr_group_barrier(g) == 0
+    L.rr_group_destroy(g)
+    q.put(rank)
 
 
-@pytest.mark.parametrize("world,rotate", [(2, False), (3, False), (2, True)])
-def test_protocol_gloo(world, rotate):
-    _run(world, "gloo", 29640 + world + 10 * rotate, ("--K", str(12 * world)) + (("--rotate-learner",) if rotate else ()))
+@pytest.mark.parametrize("world,rank0_last", [(2, False), (3, False), (3, True)])
+def test_group_rendezvous(world, rank0_last):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = "t%d_%d%d" % (os.getpid(), world, rank0_last)
+    ps = [ctx.Process(target=_group_worker, args=(r, world, name, 40, q)) for r in range(world)]
+    for p in (ps[1:] + ps[:1] if rank0_last else ps):  # the joiners must wait for rank 0's segment
+        p.start()
+    for p in ps:
+        p.join(120)
+    assert [p.exitcode for p in ps] == [0] * world
+    assert sorted(q.get() for _ in range(world)) == list(range(world))
 
 
+def test_group_skips_a_stale_segment():
+    """A segment left behind by a dead job (magic set, nobody answering) must not be joined."""
+    name = "stale%d" % os.getpid()
+    path = "/dev/shm/rela_b200." + name
+    with open(path, "wb") as f:  # looks initialised, but its rank 0 is gone
+        f.write((0x72656c6162323030).to_bytes(8, "little") + b"\0" * 8 + (2).to_bytes(4, "little") + b"\0" * (1 << 21))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    p1 = ctx.Process(target=_group_worker, args=(1, 2, name, 5, q))
+    p1.start()   # opens the stale segment first, gets no answer, retries by name
+    import time
+
+    time.sleep(1.0)
+    p0 = ctx.Process(target=_group_worker, args=(0, 2, name, 5, q))
+    p0.start()
+    p0.join(120)
+    p1.join(120)
+    assert (p0.exitcode, p1.exitcode) == (0, 0)
+    assert not os.path.exists(path)  # rank 0 unlinks the name once everybody is in
+
+
+def test_group_argument_errors():
+    sys.path.insert(0, os.path.dirname(HERE))
+    from rela_b200 import capi
+
+    L = capi.lib()
+    g = C.c_void_p()
+    assert L.rr_group_create(C.byref(g), b"x", 3, 2) == capi.RR_ERR_ARG
+    assert L.rr_group_create(C.byref(g), b"x", 0, 99) == capi.RR_ERR_ARG
+    assert L.rr_group_create(C.byref(g), b"solo%d" % os.getpid(), 0, 1) == 0  # a world of one needs nobody
+    buf = (C.c_uint8 * 8)(*range(8))
+    out = (C.c_uint8 * 8)()
+    assert L.rr_group_allgather(g, buf, 8, out) == 0 and list(out) == list(range(8))
+    assert L.rr_group_allgather(g, buf, 1 << 20, out) == capi.RR_ERR_ARG
+    L.rr_group_destroy(g)
+
+
+def _run(world, extra=(), timeout=600):
+    group = "test%d_%d" % (os.getpid(), abs(hash(extra)) % 100000)
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), OMP_NUM_THREADS="1")
+        procs.append(subprocess.Popen([sys.executable, WORKER, "--group", group, *extra], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=timeout)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append(out)
+    for r, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, "rank %d:\n%s" % (r, out[-4000:])
+        assert "SHARDED_OK rank=%d world=%d" % (r, world) in out, out[-2000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("learner,prefetch", [(-1, 0), (0, 0), (-1, 2), (1, 1)])
+def test_striped_replay_matches_one_oracle(world, learner, prefetch):
+    """learner -1: every rank draws its share of one stratified batch of world * B (a
+    data-parallel learner); learner r: one learner rank. With and without batches drawn ahead."""
+    _run(world, ("--learner", str(learner), "--prefetch", str(prefetch), "--K", str(12 * world)))
+
+
+@pytest.mark.gpu
+def test_striped_replay_full_frames_device_rows():
+    """4x84x84 rows (the bulk-copy path of the routed gather and of the owner-routed insert),
+    rows handed over in device memory."""
+    _run(2, ("--full-frames", "--device-rows", "--capacity", "400", "--cycles", "12", "--K", "40", "--prefetch", "1"))
+
+
+@pytest.mark.gpu
+def test_striped_replay_world4():
+    _run(4, ("--K", "48", "--B", "16", "--cycles", "25"))
+
+
+@pytest.mark.gpu
 def test_shard_ranges_cover_the_ring():
-    from rela_b200.sharded import shard_range
+    sys.path.insert(0, os.path.dirname(HERE))
+    from rela_b200 import capi
 
-    for S in (1, 7, 81920, 2621440, 20971520):
+    L = capi.lib()
+    for cap in (1, 6, 65536, 2097152):
+        S = int(1.25 * cap)
         for world in (1, 2, 3, 4, 8):
             cover = []
             for r in range(world):
-                lo, hi = shard_range(S, r, world)
-                assert 0 <= lo <= hi <= S
-                cover.append((lo, hi))
+                h = C.c_void_p()
+                capi.check(L.rr_create(C.byref(h), cap, 1, 0.6, 0.4, 0, 0))
+                capi.check(L.rr_set_shard(h, r, world))
+                lo, hi = C.c_int(), C.c_int()
+                capi.check(L.rr_shard_range(h, C.byref(lo), C.byref(hi)))
+                L.rr_destroy(h)
+                assert 0 <= lo.value <= hi.value <= S
+                cover.append((lo.value, hi.value))
             assert cover[0][0] == 0 and cover[-1][1] == S
             assert all(a[1] == b[0] for a, b in zip(cover, cover[1:]))
-
-
-@pytest.mark.gpu
-def test_sharded_world1_gpu():
-    _run(1, "nccl", 29651)
-
-
-@pytest.mark.gpu
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
-@pytest.mark.parametrize("extra", [(), ("--full-frames", "--capacity", "400", "--cycles", "12"), ("--rotate-learner",)])
-def test_sharded_world2_gpu(extra):
-    _run(2, "nccl", 29652, extra)
 
 
 @pytest.mark.gpu
@@ -61,8 +162,6 @@ def test_sharded_world2_gpu(extra):
 def test_replay_on_a_device_that_is_not_current():
     """The C ABI makes its device current per call and restores the caller's:
     a replay on cuda:1 driven from a thread whose current device is cuda:0."""
-    import sys
-
     sys.path.insert(0, HERE)
     from harness import CudaReplay, Oracle, apply_trace, compare_records, ff_schema, gen_trace
 

@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
 import rela_b200.rela as rela
-from bench import fill_device
+from bench import fill_fast
 
 dev = torch.device("cuda", 0)
 cap = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
@@ -19,7 +19,7 @@ prio = torch.rand((16, B), device=dev) + 0.01
 
 def run(mode):
     r = rela.FFPrioritizedReplay(cap, 7, 0.6, 0.4, 0, 0)
-    fill_device(r, torch, dev, cap, 64)
+    fill_fast(rela, torch, r, dev, cap)
     if mode != "separate":
         dt = torch.float32 if mode == "fused_f32" else torch.bfloat16
         r.set_output_format("obs.s", dt)

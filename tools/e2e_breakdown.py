@@ -3,11 +3,12 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import rela_b200.rela as rela
-from bench import fill_device
+from bench import fill_fast
 dev = torch.device("cuda", 0)
 cap = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 18
-r = rela.FFPrioritizedReplay(cap, 7, 0.6, 0.4, 0, 0)
-fill_device(r, torch, dev, cap, 64)
+pf = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+r = rela.FFPrioritizedReplay(cap, 7, 0.6, 0.4, pf, 0)
+fill_fast(rela, torch, r, dev, cap)
 B = 512
 prio = (torch.rand((16, B)) + 0.01).pin_memory()
 acc = [0.0] * 4
