@@ -621,6 +621,25 @@ class Loops:
         self.replay.update_priority(self.prio_host[k % 16])
         return w_host
 
+    def c_loop(self, depth, steps, warmup):
+        """The same calls in a loop inside the library (rr_cycle_bench): no ctypes overhead per call,
+        like the reference arm's loop (oracle/ref_driver.cc). Returns (ms per step, kernel launches)."""
+        c, L, h, R, B = self.capi, self.L, self.h, self.R, self.B
+        nf = len(self.schema)
+        flat = (C.c_void_p * (R * nf))(*[t.data_ptr() for o in self.outs for t in o])
+        ws = (C.c_void_p * R)(*[t.data_ptr() for t in self.w])
+        ps = (C.c_void_p * 16)(*[self.prio_dev[i].data_ptr() for i in range(16)])
+        ms, n = C.c_double(), C.c_uint64()
+        self.barrier()
+        c.check(L.rr_cycle_bench(h, B, depth, steps, warmup, R, flat, ws, 16, ps, c.RR_PRIO_DEVICE, C.byref(ms),
+                                 C.byref(n)))
+        ms_v = ms.value
+        if self.dist is not None:
+            t = self.torch.tensor([ms_v], device=self.dev)
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+            ms_v = float(t.item())
+        return ms_v, int(n.value)
+
     def gather_bench(self, reps, streams, outs=None, ptr_sets=None):
         c, L, h = self.capi, self.L, self.h
         outs = self.outs if outs is None else outs
@@ -634,23 +653,25 @@ class Loops:
 
 def time_value_modes(lp, K, W, stats):
     """`value`: prefetch 0 (strictly serial: a batch is drawn after the previous update) and
-    prefetch 2 (drawn ahead, like the reference's futures), device-resident priorities."""
+    prefetch 2 (drawn ahead, like the reference's futures), device-resident priorities, the C ABI
+    calls issued from a loop inside the library; the same loops driven from Python through ctypes
+    are listed beside them (`ms_per_step_ctypes`)."""
     runs = []
-    for k in range(W):
-        lp.serial(k)
-    s0 = stats()
-    ms = lp.timed(lp.serial, K, lp.own_stream)
-    s1 = stats()
-    runs.append({"prefetch": 0, "ms_per_step": ms / K, "gpu_launches": int(s1["kernel_launches"] - s0["kernel_launches"])})
-    start, cycle, drain = lp.pipelined(2)
-    start()
-    for k in range(W):
-        cycle(k)
-    s0 = stats()
-    ms = lp.timed(cycle, K, lp.own_stream)
-    s1 = stats()
-    drain()
-    runs.append({"prefetch": 2, "ms_per_step": ms / K, "gpu_launches": int(s1["kernel_launches"] - s0["kernel_launches"])})
+    for depth in (0, 2):
+        ms, launches = lp.c_loop(depth, K, W)
+        run = {"prefetch": depth, "ms_per_step": ms, "gpu_launches": launches}
+        if depth == 0:
+            for k in range(W):
+                lp.serial(k)
+            run["ms_per_step_ctypes"] = lp.timed(lp.serial, K, lp.own_stream) / K
+        else:
+            start, cycle, drain = lp.pipelined(depth)
+            start()
+            for k in range(W):
+                cycle(k)
+            run["ms_per_step_ctypes"] = lp.timed(cycle, K, lp.own_stream) / K
+            drain()
+        runs.append(run)
     return runs
 
 
@@ -779,8 +800,9 @@ def run_single(args):
         "config": workload_config(args.capacity, B, args.alpha, args.beta),
         "parallelism": "1 GPU",
         "value_runs": [dict(r, transitions_per_s=B / (r["ms_per_step"] * 1e-3)) for r in value_runs],
-        "value_note": "C ABI calls on the replay's own stream, new priorities already in HBM; prefetch 0 = every batch "
-                      "drawn after the previous update_priority; prefetch 2 = two batches drawn ahead "
+        "value_note": "C ABI calls on the replay's own stream issued from a loop inside the library (rr_cycle_bench; "
+                      "ms_per_step_ctypes: the same loop driven from Python), new priorities already in HBM; prefetch 0 = "
+                      "every batch drawn after the previous update_priority; prefetch 2 = two batches drawn ahead "
                       "(rr_prefetch_into / rr_take_prefetched, the reference's futures): the fastest is `value`",
         "e2e": {"value": B / (best_e["ms_per_step"] * 1e-3), "unit": "transitions/s", "h2d_bytes_per_step": 4 * B,
                 "d2h_bytes_per_step": 4 * B, "ms_per_step": best_e["ms_per_step"], "prefetch": best_e["prefetch"],

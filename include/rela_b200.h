@@ -292,6 +292,21 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields,
                     int reps, int streams, double* ms_per_launch,
                     uint64_t* launches, uint64_t* bytes_per_launch);
 
+/* The timed sample + update_priority loop, run inside the library (like the
+ * reference arm's loop, oracle/ref_driver.cc: no per-call foreign-function
+ * overhead): `steps` cycles after `warmup`, device-resident priorities
+ * (prio_sets[k % n_prio_sets], `batch` floats each, flags as for
+ * rr_update_priority), results into out set k % n_out_sets (out_fields[o *
+ * nfields + f], out_weights[o]), everything issued with the internal stream as
+ * the caller's stream. depth == 0: rr_sample + rr_update_priority, every batch
+ * drawn after the previous update. depth > 0: rr_take_prefetched +
+ * rr_update_priority + rr_prefetch_into with `depth` batches drawn ahead (the
+ * reference's prefetch). Timed with one CUDA-event pair on the internal stream
+ * after joining the gather streams. */
+int rr_cycle_bench(rr_replay* r, int batch, int depth, int steps, int warmup, int n_out_sets,
+                   void* const* out_fields, float* const* out_weights, int n_prio_sets,
+                   const float* const* prio_sets, unsigned prio_flags, double* ms_per_step, uint64_t* launches);
+
 /* Learner-side fusion at the batch hand-off (not in the reference; SURVEY 8(f)
  * rank 3). The reference's learner converts the sampled u8 frames right after
  * sample() with `s.float() / 255` (pyrela/net.py:46,104): a second full pass

@@ -19,7 +19,7 @@ SYMBOLS = [
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence",
     "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
-    "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_nstep_return", "rr_td_priority",
+    "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_cycle_bench", "rr_nstep_return", "rr_td_priority",
     "rr_aggregate_priority", "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_prefetch_routed",
     "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_exchange",
     "rr_set_shard", "rr_shard_range", "rr_slab_ptrs", "rr_add_sharded_rows", "rr_add_sharded_commit",
@@ -92,6 +92,7 @@ def lib():
         L.rr_set_output_format.argtypes = [vp, i, i]
         L.rr_set_profiling.argtypes = [vp, i, i]
         L.rr_gather_bench.argtypes = [vp, i, vp, i, i, vp, vp, vp]
+        L.rr_cycle_bench.argtypes = [vp, i, i, i, i, i, vp, vp, i, vp, u, vp, vp]
         L.rr_nstep_return.argtypes = [i, i, f, vp, vp, vp, vp, vp, i, vp]
         L.rr_td_priority.argtypes = [i, vp, vp, vp, vp, f, vp, vp]
         L.rr_aggregate_priority.argtypes = [i, i, vp, vp, f, i, vp, vp]

@@ -155,7 +155,7 @@ class ReplayCore {
   void shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w, unsigned flags);
   std::pair<Leaves, torch::Tensor> shardedSample(int batchsize, const std::string& device);
   void shardedUpdate(const torch::Tensor& w, unsigned flags);
-  torch::Tensor raisedForShards(const torch::Tensor& w, unsigned flags) const;
+  torch::Tensor raisedForShards(const torch::Tensor& p, int64_t offset, int64_t total) const;
 
   rr_replay* h_ = nullptr;
   int device_ = 0;

@@ -299,6 +299,7 @@ torch::Tensor ReplayCore::weightsOf(const torch::Tensor& priority, unsigned* fla
   if (priority.scalar_type() != torch::kFloat32)  // accessor<float, 1>, :59,107
     throw std::runtime_error("priority must be float32");
   torch::Tensor p = priority.detach().contiguous();
+  if (shard_.world > 1) return p;  // raised where its position in the collective block is known (sharded_core.cc)
   if (p.is_cuda()) {
     if (p.get_device() != device_) p = p.to(torch::Device(torch::kCUDA, (c10::DeviceIndex)device_));
     *flags |= RR_PRIO_DEVICE;

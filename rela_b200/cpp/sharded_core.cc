@@ -235,17 +235,24 @@ const float* stageHost(ReplayCore::Sharded& sh, const float* host, size_t n) {
 }  // namespace
 
 // In a striped replay priorities are always raised before they are exchanged, with torch::pow
-// where they live: on the CPU for host tensors -- the function the reference calls
-// (rela/prioritized_replay.h:188,239), bit-identical weights -- on the GPU for device tensors.
-torch::Tensor ReplayCore::raisedForShards(const torch::Tensor& w, unsigned flags) const {
-  if ((flags & RR_PRIO_IS_WEIGHT) || alpha_ == 1.0f) return w;
-  return torch::pow(w, alpha_);
+// where they live. For host tensors that is the function the reference calls
+// (rela/prioritized_replay.h:188,239) -- but ATen's CPU pow is not position independent: the
+// vectorised body of a tensor goes through Sleef, its last few elements through libm's powf,
+// and the two can differ in the last bit. ONE reference replay raises the whole collective
+// block at once, so this rank raises its `n` values AT THEIR POSITION `offset` inside a block
+// of `total` (the other positions hold 1): bit-identical weights whatever the vector width.
+torch::Tensor ReplayCore::raisedForShards(const torch::Tensor& p, int64_t offset, int64_t total) const {
+  if (alpha_ == 1.0f) return p;
+  if (p.is_cuda()) return torch::pow(p, alpha_);
+  torch::Tensor full = torch::ones({total}, torch::kFloat32);
+  full.narrow(0, offset, p.size(0)).copy_(p);
+  return torch::pow(full, alpha_).narrow(0, offset, p.size(0)).contiguous();
 }
 
-void ReplayCore::shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w_in, unsigned flags) {
+void ReplayCore::shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w_in, unsigned /*flags*/) {
   Sharded& sh = *sharded_;
-  const torch::Tensor w = raisedForShards(w_in, flags);
-  const int64_t n = w.size(0);
+  const int64_t n = w_in.size(0);
+  const torch::Tensor w = raisedForShards(w_in, sh.rank * n, n * sh.world);
   const int64_t n_total = n * sh.world;
   if ((size_t)n_total > kInboxFloats)
     throw std::runtime_error("add: a collective block of " + std::to_string(n_total) + " rows exceeds " +
@@ -394,7 +401,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::shardedSample(int batchsize, const 
   return {std::move(out), std::move(weights)};
 }
 
-void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned flags) {
+void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   Sharded& sh = *sharded_;
   if (sh.cur_B == 0) throw std::runtime_error("update_priority: no sampled batch is outstanding");
   c10::cuda::CUDAGuard guard((c10::DeviceIndex)device_);
@@ -408,7 +415,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned flags) {
     if (w_in.size(0) != sh.cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
       throw std::runtime_error("update_priority: " + std::to_string(w_in.size(0)) + " priorities for a batch of " +
                                std::to_string(sh.cur_B));
-    w = raisedForShards(w_in, flags);
+    w = raisedForShards(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners);
     if (w.is_cuda()) {
       mine = w.data_ptr<float>();
       xs = cs;

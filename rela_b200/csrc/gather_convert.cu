@@ -85,8 +85,8 @@ __device__ __forceinline__ void convert_field(const ConvertField& f, const int32
 }
 
 __global__ void __launch_bounds__(256) gather_convert_kernel(const ConvertParams p) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();  // after the wait (the replay's kernels all do: select.cu, `rng_early`)
   const int lane = threadIdx.x & 31;
   const uint64_t warp_id = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const uint64_t n_warps = (uint64_t)gridDim.x * (blockDim.x >> 5);

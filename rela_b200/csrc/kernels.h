@@ -182,6 +182,7 @@ struct SelectArgs {
   unsigned long long* ismax;  // in/out
   uint32_t epoch;             // > the epoch of every earlier selection that used `ismax`
   int rng_par;                // which Ctl::mt / mti this selection reads
+  int rng_early;              // the previous selection is complete: draw before griddepcontrol.wait (select.cu)
   float beta;
   int contract_fma;
   int force_ordered;    // test hook: always take the ordered walk
@@ -196,11 +197,13 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
                           float alpha, int is_weight, cudaStream_t stream);
 
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
+// early: see update_kernel (select.cu); 0 is always correct
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream);
+                          const float* prio, float alpha, int is_weight, int early, cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
-                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream);
+                                 int n, const float* prio_host, float alpha, int is_weight, int early,
+                                 cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -140,6 +140,13 @@ struct rr_replay {
   int contract_fma = 1, force_ordered = 0;
   uint32_t epoch = 0;  // selections launched so far (SelectArgs::epoch)
   int rng_par = 0;     // Ctl::mt / mti buffer the next selection reads
+  // Kernels launched on `main` so far, and the position of the last selection / of the selection
+  // that filled each id buffer. All kernels of this library trigger their programmatic dependents
+  // only after their own griddepcontrol.wait, so a kernel that is at least two launches behind a
+  // selection on `main` may read what that selection wrote BEFORE its own wait (SelectArgs::
+  // rng_early, update_kernel's `early`). Not counting a launch only makes the test conservative.
+  uint64_t main_seq = 0, last_select_seq = 0;
+  std::vector<uint64_t> sel_seq;
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
   int sm_count = 148;
@@ -258,6 +265,7 @@ int new_idslot(rr_replay* r) {
   r->idalloc.push_back(nullptr);
   r->idcap.push_back(0);
   r->idbusy.push_back(false);
+  r->sel_seq.push_back(0);
   r->slotPending.push_back(false);
   cudaEvent_t ev = nullptr;
   RR_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -307,7 +315,9 @@ struct CopyPlan {
 
 // Split the fields of one row-copy launch into the bulk (cp.async.bulk through
 // shared memory) and simt (vector ld/st) paths and size the launch.
-int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>& in, const int32_t* ids,
+// beside: the launch leaves kGatherReserve of shared memory per SM free (a gather that runs on a
+// gather stream beside the control plane)
+int plan_copy(rr_replay* r, bool beside, int rows, const std::vector<CopyField>& in, const int32_t* ids,
               int insert_start, CopyPlan* out) {
   CopyParams& p = out->p;
   memset(&p, 0, sizeof(p));
@@ -357,8 +367,7 @@ int plan_copy(rr_replay* r, bool gather, int rows, const std::vector<CopyField>&
     const size_t hdr = rr::kCopyHeaderBytes;
     // 1 KB per-CTA system reserve; a gather also leaves room for one CTA of the priority
     // update (33.5 KB static + 12 B per element) to run beside it on the same SM
-    const size_t beside = gather ? kGatherReserve : 0;
-    const size_t lim = ((size_t)227 * 1024 - beside) / (size_t)r->g_ctas - 1024;
+    const size_t lim = ((size_t)227 * 1024 - (beside ? kGatherReserve : 0)) / (size_t)r->g_ctas - 1024;
     if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
     const int want = r->sm_count * r->g_ctas;
     c.grid = (int)std::min<uint64_t>((uint64_t)want, std::max<uint64_t>(items, 1));
@@ -418,6 +427,12 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   if (device < 0 || device >= ndev) return fail(RR_ERR_ARG, "rr_create: device %d of %d", device, ndev);
   DeviceScope dev_scope(device);
   rr_replay* r = new rr_replay();
+  struct Guard {  // a failure below must not leak the half-built replay
+    rr_replay* r;
+    ~Guard() {
+      if (r != nullptr) rr_destroy(r);
+    }
+  } guard{r};
   r->capacity = capacity;
   r->S = (int)(1.25 * capacity);  // rela/prioritized_replay.h:181
   // leaves per group: 64; $RR_GROUP_LOG2 (test hook) forces smaller groups so that small
@@ -428,7 +443,6 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   r->ng = r->S_pad >> (rr::kLeafLog2 + r->group_log2);
   if (r->ng > rr::kMaxGroups) {
     const int ng = r->ng, gl = r->group_log2;
-    delete r;
     return fail(RR_ERR_ARG, "rr_create: capacity %d needs %d groups of %d slots; one replay indexes %d", capacity, ng,
                 1 << (rr::kLeafLog2 + gl), rr::kMaxGroups);
   }
@@ -449,10 +463,15 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaGetDeviceProperties(&prop, device));
   r->sm_count = prop.multiProcessorCount;
 
-  RR_CUDA(cudaStreamCreateWithFlags(&r->main, cudaStreamNonBlocking));
+  // The control plane gets the highest stream priority, the gather streams the lowest: a gather
+  // whose CTAs are still waiting for shared memory (its predecessor on the other gather stream
+  // holds it) must not keep the small selection / update kernels behind it from being placed.
+  int prio_lo = 0, prio_hi = 0;
+  RR_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  RR_CUDA(cudaStreamCreateWithPriority(&r->main, cudaStreamNonBlocking, prio_hi));
   RR_CUDA(cudaEventCreateWithFlags(&r->evIn, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
-  for (cudaStream_t& g : r->gs) RR_CUDA(cudaStreamCreateWithFlags(&g, cudaStreamNonBlocking));
+  for (cudaStream_t& g : r->gs) RR_CUDA(cudaStreamCreateWithPriority(&g, cudaStreamNonBlocking, prio_lo));
   RR_CUDA(cudaEventCreateWithFlags(&r->evSel, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming));
 
@@ -496,6 +515,7 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
     int rc = new_idslot(r);
     if (rc != RR_OK) return rc;
   }
+  guard.r = nullptr;
   *out = r;
   return RR_OK;
 }
@@ -517,16 +537,14 @@ int rr_destroy(rr_replay* r) {
     if (l.pinned) cudaFreeHost(l.pinned);
     cudaFree(l.dprio);
     cudaFree(l.dptrs);
-    cudaEventDestroy(l.copied);
-    cudaEventDestroy(l.committed);
-    cudaEventDestroy(l.in);
-    cudaEventDestroy(l.gate);
-    cudaStreamDestroy(l.stream);
+    for (cudaEvent_t ev : {l.copied, l.committed, l.in, l.gate})
+      if (ev) cudaEventDestroy(ev);
+    if (l.stream) cudaStreamDestroy(l.stream);
   }
   for (auto& s : r->pstage) {
     if (s.pinned) cudaFreeHost(s.pinned);
     cudaFree(s.dev);
-    cudaEventDestroy(s.done);
+    if (s.done) cudaEventDestroy(s.done);
   }
   for (auto* p : r->idalloc) cudaFree(p);
   auto free_pre = [](Prefetched& p) {
@@ -537,15 +555,15 @@ int rr_destroy(rr_replay* r) {
   for (auto& p : r->queue) free_pre(p);
   for (auto& p : r->pool) free_pre(p);
   for (auto* hp : r->hist) cudaFree(hp);
-  cudaEventDestroy(r->evIn);
-  cudaEventDestroy(r->evOut);
+  if (r->evIn) cudaEventDestroy(r->evIn);
+  if (r->evOut) cudaEventDestroy(r->evOut);
   for (auto ev : r->evSlot)
     if (ev) cudaEventDestroy(ev);
   if (r->evSel) cudaEventDestroy(r->evSel);
   if (r->evJoin) cudaEventDestroy(r->evJoin);
   for (cudaStream_t g : r->gs)
     if (g) cudaStreamDestroy(g);
-  cudaStreamDestroy(r->main);
+  if (r->main) cudaStreamDestroy(r->main);
   delete r;
   return RR_OK;
 }
@@ -637,6 +655,7 @@ int rr_exchange(rr_replay* r, const void* src, uint64_t bytes, void* const* dst_
   RR_CUDA(rr::launch_exchange(src, (uint32_t)bytes, dst_ptrs, flag_ptrs, n, epoch,
                               static_cast<const unsigned long long*>(wait_flags), n_wait, &r->ctl->error,
                               r->host_err_dev, 10ull * 1000 * 1000 * 1000, r->main));
+  ++r->main_seq;
   r->launches++;
   return RR_OK;
 }
@@ -932,6 +951,7 @@ int add_impl(rr_replay* r, int n, const void* const* field_base, const uint64_t*
       if (e == cudaSuccess) {
         e = rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n,
                               prio_dev ? priority : L.dprio, r->alpha, is_weight, r->main);
+        ++r->main_seq;
         r->launches++;
       }
       if (e == cudaSuccess) e = cudaEventRecord(L.committed, r->main);
@@ -1042,6 +1062,7 @@ int rr_add_sharded_commit(rr_replay* r, const float* weights_all, unsigned flags
   r->pend_add_start = -1;
   RR_CUDA(rr::launch_commit(r->ctl, r->w, tiles_of(r), r->S, start, n, weights_all, r->alpha,
                             (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0, r->main));
+  ++r->main_seq;
   r->launches++;
   r->safeTail_ = (start + n) % r->S;
   r->safeSize_ += n;
@@ -1128,6 +1149,7 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   a.ismax = r->ismax[idslot];
   a.epoch = ++r->epoch;
   a.rng_par = r->rng_par;
+  a.rng_early = (r->last_select_seq > 0 && r->main_seq > r->last_select_seq) ? 1 : 0;
   a.beta = r->beta;
   a.contract_fma = r->contract_fma;
   a.force_ordered = r->force_ordered;
@@ -1139,6 +1161,7 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   }
   RR_CUDA(rr::launch_select(a, r->main));
   r->rng_par ^= 1;
+  r->last_select_seq = r->sel_seq[(size_t)idslot] = ++r->main_seq;
   r->launches++;
   *pop_out = a.pop_n;
   return RR_OK;
@@ -1179,7 +1202,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     cf.push_back(c);
   }
   CopyPlan plan;
-  int rc = plan_copy(r, true, B, cf, ids, 0, &plan);
+  int rc = plan_copy(r, ahead, B, cf, ids, 0, &plan);
   if (rc == RR_OK && route) {
     if (conv.n > 0) rc = fail(RR_ERR_ARG, "converted fields are not available on a sharded replay");
     plan.p.dst_tab = route->dst_tab;
@@ -1214,8 +1237,10 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     cudaError_t e = rr::launch_gather_convert(conv, r->sm_count, gstream);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather_convert: %s", cudaGetErrorString(e));
     r->launches++;
+    if (gstream == r->main) ++r->main_seq;
   }
   if (rc == RR_OK) rc = launch_plan(r, plan, gstream);
+  if (rc == RR_OK && gstream == r->main) ++r->main_seq;
   if (rc == RR_OK && ahead) {
     cudaError_t e = cudaEventRecord(r->evSlot[(size_t)idslot], gstream);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
@@ -1505,13 +1530,16 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
   const float* dprio = priority;
   std::unique_lock<std::mutex> lk(r->m_);
+  // the selection that wrote this batch's ids is at least two launches back on `main`: the update
+  // may stage them before its griddepcontrol.wait (update_kernel, `early`)
+  const int early = r->main_seq > r->sel_seq[(size_t)r->cur_ids] ? 1 : 0;
   if (prio_dev) {
     int rc = order_after_caller_(r, cs);
     if (rc != RR_OK) return rc;
   } else if (n <= rr::kInlinePrio) {
     // a learner-sized batch handed over in host memory: the priorities travel in the launch parameters
     RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, priority,
-                                     r->alpha, is_weight, r->main));
+                                     r->alpha, is_weight, early, r->main));
     dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
@@ -1534,7 +1562,8 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   }
   if (dprio != nullptr)
     RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha,
-                              is_weight, r->main));
+                              is_weight, early, r->main));
+  ++r->main_seq;
   r->launches++;
   if (prio_dev && cs != r->main) {
     RR_CUDA(cudaEventRecord(r->evOut, r->main));
@@ -1639,7 +1668,7 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
         c.chunks = f.chunks;
         cf.push_back(c);
       }
-      int rc = plan_copy(r, true, B, cf, r->hist[s], 0, &plans[(size_t)s * n_out_sets + o]);
+      int rc = plan_copy(r, streams == 2, B, cf, r->hist[s], 0, &plans[(size_t)s * n_out_sets + o]);
       if (rc != RR_OK) return rc;
     }
   }
@@ -1684,6 +1713,75 @@ int rr_gather_bench(rr_replay* r, int n_out_sets, void* const* out_fields, int r
   if (ms_per_launch) *ms_per_launch = (double)ms / (double)n;
   if (launches) *launches = n;
   if (bytes_per_launch) *bytes_per_launch = 2 * rowb * (uint64_t)B;
+  return RR_OK;
+}
+
+int rr_cycle_bench(rr_replay* r, int batch, int depth, int steps, int warmup, int n_out_sets,
+                   void* const* out_fields, float* const* out_weights, int n_prio_sets,
+                   const float* const* prio_sets, unsigned prio_flags, double* ms_per_step, uint64_t* launches) {
+  if (r == nullptr || batch <= 0 || depth < 0 || depth > 8 || steps <= 0 || warmup < 0 || n_out_sets < depth + 2 ||
+      out_fields == nullptr || out_weights == nullptr || n_prio_sets <= 0 || prio_sets == nullptr)
+    return fail(RR_ERR_ARG, "rr_cycle_bench: bad argument (needs at least depth + 2 output sets)");
+  if (r->prefetch > 0) return fail(RR_ERR_STATE, "rr_cycle_bench: the replay was created with its own prefetch");
+  if (r->cur_ids >= 0 || !r->queue.empty()) return fail(RR_ERR_STATE, "rr_cycle_bench: a batch is outstanding");
+  const size_t nf = r->fields.size();
+  cudaStream_t main = r->main;
+  uint64_t issued = 0;
+  auto issue = [&]() {
+    const size_t o = (size_t)(issued++ % (uint64_t)n_out_sets);
+    return rr_prefetch_into(r, batch, out_fields + o * nf, out_weights[o], main);
+  };
+  auto cycle = [&](uint64_t k) -> int {
+    const float* p = prio_sets[k % (uint64_t)n_prio_sets];
+    int rc;
+    if (depth == 0) {
+      const size_t o = (size_t)(k % (uint64_t)n_out_sets);
+      rc = rr_sample(r, batch, out_fields + o * nf, out_weights[o], main);
+      if (rc == RR_OK) rc = rr_update_priority(r, batch, p, prio_flags, main);
+      return rc;
+    }
+    rc = rr_take_prefetched(r, main);
+    if (rc == RR_OK) rc = rr_update_priority(r, batch, p, prio_flags, main);
+    if (rc == RR_OK) rc = issue();
+    return rc;
+  };
+  DeviceScope dev_scope(r->device);
+  for (int d = 0; d < depth; ++d) {
+    int rc = issue();
+    if (rc != RR_OK) return rc;
+  }
+  for (int k = 0; k < warmup; ++k) {
+    int rc = cycle((uint64_t)k);
+    if (rc != RR_OK) return rc;
+  }
+  RR_SYNC_STREAMS(r);
+  cudaEvent_t e0, e1;
+  RR_CUDA(cudaEventCreate(&e0));
+  RR_CUDA(cudaEventCreate(&e1));
+  const uint64_t l0 = r->launches.load();
+  RR_CUDA(cudaEventRecord(e0, main));
+  for (int k = 0; k < steps; ++k) {
+    int rc = cycle((uint64_t)(warmup + k));
+    if (rc != RR_OK) return rc;
+  }
+  {
+    std::unique_lock<std::mutex> lk(r->m_);
+    int jrc = join_gather_streams(r);  // the gathers of the batches still queued belong to the timed region
+    if (jrc != RR_OK) return jrc;
+  }
+  RR_CUDA(cudaEventRecord(e1, main));
+  RR_CUDA(cudaEventSynchronize(e1));
+  float ms = 0;
+  RR_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms_per_step) *ms_per_step = (double)ms / steps;
+  if (launches) *launches = r->launches.load() - l0;
+  for (int d = 0; d < depth; ++d) {  // hand the queue back empty
+    int rc = rr_take_prefetched(r, main);
+    if (rc == RR_OK) rc = rr_update_priority(r, batch, prio_sets[0], prio_flags, main);
+    if (rc != RR_OK) return rc;
+  }
   return RR_OK;
 }
 

@@ -255,6 +255,8 @@ __global__ void __launch_bounds__(256) exchange_kernel(const uint8_t* __restrict
                                                        const unsigned long long* wait_flags, int n_wait, int* error,
                                                        int* host_error, unsigned long long timeout_ns) {
   const int tid = threadIdx.x;
+  pdl_wait();  // `src` may come from the kernel in front of this one
+  pdl_launch_dependents();
   if (bytes > 0) {
     for (int p = 0; p < n; ++p) {
       uint8_t* dst = static_cast<uint8_t*>(peers.dst[p]);

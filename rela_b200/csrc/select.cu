@@ -141,14 +141,14 @@ __device__ __forceinline__ void refresh_range(const float* w, const Tiles& tl, i
 // for the debug cross-check): afterwards the entries are maintained by the
 // kernels that change a weight.
 __global__ void __launch_bounds__(256) build_leaves_kernel(const float* __restrict__ w, const Tiles tl) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   retile_leaf(w, tl, (int)blockIdx.x * (kBuildSpan >> kLeafLog2) + (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31));
 }
 
 __global__ void __launch_bounds__(256) build_groups_kernel(const Tiles tl) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int g = (int)blockIdx.x * 8 + (int)(threadIdx.x >> 5);
   if (g < tl.ng) regroup(tl, g, (int)(threadIdx.x & 31));
 }
@@ -197,16 +197,11 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
-// Targets d_lo .. d_hi-1 of a batch of B draws (rela/prioritized_replay.h:265-280)
-// from the mt19937 state `mt` / `mti` in shared memory: libstdc++'s
-// generate_canonical<float, 24> (one 32-bit draw, * 2^-32, clamp to
-// nextafter(1, 0)) then rand = u * segment + i * segment, clamped to sum - 0.2.
-// On return `mt` holds the state after all B draws and *mti_out its index.
-// Called by every thread of the CTA (the twist synchronises).
-__device__ void gen_targets(uint32_t* mt, int mti, int B, int d_lo, int d_hi, float sumf, int contract_fma,
-                            float* out, int* mti_out) {
-  const float segment = __fdiv_rn(sumf, (float)B);
-  const float cap = __fsub_rn(sumf, 0.2f);
+// Uniform draws d_lo .. d_hi-1 of a batch of B (rela/prioritized_replay.h:267,279) from the
+// mt19937 state `mt` / `mti` in shared memory: libstdc++'s generate_canonical<float, 24> (one
+// 32-bit draw, * 2^-32, clamp to nextafter(1, 0)). On return `mt` holds the state after all B
+// draws and *mti_out its index. Called by every thread of the CTA (the twist synchronises).
+__device__ void gen_uniforms(uint32_t* mt, int mti, int B, int d_lo, int d_hi, float* out, int* mti_out) {
   const int gen_end = (mti + B - 1) / 624;  // twists needed for the whole batch
   for (int gen = 0; gen <= gen_end; ++gen) {
     if (gen > 0) mt_twist(mt);
@@ -216,19 +211,30 @@ __device__ void gen_targets(uint32_t* mt, int mti, int B, int d_lo, int d_hi, fl
       const uint32_t y = mt_temper(mt[g % 624]);
       float u = __fmul_rn(__uint2float_rn(y), 2.3283064365386963e-10f);
       if (u >= 1.0f) u = 0.99999994f;  // nextafterf(1, 0)
-      float r;
-      if (contract_fma) {
-        r = __fmaf_rn((float)d, segment, __fmaf_rn(u, segment, 0.0f));
-      } else {
-        r = __fadd_rn(__fadd_rn(__fmul_rn(u, segment), 0.0f), __fmul_rn((float)d, segment));
-      }
-      out[d - d_lo] = (cap < r) ? cap : r;
+      out[d - d_lo] = u;
     }
     __syncthreads();
   }
   *mti_out = (mti + B - 1) % 624 + 1;
 }
 
+// Target d of the batch: rand = u * segment + d * segment (the reference binary contracts
+// `dist(rng_) + i * segment` into FMAs), clamped to sum - 0.2 (lines 265-280).
+__device__ __forceinline__ float target_of(float u, int d, float sumf, int B, int contract_fma) {
+  const float segment = __fdiv_rn(sumf, (float)B);
+  const float cap = __fsub_rn(sumf, 0.2f);
+  float r;
+  if (contract_fma) {
+    r = __fmaf_rn((float)d, segment, __fmaf_rn(u, segment, 0.0f));
+  } else {
+    r = __fadd_rn(__fadd_rn(__fmul_rn(u, segment), 0.0f), __fmul_rn((float)d, segment));
+  }
+  return (cap < r) ? cap : r;
+}
+
+}  // namespace
+
+namespace {
 
 // Raw importance weight of one selected element (rela/prioritized_replay.h:320-321):
 // weights = w / sum; weights = pow(size * weights, -beta), in float like ATen,
@@ -285,7 +291,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   double* gpre = reinterpret_cast<double*>(sm_raw);
   float* gmin = reinterpret_cast<float*>(sm_raw + (size_t)ng_pad * sizeof(double));
   __shared__ __align__(16) uint32_t mt[624];
-  __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t bar, bar_rng;
   __shared__ double red_d[kSelThreads / 32];
   __shared__ float red_f[kSelThreads / 32];
   __shared__ float s_target[kSelTargets];
@@ -306,22 +312,37 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
 
   if (tid == 0) {
     mbar_init(&bar, 1);
+    mbar_init(&bar_rng, 1);
     mbar_fence_init();
   }
-  pdl_launch_dependents();
   __syncthreads();
+  // ---- 0. the uniform draws need nothing but the RNG state, which only selections write. When
+  //         the previous selection is known to be complete (rng_early: it is at least two kernels
+  //         back on this stream and every kernel since triggers its dependents after its own wait)
+  //         they are generated BEFORE the wait, while the kernel in front is still running.
+  int mti0 = 0;
+  if (a.rng_early) {
+    if (tid == 0) {
+      mbar_expect_tx(&bar_rng, 624u * 4u);
+      bulk_g2s(mt, ctl->mt[a.rng_par], 624u * 4u, &bar_rng);
+    }
+    mti0 = ctl->mti[a.rng_par];
+    mbar_wait(&bar_rng, 0);
+    gen_uniforms(mt, mti0, a.B, i0, i0 + nT, s_target, &sh_mti);
+  }
   pdl_wait();
+  pdl_launch_dependents();  // after the wait: see `rng_early`, and `early` of update_kernel
   if (probing) ctl->probe[0] = clock64();
-  // ---- 1. group sums, group minima and the RNG state by bulk copies (TMA)
+  // ---- 1. group sums and minima (and the RNG state, if not yet) by bulk copies (TMA)
   if (tid == 0) {
-    const uint32_t b2 = (uint32_t)ng_pad * 8u, bm = (uint32_t)ng_pad * 4u, br = 624u * 4u;
+    const uint32_t b2 = (uint32_t)ng_pad * 8u, bm = (uint32_t)ng_pad * 4u, br = a.rng_early ? 0u : 624u * 4u;
     mbar_expect_tx(&bar, b2 + bm + br);
     bulk_g2s(gpre, tl.grp, b2, &bar);
     bulk_g2s(gmin, tl.grpmin, bm, &bar);
-    bulk_g2s(mt, ctl->mt[a.rng_par], br, &bar);
+    if (!a.rng_early) bulk_g2s(mt, ctl->mt[a.rng_par], br, &bar);
   }
   const double sum_d = ctl->sum;
-  const int mti0 = ctl->mti[a.rng_par];
+  if (!a.rng_early) mti0 = ctl->mti[a.rng_par];
   // mass in front of head inside head's group: the slots of head's leaf and the
   // whole leaves of head's group that precede it (for the offset O below)
   double head_part = 0.0;
@@ -348,8 +369,9 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   const double unit = ldexp(1.0, ue);
   const float sumf = (float)sum_d;
 
-  // ---- 2. this CTA's targets (needs only the RNG state and sum_)
-  gen_targets(mt, mti0, a.B, i0, i0 + nT, sumf, a.contract_fma, s_target, &sh_mti);
+  // ---- 2. this CTA's targets: uniform draws (if not yet), scaled by sum_ / B
+  if (!a.rng_early) gen_uniforms(mt, mti0, a.B, i0, i0 + nT, s_target, &sh_mti);
+  if (tid < nT) s_target[tid] = target_of(s_target[tid], i0 + tid, sumf, a.B, a.contract_fma);
   if (probing) ctl->probe[1] = clock64();
 
   // ---- 3. inclusive prefix of the group sums: contiguous chunk per thread (odd
@@ -516,7 +538,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       sh_id = 0;
     }
     __syncthreads();
-    gen_targets(mt, mti0, a.B, 0, a.B, sumf, a.contract_fma, a.israw, &sh_mti);
+    gen_uniforms(mt, mti0, a.B, 0, a.B, a.israw, &sh_mti);
+    __threadfence_block();
+    __syncthreads();
+    for (int i = tid; i < a.B; i += kSelThreads) targets[i] = target_of(targets[i], i, sumf, a.B, a.contract_fma);
     __threadfence_block();
     __syncthreads();
     const int size = a.size;
@@ -724,11 +749,26 @@ __device__ __forceinline__ float prio_at(const float* p, int i) { return p[i]; }
 __device__ __forceinline__ float prio_at(const PrioInline& p, int i) { return p.v[i]; }
 
 template <typename Prio>
-__device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
-                                            const int32_t* __restrict__ ids, int n, const Prio& prio, float alpha,
-                                            int is_weight, const Tiles& tiles, int by_group) {
+struct PrioTraits {
+  static constexpr bool kInLaunch = false;  // device memory: may be produced by the kernel in front of this one
+};
+template <>
+struct PrioTraits<PrioInline> {
+  static constexpr bool kInLaunch = true;   // part of the launch packet: readable at once
+};
+
+// `early`: the selection that wrote `ids` finished at least two kernels ago on this stream, and
+// every kernel since triggers its dependents only after its own wait -- the ids (and priorities
+// that ride in the launch) can be staged BEFORE griddepcontrol.wait, i.e. while the kernel in
+// front of this one is still running. The host sets it only when it knows (replay.cu).
+template <typename Prio>
+__global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
+                                                             const int32_t* __restrict__ ids, int n,
+                                                             const __grid_constant__ Prio prio, float alpha,
+                                                             int is_weight, const Tiles tiles, int by_group,
+                                                             int early) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
-  int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // -1 for evicted
+  int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // slot id; -1 once it is known to be evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
   float* s_diff = s_new + n;
   __shared__ double r_sum[kUpdThreads / 32], r_abs[kUpdThreads / 32];
@@ -737,25 +777,42 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kUpdThreads / 32;
+  const bool prio_early = early && PrioTraits<Prio>::kInLaunch;
+  if (early) {
+    for (int i = tid; i < n; i += kUpdThreads) {
+      s_id[i] = ids[i];
+      if (prio_early) {
+        const float p = prio_at(prio, i);
+        s_new[i] = is_weight ? p : pow_alpha(p, alpha);
+      }
+    }
+  }
+  pdl_wait();
+  // the trigger comes AFTER the wait: a kernel that starts early behind this one may rely on
+  // everything this kernel waited for being complete (see `early`, and select_kernel's rng_early)
+  pdl_launch_dependents();
+  if (!early || !prio_early) {
+    for (int i = tid; i < n; i += kUpdThreads) {
+      if (!early) s_id[i] = ids[i];
+      if (!prio_early) {
+        const float p = prio_at(prio, i);
+        s_new[i] = is_weight ? p : pow_alpha(p, alpha);
+      }
+    }
+  }
+  __syncthreads();
+
   if (blockIdx.x > 0) {
     __shared__ __align__(16) float sub[kWarps][256];
     __shared__ double s_ls[64];
     __shared__ float s_lm[64];
     __shared__ unsigned long long s_mask;
     __shared__ int s_lo, s_hi;
-    for (int i = tid; i < n; i += kUpdThreads) {
-      const int id = ids[i];
-      const float p = prio_at(prio, i);
-      const bool ev = evicted[id] != 0;
-      s_new[i] = is_weight ? p : pow_alpha(p, alpha);
-      s_id[i] = ev ? -1 : id;
-    }
     if (tid == 0) {
       s_mask = 0ull;
       s_lo = n;
       s_hi = -1;
     }
-    __syncthreads();
     const int gl = tiles.group_log2;
     const int span_log2 = kLeafLog2 + gl;
     const int c = (int)blockIdx.x - 1;
@@ -763,24 +820,22 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
     if (by_group) {
       g = c;
     } else {
-      const int id = s_id[c];
-      if (id < 0) return;  // an evicted slot keeps weight 0: nothing changes (CTA-uniform)
-      g = id >> span_log2;
+      g = s_id[c] >> span_log2;
       int dup = 0;  // an earlier element of the batch in the same group: that element's CTA covers it
-      for (int j = tid; j < c; j += kUpdThreads) {
-        const int sid = s_id[j];
-        if (sid >= 0 && (sid >> span_log2) == g) dup = 1;
-      }
+      for (int j = tid; j < c; j += kUpdThreads)
+        if ((s_id[j] >> span_log2) == g) dup = 1;
       if (__syncthreads_or(dup)) return;
     }
-    // leaves of the group that hold a batch slot (final values only: not evicted),
-    // and the index range of the batch that falls into the group
+    __syncthreads();
+    // leaves of the group that hold a batch slot and the index range of the batch that falls into
+    // the group -- from the raw ids: the eviction flags are still on their way. (A leaf that only
+    // holds evicted batch slots is re-reduced from unchanged weights: same entry, bit for bit.)
     {
       unsigned long long m = 0ull;
       int lo = n, hi = -1;
       for (int j = tid; j < n; j += kUpdThreads) {
         const int sid = s_id[j];
-        if (sid >= 0 && (sid >> span_log2) == g) {
+        if ((sid >> span_log2) == g) {
           m |= 1ull << ((sid >> kLeafLog2) & ((1 << gl) - 1));
           lo = min(lo, j);
           hi = max(hi, j);
@@ -798,18 +853,42 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
     const int jlo = s_lo, jhi = s_hi;
     const int L = 1 << gl;
     const size_t lb = (size_t)g << gl;
-    // untouched leaves keep their entries: nobody writes them during this kernel
+    // one round trip for everything that depends on the ids: the eviction flags of this group's
+    // batch slots, the weights of the touched leaves (the first one per warp), the entries of the
+    // untouched leaves (nobody writes those during this kernel)
+    float4 pre0 = make_float4(0.f, 0.f, 0.f, 0.f), pre1 = pre0;
+    int kfirst = -1;
+    for (int k = warp; k < L; k += kWarps)
+      if ((mask >> k) & 1ull) {
+        kfirst = k;
+        break;
+      }
+    if (kfirst >= 0) {
+      const float4* src = reinterpret_cast<const float4*>(w + ((lb + kfirst) << kLeafLog2)) + lane * 2;
+      pre0 = src[0];
+      pre1 = src[1];
+    }
     if (tid < L && !((mask >> tid) & 1ull)) {
       s_ls[tid] = tiles.leaf[lb + tid];
       s_lm[tid] = tiles.leafmin[lb + tid];
     }
+    for (int j = jlo + tid; j <= jhi; j += kUpdThreads) {
+      const int sid = s_id[j];
+      if ((sid >> span_log2) == g && evicted[sid] != 0) s_id[j] = -1;  // an evicted slot keeps weight 0
+    }
+    __syncthreads();
     float* mine = sub[warp];
     for (int k = warp; k < L; k += kWarps) {
       if (!((mask >> k) & 1ull)) continue;  // warp-uniform
       const int base = (int)(lb + k) << kLeafLog2;
-      const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
-      reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
-      reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
+      if (k == kfirst) {
+        reinterpret_cast<float4*>(mine)[lane * 2] = pre0;
+        reinterpret_cast<float4*>(mine)[lane * 2 + 1] = pre1;
+      } else {
+        const float4* src = reinterpret_cast<const float4*>(w + base) + lane * 2;
+        reinterpret_cast<float4*>(mine)[lane * 2] = src[0];
+        reinterpret_cast<float4*>(mine)[lane * 2 + 1] = src[1];
+      }
       __syncwarp();
       for (int j = jlo + lane; j <= jhi; j += 32) {
         const int sid = s_id[j];
@@ -843,15 +922,15 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
     }
     return;
   }
+
+  // ---- CTA 0: ConcurrentQueue::update itself
   float* s_old = s_diff;  // old weight, replaced by the difference below
   for (int i = tid; i < n; i += kUpdThreads) {
-    const int id = ids[i];
-    const float p = prio_at(prio, i);
+    const int id = s_id[i];
     const bool ev = evicted[id] != 0;  // both dependent loads are issued together
     const float old = w[id];
-    s_new[i] = is_weight ? p : pow_alpha(p, alpha);
-    s_id[i] = ev ? -1 : id;
     s_old[i] = old;
+    if (ev) s_id[i] = -1;
   }
   __syncthreads();
   double sum = 0.0, asum = 0.0;
@@ -912,16 +991,6 @@ __device__ __forceinline__ void update_body(Ctl* ctl, float* w, const uint8_t* _
   }
 }
 
-template <typename Prio>
-__global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w, const uint8_t* __restrict__ evicted,
-                                                             const int32_t* __restrict__ ids, int n,
-                                                             const __grid_constant__ Prio prio, float alpha,
-                                                             int is_weight, const Tiles tiles, int by_group) {
-  pdl_launch_dependents();
-  pdl_wait();
-  update_body<Prio>(ctl, w, evicted, ids, n, prio, alpha, is_weight, tiles, by_group);
-}
-
 // ----------------------------------------------------------------- launches
 cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cudaStream_t stream) {
   cudaError_t e = launch_pdl(build_leaves_kernel, dim3(S_pad / kBuildSpan), dim3(256), 0, stream, w, t);
@@ -952,18 +1021,19 @@ inline int update_grid(const Tiles& tiles, int n, int* by_group) {
 }  // namespace
 
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, cudaStream_t stream) {
+                          const float* prio, float alpha, int is_weight, int early, cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    prio, alpha, is_weight, tiles, by_group);
+                    prio, alpha, is_weight, tiles, by_group, early);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
-                                 int n, const float* prio_host, float alpha, int is_weight, cudaStream_t stream) {
+                                 int n, const float* prio_host, float alpha, int is_weight, int early,
+                                 cudaStream_t stream) {
   if (n > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
   memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
@@ -973,7 +1043,7 @@ cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const u
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    pin, alpha, is_weight, tiles, by_group);
+                    pin, alpha, is_weight, tiles, by_group, early);
 }
 
 }  // namespace rr

@@ -113,6 +113,17 @@ def main():
             capi.check(L.rr_take_prefetched(h, own))
             capi.check(L.rr_update_priority(h, B, C.c_void_p(prio[0].data_ptr()), capi.RR_PRIO_DEVICE, own))
 
+    # the same loops from inside the library (no ctypes per call)
+    nfl = len(schema)
+    flat_all = (C.c_void_p * (R * nfl))(*[t.data_ptr() for o in outs for t in o])
+    wsp = (C.c_void_p * R)(*[t.data_ptr() for t in ws])
+    psp = (C.c_void_p * 16)(*[prio[i].data_ptr() for i in range(16)])
+    for depth in (0, 1, 2, 3):
+        ms, nl = C.c_double(), C.c_uint64()
+        capi.check(L.rr_cycle_bench(h, B, depth, steps, 50, R, flat_all, wsp, 16, psp, capi.RR_PRIO_DEVICE,
+                                    C.byref(ms), C.byref(nl)))
+        res["c_loop_depth%d_us" % depth] = ms.value * 1e3
+
     # gather kernel alone
     capi.check(L.rr_set_profiling(h, 1, B))
     for k in range(16):
