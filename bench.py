@@ -1250,8 +1250,8 @@ def run_striped(args):
 
         def e2e_cycle(k):
             batch, w = rep.sample(B, dev_str)
-            wh = w_pinned[k & 1]
-            wh.copy_(w, non_blocking=True)
+            if w is not None:  # a learner: read the step's result back (also its sync point)
+                w_pinned[k & 1].copy_(w, non_blocking=True)
             stream.synchronize()
             rep.update_priority(prio_host[k % 16])
 

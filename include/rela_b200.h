@@ -357,6 +357,11 @@ int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host)
  * Copies min(cap, tiles) entries; returns the number of tiles (< 0: error). */
 int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums_host,
                    float* out_mins_host, int cap, int* out_tile_slots);
+/* Kernel timeline: returns (and clears) up to `cap` stamps recorded since the last call, oldest
+ * first, then switches recording on / off. A stamp is (globaltimer ns << 4 | code), written by
+ * CTA 0 of each kernel after its dependency wait and at its end; codes: 1 / 2 selection begin /
+ * end, 3 / 4 update, 5 / 6 gather. Returns the number of stamps (< 0: error). */
+int rr_debug_timeline(rr_replay* r, int enable, uint64_t* out_host, int cap);
 /* clock64 stamps at the phase boundaries of the last selection kernel (16 x u64). */
 int rr_debug_select_probe(rr_replay* r, uint64_t* out16);
 

@@ -17,7 +17,7 @@ RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
     "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
-    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_stream_fence",
+    "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_debug_timeline", "rr_stream_fence",
     "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
     "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_cycle_bench", "rr_nstep_return", "rr_td_priority",
     "rr_aggregate_priority", "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_prefetch_routed",
@@ -81,6 +81,7 @@ def lib():
         L.rr_debug_weights.argtypes = [vp, vp, vp]
         L.rr_debug_tiles.argtypes = [vp, i, i, vp, vp, i, vp]
         L.rr_debug_select_probe.argtypes = [vp, vp]
+        L.rr_debug_timeline.argtypes = [vp, i, vp, i]
         L.rr_stream_fence.argtypes = [vp, vp]
         L.rr_get_stream.argtypes = [vp, vp]
         L.rr_prefetch_into.argtypes = [vp, i, vp, vp, vp]

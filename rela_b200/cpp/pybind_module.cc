@@ -142,6 +142,10 @@ torch::Tensor aggregatePriority(const torch::Tensor& priority, const torch::Tens
 
 PYBIND11_MODULE(_C, m) {
   m.doc() = "rela_b200: B200-native prioritized replay behind rela's replay API";
+  // priority ^ alpha of a shard's slice at its position inside the collective block
+  // (ReplayCore::raiseAtPosition, sharded_core.cc); exposed for tests/test_sharded.py
+  m.def("raise_at_position", &ReplayCore::raiseAtPosition, py::arg("priority"), py::arg("offset"), py::arg("total"),
+        py::arg("alpha"));
   m.def("nstep_return", &nstepReturn, py::arg("reward"), py::arg("terminal"), py::arg("gamma"),
         py::arg("contract_fma") = true);
   m.def("td_priority", &tdPriority, py::arg("reward"), py::arg("bootstrap"), py::arg("q_next"), py::arg("q_sa"),

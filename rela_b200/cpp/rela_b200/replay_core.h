@@ -125,6 +125,9 @@ class ReplayCore {
   int device() const { return device_; }
   const std::vector<LeafSpec>& schema() const { return schema_; }
   struct Sharded;  // state of the striped-replay protocol (sharded_core.cc)
+  // priority ^ alpha for `p` = elements [offset, offset + n) of a block of `total` priorities that
+  // ONE replay would raise with a single torch::pow: bit-identical to that call's slice
+  static torch::Tensor raiseAtPosition(const torch::Tensor& p, int64_t offset, int64_t total, float alpha);
   int shardRank() const { return shard_.rank; }
   int shardWorld() const { return shard_.world; }
 
@@ -155,7 +158,6 @@ class ReplayCore {
   void shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w, unsigned flags);
   std::pair<Leaves, torch::Tensor> shardedSample(int batchsize, const std::string& device);
   void shardedUpdate(const torch::Tensor& w, unsigned flags);
-  torch::Tensor raisedForShards(const torch::Tensor& p, int64_t offset, int64_t total) const;
 
   rr_replay* h_ = nullptr;
   int device_ = 0;

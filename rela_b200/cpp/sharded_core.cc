@@ -241,18 +241,18 @@ const float* stageHost(ReplayCore::Sharded& sh, const float* host, size_t n) {
 // and the two can differ in the last bit. ONE reference replay raises the whole collective
 // block at once, so this rank raises its `n` values AT THEIR POSITION `offset` inside a block
 // of `total` (the other positions hold 1): bit-identical weights whatever the vector width.
-torch::Tensor ReplayCore::raisedForShards(const torch::Tensor& p, int64_t offset, int64_t total) const {
-  if (alpha_ == 1.0f) return p;
-  if (p.is_cuda()) return torch::pow(p, alpha_);
+torch::Tensor ReplayCore::raiseAtPosition(const torch::Tensor& p, int64_t offset, int64_t total, float alpha) {
+  if (alpha == 1.0f) return p;
+  if (p.is_cuda()) return torch::pow(p, alpha);
   torch::Tensor full = torch::ones({total}, torch::kFloat32);
   full.narrow(0, offset, p.size(0)).copy_(p);
-  return torch::pow(full, alpha_).narrow(0, offset, p.size(0)).contiguous();
+  return torch::pow(full, alpha).narrow(0, offset, p.size(0)).contiguous();
 }
 
 void ReplayCore::shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tensor& w_in, unsigned /*flags*/) {
   Sharded& sh = *sharded_;
   const int64_t n = w_in.size(0);
-  const torch::Tensor w = raisedForShards(w_in, sh.rank * n, n * sh.world);
+  const torch::Tensor w = raiseAtPosition(w_in, sh.rank * n, n * sh.world, alpha_);
   const int64_t n_total = n * sh.world;
   if ((size_t)n_total > kInboxFloats)
     throw std::runtime_error("add: a collective block of " + std::to_string(n_total) + " rows exceeds " +
@@ -281,7 +281,7 @@ void ReplayCore::shardedAdd(std::vector<torch::Tensor>& rows, const torch::Tenso
   check(rr_add_sharded_commit(h_, all, RR_PRIO_IS_WEIGHT), "add");
   // `rows` (and a device `w`) are released when this returns: later work on the caller's stream
   // must not reuse their memory before the insert has read it
-  check(rr_stream_fence(h_, cs), "add");
+  if (cs != sh.main) check(rr_stream_fence(h_, cs), "add");
 }
 
 namespace {
@@ -415,7 +415,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
     if (w_in.size(0) != sh.cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
       throw std::runtime_error("update_priority: " + std::to_string(w_in.size(0)) + " priorities for a batch of " +
                                std::to_string(sh.cur_B));
-    w = raisedForShards(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners);
+    w = raiseAtPosition(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners, alpha_);
     if (w.is_cuda()) {
       mine = w.data_ptr<float>();
       xs = cs;
@@ -427,7 +427,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   check(rr_update_priority(h_, (int)(n * (size_t)sh.n_learners), all, RR_PRIO_DEVICE | RR_PRIO_IS_WEIGHT, sh.main),
         "update_priority");
   sh.cur_B = 0;
-  if (w.defined() && w.is_cuda()) check(rr_stream_fence(h_, cs), "update_priority");
+  if (w.defined() && w.is_cuda() && cs != sh.main) check(rr_stream_fence(h_, cs), "update_priority");
 }
 
 }  // namespace rela_b200

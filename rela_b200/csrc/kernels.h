@@ -12,6 +12,7 @@ namespace rr {
 //                layout [T, B, chunk] (reference rela/types.cc:8-46,140-182)
 //   INSERT (K1): src row = producer batch row b, dst = slab[(start + b) % S]
 //                (reference rela/prioritized_replay.h:61-66)
+struct Ctl;
 constexpr int kMaxCopyFields = 24;
 constexpr int kMaxPeers = 8;       // GPUs of one NVSwitch box
 
@@ -71,6 +72,7 @@ struct CopyParams {
   const unsigned long long* norm_max;
   float* norm_out;
   int norm_n;
+  struct Ctl* tl_ctl;  // debug timeline (Ctl::tl), gathers only; may be null
 };
 
 // shared-memory header of row_copy_kernel: barriers + per-stage piece records
@@ -113,6 +115,7 @@ constexpr int kSelThreads = 256;
 constexpr int kSelTargets = 8;     // targets per CTA of select_kernel: one per warp
 constexpr int kInlinePrio = 1024;  // largest update whose priorities travel as kernel parameters
 constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
+constexpr int kTimelineCap = 1024;
 
 // Device-resident control block: ConcurrentQueue::sum_ and the mt19937 of
 // PrioritizedReplay (reference rela/prioritized_replay.h:166,343). The RNG
@@ -130,7 +133,15 @@ struct Ctl {
   unsigned long long n_ordered;    // samples that needed the ordered walk
   unsigned long long n_popped;
   unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel (CTA 0)
+  // Debug timeline (rr_debug_timeline): while tl_on != 0, CTA 0 of every selection, update and
+  // gather kernel stamps (globaltimer_ns << 4 | code) at its start (after its wait) and end.
+  unsigned int tl_on, tl_n;
+  unsigned long long tl_umax, tl_gmax;  // latest end of any CTA of the last update / gather kernel
+  unsigned long long tl[kTimelineCap];
 };
+
+// codes of Ctl::tl entries
+enum { kTlSelectBegin = 1, kTlSelectEnd = 2, kTlUpdateBegin = 3, kTlUpdateEnd = 4, kTlGatherBegin = 5, kTlGatherEnd = 6, kTlUpdateAllEnd = 7, kTlGatherAllEnd = 8 };
 
 // ------------------------------------------------- gather with conversion
 // A u8 field gathered as float32 / bfloat16 = byte / 255 (gather_convert.cu).

@@ -54,6 +54,23 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
       : "memory");
 }
 
+// Same with an L2 cache policy (createpolicy): the gather's source rows are read once, so they
+// are marked evict-first and do not push the control state out of L2.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+
+__device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar,
+                                              uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
 // shared -> global bulk copy, tracked by the thread's bulk async-group.
 __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
@@ -107,6 +124,15 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+
+// Debug timeline stamp (Ctl::tl in kernels.h): one thread per kernel event.
+#define RR_TL_STAMP(ctl, code)                                                                       \
+  do {                                                                                               \
+    if ((ctl) != nullptr && *reinterpret_cast<volatile unsigned int*>(&(ctl)->tl_on) != 0u) {       \
+      const unsigned int i_ = atomicAdd(&(ctl)->tl_n, 1u) % (unsigned int)kTimelineCap;              \
+      (ctl)->tl[i_] = (globaltimer_ns() << 4) | (unsigned long long)(code);                          \
+    }                                                                                                \
+  } while (0)
 
 // Host: opt a kernel in to `bytes` of dynamic shared memory. The attribute is
 // per device (context), and several host threads may launch at once, so the

@@ -156,6 +156,8 @@ struct rr_replay {
   uint64_t slab_bytes = 0;
 
   // device state
+  uint8_t* control = nullptr;  // one allocation holding the six arrays below (rr_create)
+  size_t control_bytes = 0;
   float* w = nullptr;
   uint8_t* evicted = nullptr;
   double* leaf = nullptr;  // rr::Tiles: leaf (256-slot) and group sums / minima
@@ -276,7 +278,15 @@ int new_idslot(rr_replay* r) {
 // The batch of id slot `slot` becomes visible to the caller's stream `cs`.
 int publish_batch(rr_replay* r, cudaStream_t cs, int slot) {
   if (slot >= 0 && r->slotPending[(size_t)slot]) {
-    // its gather ran on a gather stream: evSlot covers it and, through evSel, its selection
+    // its gather ran on a gather stream: evSlot covers it and, through evSel, its selection. A
+    // batch drawn two samples ago has usually been gathered by now: then nothing is queued (a
+    // wait in front of the update would break its programmatic launch chain for nothing).
+    const cudaError_t q = cudaEventQuery(r->evSlot[(size_t)slot]);
+    if (q == cudaSuccess) {
+      r->slotPending[(size_t)slot] = false;
+      return RR_OK;
+    }
+    if (q != cudaErrorNotReady) RR_CUDA(q);
     RR_CUDA(cudaStreamWaitEvent(cs, r->evSlot[(size_t)slot], 0));
     if (cs == r->main) r->slotPending[(size_t)slot] = false;
     return RR_OK;
@@ -463,25 +473,56 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   RR_CUDA(cudaGetDeviceProperties(&prop, device));
   r->sm_count = prop.multiProcessorCount;
 
-  // The control plane gets the highest stream priority, the gather streams the lowest: a gather
-  // whose CTAs are still waiting for shared memory (its predecessor on the other gather stream
-  // holds it) must not keep the small selection / update kernels behind it from being placed.
-  int prio_lo = 0, prio_hi = 0;
-  RR_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-  RR_CUDA(cudaStreamCreateWithPriority(&r->main, cudaStreamNonBlocking, prio_hi));
+  // (Stream priorities -- control plane high, gather streams low -- and shared-memory carve-out
+  // preferences were measured and dropped: no effect / up to 3.6 us slower per pipelined cycle,
+  // profiles/README.md captures r2e and r2l.)
+  RR_CUDA(cudaStreamCreateWithFlags(&r->main, cudaStreamNonBlocking));
   RR_CUDA(cudaEventCreateWithFlags(&r->evIn, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evOut, cudaEventDisableTiming));
-  for (cudaStream_t& g : r->gs) RR_CUDA(cudaStreamCreateWithPriority(&g, cudaStreamNonBlocking, prio_lo));
+  for (cudaStream_t& g : r->gs) RR_CUDA(cudaStreamCreateWithFlags(&g, cudaStreamNonBlocking));
   RR_CUDA(cudaEventCreateWithFlags(&r->evSel, cudaEventDisableTiming));
   RR_CUDA(cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming));
 
   const size_t ng_pad = ((size_t)r->ng + 3) & ~(size_t)3;  // padded: bulk copies move 16-byte units
-  RR_CUDA(cudaMalloc(&r->w, sizeof(float) * (size_t)r->S_pad));
-  RR_CUDA(cudaMalloc(&r->evicted, (size_t)r->S_pad));
-  RR_CUDA(cudaMalloc(&r->leaf, sizeof(double) * ((size_t)r->S_pad >> rr::kLeafLog2)));
-  RR_CUDA(cudaMalloc(&r->leafmin, sizeof(float) * ((size_t)r->S_pad >> rr::kLeafLog2)));
-  RR_CUDA(cudaMalloc(&r->grp, sizeof(double) * ng_pad));
-  RR_CUDA(cudaMalloc(&r->grpmin, sizeof(float) * ng_pad));
+  {
+    // The control state lives in ONE allocation: weights | eviction flags | leaf sums | leaf minima |
+    // group sums | group minima (5.3 B per slot, 13.3 MB at 2^21 transitions). The selection and
+    // update kernels are chains of dependent reads of it; the gathers stream ~58 MB per batch
+    // through the same L2 and would keep evicting it, so the internal stream asks L2 to keep this
+    // window resident (persisting access policy; the gather's reads are marked evict-first).
+    const size_t nleaf = (size_t)r->S_pad >> rr::kLeafLog2;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_w = 0, o_ev = up(o_w + sizeof(float) * (size_t)r->S_pad), o_leaf = up(o_ev + (size_t)r->S_pad),
+                 o_lmin = up(o_leaf + sizeof(double) * nleaf), o_grp = up(o_lmin + sizeof(float) * nleaf),
+                 o_gmin = up(o_grp + sizeof(double) * ng_pad), total = up(o_gmin + sizeof(float) * ng_pad);
+    RR_CUDA(cudaMalloc(&r->control, total));
+    r->control_bytes = total;
+    r->w = reinterpret_cast<float*>(r->control + o_w);
+    r->evicted = r->control + o_ev;
+    r->leaf = reinterpret_cast<double*>(r->control + o_leaf);
+    r->leafmin = reinterpret_cast<float*>(r->control + o_lmin);
+    r->grp = reinterpret_cast<double*>(r->control + o_grp);
+    r->grpmin = reinterpret_cast<float*>(r->control + o_gmin);
+    {
+      cudaDeviceProp pr;
+      RR_CUDA(cudaGetDeviceProperties(&pr, device));
+      const size_t window = std::min(total, (size_t)std::max(pr.accessPolicyMaxWindowSize, 0));
+      const size_t carve = std::min(window, (size_t)std::max(pr.persistingL2CacheMaxSize, 0));
+      if (window > 0 && carve > 0) {
+        size_t cur = 0;
+        RR_CUDA(cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize));
+        if (cur < carve) RR_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+        cudaStreamAttrValue av;
+        memset(&av, 0, sizeof(av));
+        av.accessPolicyWindow.base_ptr = r->control;
+        av.accessPolicyWindow.num_bytes = window;
+        av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)window);
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        RR_CUDA(cudaStreamSetAttribute(r->main, cudaStreamAttributeAccessPolicyWindow, &av));
+      }
+    }
+  }
   RR_CUDA(cudaMalloc(&r->ctl, sizeof(rr::Ctl)));
   RR_CUDA(cudaHostAlloc(&r->host_err, sizeof(int), cudaHostAllocMapped));
   *r->host_err = 0;
@@ -525,12 +566,7 @@ int rr_destroy(rr_replay* r) {
   DeviceScope dev_scope(r->device);
   cudaDeviceSynchronize();
   for (auto& f : r->fields) cudaFree(f.slab);
-  cudaFree(r->w);
-  cudaFree(r->evicted);
-  cudaFree(r->leaf);
-  cudaFree(r->leafmin);
-  cudaFree(r->grp);
-  cudaFree(r->grpmin);
+  cudaFree(r->control);
   cudaFree(r->ctl);
   if (r->host_err) cudaFreeHost(r->host_err);
   for (auto& l : r->lanes) {
@@ -1156,7 +1192,11 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   a.host_err = r->host_err_dev;
   if (r->slotPending[(size_t)idslot]) {
     // the previous gather out of this id buffer (gather stream) must be done reading it
-    RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)idslot], 0));
+    const cudaError_t q = cudaEventQuery(r->evSlot[(size_t)idslot]);
+    if (q != cudaSuccess) {
+      if (q != cudaErrorNotReady) RR_CUDA(q);
+      RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)idslot], 0));
+    }
     r->slotPending[(size_t)idslot] = false;
   }
   RR_CUDA(rr::launch_select(a, r->main));
@@ -1213,6 +1253,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     for (int i = 0; i < route->n_signals; ++i) plan.p.signal[i] = route->signals[i];
     plan.p.signal_val = r->epoch;  // the same on every shard: all shards run all selections
   }
+  plan.p.tl_ctl = r->ctl;
   if (rc == RR_OK && out_w != nullptr) {
     const int l = route ? route->my_learner : 0;
     if (l >= 0) {
@@ -1832,6 +1873,23 @@ int rr_debug_select_probe(rr_replay* r, uint64_t* out16) {
   RR_SYNC_STREAMS(r);
   RR_CUDA(cudaMemcpy(out16, r->ctl->probe, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
   return RR_OK;
+}
+
+int rr_debug_timeline(rr_replay* r, int enable, uint64_t* out, int cap) {
+  if (r == nullptr) return fail(RR_ERR_ARG, "rr_debug_timeline: null");
+  DeviceScope dev_scope(r->device);
+  RR_SYNC_STREAMS(r);
+  rr::Ctl* h = new rr::Ctl();
+  RR_CUDA(cudaMemcpy(h, r->ctl, sizeof(*h), cudaMemcpyDeviceToHost));
+  const int n = (int)std::min<unsigned int>(h->tl_n, (unsigned int)rr::kTimelineCap);
+  const int m = std::min(n, cap);
+  // oldest first: when the ring has wrapped, entry tl_n % cap is the oldest
+  const unsigned int first = h->tl_n > (unsigned int)rr::kTimelineCap ? h->tl_n % rr::kTimelineCap : 0u;
+  for (int i = 0; i < m && out != nullptr; ++i) out[i] = h->tl[(first + (unsigned int)(n - m) + (unsigned int)i) % rr::kTimelineCap];
+  delete h;
+  const unsigned int vals[2] = {enable ? 1u : 0u, 0u};
+  RR_CUDA(cudaMemcpy(&r->ctl->tl_on, vals, sizeof(vals), cudaMemcpyHostToDevice));
+  return m;
 }
 
 int rr_debug_weights(rr_replay* r, float* out_w, uint8_t* out_evicted) {

@@ -148,7 +148,9 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     pdl_wait();
     pdl_launch_dependents();
     if (probe && tid == 0) probe[2] = clock64();
+    if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP(p.tl_ctl, kTlGatherBegin);
     if (active) {
+      const uint64_t evict_first = l2_policy_evict_first();  // a gather reads every source row once
       uint32_t use = 0;
       for (uint32_t j = (uint32_t)tid; j < mine; j += NS) {
         if (j != (uint32_t)tid) it = decode_item(p, first + j * step);
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
         const uint8_t* src = row_src(p, *it.f, it.b, it.t, it.off, local);
         if (p.ids == nullptr) it.dst = row_dst(p, *it.f, it.b, it.t, it.off, local);
         mbar_expect_tx(bar, it.bytes);
-        bulk_g2s(stage, src, it.bytes, bar);
+        if (p.ids != nullptr) bulk_g2s_hint(stage, src, it.bytes, bar, evict_first); else bulk_g2s(stage, src, it.bytes, bar);
         if (probe && tid == 0 && use == 0) probe[3] = clock64();
         mbar_wait(bar, use & 1u);
         if (probe && tid == 0 && use == 0) probe[4] = clock64();
@@ -171,6 +173,10 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       // exits; kernel completion makes them visible. With a completion signal
       // they must be complete before the flag is published.
       if (p.n_signals > 0) bulk_wait_all<0>(); else bulk_wait_read<0>();
+      if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP(p.tl_ctl, kTlGatherEnd);
+      if (tid == 0 && p.ids != nullptr && p.tl_ctl != nullptr &&
+          *reinterpret_cast<volatile unsigned int*>(&p.tl_ctl->tl_on) != 0u)
+        atomicMax(&p.tl_ctl->tl_gmax, globaltimer_ns());
       if (probe && tid == 0) {
         probe[6] = clock64();
         probe[7] = globaltimer_ns();

@@ -332,7 +332,15 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   pdl_wait();
   pdl_launch_dependents();  // after the wait: see `rng_early`, and `early` of update_kernel
-  if (probing) ctl->probe[0] = clock64();
+  if (probing) {
+    ctl->probe[0] = clock64();
+    RR_TL_STAMP(ctl, kTlSelectBegin);
+    if (*reinterpret_cast<volatile unsigned int*>(&ctl->tl_on) != 0u) {
+      const unsigned long long um = atomicExch(&ctl->tl_umax, 0ull), gm = atomicExch(&ctl->tl_gmax, 0ull);
+      if (um) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (um << 4) | kTlUpdateAllEnd;
+      if (gm) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (gm << 4) | kTlGatherAllEnd;
+    }
+  }
   // ---- 1. group sums and minima (and the RNG state, if not yet) by bulk copies (TMA)
   if (tid == 0) {
     const uint32_t b2 = (uint32_t)ng_pad * 8u, bm = (uint32_t)ng_pad * 4u, br = a.rng_early ? 0u : 624u * 4u;
@@ -601,7 +609,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
       publish_max(a.ismax, a.epoch, v);
     }
   }
-  if (probing) ctl->probe[4] = clock64();
+  if (probing) {
+    ctl->probe[4] = clock64();
+    RR_TL_STAMP(ctl, kTlSelectEnd);
+  }
 
   // ---- 7. RNG state after the B draws and the counters: CTA 0 (every CTA ran
   //         the same twists, so every CTA holds the successor state)
@@ -767,6 +778,13 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
                                                              const __grid_constant__ Prio prio, float alpha,
                                                              int is_weight, const Tiles tiles, int by_group,
                                                              int early) {
+  struct EndStamp {  // debug timeline: the latest end of any CTA of this kernel
+    Ctl* c;
+    __device__ ~EndStamp() {
+      if (threadIdx.x == 0 && *reinterpret_cast<volatile unsigned int*>(&c->tl_on) != 0u)
+        atomicMax(&c->tl_umax, globaltimer_ns());
+    }
+  } end_stamp{ctl};
   extern __shared__ __align__(128) uint8_t sm_raw[];
   int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // slot id; -1 once it is known to be evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
@@ -791,6 +809,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
   // the trigger comes AFTER the wait: a kernel that starts early behind this one may rely on
   // everything this kernel waited for being complete (see `early`, and select_kernel's rng_early)
   pdl_launch_dependents();
+  if (blockIdx.x == 0 && tid == 0) RR_TL_STAMP(ctl, kTlUpdateBegin);
   if (!early || !prio_early) {
     for (int i = tid; i < n; i += kUpdThreads) {
       if (!early) s_id[i] = ids[i];
@@ -989,6 +1008,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     for (int i = 0; i < n; ++i) diff += (double)s_diff[i];  // evicted entries hold +0.0f
     ctl->sum += diff;
   }
+  if (tid == 0) RR_TL_STAMP(ctl, kTlUpdateEnd);
 }
 
 // ----------------------------------------------------------------- launches

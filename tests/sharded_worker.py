@@ -1,4 +1,4 @@
-"""Worker of the striped-replay tests: one process per rank, several ranks may share one GPU.
+"""Worker of the striped-replay tests: one process per rank, one GPU per rank.
 
   RANK=r WORLD_SIZE=N python tests/sharded_worker.py --group NAME [--learner -1|r] [--prefetch P] ...
 
@@ -57,7 +57,8 @@ def main():
     from rela_b200 import _C, capi
 
     ndev = torch.cuda.device_count()
-    dev_index = rank % ndev
+    assert ndev >= world, "one GPU per rank: the shards' kernels wait on each other's flags"
+    dev_index = rank
     torch.cuda.set_device(dev_index)
     dev = torch.device("cuda", dev_index)
     schema = ff_schema() if a.full_frames else ff_schema(frame=(2, 12, 12), n_actions=5)

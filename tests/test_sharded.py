@@ -2,12 +2,14 @@
 single-buffer oracle bit for bit.
 
 CPU: the rendezvous the shards set themselves up with (rr_group_*: shared memory, several
-processes, stale segments) and the shard ranges.
-GPU: the real thing through the C++ host layer (rela_b200/cpp/sharded_core.cc). The ranks are
-plain processes; with fewer GPUs than ranks several ranks share a device (peer memory is then
-the same device's memory, mapped through CUDA IPC), so the whole protocol -- routed gathers
-into the learners' batch tensors, completion flags, the all-gather of priorities, the
-owner-routed inserts -- runs and is compared byte for byte on a ONE-GPU box too."""
+processes, stale segments), and the position-aware priority ^ alpha of the host layer.
+GPU: the real thing through the C++ host layer (rela_b200/cpp/sharded_core.cc), one process per
+rank, ONE GPU PER RANK: the shards' kernels wait for each other's flags, and kernels that wait
+on one another must not share a GPU (nothing guarantees that they run at the same time; ranks
+sharing one B200 as processes have raised Xid 109 context-switch timeouts, B200_PROFILING.md).
+So these tests need as many GPUs as ranks (`gpurun --gpus 2/4`) and are skipped on a smaller
+box; on the driver's boxes the same comparison -- ids, bytes and weights of every rank against
+ONE oracle -- runs inside `bench.py --gpus N` before anything is timed (`parity` in its line)."""
 import ctypes as C
 import multiprocessing as mp
 import os
@@ -92,7 +94,13 @@ def test_group_argument_errors():
     L.rr_group_destroy(g)
 
 
+def _need_gpus(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs: one per rank (gpurun --gpus %d)" % (world, world))
+
+
 def _run(world, extra=(), timeout=600):
+    _need_gpus(world)
     group = "test%d_%d" % (os.getpid(), abs(hash(extra)) % 100000)
     procs = []
     for r in range(world):
@@ -111,6 +119,30 @@ def _run(world, extra=(), timeout=600):
     for r, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, "rank %d:\n%s" % (r, out[-4000:])
         assert "SHARDED_OK rank=%d world=%d" % (r, world) in out, out[-2000:]
+
+
+def test_priorities_are_raised_at_their_position_in_the_block():
+    """ATen's CPU pow sends the vectorised body of a tensor through Sleef and its tail through
+    libm: the two differ in the last bit for ~1 element in 4. ONE reference replay raises a whole
+    collective block at once, so a shard must raise its slice at its position inside the block."""
+    from rela_b200 import _C
+
+    import numpy as np
+
+    g = torch.Generator().manual_seed(0)
+    differs = 0
+    alpha = float(np.float32(0.6))  # the reference's alpha_ is a float (prioritized_replay.h:330)
+    for total, world in ((36, 3), (24, 2), (4096, 8), (100, 4), (48, 4)):
+        n = total // world
+        x = torch.rand(total, generator=g) + 0.01
+        full = torch.pow(x, alpha)
+        for r in range(world):
+            mine = x[r * n:(r + 1) * n].contiguous()
+            got = _C.raise_at_position(mine, r * n, total, 0.6)
+            assert torch.equal(got, full[r * n:(r + 1) * n]), (total, world, r)
+            differs += int((torch.pow(mine, alpha) != full[r * n:(r + 1) * n]).sum())
+        assert torch.equal(_C.raise_at_position(x, 0, total, 1.0), x)  # alpha == 1: the identity, like ATen
+    assert differs > 0, "the naive slice-wise pow was expected to differ somewhere (else this test is vacuous)"
 
 
 @pytest.mark.gpu

@@ -123,6 +123,10 @@ def main():
         capi.check(L.rr_cycle_bench(h, B, depth, steps, 50, R, flat_all, wsp, 16, psp, capi.RR_PRIO_DEVICE,
                                     C.byref(ms), C.byref(nl)))
         res["c_loop_depth%d_us" % depth] = ms.value * 1e3
+        if depth == 2:  # phases of the last selection that ran beside a gather
+            capi.check(L.rr_debug_select_probe(h, pr.ctypes.data))
+            d = np.diff(pr[:5].astype(np.int64))
+            res["select_phases_pipelined_us"] = [round(float(v) / 1.9e3, 2) for v in d]
 
     # gather kernel alone
     capi.check(L.rr_set_profiling(h, 1, B))
