@@ -1338,6 +1338,11 @@ def run_striped(args):
                              "the same bytes at a fraction of its peak",
                      "linear_cap": {"n_times_nvlink_ingress_cap": nvlink_cap_rate,
                                     "value_frac_of_cap": value / nvlink_cap_rate},
+                     "bounded_by": ("NVLink ingress (>= 2/3 of the 900 GB/s port)" if ingress(value) / 900.0 >= 0.66 else
+                                    "the control plane's latency chain: selection + update of %d targets and the two "
+                                    "flag exchanges per step run back to back on every shard (%.0f us per step), "
+                                    "the NVLink port is at %.0f %%" % (Bg, best_v["value_ms"] * 1e3,
+                                                                       100 * ingress(value) / 900.0)),
                      "hbm_peak": peak, "hbm_peak_source": peak_src},
         "single_learner": {"value": tps(single["value_ms"], B), "e2e": tps(single["e2e_ms"], B), "unit": "transitions/s",
                            "ms_per_step": single["value_ms"], "prefetch": 2, "batch": B,

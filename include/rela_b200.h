@@ -200,11 +200,23 @@ typedef struct rr_route {
 /* rr_prefetch_into for a shard of a striped replay: select batch_total ids
  * (identically on every shard), gather the rows this shard owns to their
  * learners, queue the batch. rr_take_prefetched then makes it current and, on a
- * learner, appends a one-warp kernel to `stream` that acquires the wait_n
- * flags: the batch is complete, in stream order, when that kernel is. Every
- * rank passes wait_flags (rr_add_sharded_rows waits on them before it reuses
- * slots a queued gather may still read); only learners wait when they take. */
+ * learner, orders the batch on `stream`: a learner's gather kernel ends by
+ * acquiring the wait_n flags itself, so the batch is complete when that kernel
+ * is. Every rank passes wait_flags (rr_add_sharded_rows waits on them before it
+ * reuses slots a queued gather may still read). */
 int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* route, void* stream);
+
+/* update_priority on a striped replay: every rank applies the priorities of ALL learners, which
+ * the update kernel itself all-gathers through peer memory. This rank contributes n_mine values
+ * (priority_mine: host memory, or device memory with RR_PRIO_DEVICE) for elements [offset, offset +
+ * n_mine) of the batch of n_total; inbox_ptrs[i] / flag_ptrs[i]: rank i's inbox data and this rank's
+ * flag in it (peer-mapped, n_dst = world, this rank included); my_inbox: this rank's own inbox
+ * data (n_total floats once wait_flags[0..n_wait), one flag per learner, have reached `epoch`).
+ * A rank that is no learner passes n_mine == 0 and only waits. All ranks pass the same `flags`. */
+int rr_update_priority_sharded(rr_replay* r, int n_total, const float* priority_mine, int n_mine, int offset,
+                               unsigned flags, void* const* inbox_ptrs, void* const* flag_ptrs, int n_dst,
+                               uint64_t epoch, const void* wait_flags, int n_wait, const float* my_inbox,
+                               void* stream);
 
 /* Collective add into a striped replay. Step 1 reserves the block of n_total
  * slots (identically on every shard) and moves THIS rank's rows -- rows

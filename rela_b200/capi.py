@@ -16,7 +16,7 @@ RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
 
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
-    "rr_update_priority", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
+    "rr_update_priority", "rr_update_priority_sharded", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_debug_timeline", "rr_stream_fence",
     "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
     "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_cycle_bench", "rr_nstep_return", "rr_td_priority",
@@ -72,6 +72,7 @@ def lib():
         L.rr_add_rows.argtypes = [vp, i, vp, vp, u, vp]
         L.rr_sample.argtypes = [vp, i, vp, vp, vp]
         L.rr_update_priority.argtypes = [vp, i, vp, u, vp]
+        L.rr_update_priority_sharded.argtypes = [vp, i, vp, i, i, u, vp, vp, i, C.c_uint64, vp, i, vp, vp]
         L.rr_size.argtypes = [vp]
         L.rr_num_add.argtypes = [vp]
         L.rr_sync.argtypes = [vp]

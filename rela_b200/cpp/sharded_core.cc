@@ -406,25 +406,48 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   if (sh.cur_B == 0) throw std::runtime_error("update_priority: no sampled batch is outstanding");
   c10::cuda::CUDAGuard guard((c10::DeviceIndex)device_);
   void* cs = streamOf(device_);
-  const float* mine = nullptr;
-  void* xs = sh.main;
   const size_t n = (size_t)sh.cur_B;
+  const size_t total = n * (size_t)sh.n_learners;
+  if (total > kInboxFloats) throw std::runtime_error("update_priority: batch too large for the peer inbox");
   torch::Tensor w;
+  unsigned f = RR_PRIO_IS_WEIGHT;
+  void* xs = sh.main;
   if (sh.my_learner >= 0) {
     // every learner passes the priorities of ITS rows (the other ranks' argument is ignored)
     if (w_in.size(0) != sh.cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
       throw std::runtime_error("update_priority: " + std::to_string(w_in.size(0)) + " priorities for a batch of " +
                                std::to_string(sh.cur_B));
-    w = raiseAtPosition(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners, alpha_);
-    if (w.is_cuda()) {
-      mine = w.data_ptr<float>();
+    if (w_in.is_cuda() && sh.learner < 0) {
+      // every rank is a learner and sees what kind of tensor it was given (all learners must pass
+      // the same kind): device priorities stay raw and are raised by the update kernel
+      w = w_in;
+      f = RR_PRIO_DEVICE;
       xs = cs;
     } else {
-      mine = stageHost(sh, w.data_ptr<float>(), n);
+      w = raiseAtPosition(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners, alpha_);
+      if (w.is_cuda()) {
+        f |= RR_PRIO_DEVICE;
+        xs = cs;
+      }
     }
   }
-  const float* all = exchange(sh, h_, mine, sh.my_learner >= 0 ? n : 0, (size_t)std::max(sh.my_learner, 0) * n, xs);
-  check(rr_update_priority(h_, (int)(n * (size_t)sh.n_learners), all, RR_PRIO_DEVICE | RR_PRIO_IS_WEIGHT, sh.main),
+  // the update kernel all-gathers the learners' priorities itself (ExchangeArgs): every rank
+  // publishes its flag, contribution or not, so a returned wait also means that every rank has
+  // consumed the previous block of this parity and issued everything ordered before its flag
+  const uint64_t x = ++sh.xseq;
+  const size_t par = (size_t)(x & 1);
+  const size_t data_off = kInboxHeader + par * kInboxFloats * sizeof(float);
+  void* dst[8];
+  void* flg[8];
+  for (int r = 0; r < sh.world; ++r) {
+    dst[r] = sh.inbox[(size_t)r] + data_off;
+    flg[r] = sh.inbox[(size_t)r] + (par * 16 + (size_t)sh.rank) * 8;
+  }
+  uint8_t* mine = sh.inbox[(size_t)sh.rank];
+  const bool learner = sh.my_learner >= 0;
+  check(rr_update_priority_sharded(h_, (int)total, learner ? w.data_ptr<float>() : nullptr, learner ? (int)n : 0,
+                                   learner ? (int)((size_t)sh.my_learner * n) : 0, f, dst, flg, sh.world, x,
+                                   mine + par * 16 * 8, sh.world, reinterpret_cast<const float*>(mine + data_off), xs),
         "update_priority");
   sh.cur_B = 0;
   if (w.defined() && w.is_cuda() && cs != sh.main) check(rr_stream_fence(h_, cs), "update_priority");

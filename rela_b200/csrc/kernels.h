@@ -66,6 +66,13 @@ struct CopyParams {
   unsigned long long* signal[kMaxPeers];
   int n_signals;
   unsigned long long signal_val;
+  // ... and, on a rank that consumes the batch, then acquires until wait_flags[0..wait_n) (its own
+  // memory: one flag per shard) have all reached signal_val: the kernel is complete when the
+  // BATCH is, no separate wait kernel (timeout -> *wait_error / *wait_host_error = RR_ERR_CUDA).
+  const unsigned long long* wait_flags;
+  int wait_n;
+  int* wait_error;
+  int* wait_host_error;
   // Importance weights (select.cu, SelectArgs::israw): out[i] = raw[i] / max for
   // i < norm_n, by the narrow-field warps (rela/prioritized_replay.h:322).
   const float* norm_raw;
@@ -207,14 +214,33 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
 cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int start, int n, const float* prio,
                           float alpha, int is_weight, cudaStream_t stream);
 
+// The all-gather of new priorities between the shards of a striped replay, fused into the update
+// kernel: CTA 0 stores this rank's n_mine values (the kernel's `prio` argument) at [offset,
+// offset + n_mine) of every rank's inbox (dst[i], its own included), publishes `epoch` at its flag
+// in each of them (st.release.sys); every CTA then acquires until the n_wait contributors' flags
+// in THIS rank's inbox have reached `epoch` and reads all n priorities from `inbox`.
+struct ExchangeArgs {
+  int on;                        // 0: no exchange, `prio` holds all n priorities
+  int n_mine;
+  float* dst[kMaxPeers];         // every rank's inbox data + offset (peer-mapped)
+  unsigned long long* flag[kMaxPeers];
+  int n_dst;
+  unsigned long long epoch;
+  const unsigned long long* wait_flags;
+  int n_wait;
+  const float* inbox;            // this rank's inbox data: all n priorities once the flags are in
+  int* host_err;
+};
+
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
 // early: see update_kernel (select.cu); 0 is always correct
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, int early, cudaStream_t stream);
+                          const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
+                          cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,
-                                 cudaStream_t stream);
+                                 const ExchangeArgs* xa, cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -1144,6 +1144,8 @@ struct Route {
   unsigned long long* signals[rr::kMaxPeers] = {};
   int n_signals = 0;
   int my_learner = -1;
+  const unsigned long long* wait_flags = nullptr;  // a learner's gather waits for every shard's flag itself
+  int wait_n = 0;
 };
 
 // sample_ (rela/prioritized_replay.h:258-328) in two stream-ordered steps: (1) selection +
@@ -1252,6 +1254,12 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     plan.p.n_signals = route->n_signals;
     for (int i = 0; i < route->n_signals; ++i) plan.p.signal[i] = route->signals[i];
     plan.p.signal_val = r->epoch;  // the same on every shard: all shards run all selections
+    if (route->my_learner >= 0 && route->wait_n > 0) {
+      plan.p.wait_flags = route->wait_flags;
+      plan.p.wait_n = route->wait_n;
+      plan.p.wait_error = &r->ctl->error;
+      plan.p.wait_host_error = r->host_err_dev;
+    }
   }
   plan.p.tl_ctl = r->ctl;
   if (rc == RR_OK && out_w != nullptr) {
@@ -1478,9 +1486,12 @@ int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* rt, void* 
   route.n_signals = rt->n_signals;
   for (int i = 0; i < rt->n_signals; ++i) route.signals[i] = static_cast<unsigned long long*>(rt->signal_ptrs[i]);
   route.my_learner = rt->my_learner;
+  route.wait_flags = static_cast<const unsigned long long*>(rt->wait_flags);
+  route.wait_n = rt->wait_flags ? rt->wait_n : 0;
   return prefetch_impl(r, batch_total, nullptr, rt->my_learner >= 0 ? rt->out_weights : nullptr, &route,
                        static_cast<const unsigned long long*>(rt->wait_flags), rt->wait_flags ? rt->wait_n : 0,
-                       rt->my_learner >= 0, rt->on_demand == 0, static_cast<cudaStream_t>(stream));
+                       false /* a learner's gather kernel waits itself */, rt->on_demand == 0,
+                       static_cast<cudaStream_t>(stream));
 }
 
 int rr_take_prefetched(rr_replay* r, void* stream) {
@@ -1558,8 +1569,44 @@ int rr_sample_gather(rr_replay* r, void* const* out_fields, void* stream) {
   return publish_batch(r, cs, slot);
 }
 
+namespace {
+int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, const rr::ExchangeArgs* xa, void* stream);
+}
+
 int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flags, void* stream) {
   if (r == nullptr || priority == nullptr || n < 0) return fail(RR_ERR_ARG, "rr_update_priority: bad argument");
+  return update_impl(r, n, priority, flags, nullptr, stream);
+}
+
+int rr_update_priority_sharded(rr_replay* r, int n_total, const float* priority_mine, int n_mine, int offset,
+                               unsigned flags, void* const* inbox_ptrs, void* const* flag_ptrs, int n_dst,
+                               uint64_t epoch, const void* wait_flags, int n_wait, const float* my_inbox,
+                               void* stream) {
+  if (r == nullptr || n_total < 0 || n_mine < 0 || offset < 0 || offset + n_mine > n_total || n_dst < 0 ||
+      n_dst > rr::kMaxPeers || n_wait < 0 || n_wait > rr::kMaxPeers || my_inbox == nullptr ||
+      (n_mine > 0 && priority_mine == nullptr) || (n_dst > 0 && (!inbox_ptrs || !flag_ptrs)) ||
+      (n_wait > 0 && wait_flags == nullptr))
+    return fail(RR_ERR_ARG, "rr_update_priority_sharded: bad argument");
+  rr::ExchangeArgs xa;
+  memset(&xa, 0, sizeof(xa));
+  xa.on = 1;
+  xa.n_mine = n_mine;
+  for (int i = 0; i < n_dst; ++i) {
+    xa.dst[i] = static_cast<float*>(inbox_ptrs[i]) + offset;
+    xa.flag[i] = static_cast<unsigned long long*>(flag_ptrs[i]);
+  }
+  xa.n_dst = n_dst;
+  xa.epoch = epoch;
+  xa.wait_flags = static_cast<const unsigned long long*>(wait_flags);
+  xa.n_wait = n_wait;
+  xa.inbox = my_inbox;
+  xa.host_err = r->host_err_dev;
+  static const float none = 0.0f;
+  return update_impl(r, n_total, n_mine > 0 ? priority_mine : &none, flags, &xa, stream);
+}
+
+namespace {
+int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, const rr::ExchangeArgs* xa, void* stream) {
   if (r->cur_ids < 0) return fail(RR_ERR_STATE, "rr_update_priority: no sampled batch is outstanding");
   if (n != r->cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
     return fail(RR_ERR_ARG, "rr_update_priority: %d priorities for a batch of %d", n, r->cur_B);
@@ -1577,10 +1624,10 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   if (prio_dev) {
     int rc = order_after_caller_(r, cs);
     if (rc != RR_OK) return rc;
-  } else if (n <= rr::kInlinePrio) {
+  } else if ((xa ? xa->n_mine : n) <= rr::kInlinePrio) {
     // a learner-sized batch handed over in host memory: the priorities travel in the launch parameters
     RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, priority,
-                                     r->alpha, is_weight, early, r->main));
+                                     r->alpha, is_weight, early, xa, r->main));
     dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
@@ -1596,14 +1643,15 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
       RR_CUDA(cudaMalloc(&st.dev, sizeof(float) * cap));
       st.cap = cap;
     }
-    memcpy(st.pinned, priority, sizeof(float) * (size_t)n);
-    RR_CUDA(cudaMemcpyAsync(st.dev, st.pinned, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, r->main));
+    const size_t n_host = (size_t)(xa ? xa->n_mine : n);  // with an exchange: this rank's share only
+    memcpy(st.pinned, priority, sizeof(float) * n_host);
+    RR_CUDA(cudaMemcpyAsync(st.dev, st.pinned, sizeof(float) * n_host, cudaMemcpyHostToDevice, r->main));
     RR_CUDA(cudaEventRecord(st.done, r->main));
     dprio = st.dev;
   }
   if (dprio != nullptr)
     RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha,
-                              is_weight, early, r->main));
+                              is_weight, early, xa, r->main));
   ++r->main_seq;
   r->launches++;
   if (prio_dev && cs != r->main) {
@@ -1615,6 +1663,7 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
   r->cur_B = 0;
   return RR_OK;
 }
+}  // namespace
 
 int rr_sync(rr_replay* r) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_sync: null");

@@ -202,8 +202,28 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     }
   }
   __syncthreads();
-  if (sh_last && tid < p.n_signals)
+  if (!sh_last) return;
+  if (tid < p.n_signals)
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.signal[tid]), "l"(p.signal_val) : "memory");
+  // a rank that consumes the batch: wait here for the other shards' flags, so that this kernel's
+  // completion IS the batch's (the flags are in this GPU's memory; one CTA polls them)
+  if (tid < p.wait_n) {
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+      unsigned long long v;
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p.wait_flags + tid) : "memory");
+      if (v >= p.signal_val) break;
+      if (globaltimer_ns() - t0 > 10ull * 1000 * 1000 * 1000) {
+        *p.wait_error = 2;  // RR_ERR_CUDA: a shard never signalled
+        if (p.wait_host_error != nullptr) {
+          *reinterpret_cast<volatile int*>(p.wait_host_error) = 2;
+          __threadfence_system();
+        }
+        break;
+      }
+      __nanosleep(100);
+    }
+  }
 }
 
 __global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsigned long long val, int* error,

@@ -777,7 +777,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
                                                              const int32_t* __restrict__ ids, int n,
                                                              const __grid_constant__ Prio prio, float alpha,
                                                              int is_weight, const Tiles tiles, int by_group,
-                                                             int early) {
+                                                             int early, const ExchangeArgs xa) {
   struct EndStamp {  // debug timeline: the latest end of any CTA of this kernel
     Ctl* c;
     __device__ ~EndStamp() {
@@ -795,7 +795,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kUpdThreads / 32;
-  const bool prio_early = early && PrioTraits<Prio>::kInLaunch;
+  const bool prio_early = early && PrioTraits<Prio>::kInLaunch && !xa.on;
   if (early) {
     for (int i = tid; i < n; i += kUpdThreads) {
       s_id[i] = ids[i];
@@ -810,11 +810,41 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
   // everything this kernel waited for being complete (see `early`, and select_kernel's rng_early)
   pdl_launch_dependents();
   if (blockIdx.x == 0 && tid == 0) RR_TL_STAMP(ctl, kTlUpdateBegin);
+  if (xa.on) {
+    // striped replay: all-gather of the learners' priorities through peer memory (ExchangeArgs)
+    if (blockIdx.x == 0) {
+      for (int p = 0; p < xa.n_dst; ++p)
+        for (int i = tid; i < xa.n_mine; i += kUpdThreads) xa.dst[p][i] = prio_at(prio, i);
+      __threadfence_system();
+      __syncthreads();
+      if (tid < xa.n_dst) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(xa.flag[tid]), "l"(xa.epoch) : "memory");
+    }
+    if (tid < xa.n_wait) {
+      const unsigned long long t0 = globaltimer_ns();
+      for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(xa.wait_flags + tid) : "memory");
+        if (v >= xa.epoch) break;
+        if (globaltimer_ns() - t0 > 10ull * 1000 * 1000 * 1000) {
+          ctl->error = 2;  // RR_ERR_CUDA: a shard never published its priorities
+          if (xa.host_err != nullptr) {
+            *reinterpret_cast<volatile int*>(xa.host_err) = 2;
+            __threadfence_system();
+          }
+          break;
+        }
+        __nanosleep(100);
+      }
+    }
+    __syncthreads();
+  }
   if (!early || !prio_early) {
     for (int i = tid; i < n; i += kUpdThreads) {
       if (!early) s_id[i] = ids[i];
       if (!prio_early) {
-        const float p = prio_at(prio, i);
+        // after an exchange the priorities of all learners are in this rank's inbox (written by
+        // other GPUs: read through L2)
+        const float p = xa.on ? __ldcg(xa.inbox + i) : prio_at(prio, i);
         s_new[i] = is_weight ? p : pow_alpha(p, alpha);
       }
     }
@@ -1041,29 +1071,35 @@ inline int update_grid(const Tiles& tiles, int n, int* by_group) {
 }  // namespace
 
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
-                          const float* prio, float alpha, int is_weight, int early, cudaStream_t stream) {
+                          const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
+                          cudaStream_t stream) {
   const size_t smem = (size_t)n * 12;
+  ExchangeArgs none;
+  memset(&none, 0, sizeof(none));
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
   if (e != cudaSuccess) return e;
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    prio, alpha, is_weight, tiles, by_group, early);
+                    prio, alpha, is_weight, tiles, by_group, early, xa ? *xa : none);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,
-                                 cudaStream_t stream) {
-  if (n > kInlinePrio) return cudaErrorInvalidValue;
+                                 const ExchangeArgs* xa, cudaStream_t stream) {
+  const int n_host = xa ? xa->n_mine : n;  // with an exchange the launch carries this rank's share only
+  if (n_host > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
-  memcpy(pin.v, prio_host, sizeof(float) * (size_t)n);
+  memcpy(pin.v, prio_host, sizeof(float) * (size_t)n_host);
+  ExchangeArgs none;
+  memset(&none, 0, sizeof(none));
   const size_t smem = (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<PrioInline>, smem);
   if (e != cudaSuccess) return e;
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    pin, alpha, is_weight, tiles, by_group, early);
+                    pin, alpha, is_weight, tiles, by_group, early, xa ? *xa : none);
 }
 
 }  // namespace rr

@@ -1,10 +1,10 @@
 mkdir -p gpurun_out
 O=gpurun_out
 {
-echo "== 1: carve-out max for G only"; RR_DEV_CARVEOUT_G=100 timeout 300 python tools/timeline_probe.py $((1<<20)) 2 6 2>&1 | tail -2 | cut -c1-1000
-echo "== 2: carve-out max for all"; RR_DEV_CARVEOUT_G=100 RR_DEV_CARVEOUT_CTL=100 timeout 300 python tools/timeline_probe.py $((1<<20)) 2 6 2>&1 | tail -2 | cut -c1-1000
-echo "== 3: G 19 stages"; RR_GATHER_STAGES=19 timeout 300 python tools/timeline_probe.py $((1<<20)) 2 6 2>&1 | tail -2 | cut -c1-1000
-echo "== 4: G 19 stages + carve-out max for G"; RR_GATHER_STAGES=19 RR_DEV_CARVEOUT_G=100 timeout 300 python tools/timeline_probe.py $((1<<20)) 2 6 2>&1 | tail -2 | cut -c1-1000
-echo "== 5: G 14 stages"; RR_GATHER_STAGES=14 timeout 300 python tools/timeline_probe.py $((1<<20)) 2 6 2>&1 | tail -2 | cut -c1-1000
-} > $O/r2l_log.txt 2>&1
-tail -40 $O/r2l_log.txt
+nvidia-smi -L
+echo "== striped tests (2 GPUs: world-2 cases)"; timeout 900 python -m pytest tests/test_sharded.py -m gpu -q 2>&1 | grep -v "DeprecationWarning\|warnings.warn" | tail -30
+echo "== bench --gpus 2"
+timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 300 --warmup 20 > $O/r2m_bench_2gpu.json 2> $O/r2m_bench_2gpu.err
+echo "rc=$?"; tail -c 2500 $O/r2m_bench_2gpu.err; echo; head -c 6000 $O/r2m_bench_2gpu.json
+} > $O/r2m_log.txt 2>&1
+tail -100 $O/r2m_log.txt
