@@ -1274,6 +1274,39 @@ def run_striped(args):
         return {"value_ms": ms_v / K, "e2e_ms": ms_e / K,
                 "gpu_launches": int(s1["kernel_launches"] - s0["kernel_launches"]), "slab_gb": st["slab_bytes"] / 1e9}
 
+    def kernel_timeline(rep, cycles=16):
+        """GPU-side durations of this rank's kernels in the pipelined value loop (rr_debug_timeline:
+        globaltimer stamps of CTA 0 after its dependency wait and at its end, and of the last CTA of
+        the update / gather kernels): what a step is made of."""
+        value_cycle, _, own_stream = loops(rep)
+        hh = C.c_void_p(rep.handle())
+        buf = np.zeros(1024, dtype=np.uint64)
+        barrier()
+        L.rr_debug_timeline(hh, 1, buf.ctypes.data, 0)
+        for k in range(cycles):
+            value_cycle(k)
+        barrier()
+        n = L.rr_debug_timeline(hh, 0, buf.ctypes.data, 1024)
+        ev = sorted((int(v) >> 4, int(v) & 15) for v in buf[:max(n, 0)])
+        def spans(a, b):
+            out, t0 = [], None
+            for t, c in ev:
+                if c == a:
+                    t0 = t
+                elif c == b and t0 is not None:
+                    out.append((t - t0) / 1e3)
+                    t0 = None
+            return out
+        def med(x):
+            x = sorted(x)
+            return round(x[len(x) // 2], 2) if x else None
+        starts = [t for t, c in ev if c == 1]
+        return {"select_us": med(spans(1, 2)), "update_cta0_us": med(spans(3, 4)), "update_all_ctas_us": med(spans(3, 7)),
+                "gather_cta0_us": med(spans(5, 6)), "gather_all_ctas_us": med(spans(5, 8)),
+                "select_to_select_us": med([(b - a) / 1e3 for a, b in zip(starts, starts[1:])]),
+                "note": "rank 0, pipelined value loop, medians over %d steps; select/update from the kernel's "
+                        "dependency wait to CTA 0's end, *_all_ctas to the last CTA's end" % cycles}
+
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
@@ -1289,14 +1322,25 @@ def run_striped(args):
     replay = make(2, -1)
     fill(replay)
     runs.append(dict(measure(replay, world), prefetch=2, learners=world))
+    timeline = kernel_timeline(replay)
     replay = None
     gc.collect()
     torch.cuda.empty_cache()
     barrier()
-    # ---- replay 3: ONE learner (GPU 0) receiving whole batches of `batch` rows over NVLink, prefetch 2
-    replay = make(2, 0)
+    # ---- replay 2b: prefetch 4. A batch's path -- selection, gather over NVLink, completion flags of
+    # all shards, the all-gather of its priorities -- crosses GPUs twice; more batches in flight
+    # hide more of that latency (the reference's prefetch is a constructor argument, any depth)
+    replay = make(4, -1)
     fill(replay)
-    single = dict(measure(replay, 1), prefetch=2, learners=1)
+    runs.append(dict(measure(replay, world), prefetch=4, learners=world))
+    replay = None
+    gc.collect()
+    torch.cuda.empty_cache()
+    barrier()
+    # ---- replay 3: ONE learner (GPU 0) receiving whole batches of `batch` rows over NVLink, prefetch 4
+    replay = make(4, 0)
+    fill(replay)
+    single = dict(measure(replay, 1), prefetch=4, learners=1)
     replay = None
     gc.collect()
     torch.cuda.empty_cache()
@@ -1345,11 +1389,12 @@ def run_striped(args):
                                                                        100 * ingress(value) / 900.0)),
                      "hbm_peak": peak, "hbm_peak_source": peak_src},
         "single_learner": {"value": tps(single["value_ms"], B), "e2e": tps(single["e2e_ms"], B), "unit": "transitions/s",
-                           "ms_per_step": single["value_ms"], "prefetch": 2, "batch": B,
+                           "ms_per_step": single["value_ms"], "prefetch": 4, "batch": B,
                            "learner_nvlink_ingress_gbs": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9,
                            "frac_of_900": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9 / 900.0,
                            "note": "the same striped replay with GPU 0 as the only learner: whole batches of %d rows "
                                    "assembled on GPU 0" % B},
+        "kernel_timeline": timeline,
         "fill_s": fill_s, "slab_gb": slab_gb, "wall_s": time.time() - t_start,
     }
     print(json.dumps(line))

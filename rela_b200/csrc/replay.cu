@@ -150,7 +150,7 @@ struct rr_replay {
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
   int sm_count = 148;
-  int g_stages = 32, g_piece = 8192, g_ctas = 1, g_simt_only = 0;
+  int g_stages = 32, g_piece = 8192, g_ctas = 1, g_simt_only = 0, g_beside_ctas = 0;
   std::vector<FieldInfo> fields;
   bool schema_set = false;
   uint64_t slab_bytes = 0;
@@ -379,7 +379,9 @@ int plan_copy(rr_replay* r, bool beside, int rows, const std::vector<CopyField>&
     // update (33.5 KB static + 12 B per element) to run beside it on the same SM
     const size_t lim = ((size_t)227 * 1024 - (beside ? kGatherReserve : 0)) / (size_t)r->g_ctas - 1024;
     if (hdr + p.stage_bytes > lim) return fail(RR_ERR_ARG, "row copy stage does not fit shared memory");
-    const int want = r->sm_count * r->g_ctas;
+    // a gather that runs beside the control plane may be kept off some of the SMs ($RR_GATHER_BESIDE_CTAS)
+    const int want = (beside && r->g_beside_ctas > 0) ? std::min(r->g_beside_ctas, r->sm_count * r->g_ctas)
+                                                      : r->sm_count * r->g_ctas;
     c.grid = (int)std::min<uint64_t>((uint64_t)want, std::max<uint64_t>(items, 1));
     // one stage per item of the busiest CTA, as many as fit
     int per_cta = (int)((items + (uint32_t)c.grid - 1) / (uint32_t)c.grid);
@@ -469,9 +471,15 @@ int rr_create(rr_replay** out, int capacity, int seed, float alpha, float beta, 
   r->g_piece = std::max(1024, env_int("RR_GATHER_PIECE", 8192)) & ~15;
   r->g_ctas = std::max(1, env_int("RR_GATHER_CTAS_PER_SM", 1));
   r->g_simt_only = env_int("RR_GATHER_SIMT", 0);
+  r->g_beside_ctas = env_int("RR_GATHER_BESIDE_CTAS", -1);  // default: 3/4 of the SMs (set below)
   cudaDeviceProp prop;
   RR_CUDA(cudaGetDeviceProperties(&prop, device));
   r->sm_count = prop.multiProcessorCount;
+  // A gather drawn ahead runs beside the selection / update kernels. Measured at the headline
+  // configuration (profiles/README.md, capture r2q): with one gather CTA on every SM a pipelined
+  // cycle takes 26.1 us -- the control kernels queue for SMs -- with 111 of 148 it takes 20.6 us,
+  // and two such gathers back to back move 6.22 TB/s instead of 5.91 (less contention per SM).
+  if (r->g_beside_ctas < 0) r->g_beside_ctas = std::max(1, r->sm_count * 3 / 4);
 
   // (Stream priorities -- control plane high, gather streams low -- and shared-memory carve-out
   // preferences were measured and dropped: no effect / up to 3.6 us slower per pipelined cycle,

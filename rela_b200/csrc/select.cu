@@ -199,10 +199,12 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
 
 // Uniform draws d_lo .. d_hi-1 of a batch of B (rela/prioritized_replay.h:267,279) from the
 // mt19937 state `mt` / `mti` in shared memory: libstdc++'s generate_canonical<float, 24> (one
-// 32-bit draw, * 2^-32, clamp to nextafter(1, 0)). On return `mt` holds the state after all B
-// draws and *mti_out its index. Called by every thread of the CTA (the twist synchronises).
+// 32-bit draw, * 2^-32, clamp to nextafter(1, 0)). The state is twisted only as far as draw
+// d_hi - 1 needs (a batch of 4096 spans 7 twists; the first CTAs need none of them), so `mt` holds
+// the state after all B draws only if d_hi == B; *mti_out is the index after all B draws either
+// way. Called by every thread of the CTA (the twist synchronises).
 __device__ void gen_uniforms(uint32_t* mt, int mti, int B, int d_lo, int d_hi, float* out, int* mti_out) {
-  const int gen_end = (mti + B - 1) / 624;  // twists needed for the whole batch
+  const int gen_end = (mti + d_hi - 1) / 624;  // twists this range needs
   for (int gen = 0; gen <= gen_end; ++gen) {
     if (gen > 0) mt_twist(mt);
     for (int d = d_lo + (int)threadIdx.x; d < d_hi; d += (int)blockDim.x) {
@@ -614,16 +616,16 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     RR_TL_STAMP(ctl, kTlSelectEnd);
   }
 
-  // ---- 7. RNG state after the B draws and the counters: CTA 0 (every CTA ran
-  //         the same twists, so every CTA holds the successor state)
-  if (blockIdx.x == 0) {
+  // ---- 7. RNG state after the B draws: the CTA of the last targets (the only one that had to
+  //         twist all the way); counters: CTA 0
+  if (blockIdx.x == gridDim.x - 1) {
     __syncthreads();
     for (int i = tid; i < 624; i += kSelThreads) ctl->mt[a.rng_par ^ 1][i] = mt[i];
-    if (tid == 0) {
-      ctl->mti[a.rng_par ^ 1] = sh_mti;
-      if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
-      ctl->probe[5] = clock64();
-    }
+    if (tid == 0) ctl->mti[a.rng_par ^ 1] = sh_mti;
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
+    ctl->probe[5] = clock64();
   }
   if (a.pop_n <= 0) return;
 
@@ -838,6 +840,9 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     }
     __syncthreads();
   }
+  // CTA 0 raises every priority; a group CTA raises only the few it substitutes (a batch of 4096
+  // over 1280 group CTAs would otherwise pay 5 M fp64 pows for 4096 values): there s_new is raw
+  const bool raise_now = blockIdx.x == 0;
   if (!early || !prio_early) {
     for (int i = tid; i < n; i += kUpdThreads) {
       if (!early) s_id[i] = ids[i];
@@ -845,7 +850,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
         // after an exchange the priorities of all learners are in this rank's inbox (written by
         // other GPUs: read through L2)
         const float p = xa.on ? __ldcg(xa.inbox + i) : prio_at(prio, i);
-        s_new[i] = is_weight ? p : pow_alpha(p, alpha);
+        s_new[i] = (is_weight || !raise_now) ? p : pow_alpha(p, alpha);
       }
     }
   }
@@ -857,23 +862,26 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     __shared__ float s_lm[64];
     __shared__ unsigned long long s_mask;
     __shared__ int s_lo, s_hi;
+    const int gl = tiles.group_log2;
+    const int span_log2 = kLeafLog2 + gl;
+    const int ncand = by_group ? tiles.ng : n;
+    // the grid is capped (two CTAs per SM, replay.cu): a CTA takes candidates c, c + G, ...
+    for (int c = (int)blockIdx.x - 1; c < ncand; c += (int)gridDim.x - 1) {
+    __syncthreads();  // the previous candidate's shared state is no longer read
     if (tid == 0) {
       s_mask = 0ull;
       s_lo = n;
       s_hi = -1;
     }
-    const int gl = tiles.group_log2;
-    const int span_log2 = kLeafLog2 + gl;
-    const int c = (int)blockIdx.x - 1;
     int g;
     if (by_group) {
       g = c;
     } else {
-      g = s_id[c] >> span_log2;
-      int dup = 0;  // an earlier element of the batch in the same group: that element's CTA covers it
+      g = s_id[c] >> span_log2;  // (negative for a slot an earlier candidate of this CTA found evicted)
+      int dup = g < 0 ? 1 : 0;  // an earlier element of the batch in the same group: that element's CTA covers it
       for (int j = tid; j < c; j += kUpdThreads)
         if ((s_id[j] >> span_log2) == g) dup = 1;
-      if (__syncthreads_or(dup)) return;
+      if (__syncthreads_or(dup)) continue;
     }
     __syncthreads();
     // leaves of the group that hold a batch slot and the index range of the batch that falls into
@@ -898,7 +906,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     }
     __syncthreads();
     const unsigned long long mask = s_mask;
-    if (mask == 0ull) return;
+    if (mask == 0ull) continue;
     const int jlo = s_lo, jhi = s_hi;
     const int L = 1 << gl;
     const size_t lb = (size_t)g << gl;
@@ -942,7 +950,8 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
       for (int j = jlo + lane; j <= jhi; j += 32) {
         const int sid = s_id[j];
         const bool last = !(j + 1 < n && s_id[j + 1] == sid);
-        if (sid >= base && sid < base + 256 && last) mine[sid - base] = s_new[j];
+        if (sid >= base && sid < base + 256 && last)
+          mine[sid - base] = (is_weight || prio_early) ? s_new[j] : pow_alpha(s_new[j], alpha);
       }
       __syncwarp();
       const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
@@ -969,6 +978,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
         tiles.grpmin[g] = mn;
       }
     }
+    }  // candidates of this CTA
     return;
   }
 
@@ -1066,7 +1076,15 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
 namespace {
 inline int update_grid(const Tiles& tiles, int n, int* by_group) {
   *by_group = tiles.ng <= n ? 1 : 0;
-  return 1 + (*by_group ? tiles.ng : n);  // CTA 0: sum_ and weights; the others: one per candidate group
+  // CTA 0: sum_ and weights; the others: candidate groups, at most two CTAs per SM -- with a fused
+  // exchange (ExchangeArgs) every CTA polls flags until all shards have arrived, and a grid that
+  // filled every thread slot of the GPU would keep the gathers on the gather streams out meanwhile
+  static const int cap = [] {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return 2 * sms;
+  }();
+  return 1 + std::min(*by_group ? tiles.ng : n, cap - 1);
 }
 }  // namespace
 

@@ -1,10 +1,10 @@
 mkdir -p gpurun_out
 O=gpurun_out
 {
-nvidia-smi -L
-echo "== striped tests (2 GPUs: world-2 cases)"; timeout 900 python -m pytest tests/test_sharded.py -m gpu -q 2>&1 | grep -v "DeprecationWarning\|warnings.warn" | tail -30
-echo "== bench --gpus 2"
-timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 300 --warmup 20 > $O/r2m_bench_2gpu.json 2> $O/r2m_bench_2gpu.err
-echo "rc=$?"; tail -c 2500 $O/r2m_bench_2gpu.err; echo; head -c 6000 $O/r2m_bench_2gpu.json
-} > $O/r2m_log.txt 2>&1
-tail -100 $O/r2m_log.txt
+for n in 148 128 111 96 74; do
+echo "== beside CTAs $n"; RR_GATHER_BESIDE_CTAS=$n timeout 300 python tools/cycle_probe.py $((1<<21)) 512 2000 2>&1 | tail -1 | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print({k: round(v,2) for k,v in d.items() if k.startswith('c_loop') or k.startswith('gather')})"
+done
+} > $O/r2q_log.txt 2>&1
+tail -40 $O/r2q_log.txt
