@@ -697,7 +697,11 @@ def run_single(args):
     replay = rela.FFPrioritizedReplay(args.capacity, 7, args.alpha, args.beta, 0, 0)
     _CAP[id(replay)] = args.capacity
     t0 = time.time()
-    serial_of_slot = fill_k80(rela, torch, replay, dev, prios)
+    if args.no_parity:  # development / profiling runs: 257 adds of 8192 rows instead of 26,215 of 80
+        serial_of_slot = None
+        fill_fast(rela, torch, replay, dev, args.capacity, extra=prios.size - args.capacity)
+    else:
+        serial_of_slot = fill_k80(rela, torch, replay, dev, prios)
     fill_s = time.time() - t0
     h = C.c_void_p(replay.handle())
     assert replay.size() == prios.size and sum(t[4] for t in replay.schema()) == ROW_BYTES
@@ -734,8 +738,8 @@ def run_single(args):
     for k in range(16):
         lp.serial(k)
     capi.check(L.rr_set_profiling(h, 0, B))
-    g1_us, g1_n, gbytes = lp.gather_bench(max(1, K // 16), 1)
-    g2_us, g2_n, _ = lp.gather_bench(max(1, K // 16), 2)
+    g1_us, g1_n, gbytes = lp.gather_bench(max(16, K // 16), 1)   # >= 256 launches whatever --steps says
+    g2_us, g2_n, _ = lp.gather_bench(max(16, K // 16), 2)
     big = None
     if B <= 1024:
         B2 = 8 * B
@@ -749,7 +753,7 @@ def run_single(args):
             capi.check(L.rr_sample(h, B2, ptrs2[k % 2], C.c_void_p(w2.data_ptr()), lp.own))
             capi.check(L.rr_update_priority(h, B2, C.c_void_p(prio2.data_ptr()), capi.RR_PRIO_DEVICE, lp.own))
         capi.check(L.rr_set_profiling(h, 0, B2))
-        us2, n2, b2 = lp.gather_bench(max(1, K // 128), 1, outs2)
+        us2, n2, b2 = lp.gather_bench(max(2, K // 128), 1, outs2)
         big = {"batch": B2, "kernel_us": us2, "launches_timed": n2, "bytes_per_launch": b2,
                "achieved": b2 / (us2 * 1e-6) / 1e9, "frac": b2 / (us2 * 1e-6) / 1e9 / peak}
         del outs2, ptrs2

@@ -1,10 +1,15 @@
 mkdir -p gpurun_out
 O=gpurun_out
 {
-for n in 148 128 111 96 74; do
-echo "== beside CTAs $n"; RR_GATHER_BESIDE_CTAS=$n timeout 300 python tools/cycle_probe.py $((1<<21)) 512 2000 2>&1 | tail -1 | python -c "
-import json,sys
-d=json.loads(sys.stdin.read()); print({k: round(v,2) for k,v in d.items() if k.startswith('c_loop') or k.startswith('gather')})"
-done
-} > $O/r2q_log.txt 2>&1
-tail -40 $O/r2q_log.txt
+echo "== launch list at the full configuration"
+CMD="python bench.py --steps 200 --warmup 10 --no-cpu-baseline --no-extras --no-parity"
+timeout 600 $CMD > $O/r2_plain_full.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:select_kernel|update_kernel|row_copy_kernel" -s 300 -c 3000 --csv --log-file $O/r2_launches_full_capacity.csv $CMD > $O/r2_ncu1.log 2>&1
+echo "rc=$?"
+echo "== ncu --set full, capacity 131072"
+CMD2="python bench.py --capacity 131072 --steps 40 --warmup 5 --no-cpu-baseline --no-extras --no-parity"
+timeout 600 $CMD2 > $O/r2_plain_small.log 2>&1 &&
+timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:select_kernel|update_kernel|row_copy_kernel" -s 120 -c 9 -o $O/r2_full $CMD2 > $O/r2_ncu2.log 2>&1
+echo "rc=$?"; tail -3 $O/r2_ncu2.log | cut -c1-200
+} > $O/r2r_log.txt 2>&1
+tail -30 $O/r2r_log.txt
