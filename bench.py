@@ -1261,13 +1261,30 @@ def run_striped(args):
 
         return value_cycle, e2e_cycle, own_stream
 
+    def timed_cpp(rep, steps, on):
+        """The value loop issued by a C++ caller (pybind `cycle_loop`: the typed sample() +
+        updatePriority() of the host layer in a C++ for loop), device-resident priorities."""
+        hh = C.c_void_p(rep.handle())
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(on):
+            e0.record(on)
+            rep.cycle_loop(B, dev_str, prio_dev, steps)
+            capi.check(L.rr_stream_fence(hh, C.c_void_p(on.cuda_stream)))
+            e1.record(on)
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     def measure(rep, learners):
         value_cycle, e2e_cycle, own_stream = loops(rep)
         hh = C.c_void_p(rep.handle())
         for k in range(W):
             value_cycle(k)
+        ms_py = timed(rep, value_cycle, max(1, K // 4), own_stream) / max(1, K // 4)
         s0 = get_stats(capi, L, hh)
-        ms_v = timed(rep, value_cycle, K, own_stream)
+        ms_v = timed_cpp(rep, K, own_stream)
         s1 = get_stats(capi, L, hh)
         for k in range(W):
             e2e_cycle(k)
@@ -1275,7 +1292,7 @@ def run_striped(args):
         rep.sync()
         st = get_stats(capi, L, hh)
         assert st["samples_ordered"] == 0 and st["device_errors"] == 0
-        return {"value_ms": ms_v / K, "e2e_ms": ms_e / K,
+        return {"value_ms": ms_v / K, "value_ms_python_loop": ms_py, "e2e_ms": ms_e / K,
                 "gpu_launches": int(s1["kernel_launches"] - s0["kernel_launches"]), "slab_gb": st["slab_bytes"] / 1e9}
 
     def kernel_timeline(rep, cycles=16):
@@ -1287,11 +1304,12 @@ def run_striped(args):
         buf = np.zeros(1024, dtype=np.uint64)
         barrier()
         L.rr_debug_timeline(hh, 1, buf.ctypes.data, 0)
-        for k in range(cycles):
-            value_cycle(k)
+        with torch.cuda.stream(own_stream):
+            rep.cycle_loop(B, dev_str, prio_dev, cycles)
         barrier()
         n = L.rr_debug_timeline(hh, 0, buf.ctypes.data, 1024)
-        ev = sorted((int(v) >> 4, int(v) & 15) for v in buf[:max(n, 0)])
+        raw = sorted((int(v) >> 8, int(v) & 15, (int(v) >> 4) & 15) for v in buf[:max(n, 0)])
+        ev = [(t, c) for t, c, _ in raw]
         def spans(a, b):
             out, t0 = [], None
             for t, c in ev:
@@ -1305,9 +1323,19 @@ def run_striped(args):
             x = sorted(x)
             return round(x[len(x) // 2], 2) if x else None
         starts = [t for t, c in ev if c == 1]
-        return {"select_us": med(spans(1, 2)), "update_cta0_us": med(spans(3, 4)), "update_all_ctas_us": med(spans(3, 7)),
+        return {"select_us": med(spans(1, 2)), "update_cta0_us": med(spans(3, 4)),
+                "update_wait_for_all_shards_us": med(spans(3, 9)), "update_all_ctas_us": med(spans(3, 7)),
                 "gather_cta0_us": med(spans(5, 6)), "gather_all_ctas_us": med(spans(5, 8)),
                 "select_to_select_us": med([(b - a) / 1e3 for a, b in zip(starts, starts[1:])]),
+                "events": " ".join("%s%s@%.1f" % ({1: "S+", 2: "S-", 3: "U+", 4: "U-", 5: "G+", 6: "G-", 7: "Uall-",
+                                                    8: "Gall-", 9: "Ux", 10: "S0", 11: "U0", 12: "G0", 13: "Gsig",
+                                                    14: "Gdone"}.get(c, str(c)), "" if c in (7, 8) else ":%x" % g,
+                                                   (t - raw[0][0]) / 1e3)
+                                   for t, c, g in raw[len(raw) // 2:len(raw) // 2 + 96]) if raw else "",
+                "events_legend": "name:tag@us -- tag = low 4 bits of the batch's epoch (S, G) or of the exchange "
+                                 "sequence (U); S0/U0/G0 = CTA 0 resident (before its dependency wait), S+/U+/G+ after "
+                                 "the wait, Ux = all shards' priorities in, Gsig = this shard's rows stored and "
+                                 "signalled, Gdone = all shards' rows of the batch in",
                 "note": "rank 0, pipelined value loop, medians over %d steps; select/update from the kernel's "
                         "dependency wait to CTA 0's end, *_all_ctas to the last CTA's end" % cycles}
 
@@ -1370,7 +1398,11 @@ def run_striped(args):
                        "rows of one stratified batch of %d per step; rows travel GPU to GPU over NVLink"
                        % (total_cap, world, slab_gb, B, Bg),
         "value_runs": [{"prefetch": r["prefetch"], "ms_per_step": r["value_ms"], "transitions_per_s": tps(r["value_ms"], Bg),
-                        "gpu_launches": r["gpu_launches"]} for r in runs],
+                        "ms_per_step_python_loop": r["value_ms_python_loop"], "gpu_launches": r["gpu_launches"]}
+                       for r in runs],
+        "value_note": "sample(B) + update_priority(device priorities) of the C++ host layer on every rank, on the replay's "
+                      "own stream, issued by a C++ loop (pybind cycle_loop); ms_per_step_python_loop: the same calls "
+                      "issued from the interpreter",
         "e2e": {"value": tps(best_e["e2e_ms"], Bg), "unit": "transitions/s", "h2d_bytes_per_step": 4 * B * world,
                 "d2h_bytes_per_step": 4 * B * world, "ms_per_step": best_e["e2e_ms"], "prefetch": best_e["prefetch"],
                 "runs": [{"prefetch": r["prefetch"], "ms_per_step": r["e2e_ms"], "transitions_per_s": tps(r["e2e_ms"], Bg)}

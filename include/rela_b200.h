@@ -134,6 +134,31 @@ int rr_prefetch_into(rr_replay* r, int batch, void* const* out_fields,
                      float* out_weights, void* stream);
 int rr_take_prefetched(rr_replay* r, void* stream);
 int rr_prefetched(rr_replay* r);
+/* Two special `stream` values of rr_take_prefetched, for a host layer that
+ * knows more than a stream order can say:
+ * RR_STREAM_NONE          the batch is not ordered on any stream: the caller
+ *                         waits for the event it recorded with
+ *                         rr_record_prefetched (below) wherever it consumes
+ *                         the batch.
+ * RR_STREAM_OWN_DEFERRED  the consumer works on the replay's own stream
+ *                         (rr_get_stream) AND the caller's next call is a
+ *                         prefetch (rr_prefetch_into / rr_prefetch_routed):
+ *                         that selection carries the wait for this batch's
+ *                         gather, so work the caller puts on the own stream
+ *                         AFTER that prefetch call sees the batch. (A stream
+ *                         wait in front of the selection would cut the
+ *                         programmatic launch chain update -> select; this
+ *                         keeps it. Any other call in between falls back to
+ *                         the plain stream wait.) */
+#define RR_STREAM_NONE ((void*)(intptr_t)-1)
+#define RR_STREAM_OWN_DEFERRED ((void*)(intptr_t)-2)
+/* Record `event` (a cudaEvent_t of the caller, created on the replay's device)
+ * behind the gather of the batch most recently queued by rr_prefetch_into: a
+ * host layer that issues from one thread and hands batches out on another
+ * makes the consumer's stream wait for this event instead of going through
+ * rr_take_prefetched's hand-shake (which it then calls with the replay's own
+ * stream, rr_get_stream). */
+int rr_record_prefetched(rr_replay* r, void* event);
 
 /* rr_sample in two steps, so that a host layer can allocate the batch tensors
  * while the selection kernel already runs: rr_sample_select issues the
@@ -209,14 +234,15 @@ int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* route, voi
 /* update_priority on a striped replay: every rank applies the priorities of ALL learners, which
  * the update kernel itself all-gathers through peer memory. This rank contributes n_mine values
  * (priority_mine: host memory, or device memory with RR_PRIO_DEVICE) for elements [offset, offset +
- * n_mine) of the batch of n_total; inbox_ptrs[i] / flag_ptrs[i]: rank i's inbox data and this rank's
- * flag in it (peer-mapped, n_dst = world, this rank included); my_inbox: this rank's own inbox
- * data (n_total floats once wait_flags[0..n_wait), one flag per learner, have reached `epoch`).
- * A rank that is no learner passes n_mine == 0 and only waits. All ranks pass the same `flags`. */
+ * n_mine) of the batch of n_total. A priority travels as one 8-byte word (epoch << 32 | float
+ * bits), valid when its upper half equals `epoch`: slot_ptrs[i] = rank i's array of n_total such
+ * words (peer-mapped, n_dst = world, this rank included), my_slots = this rank's own array.
+ * `epoch`: the same non-zero value on every rank, different from the value of the previous
+ * exchange through the same arrays (the caller alternates between two arrays per rank).
+ * A rank that is no learner passes n_mine == 0 and only receives. All ranks pass the same `flags`. */
 int rr_update_priority_sharded(rr_replay* r, int n_total, const float* priority_mine, int n_mine, int offset,
-                               unsigned flags, void* const* inbox_ptrs, void* const* flag_ptrs, int n_dst,
-                               uint64_t epoch, const void* wait_flags, int n_wait, const float* my_inbox,
-                               void* stream);
+                               unsigned flags, void* const* slot_ptrs, int n_dst, uint32_t epoch,
+                               const void* my_slots, void* stream);
 
 /* Collective add into a striped replay. Step 1 reserves the block of n_total
  * slots (identically on every shard) and moves THIS rank's rows -- rows
@@ -370,7 +396,7 @@ int rr_debug_weights(rr_replay* r, float* out_w_host, uint8_t* out_evicted_host)
 int rr_debug_tiles(rr_replay* r, int rebuild, int level, double* out_sums_host,
                    float* out_mins_host, int cap, int* out_tile_slots);
 /* Kernel timeline: returns (and clears) up to `cap` stamps recorded since the last call, oldest
- * first, then switches recording on / off. A stamp is (globaltimer ns << 4 | code), written by
+ * first, then switches recording on / off. A stamp is (globaltimer ns << 8 | tag << 4 | code; tag = low 4 bits of the batch's epoch), written by
  * CTA 0 of each kernel after its dependency wait and at its end; codes: 1 / 2 selection begin /
  * end, 3 / 4 update, 5 / 6 gather. Returns the number of stamps (< 0: error). */
 int rr_debug_timeline(rr_replay* r, int enable, uint64_t* out_host, int cap);

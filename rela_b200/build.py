@@ -64,7 +64,7 @@ def _torch_flags():
 
 CPP = os.path.join(HERE, "cpp")
 SHIM = os.path.join(HERE, "_C.so")
-SHIM_SOURCES = ["replay_core.cc", "sharded_core.cc", "sequence_assembler.cc", "pybind_module.cc"]
+SHIM_SOURCES = ["replay_core.cc", "sharded_core.cc", "issuer_core.cc", "sequence_assembler.cc", "pybind_module.cc"]
 
 
 def build_shim(force=False):

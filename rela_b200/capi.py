@@ -19,6 +19,7 @@ SYMBOLS = [
     "rr_update_priority", "rr_update_priority_sharded", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_debug_timeline", "rr_stream_fence",
     "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
+    "rr_record_prefetched",
     "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_cycle_bench", "rr_nstep_return", "rr_td_priority",
     "rr_aggregate_priority", "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_prefetch_routed",
     "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_exchange",
@@ -72,7 +73,7 @@ def lib():
         L.rr_add_rows.argtypes = [vp, i, vp, vp, u, vp]
         L.rr_sample.argtypes = [vp, i, vp, vp, vp]
         L.rr_update_priority.argtypes = [vp, i, vp, u, vp]
-        L.rr_update_priority_sharded.argtypes = [vp, i, vp, i, i, u, vp, vp, i, C.c_uint64, vp, i, vp, vp]
+        L.rr_update_priority_sharded.argtypes = [vp, i, vp, i, i, u, vp, i, C.c_uint32, vp, vp]
         L.rr_size.argtypes = [vp]
         L.rr_num_add.argtypes = [vp]
         L.rr_sync.argtypes = [vp]
@@ -110,6 +111,7 @@ def lib():
         L.rr_add_sharded_commit.argtypes = [vp, vp, u]
         L.rr_restore_prefetched.argtypes = [vp, i, vp, vp, vp]
         L.rr_prefetched_batch.argtypes = [vp, i]
+        L.rr_record_prefetched.argtypes = [vp, vp]
         L.rr_group_create.argtypes = [C.POINTER(vp), C.c_char_p, i, i]
         L.rr_group_allgather.argtypes = [vp, vp, C.c_uint64, vp]
         L.rr_group_barrier.argtypes = [vp]

@@ -61,6 +61,18 @@ void bindCommon(PyClass& c) {
       .def("sample", &Replay::sample, py::call_guard<py::gil_scoped_release>())
       .def("update_priority", &Replay::updatePriority, py::call_guard<py::gil_scoped_release>())
       .def("sync", [](Replay& r) { r.core().sync(); }, py::call_guard<py::gil_scoped_release>())
+      // measurement: `steps` sample + update_priority cycles issued by a C++ caller (what a C++
+      // learner's loop costs, without the interpreter between the calls); priority_pool [k, B]
+      .def("cycle_loop",
+           [](Replay& r, int batchsize, const std::string& device, const torch::Tensor& priority_pool, int steps) {
+             const int64_t k = priority_pool.size(0);
+             for (int s = 0; s < steps; ++s) {
+               auto batch = r.sample(batchsize, device);
+               r.updatePriority(priority_pool[s % k]);
+             }
+           },
+           py::arg("batchsize"), py::arg("device"), py::arg("priority_pool"), py::arg("steps"),
+           py::call_guard<py::gil_scoped_release>())
       .def("set_output_format",
            [](Replay& r, const std::string& leaf, py::object dtype) {
              r.core().setOutputFormat(leaf, torch::python::detail::py_object_to_dtype(dtype));

@@ -125,6 +125,7 @@ class ReplayCore {
   int device() const { return device_; }
   const std::vector<LeafSpec>& schema() const { return schema_; }
   struct Sharded;  // state of the striped-replay protocol (sharded_core.cc)
+  struct Issuer;   // the thread that issues batches drawn ahead and host-priority updates (issuer_core.cc)
   // priority ^ alpha for `p` = elements [offset, offset + n) of a block of `total` priorities that
   // ONE replay would raise with a single torch::pow: bit-identical to that call's slice
   static torch::Tensor raiseAtPosition(const torch::Tensor& p, int64_t offset, int64_t total, float alpha);
@@ -140,6 +141,9 @@ class ReplayCore {
     int64_t B = 0;
     std::vector<torch::Tensor> fields;
     torch::Tensor weights;
+    // issuer mode: a cudaEvent_t recorded behind the gather that fills this set (shared by the
+    // copies of the set; destroyed with the last one)
+    std::shared_ptr<void> ready;
   };
   std::vector<BatchSet> pool_;  // batch tensors reused once the caller has released them
   std::deque<BatchSet> inflight_;  // batches drawn ahead (prefetch), oldest first
@@ -151,6 +155,20 @@ class ReplayCore {
   void init(int capacity, int seed, float alpha, float beta, int prefetch, int device);
   void applySchema(const std::vector<LeafSpec>& specs);
   std::string shardFile(const std::string& path) const;
+  // issuer_core.cc: with prefetch > 0 the reference draws batches ahead on other threads
+  // (std::async futures, rela/prioritized_replay.h:215-230). Here ONE issuer thread owns the
+  // replay's control stream: it launches the selections / gathers of batches drawn ahead and the
+  // updates whose priorities arrive in host memory, in call order, while the calling thread only
+  // waits for a batch's event and hands it out. See issuer_core.cc for what stays synchronous.
+  void startIssuer();
+  void stopIssuer();
+  void drainIssuer();  // returns when the issuer has executed everything posted; rethrows its error
+  std::pair<Leaves, torch::Tensor> issuerSample(int batchsize, const std::string& device);
+  void issuerUpdate(const torch::Tensor& priority);
+  void issuerAdopt(BatchSet set, void* stream);  // load(): a restored batch joins the batches drawn ahead
+  int issuerQueued() const;
+  std::shared_ptr<void> newReadyEvent() const;
+  void issueInto(BatchSet& set, int batchsize, void* stream);  // rr_prefetch_into + ready event
   // sharded_core.cc
   void startSharded();
   void stopSharded();
@@ -160,6 +178,7 @@ class ReplayCore {
   void shardedUpdate(const torch::Tensor& w, unsigned flags);
 
   rr_replay* h_ = nullptr;
+  void* own_stream_ = nullptr;  // rr_get_stream
   int device_ = 0;
   float alpha_ = 1.0f;
   bool host_pow_ = true;
@@ -170,6 +189,8 @@ class ReplayCore {
   // striped replay (ShardConfig): the SPMD protocol lives in sharded_core.cc
   ShardConfig shard_;
   std::shared_ptr<Sharded> sharded_;  // shared_ptr: the type is complete only in sharded_core.cc
+  std::shared_ptr<Issuer> issuer_;    // null: prefetch == 0, striped replay, or RELA_B200_ISSUER_THREAD=0
+  std::mutex pool_m_;                 // pool_ / inflight_ when the issuer thread is running
 };
 
 [[noreturn]] void throwLast(int code, const char* where);

@@ -104,10 +104,13 @@ void ReplayCore::init(int capacity, int seed, float alpha, float beta, int prefe
   // prefetch and nothing is copied when a batch is handed out.
   prefetch_ = std::max(0, prefetch);
   check(rr_create(&h_, capacity, seed, alpha, beta, 0, device_), "PrioritizedReplay");
+  check(rr_get_stream(h_, &own_stream_), "PrioritizedReplay");
   if (shard_.world > 1) startSharded();
+  startIssuer();
 }
 
 ReplayCore::~ReplayCore() {
+  stopIssuer();
   inflight_.clear();
   stopSharded();
   if (h_ != nullptr) rr_destroy(h_);
@@ -115,12 +118,16 @@ ReplayCore::~ReplayCore() {
 
 int ReplayCore::size() const { return rr_size(h_); }
 int ReplayCore::numAdd() const { return rr_num_add(h_); }
-void ReplayCore::sync() { check(rr_sync(h_), "sync"); }
+void ReplayCore::sync() {
+  drainIssuer();
+  check(rr_sync(h_), "sync");
+}
 // The C ABI checkpoint holds bytes; dtypes and shapes of the leaves are the host
 // layer's business and go into a text sidecar (<path>.schema), one leaf per
 // line: name dtype chunks time_major row_bytes ndim dims...
 void ReplayCore::save(const std::string& path) {
   if (!schema_set_.load(std::memory_order_acquire)) throw std::runtime_error("save: nothing has been added yet");
+  drainIssuer();
   const std::string file = shard_.world > 1 ? shardFile(path) : path;
   check(rr_save(h_, file.c_str()), "save");  // batches drawn ahead (inflight_) are saved with it
   if (shard_.rank != 0) return;
@@ -167,11 +174,18 @@ void ReplayCore::load(const std::string& path) {
   const int queued = rr_prefetched(h_);
   void* stream = streamOf(device_);
   for (int k = 0; k < queued; ++k) {
-    BatchSet set = acquireSet(rr_prefetched_batch(h_, k));
+    BatchSet set;
+    {
+      std::lock_guard<std::mutex> pl(pool_m_);
+      set = acquireSet(rr_prefetched_batch(h_, k));
+    }
     std::vector<void*> ptrs(schema_.size() ? schema_.size() : 1, nullptr);
     for (size_t i = 0; i < schema_.size(); ++i) ptrs[i] = set.fields[i].data_ptr();
     check(rr_restore_prefetched(h_, k, ptrs.data(), set.weights.data_ptr<float>(), stream), "load");
-    inflight_.push_back(std::move(set));
+    if (issuer_)
+      issuerAdopt(std::move(set), stream);
+    else
+      inflight_.push_back(std::move(set));
   }
 }
 
@@ -239,9 +253,10 @@ void ReplayCore::setSchema(const std::vector<LeafSpec>& specs) {
 }
 
 void ReplayCore::setOutputFormat(const std::string& name, torch::ScalarType dtype) {
+  drainIssuer();
   std::lock_guard<std::mutex> lk(schema_m_);
   if (!schema_set_.load(std::memory_order_acquire)) throw std::runtime_error("set_output_format: the schema is not known yet (add or load first)");
-  if (!inflight_.empty()) throw std::runtime_error("set_output_format: prefetched batches are pending");
+  if (!inflight_.empty() || issuerQueued() > 0) throw std::runtime_error("set_output_format: prefetched batches are pending");
   for (size_t i = 0; i < schema_.size(); ++i) {
     LeafSpec& s = schema_[i];
     if (s.name != name) continue;
@@ -259,7 +274,10 @@ void ReplayCore::setOutputFormat(const std::string& name, torch::ScalarType dtyp
     check(rr_set_output_format(h_, (int)i, fmt), "set_output_format");
     s.converted = fmt != RR_OUT_RAW;
     s.out_dtype = dtype;
-    pool_.clear();  // pooled batch sets have the old dtype
+    {
+      std::lock_guard<std::mutex> pl(pool_m_);
+      pool_.clear();  // pooled batch sets have the old dtype
+    }
     return;
   }
   throw std::runtime_error("set_output_format: no leaf named '" + name + "'");
@@ -419,6 +437,7 @@ ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
   for (const LeafSpec& s : schema_)
     set.fields.push_back(torch::empty(batchShape(s, B),
                                       torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
+  if (issuer_) set.ready = newReadyEvent();
   if (pool_.size() < (size_t)(4 + prefetch_)) pool_.push_back(set);
   return set;
 }
@@ -461,12 +480,12 @@ std::pair<Leaves, torch::Tensor> ReplayCore::samplePrefetched(int batchsize, con
   };
   if (!inflight_.empty() && inflight_.front().B != B) throw std::runtime_error("sample: batch size differs from the prefetched one");
   if (inflight_.empty()) issue();
-  check(rr_take_prefetched(h_, stream), "sample");
+  // (a caller on the replay's own stream: the prefetch issued below carries the wait for this batch)
+  check(rr_take_prefetched(h_, (stream == own_stream_ && prefetch_ > 0) ? RR_STREAM_OWN_DEFERRED : stream), "sample");
   BatchSet set = std::move(inflight_.front());
   inflight_.pop_front();
-  auto out = handOut(set, device);
   while ((int)inflight_.size() < prefetch_) issue();
-  return out;
+  return handOut(set, device);
 }
 
 std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::string& device) {
@@ -475,6 +494,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
     throw std::runtime_error("sample: the replay buffer is empty");
   }
   if (shard_.world > 1) return shardedSample(batchsize, device);
+  if (issuer_) return issuerSample(batchsize, device);
   if (prefetch_ > 0 || !inflight_.empty()) return samplePrefetched(batchsize, device);
   // Batch tensors come from a small pool. The caller never receives the pooled
   // tensor objects, only fresh aliases of their storages; a set is reused once
@@ -519,6 +539,10 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
 }
 
 void ReplayCore::updatePriority(const torch::Tensor& priority) {
+  if (issuer_) {
+    issuerUpdate(priority);
+    return;
+  }
   unsigned flags = 0;
   torch::Tensor w = weightsOf(priority, &flags);
   if (shard_.world > 1) {

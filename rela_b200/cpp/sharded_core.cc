@@ -55,8 +55,12 @@ inline void* streamOf(int device) {
   return (void*)c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
 }
 
-constexpr size_t kInboxFloats = 1u << 20;  // largest block of weights one exchange moves
+constexpr size_t kInboxFloats = 1u << 20;  // largest block of weights one exchange moves (adds)
 constexpr size_t kInboxHeader = 256;       // 2 parities x 16 ranks x 8-byte flags
+constexpr size_t kUpdateSlots = 16384;     // largest batch (all learners) of one update_priority: kMaxBatch
+// an inbox: [flags][weights of an add, parity 0][parity 1][update slots, parity 0][parity 1]
+constexpr size_t kInboxSlotsOff = kInboxHeader + 2 * kInboxFloats * sizeof(float);
+constexpr size_t kInboxBytes = kInboxSlotsOff + 2 * kUpdateSlots * sizeof(uint64_t);
 constexpr size_t kAlign = 256;
 
 inline size_t alignUp(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
@@ -75,9 +79,10 @@ struct ReplayCore::Sharded {
 
   void* slab_tab = nullptr;  // device uint64[world * nfields]
 
-  // inbox of every rank: [flags 2 x 16][data parity 0: kInboxFloats][data parity 1]
+  // inbox of every rank: [flags 2 x 16][data parity 0: kInboxFloats][data parity 1][update slots x 2]
   std::vector<uint8_t*> inbox;
-  uint64_t xseq = 0;
+  uint64_t xseq = 0;  // exchanges of adds (rr_exchange)
+  uint64_t useq = 0;  // exchanges of update_priority (8-byte words tagged with the sequence number)
   float* stage_pinned[2] = {nullptr, nullptr};
   float* stage_dev[2] = {nullptr, nullptr};
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
@@ -122,7 +127,8 @@ void ReplayCore::startSharded() {
   c10::cuda::CUDAGuard guard((c10::DeviceIndex)device_);
   // inbox for the all-gather of weights (rr_exchange)
   void* mine = nullptr;
-  check(rr_device_alloc(device_, kInboxHeader + 2 * kInboxFloats * sizeof(float), &mine), "sharded replay (inbox)");
+  check(rr_device_alloc(device_, kInboxBytes, &mine), "sharded replay (inbox)");
+  cuda(cudaMemset(mine, 0, kInboxBytes), "sharded replay (inbox)");  // no slot carries a valid tag yet
   sh.owned.push_back(mine);
   uint8_t handle[64];
   check(rr_ipc_export(device_, mine, handle), "sharded replay (inbox)");
@@ -379,7 +385,9 @@ std::pair<Leaves, torch::Tensor> ReplayCore::shardedSample(int batchsize, const 
   if (!sh.inflight.empty() && sh.inflight.front().first != &a)
     throw std::runtime_error("sample: batch size differs from the prefetched one");
   if (sh.inflight.empty()) issue(prefetch_ == 0);
-  check(rr_take_prefetched(h_, cs), "sample");
+  // a caller on the replay's own stream with batches drawn ahead: the prefetch issued right below
+  // carries the wait for this batch (RR_STREAM_OWN_DEFERRED keeps the update -> select launch chain)
+  check(rr_take_prefetched(h_, (cs == sh.main && prefetch_ > 0) ? RR_STREAM_OWN_DEFERRED : cs), "sample");
   sh.cur_B = B;
   const int k = sh.inflight.front().second;
   sh.inflight.pop_front();
@@ -408,7 +416,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   void* cs = streamOf(device_);
   const size_t n = (size_t)sh.cur_B;
   const size_t total = n * (size_t)sh.n_learners;
-  if (total > kInboxFloats) throw std::runtime_error("update_priority: batch too large for the peer inbox");
+  if (total > kUpdateSlots) throw std::runtime_error("update_priority: batch too large for the peer inbox");
   torch::Tensor w;
   unsigned f = RR_PRIO_IS_WEIGHT;
   void* xs = sh.main;
@@ -431,23 +439,18 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
       }
     }
   }
-  // the update kernel all-gathers the learners' priorities itself (ExchangeArgs): every rank
-  // publishes its flag, contribution or not, so a returned wait also means that every rank has
-  // consumed the previous block of this parity and issued everything ordered before its flag
-  const uint64_t x = ++sh.xseq;
-  const size_t par = (size_t)(x & 1);
-  const size_t data_off = kInboxHeader + par * kInboxFloats * sizeof(float);
+  // the update kernel all-gathers the learners' priorities itself (ExchangeArgs): 8-byte words
+  // tagged with the sequence number, two slot arrays alternating -- a rank can be at most one
+  // update ahead of the slowest one, whose values it needed to finish the previous update
+  const uint64_t x = ++sh.useq;
+  const uint32_t tag = (uint32_t)(x % 0xffffffffull) + 1u;  // never 0 (the cleared arrays)
+  const size_t slots_off = kInboxSlotsOff + (size_t)(x & 1) * kUpdateSlots * sizeof(uint64_t);
   void* dst[8];
-  void* flg[8];
-  for (int r = 0; r < sh.world; ++r) {
-    dst[r] = sh.inbox[(size_t)r] + data_off;
-    flg[r] = sh.inbox[(size_t)r] + (par * 16 + (size_t)sh.rank) * 8;
-  }
-  uint8_t* mine = sh.inbox[(size_t)sh.rank];
+  for (int r = 0; r < sh.world; ++r) dst[r] = sh.inbox[(size_t)r] + slots_off;
   const bool learner = sh.my_learner >= 0;
   check(rr_update_priority_sharded(h_, (int)total, learner ? w.data_ptr<float>() : nullptr, learner ? (int)n : 0,
-                                   learner ? (int)((size_t)sh.my_learner * n) : 0, f, dst, flg, sh.world, x,
-                                   mine + par * 16 * 8, sh.world, reinterpret_cast<const float*>(mine + data_off), xs),
+                                   learner ? (int)((size_t)sh.my_learner * n) : 0, f, dst, sh.world, tag,
+                                   sh.inbox[(size_t)sh.rank] + slots_off, xs),
         "update_priority");
   sh.cur_B = 0;
   if (w.defined() && w.is_cuda() && cs != sh.main) check(rr_stream_fence(h_, cs), "update_priority");

@@ -121,6 +121,7 @@ constexpr int kMaxGroups = 2048;   // group prefixes held in shared memory (24 K
 constexpr int kSelThreads = 256;
 constexpr int kSelTargets = 8;     // targets per CTA of select_kernel: one per warp
 constexpr int kInlinePrio = 1024;  // largest update whose priorities travel as kernel parameters
+constexpr int kUpdStaged = 512;    // largest update every CTA stages in shared memory (update_kernel)
 constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
 constexpr int kTimelineCap = 1024;
 
@@ -135,20 +136,24 @@ struct Ctl {
   int mti[2];
   int error;                       // sticky RR_ERR_* raised by a kernel (mirrored to a mapped host word)
   unsigned int done_ctas;          // select_kernel with an eviction: CTAs that finished their targets
-  unsigned int gather_done;        // row_copy_kernel: CTAs that finished their stores (completion signal)
+  unsigned int pad_;
+  // row_copy_kernel with a completion signal: CTAs that finished their stores. One counter per
+  // stream a gather can run on (main, the two gather streams): gathers on different streams overlap.
+  unsigned int gather_done[4];
   unsigned long long n_exact;      // samples selected by the parallel search
   unsigned long long n_ordered;    // samples that needed the ordered walk
   unsigned long long n_popped;
   unsigned long long probe[16];    // clock64 at the phase boundaries of the last select_kernel (CTA 0)
   // Debug timeline (rr_debug_timeline): while tl_on != 0, CTA 0 of every selection, update and
-  // gather kernel stamps (globaltimer_ns << 4 | code) at its start (after its wait) and end.
+  // gather kernel stamps (globaltimer_ns << 8 | tag << 4 | code) at its start (after its wait) and end.
   unsigned int tl_on, tl_n;
   unsigned long long tl_umax, tl_gmax;  // latest end of any CTA of the last update / gather kernel
   unsigned long long tl[kTimelineCap];
 };
 
 // codes of Ctl::tl entries
-enum { kTlSelectBegin = 1, kTlSelectEnd = 2, kTlUpdateBegin = 3, kTlUpdateEnd = 4, kTlGatherBegin = 5, kTlGatherEnd = 6, kTlUpdateAllEnd = 7, kTlGatherAllEnd = 8 };
+enum { kTlSelectBegin = 1, kTlSelectEnd = 2, kTlUpdateBegin = 3, kTlUpdateEnd = 4, kTlGatherBegin = 5, kTlGatherEnd = 6, kTlUpdateAllEnd = 7, kTlGatherAllEnd = 8, kTlUpdateFlagsIn = 9,
+       kTlSelectEnter = 10, kTlUpdateEnter = 11, kTlGatherEnter = 12, kTlGatherSignalled = 13, kTlGatherComplete = 14 };
 
 // ------------------------------------------------- gather with conversion
 // A u8 field gathered as float32 / bfloat16 = byte / 255 (gather_convert.cu).
@@ -205,6 +210,13 @@ struct SelectArgs {
   int contract_fma;
   int force_ordered;    // test hook: always take the ordered walk
   int* host_err;        // mapped pinned host word mirroring Ctl::error (device pointer)
+  // A batch taken with RR_STREAM_OWN_DEFERRED: this kernel completes only after the gather of
+  // THAT batch has published `wait_val` in wait_flags[0..wait_n) -- the dependency rides in the
+  // kernel (one polling warp of CTA 0, after its own work) instead of a stream wait in front of
+  // it, which would cut the programmatic launch chain update -> select.
+  const unsigned long long* wait_flags;
+  int wait_n;
+  unsigned long long wait_val;
 };
 
 cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cudaStream_t stream);
@@ -215,32 +227,33 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
                           float alpha, int is_weight, cudaStream_t stream);
 
 // The all-gather of new priorities between the shards of a striped replay, fused into the update
-// kernel: CTA 0 stores this rank's n_mine values (the kernel's `prio` argument) at [offset,
-// offset + n_mine) of every rank's inbox (dst[i], its own included), publishes `epoch` at its flag
-// in each of them (st.release.sys); every CTA then acquires until the n_wait contributors' flags
-// in THIS rank's inbox have reached `epoch` and reads all n priorities from `inbox`.
+// kernel. Every priority travels as ONE 8-byte word (epoch << 32 | float bits): CTA 0 stores this
+// rank's n_mine values (the kernel's `prio` argument) at [offset, offset + n_mine) of every rank's
+// slot array (dst[i], its own included) with plain 64-bit stores -- no fence, no flag: a word is
+// valid when its upper half equals `epoch`. A CTA that needs element j polls word j of THIS rank's
+// array (`slots`) until then. One NVLink crossing per value instead of data, fence, flag.
+// Two arrays alternate by the parity of the exchange sequence: a sender can be at most one
+// exchange ahead of the slowest receiver (it needed that receiver's values to finish the previous one).
 struct ExchangeArgs {
   int on;                        // 0: no exchange, `prio` holds all n priorities
   int n_mine;
-  float* dst[kMaxPeers];         // every rank's inbox data + offset (peer-mapped)
-  unsigned long long* flag[kMaxPeers];
+  unsigned long long* dst[kMaxPeers];  // every rank's slot array + offset (peer-mapped)
   int n_dst;
-  unsigned long long epoch;
-  const unsigned long long* wait_flags;
-  int n_wait;
-  const float* inbox;            // this rank's inbox data: all n priorities once the flags are in
+  unsigned int epoch;            // low 32 bits of the exchange sequence number (never 0)
+  const unsigned long long* slots;     // this rank's slot array: all n priorities
   int* host_err;
 };
 
 // updatePriority (K2 + K7, prioritized_replay.h:105-119,235-245)
 // early: see update_kernel (select.cu); 0 is always correct
+// scratch: 12 * n bytes of device memory, needed when n > kUpdStaged (else ignored)
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
-                          cudaStream_t stream);
+                          void* scratch, cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,
-                                 const ExchangeArgs* xa, cudaStream_t stream);
+                                 const ExchangeArgs* xa, void* scratch, cudaStream_t stream);
 
 // ------------------------------------------------------------ actor math
 cudaError_t launch_nstep(int n_step, int K, float gamma, const float* reward, const uint8_t* terminal,

@@ -126,13 +126,16 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 // Debug timeline stamp (Ctl::tl in kernels.h): one thread per kernel event.
-#define RR_TL_STAMP(ctl, code)                                                                       \
+// stamp = globaltimer ns << 8 | tag << 4 | code; tag: low 4 bits of the batch's epoch (which batch)
+#define RR_TL_STAMP_TAG(ctl, code, tag)                                                              \
   do {                                                                                               \
     if ((ctl) != nullptr && *reinterpret_cast<volatile unsigned int*>(&(ctl)->tl_on) != 0u) {       \
       const unsigned int i_ = atomicAdd(&(ctl)->tl_n, 1u) % (unsigned int)kTimelineCap;              \
-      (ctl)->tl[i_] = (globaltimer_ns() << 4) | (unsigned long long)(code);                          \
+      (ctl)->tl[i_] = (globaltimer_ns() << 8) | (((unsigned long long)(tag) & 15ull) << 4) |         \
+                      (unsigned long long)(code);                                                    \
     }                                                                                                \
   } while (0)
+#define RR_TL_STAMP(ctl, code) RR_TL_STAMP_TAG(ctl, code, 0)
 
 // Host: opt a kernel in to `bytes` of dynamic shared memory. The attribute is
 // per device (context), and several host threads may launch at once, so the

@@ -107,6 +107,10 @@ struct Prefetched {
   int wait_n = 0;
   bool take_waits = false;  // this rank consumes the batch (a learner)
   unsigned long long epoch = 0;
+  // completion of the gather as a device-side flag (gathers drawn ahead publish the epoch in the
+  // second word of their id slot's header; a striped learner's batch has wait_flags above)
+  const unsigned long long* done_flags = nullptr;
+  int done_n = 0;
   bool restored = false;  // put back by rr_load for a host layer that owns its batch buffers (rr_restore_prefetched)
 };
 
@@ -202,6 +206,16 @@ struct rr_replay {
   std::vector<float*> israw;
   std::vector<unsigned long long*> ismax;
   std::vector<void*> idalloc;
+  cudaStream_t last_gstream = nullptr;  // the stream the most recent gather was launched on
+  // RR_STREAM_OWN_DEFERRED: the batch taken last is complete once defer_flags[0..defer_n) hold
+  // defer_val; the next selection carries the wait (SelectArgs::wait_flags), anything else that
+  // goes onto `main` first falls back to a stream wait for evSlot[defer_slot] (flush_pend_wait)
+  const unsigned long long* defer_flags = nullptr;
+  int defer_n = 0;
+  unsigned long long defer_val = 0;
+  int defer_slot = -1;
+  void* upd_scratch = nullptr;  // work area of update_kernel's CTA 0 for batches it does not stage (kUpdStaged)
+  size_t upd_scratch_cap = 0;
   std::vector<int> idcap;
   std::vector<bool> idbusy;
   int cur_ids = -1, cur_B = 0;
@@ -233,6 +247,7 @@ int join_gather_streams(rr_replay* r) {
     RR_CUDA(cudaStreamWaitEvent(r->main, r->evJoin, 0));
   }
   std::fill(r->slotPending.begin(), r->slotPending.end(), false);
+  r->defer_slot = -1;  // a deferred wait (RR_STREAM_OWN_DEFERRED) is covered by the join
   return RR_OK;
 }
 
@@ -272,6 +287,19 @@ int new_idslot(rr_replay* r) {
   cudaEvent_t ev = nullptr;
   RR_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   r->evSlot.push_back(ev);
+  return RR_OK;
+}
+
+// A batch taken with RR_STREAM_OWN_DEFERRED whose wait no selection has picked up: anything else
+// that is about to go onto `main` (or to hand main's order to somebody) orders it the plain way.
+int flush_pend_wait(rr_replay* r) {
+  if (r->defer_slot < 0) return RR_OK;
+  const int slot = r->defer_slot;
+  r->defer_slot = -1;
+  if (r->slotPending[(size_t)slot]) {
+    RR_CUDA(cudaStreamWaitEvent(r->main, r->evSlot[(size_t)slot], 0));
+    r->slotPending[(size_t)slot] = false;
+  }
   return RR_OK;
 }
 
@@ -591,6 +619,7 @@ int rr_destroy(rr_replay* r) {
     if (s.done) cudaEventDestroy(s.done);
   }
   for (auto* p : r->idalloc) cudaFree(p);
+  cudaFree(r->upd_scratch);
   auto free_pre = [](Prefetched& p) {
     if (p.external) return;  // the caller's buffers
     for (auto* f : p.fields) cudaFree(f);
@@ -1171,7 +1200,7 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   if (r->epoch == 0xfffffffeu) {  // the epoch tags of SelectArgs::ismax wrap: start over from a clean slate
     RR_SYNC_STREAMS(r);
     for (size_t i = 0; i < r->ismax.size(); ++i)
-      if (r->ismax[i]) RR_CUDA(cudaMemset(r->ismax[i], 0, sizeof(unsigned long long)));
+      if (r->ismax[i]) RR_CUDA(cudaMemset(r->ismax[i], 0, 2 * sizeof(unsigned long long)));  // + gather-done word
     r->epoch = 0;
   }
   rr::SelectArgs a;
@@ -1200,6 +1229,13 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
   a.contract_fma = r->contract_fma;
   a.force_ordered = r->force_ordered;
   a.host_err = r->host_err_dev;
+  if (r->defer_slot >= 0) {  // the batch taken just before: this selection completes after its gather
+    a.wait_flags = r->defer_flags;
+    a.wait_n = r->defer_n;
+    a.wait_val = r->defer_val;
+    r->slotPending[(size_t)r->defer_slot] = false;
+    r->defer_slot = -1;
+  }
   if (r->slotPending[(size_t)idslot]) {
     // the previous gather out of this id buffer (gather stream) must be done reading it
     const cudaError_t q = cudaEventQuery(r->evSlot[(size_t)idslot]);
@@ -1258,7 +1294,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     plan.p.dst_tab = route->dst_tab;
     plan.p.tab_cols = (int)r->fields.size();
     plan.p.rows_per_dst = rows_per_dst;
-    plan.p.done_counter = &r->ctl->gather_done;
+    plan.p.done_counter = nullptr;  // chosen with the stream below
     plan.p.n_signals = route->n_signals;
     for (int i = 0; i < route->n_signals; ++i) plan.p.signal[i] = route->signals[i];
     plan.p.signal_val = r->epoch;  // the same on every shard: all shards run all selections
@@ -1270,6 +1306,13 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     }
   }
   plan.p.tl_ctl = r->ctl;
+  plan.p.signal_val = r->epoch;  // (also the tag of this gather's timeline stamps)
+  if (rc == RR_OK && ahead && plan.p.n_signals == 0) {
+    // a gather drawn ahead publishes its completion in the id slot's header (see Prefetched::done_flags)
+    plan.p.done_counter = nullptr;  // chosen with the stream below
+    plan.p.n_signals = 1;
+    plan.p.signal[0] = r->ismax[idslot] + 1;
+  }
   if (rc == RR_OK && out_w != nullptr) {
     const int l = route ? route->my_learner : 0;
     if (l >= 0) {
@@ -1288,6 +1331,8 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     if (e == cudaSuccess) e = cudaStreamWaitEvent(gstream, r->evSel, 0);
     if (e != cudaSuccess) rc = fail(RR_ERR_CUDA, "gather stream: %s", cudaGetErrorString(e));
   }
+  if (plan.p.n_signals > 0)
+    plan.p.done_counter = &r->ctl->gather_done[gstream == r->main ? 0 : (gstream == r->gs[0] ? 1 : 2)];
   if (rc == RR_OK && conv.n > 0) {
     conv.B = B;
     conv.ids = ids;
@@ -1297,6 +1342,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     if (gstream == r->main) ++r->main_seq;
   }
   if (rc == RR_OK) rc = launch_plan(r, plan, gstream);
+  r->last_gstream = gstream;
   if (rc == RR_OK && gstream == r->main) ++r->main_seq;
   if (rc == RR_OK && ahead) {
     cudaError_t e = cudaEventRecord(r->evSlot[(size_t)idslot], gstream);
@@ -1462,6 +1508,13 @@ int prefetch_impl(rr_replay* r, int batch, void* const* out_fields, float* out_w
   p.wait_n = wait_n;
   p.take_waits = take_waits;
   p.epoch = r->epoch;
+  if (wait_n > 0 && route != nullptr && route->my_learner >= 0) {
+    p.done_flags = wait_flags;
+    p.done_n = wait_n;
+  } else if (ahead && route == nullptr) {
+    p.done_flags = r->ismax[slot] + 1;
+    p.done_n = 1;
+  }
   r->queue.push_back(p);
   return RR_OK;
 }
@@ -1511,12 +1564,29 @@ int rr_take_prefetched(rr_replay* r, void* stream) {
     return fail(RR_ERR_STATE, "rr_take_prefetched: no batch queued by rr_prefetch_into");
   int rc = check_device_error(r, "rr_take_prefetched");
   if (rc != RR_OK) return rc;
-  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  const bool no_stream = stream == RR_STREAM_NONE;
+  const bool deferred = stream == RR_STREAM_OWN_DEFERRED;
+  cudaStream_t cs = (no_stream || deferred) ? r->main : static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
+  rc = flush_pend_wait(r);
+  if (rc != RR_OK) return rc;
   Prefetched p = r->queue.front();
   r->queue.pop_front();
   r->cur_ids = p.idslot;
   r->cur_B = p.B;
+  if (no_stream) return RR_OK;  // the caller holds an event behind this batch's gather (rr_record_prefetched)
+  if (deferred && p.done_n > 0 && r->slotPending[(size_t)p.idslot]) {
+    std::unique_lock<std::mutex> lk(r->m_);  // rr_add reads slotPending
+    if (cudaEventQuery(r->evSlot[(size_t)p.idslot]) == cudaSuccess) {
+      r->slotPending[(size_t)p.idslot] = false;
+    } else {
+      r->defer_flags = p.done_flags;
+      r->defer_n = p.done_n;
+      r->defer_val = p.epoch;
+      r->defer_slot = p.idslot;
+    }
+    return RR_OK;
+  }
   rc = publish_batch(r, cs, p.idslot);
   if (rc == RR_OK && p.wait_n > 0 && p.take_waits) {
     // a learner of a striped replay: the batch is complete when every shard has published its epoch
@@ -1531,6 +1601,15 @@ int rr_take_prefetched(rr_replay* r, void* stream) {
 }
 
 int rr_prefetched(rr_replay* r) { return r == nullptr ? 0 : (int)r->queue.size(); }
+
+int rr_record_prefetched(rr_replay* r, void* event) {
+  if (r == nullptr || event == nullptr) return fail(RR_ERR_ARG, "rr_record_prefetched: bad argument");
+  if (r->queue.empty() || !r->queue.back().external)
+    return fail(RR_ERR_STATE, "rr_record_prefetched: no batch queued by rr_prefetch_into");
+  DeviceScope dev_scope(r->device);
+  RR_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(event), r->last_gstream ? r->last_gstream : r->main));
+  return RR_OK;
+}
 
 int rr_sample_select(rr_replay* r, int batch, float* out_weights, void* stream) {
   if (r == nullptr || batch <= 0 || out_weights == nullptr) return fail(RR_ERR_ARG, "rr_sample_select: bad argument");
@@ -1587,27 +1666,20 @@ int rr_update_priority(rr_replay* r, int n, const float* priority, unsigned flag
 }
 
 int rr_update_priority_sharded(rr_replay* r, int n_total, const float* priority_mine, int n_mine, int offset,
-                               unsigned flags, void* const* inbox_ptrs, void* const* flag_ptrs, int n_dst,
-                               uint64_t epoch, const void* wait_flags, int n_wait, const float* my_inbox,
-                               void* stream) {
+                               unsigned flags, void* const* slot_ptrs, int n_dst, uint32_t epoch,
+                               const void* my_slots, void* stream) {
   if (r == nullptr || n_total < 0 || n_mine < 0 || offset < 0 || offset + n_mine > n_total || n_dst < 0 ||
-      n_dst > rr::kMaxPeers || n_wait < 0 || n_wait > rr::kMaxPeers || my_inbox == nullptr ||
-      (n_mine > 0 && priority_mine == nullptr) || (n_dst > 0 && (!inbox_ptrs || !flag_ptrs)) ||
-      (n_wait > 0 && wait_flags == nullptr))
+      n_dst > rr::kMaxPeers || my_slots == nullptr || epoch == 0 || (n_mine > 0 && priority_mine == nullptr) ||
+      (n_dst > 0 && !slot_ptrs))
     return fail(RR_ERR_ARG, "rr_update_priority_sharded: bad argument");
   rr::ExchangeArgs xa;
   memset(&xa, 0, sizeof(xa));
   xa.on = 1;
   xa.n_mine = n_mine;
-  for (int i = 0; i < n_dst; ++i) {
-    xa.dst[i] = static_cast<float*>(inbox_ptrs[i]) + offset;
-    xa.flag[i] = static_cast<unsigned long long*>(flag_ptrs[i]);
-  }
+  for (int i = 0; i < n_dst; ++i) xa.dst[i] = static_cast<unsigned long long*>(slot_ptrs[i]) + offset;
   xa.n_dst = n_dst;
   xa.epoch = epoch;
-  xa.wait_flags = static_cast<const unsigned long long*>(wait_flags);
-  xa.n_wait = n_wait;
-  xa.inbox = my_inbox;
+  xa.slots = static_cast<const unsigned long long*>(my_slots);
   xa.host_err = r->host_err_dev;
   static const float none = 0.0f;
   return update_impl(r, n_total, n_mine > 0 ? priority_mine : &none, flags, &xa, stream);
@@ -1622,6 +1694,8 @@ int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, cons
   if (erc != RR_OK) return erc;
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DeviceScope dev_scope(r->device);
+  erc = flush_pend_wait(r);
+  if (erc != RR_OK) return erc;
   const bool prio_dev = (flags & RR_PRIO_DEVICE) != 0;
   const int is_weight = (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0;
   const float* dprio = priority;
@@ -1629,13 +1703,22 @@ int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, cons
   // the selection that wrote this batch's ids is at least two launches back on `main`: the update
   // may stage them before its griddepcontrol.wait (update_kernel, `early`)
   const int early = r->main_seq > r->sel_seq[(size_t)r->cur_ids] ? 1 : 0;
+  if ((size_t)n > r->upd_scratch_cap) {
+    RR_CUDA(cudaStreamSynchronize(r->main));  // an update in flight may still work in the old area
+    RR_CUDA(cudaFree(r->upd_scratch));
+    r->upd_scratch = nullptr;
+    r->upd_scratch_cap = 0;
+    const size_t cap = std::max((size_t)n, (size_t)4096);
+    RR_CUDA(cudaMalloc(&r->upd_scratch, 12 * cap));
+    r->upd_scratch_cap = cap;
+  }
   if (prio_dev) {
     int rc = order_after_caller_(r, cs);
     if (rc != RR_OK) return rc;
   } else if ((xa ? xa->n_mine : n) <= rr::kInlinePrio) {
     // a learner-sized batch handed over in host memory: the priorities travel in the launch parameters
     RR_CUDA(rr::launch_update_inline(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, priority,
-                                     r->alpha, is_weight, early, xa, r->main));
+                                     r->alpha, is_weight, early, xa, r->upd_scratch, r->main));
     dprio = nullptr;
   } else {
     PrioStage& st = r->pstage[r->pstage_next];
@@ -1659,7 +1742,7 @@ int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, cons
   }
   if (dprio != nullptr)
     RR_CUDA(rr::launch_update(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, dprio, r->alpha,
-                              is_weight, early, xa, r->main));
+                              is_weight, early, xa, r->upd_scratch, r->main));
   ++r->main_seq;
   r->launches++;
   if (prio_dev && cs != r->main) {
@@ -1697,6 +1780,8 @@ int rr_stream_fence(rr_replay* r, void* stream) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_stream_fence: null");
   DeviceScope dev_scope(r->device);
   std::unique_lock<std::mutex> lk(r->m_);
+  int prc = flush_pend_wait(r);
+  if (prc != RR_OK) return prc;
   if (static_cast<cudaStream_t>(stream) == r->main) return join_gather_streams(r);
   RR_CUDA(cudaEventRecord(r->evOut, r->main));
   RR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->evOut, 0));
@@ -1838,9 +1923,11 @@ int rr_cycle_bench(rr_replay* r, int batch, int depth, int steps, int warmup, in
       if (rc == RR_OK) rc = rr_update_priority(r, batch, p, prio_flags, main);
       return rc;
     }
-    rc = rr_take_prefetched(r, main);
-    if (rc == RR_OK) rc = rr_update_priority(r, batch, p, prio_flags, main);
+    // the reference's order (rela/prioritized_replay.h:208-232): hand out the oldest batch, draw a
+    // new one, and only then the update of the batch handed out
+    rc = rr_take_prefetched(r, RR_STREAM_OWN_DEFERRED);
     if (rc == RR_OK) rc = issue();
+    if (rc == RR_OK) rc = rr_update_priority(r, batch, p, prio_flags, main);
     return rc;
   };
   DeviceScope dev_scope(r->device);

@@ -145,10 +145,11 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
     // The trigger comes AFTER the wait: a dependent that starts early (the
     // priority update, which does not need this kernel's output) may then rely
     // on everything this kernel waited for -- the selection -- being complete.
+    if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP_TAG(p.tl_ctl, kTlGatherEnter, p.signal_val);
     pdl_wait();
     pdl_launch_dependents();
     if (probe && tid == 0) probe[2] = clock64();
-    if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP(p.tl_ctl, kTlGatherBegin);
+    if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP_TAG(p.tl_ctl, kTlGatherBegin, p.signal_val);
     if (active) {
       const uint64_t evict_first = l2_policy_evict_first();  // a gather reads every source row once
       uint32_t use = 0;
@@ -173,7 +174,7 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       // exits; kernel completion makes them visible. With a completion signal
       // they must be complete before the flag is published.
       if (p.n_signals > 0) bulk_wait_all<0>(); else bulk_wait_read<0>();
-      if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP(p.tl_ctl, kTlGatherEnd);
+      if (blockIdx.x == 0 && tid == 0 && p.ids != nullptr) RR_TL_STAMP_TAG(p.tl_ctl, kTlGatherEnd, p.signal_val);
       if (tid == 0 && p.ids != nullptr && p.tl_ctl != nullptr &&
           *reinterpret_cast<volatile unsigned int*>(&p.tl_ctl->tl_on) != 0u)
         atomicMax(&p.tl_ctl->tl_gmax, globaltimer_ns());
@@ -196,15 +197,15 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
   if (tid == 0) {
     __threadfence_system();
     sh_last = atomicAdd(p.done_counter, 1u) == gridDim.x - 1;
-    if (sh_last) {
-      atomicExch(p.done_counter, 0u);
-      __threadfence_system();
-    }
+    // (the other CTAs' fenced stores happen-before their increments, which this CTA's increment
+    // has observed: the release stores below publish them all, no further fence is needed)
+    if (sh_last) atomicExch(p.done_counter, 0u);
   }
   __syncthreads();
   if (!sh_last) return;
   if (tid < p.n_signals)
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.signal[tid]), "l"(p.signal_val) : "memory");
+  if (tid == 0 && p.ids != nullptr) RR_TL_STAMP_TAG(p.tl_ctl, kTlGatherSignalled, p.signal_val);
   // a rank that consumes the batch: wait here for the other shards' flags, so that this kernel's
   // completion IS the batch's (the flags are in this GPU's memory; one CTA polls them)
   if (tid < p.wait_n) {
@@ -223,6 +224,10 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
       }
       __nanosleep(100);
     }
+  }
+  if (p.wait_n > 0) {
+    __syncthreads();
+    if (tid == 0 && p.ids != nullptr) RR_TL_STAMP_TAG(p.tl_ctl, kTlGatherComplete, p.signal_val);
   }
 }
 

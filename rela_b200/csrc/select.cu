@@ -332,15 +332,16 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
     mbar_wait(&bar_rng, 0);
     gen_uniforms(mt, mti0, a.B, i0, i0 + nT, s_target, &sh_mti);
   }
+  if (probing) RR_TL_STAMP_TAG(ctl, kTlSelectEnter, a.epoch);
   pdl_wait();
   pdl_launch_dependents();  // after the wait: see `rng_early`, and `early` of update_kernel
   if (probing) {
     ctl->probe[0] = clock64();
-    RR_TL_STAMP(ctl, kTlSelectBegin);
+    RR_TL_STAMP_TAG(ctl, kTlSelectBegin, a.epoch);
     if (*reinterpret_cast<volatile unsigned int*>(&ctl->tl_on) != 0u) {
       const unsigned long long um = atomicExch(&ctl->tl_umax, 0ull), gm = atomicExch(&ctl->tl_gmax, 0ull);
-      if (um) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (um << 4) | kTlUpdateAllEnd;
-      if (gm) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (gm << 4) | kTlGatherAllEnd;
+      if (um) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (um << 8) | kTlUpdateAllEnd;
+      if (gm) ctl->tl[atomicAdd(&ctl->tl_n, 1u) % kTimelineCap] = (gm << 8) | kTlGatherAllEnd;
     }
   }
   // ---- 1. group sums and minima (and the RNG state, if not yet) by bulk copies (TMA)
@@ -613,7 +614,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   if (probing) {
     ctl->probe[4] = clock64();
-    RR_TL_STAMP(ctl, kTlSelectEnd);
+    RR_TL_STAMP_TAG(ctl, kTlSelectEnd, a.epoch);
   }
 
   // ---- 7. RNG state after the B draws: the CTA of the last targets (the only one that had to
@@ -626,6 +627,19 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   if (blockIdx.x == 0 && tid == 0) {
     if (exact) ctl->n_exact += 1; else ctl->n_ordered += 1;
     ctl->probe[5] = clock64();
+  }
+  if (blockIdx.x == 0 && tid < a.wait_n) {  // SelectArgs::wait_flags: normally long published
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+      unsigned long long v;
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.wait_flags + tid) : "memory");
+      if (v >= a.wait_val) break;
+      if (globaltimer_ns() - t0 > 10ull * 1000 * 1000 * 1000) {
+        raise_error(a, RR_ERR_CUDA);  // the gather of the batch taken before this selection never finished
+        break;
+      }
+      __nanosleep(100);
+    }
   }
   if (a.pop_n <= 0) return;
 
@@ -779,7 +793,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
                                                              const int32_t* __restrict__ ids, int n,
                                                              const __grid_constant__ Prio prio, float alpha,
                                                              int is_weight, const Tiles tiles, int by_group,
-                                                             int early, const ExchangeArgs xa) {
+                                                             int early, const ExchangeArgs xa, uint8_t* scratch) {
   struct EndStamp {  // debug timeline: the latest end of any CTA of this kernel
     Ctl* c;
     __device__ ~EndStamp() {
@@ -788,7 +802,14 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     }
   } end_stamp{ctl};
   extern __shared__ __align__(128) uint8_t sm_raw[];
-  int32_t* s_id = reinterpret_cast<int32_t*>(sm_raw);  // slot id; -1 once it is known to be evicted
+  // A learner-sized batch (kUpdStaged) is staged in shared memory by every CTA. A larger one (the
+  // batch of all learners of a striped replay) is not: two resident CTAs per SM must fit into the
+  // shared memory a gather drawn ahead leaves free (kGatherReserve), or the CTAs polling the
+  // exchange flags below keep the gathers -- whose rows the other shards are waiting for -- off
+  // the SMs. The group CTAs then read ids and priorities from L2, CTA 0 works in `scratch`.
+  const bool staged = scratch == nullptr;
+  uint8_t* work = staged ? sm_raw : scratch;
+  int32_t* s_id = reinterpret_cast<int32_t*>(work);  // slot id; -1 once it is known to be evicted
   float* s_new = reinterpret_cast<float*>(s_id + n);
   float* s_diff = s_new + n;
   __shared__ double r_sum[kUpdThreads / 32], r_abs[kUpdThreads / 32];
@@ -797,8 +818,8 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kUpdThreads / 32;
-  const bool prio_early = early && PrioTraits<Prio>::kInLaunch && !xa.on;
-  if (early) {
+  const bool prio_early = staged && early && PrioTraits<Prio>::kInLaunch && !xa.on;
+  if (early && staged) {
     for (int i = tid; i < n; i += kUpdThreads) {
       s_id[i] = ids[i];
       if (prio_early) {
@@ -807,26 +828,31 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
       }
     }
   }
+  if (blockIdx.x == 0 && tid == 0) RR_TL_STAMP_TAG(ctl, kTlUpdateEnter, xa.epoch);
   pdl_wait();
   // the trigger comes AFTER the wait: a kernel that starts early behind this one may rely on
   // everything this kernel waited for being complete (see `early`, and select_kernel's rng_early)
   pdl_launch_dependents();
-  if (blockIdx.x == 0 && tid == 0) RR_TL_STAMP(ctl, kTlUpdateBegin);
-  if (xa.on) {
+  if (blockIdx.x == 0 && tid == 0) RR_TL_STAMP_TAG(ctl, kTlUpdateBegin, xa.epoch);
+  if (xa.on && blockIdx.x == 0) {
     // striped replay: all-gather of the learners' priorities through peer memory (ExchangeArgs)
-    if (blockIdx.x == 0) {
-      for (int p = 0; p < xa.n_dst; ++p)
-        for (int i = tid; i < xa.n_mine; i += kUpdThreads) xa.dst[p][i] = prio_at(prio, i);
-      __threadfence_system();
-      __syncthreads();
-      if (tid < xa.n_dst) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(xa.flag[tid]), "l"(xa.epoch) : "memory");
-    }
-    if (tid < xa.n_wait) {
+    for (int p = 0; p < xa.n_dst; ++p)
+      for (int i = tid; i < xa.n_mine; i += kUpdThreads) {
+        const unsigned long long word =
+            ((unsigned long long)xa.epoch << 32) | (unsigned long long)__float_as_uint(prio_at(prio, i));
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(xa.dst[p] + i), "l"(word) : "memory");
+      }
+  }
+  // priority j of the exchanged block: poll its word until it carries this exchange's epoch
+  auto exchanged = [&](int j) -> float {
+    const unsigned long long* slot = xa.slots + j;
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+    if ((unsigned int)(v >> 32) != xa.epoch) {
       const unsigned long long t0 = globaltimer_ns();
       for (;;) {
-        unsigned long long v;
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(xa.wait_flags + tid) : "memory");
-        if (v >= xa.epoch) break;
+        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+        if ((unsigned int)(v >> 32) == xa.epoch) break;
         if (globaltimer_ns() - t0 > 10ull * 1000 * 1000 * 1000) {
           ctl->error = 2;  // RR_ERR_CUDA: a shard never published its priorities
           if (xa.host_err != nullptr) {
@@ -835,26 +861,24 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
           }
           break;
         }
-        __nanosleep(100);
       }
     }
-    __syncthreads();
-  }
+    return __uint_as_float((unsigned int)v);
+  };
   // CTA 0 raises every priority; a group CTA raises only the few it substitutes (a batch of 4096
   // over 1280 group CTAs would otherwise pay 5 M fp64 pows for 4096 values): there s_new is raw
   const bool raise_now = blockIdx.x == 0;
-  if (!early || !prio_early) {
+  if ((staged || blockIdx.x == 0) && (!early || !prio_early)) {
     for (int i = tid; i < n; i += kUpdThreads) {
-      if (!early) s_id[i] = ids[i];
+      if (!early || !staged) s_id[i] = ids[i];
       if (!prio_early) {
-        // after an exchange the priorities of all learners are in this rank's inbox (written by
-        // other GPUs: read through L2)
-        const float p = xa.on ? __ldcg(xa.inbox + i) : prio_at(prio, i);
+        const float p = xa.on ? exchanged(i) : prio_at(prio, i);
         s_new[i] = (is_weight || !raise_now) ? p : pow_alpha(p, alpha);
       }
     }
   }
   __syncthreads();
+  if (xa.on && blockIdx.x == 0 && tid == 0) RR_TL_STAMP_TAG(ctl, kTlUpdateFlagsIn, xa.epoch);
 
   if (blockIdx.x > 0) {
     __shared__ __align__(16) float sub[kWarps][256];
@@ -865,6 +889,13 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     const int gl = tiles.group_log2;
     const int span_log2 = kLeafLog2 + gl;
     const int ncand = by_group ? tiles.ng : n;
+    auto id_at = [&](int j) -> int { return staged ? s_id[j] : ids[j]; };
+    // the final weight of batch element j (only ever asked for elements this CTA substitutes)
+    auto weight_at = [&](int j) -> float {
+      if (staged) return (is_weight || prio_early) ? s_new[j] : pow_alpha(s_new[j], alpha);
+      const float p = xa.on ? exchanged(j) : prio_at(prio, j);
+      return is_weight ? p : pow_alpha(p, alpha);
+    };
     // the grid is capped (two CTAs per SM, replay.cu): a CTA takes candidates c, c + G, ...
     for (int c = (int)blockIdx.x - 1; c < ncand; c += (int)gridDim.x - 1) {
     __syncthreads();  // the previous candidate's shared state is no longer read
@@ -877,10 +908,10 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     if (by_group) {
       g = c;
     } else {
-      g = s_id[c] >> span_log2;  // (negative for a slot an earlier candidate of this CTA found evicted)
+      g = id_at(c) >> span_log2;  // (negative for a slot an earlier candidate of this CTA found evicted)
       int dup = g < 0 ? 1 : 0;  // an earlier element of the batch in the same group: that element's CTA covers it
       for (int j = tid; j < c; j += kUpdThreads)
-        if ((s_id[j] >> span_log2) == g) dup = 1;
+        if ((id_at(j) >> span_log2) == g) dup = 1;
       if (__syncthreads_or(dup)) continue;
     }
     __syncthreads();
@@ -891,7 +922,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
       unsigned long long m = 0ull;
       int lo = n, hi = -1;
       for (int j = tid; j < n; j += kUpdThreads) {
-        const int sid = s_id[j];
+        const int sid = id_at(j);
         if ((sid >> span_log2) == g) {
           m |= 1ull << ((sid >> kLeafLog2) & ((1 << gl) - 1));
           lo = min(lo, j);
@@ -929,10 +960,11 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
       s_ls[tid] = tiles.leaf[lb + tid];
       s_lm[tid] = tiles.leafmin[lb + tid];
     }
-    for (int j = jlo + tid; j <= jhi; j += kUpdThreads) {
-      const int sid = s_id[j];
-      if ((sid >> span_log2) == g && evicted[sid] != 0) s_id[j] = -1;  // an evicted slot keeps weight 0
-    }
+    if (staged)
+      for (int j = jlo + tid; j <= jhi; j += kUpdThreads) {
+        const int sid = s_id[j];
+        if ((sid >> span_log2) == g && evicted[sid] != 0) s_id[j] = -1;  // an evicted slot keeps weight 0
+      }
     __syncthreads();
     float* mine = sub[warp];
     for (int k = warp; k < L; k += kWarps) {
@@ -948,10 +980,10 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
       }
       __syncwarp();
       for (int j = jlo + lane; j <= jhi; j += 32) {
-        const int sid = s_id[j];
-        const bool last = !(j + 1 < n && s_id[j + 1] == sid);
-        if (sid >= base && sid < base + 256 && last)
-          mine[sid - base] = (is_weight || prio_early) ? s_new[j] : pow_alpha(s_new[j], alpha);
+        const int sid = id_at(j);
+        const bool last = !(j + 1 < n && id_at(j + 1) == sid);
+        if (sid >= base && sid < base + 256 && last && (staged || evicted[sid] == 0))
+          mine[sid - base] = weight_at(j);
       }
       __syncwarp();
       const float4 a = reinterpret_cast<const float4*>(mine)[lane * 2];
@@ -1048,7 +1080,7 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     for (int i = 0; i < n; ++i) diff += (double)s_diff[i];  // evicted entries hold +0.0f
     ctl->sum += diff;
   }
-  if (tid == 0) RR_TL_STAMP(ctl, kTlUpdateEnd);
+  if (tid == 0) RR_TL_STAMP_TAG(ctl, kTlUpdateEnd, xa.epoch);
 }
 
 // ----------------------------------------------------------------- launches
@@ -1074,6 +1106,13 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
 }
 
 namespace {
+inline int upd_staged_max() {  // EXPERIMENT (to be removed): RR_UPD_STAGED overrides kUpdStaged
+  static const int v = [] {
+    const char* e = getenv("RR_UPD_STAGED");
+    return e ? atoi(e) : kUpdStaged;
+  }();
+  return v;
+}
 inline int update_grid(const Tiles& tiles, int n, int* by_group) {
   *by_group = tiles.ng <= n ? 1 : 0;
   // CTA 0: sum_ and weights; the others: candidate groups, at most two CTAs per SM -- with a fused
@@ -1090,8 +1129,10 @@ inline int update_grid(const Tiles& tiles, int n, int* by_group) {
 
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
-                          cudaStream_t stream) {
-  const size_t smem = (size_t)n * 12;
+                          void* scratch, cudaStream_t stream) {
+  if (n > upd_staged_max() && scratch == nullptr) return cudaErrorInvalidValue;
+  uint8_t* sc = n > upd_staged_max() ? static_cast<uint8_t*>(scratch) : nullptr;
+  const size_t smem = sc ? 0 : (size_t)n * 12;
   ExchangeArgs none;
   memset(&none, 0, sizeof(none));
   cudaError_t e = ensure_dynamic_smem(update_kernel<const float*>, smem);
@@ -1099,25 +1140,27 @@ cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t*
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    prio, alpha, is_weight, tiles, by_group, early, xa ? *xa : none);
+                    prio, alpha, is_weight, tiles, by_group, early, xa ? *xa : none, sc);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,
-                                 const ExchangeArgs* xa, cudaStream_t stream) {
+                                 const ExchangeArgs* xa, void* scratch, cudaStream_t stream) {
+  if (n > upd_staged_max() && scratch == nullptr) return cudaErrorInvalidValue;
+  uint8_t* sc = n > upd_staged_max() ? static_cast<uint8_t*>(scratch) : nullptr;
   const int n_host = xa ? xa->n_mine : n;  // with an exchange the launch carries this rank's share only
   if (n_host > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
   memcpy(pin.v, prio_host, sizeof(float) * (size_t)n_host);
   ExchangeArgs none;
   memset(&none, 0, sizeof(none));
-  const size_t smem = (size_t)n * 12;
+  const size_t smem = sc ? 0 : (size_t)n * 12;
   cudaError_t e = ensure_dynamic_smem(update_kernel<PrioInline>, smem);
   if (e != cudaSuccess) return e;
   int by_group;
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<PrioInline>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
-                    pin, alpha, is_weight, tiles, by_group, early, xa ? *xa : none);
+                    pin, alpha, is_weight, tiles, by_group, early, xa ? *xa : none, sc);
 }
 
 }  // namespace rr

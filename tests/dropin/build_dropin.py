@@ -52,6 +52,7 @@ def build(force=False):
         "types.o": os.path.join(REF, "rela", "types.cc"),
         "replay_core.o": os.path.join(cpp, "replay_core.cc"),
         "sharded_core.o": os.path.join(cpp, "sharded_core.cc"),
+        "issuer_core.o": os.path.join(cpp, "issuer_core.cc"),
         "counting_env.o": os.path.join(HERE, "counting_env.cc"),
         "seq_fixture.o": os.path.join(HERE, "seq_fixture.cc"),
         "sequence_assembler.o": os.path.join(cpp, "sequence_assembler.cc"),
@@ -76,18 +77,18 @@ def build(force=False):
     os.makedirs(o("reference"), exist_ok=True)
     lib = ["-L" + os.path.join(ROOT, "rela_b200"), "-lrela_b200",
            "-Wl,-rpath," + os.path.join("$ORIGIN", "..", "..", "..", "rela_b200")]
-    subprocess.run(["g++", "-shared", "-o", o("rela.so"), o("pybind.o"), o("types.o"), o("replay_core.o"), o("sharded_core.o")] + lib + ld,
+    subprocess.run(["g++", "-shared", "-o", o("rela.so"), o("pybind.o"), o("types.o"), o("replay_core.o"), o("sharded_core.o"), o("issuer_core.o")] + lib + ld,
                    check=True)
     subprocess.run(["g++", "-shared", "-o", o("counting_env.so"), o("counting_env.o")] + ld, check=True)
     subprocess.run(["g++", "-shared", "-o", o("seq_fixture.so"), o("seq_fixture.o"), o("sequence_assembler.o"),
-                    o("replay_core.o"), o("sharded_core.o"), o("types.o")] + lib + ld, check=True)
+                    o("replay_core.o"), o("sharded_core.o"), o("issuer_core.o"), o("types.o")] + lib + ld, check=True)
     subprocess.run(["g++", "-shared", "-o", os.path.join(o("reference"), "rela.so"), o("pybind_ref.o"), o("types.o")] + ld,
                    check=True)
     import nvidia.cuda_runtime as cr
 
     ld = ld + ["-L" + os.path.join(list(cr.__path__)[0], "lib"), "-l:libcudart.so.12"]
     pyld = subprocess.run(["python3-config", "--ldflags", "--embed"], capture_output=True, text=True).stdout.split()
-    subprocess.run(["g++", "-o", o("test_preplay"), o("test_preplay.o"), o("types.o"), o("replay_core.o"), o("sharded_core.o")] + lib + ld
+    subprocess.run(["g++", "-o", o("test_preplay"), o("test_preplay.o"), o("types.o"), o("replay_core.o"), o("sharded_core.o"), o("issuer_core.o")] + lib + ld
                    + pyld, check=True)
     return True
 

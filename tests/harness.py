@@ -664,6 +664,7 @@ class CppReplay(CudaReplay):
     def sample(self, B, want_rows=True):
         batch, w = self.r.sample(B, str(self.dev))
         ids = np.zeros(B, dtype=np.int32)
+        self.r.sync()  # with prefetch > 0 the host layer's issuer thread makes the batch current asynchronously
         self.capi.check(self.lib.rr_last_sample_ids(self.h, B, ids.ctypes.data))
         rows = None
         if want_rows:
@@ -691,6 +692,10 @@ class CppReplay(CudaReplay):
 
     def num_add(self):
         return self.r.num_add()
+
+    def sync(self):
+        self.r.sync()  # the host layer's own sync: also drains its issuer thread
+        return 0
 
 
 # ---------------------------------------------------------------- golden vectors

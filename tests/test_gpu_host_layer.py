@@ -62,6 +62,67 @@ def test_host_layer_python_surface():
     r.sync()
 
 
+@pytest.mark.parametrize("issuer", ["1", "0"])
+@pytest.mark.parametrize("prefetch", [1, 3])
+def test_prefetch_through_the_host_layer_matches_oracle(monkeypatch, prefetch, issuer):
+    """prefetch > 0 through the C++ host layer, with its issuer thread (rela_b200/cpp/issuer_core.cc:
+    batches drawn ahead and host-priority updates are launched by one background thread in call
+    order) and without it (RELA_B200_ISSUER_THREAD=0: everything on the calling thread): the
+    reference's prefetch semantics either way -- ids, bytes, weights, ring state, sum_."""
+    monkeypatch.setenv("RELA_B200_ISSUER_THREAD", issuer)
+    schema = ff_schema(frame=(1, 12, 12), n_actions=4)
+    cap, alpha = 256, 0.6
+    ops = gen_trace(schema, cap, 19 + prefetch, 80, 20, 32)
+    orc = Oracle(schema, cap, 3, alpha, 0.4, prefetch)
+    cu = CppReplay(schema, cap, 3, alpha, 0.4, prefetch)
+    ra = apply_trace(orc, ops, alpha, False)
+    rb = apply_trace(cu, ops, alpha, True)
+    assert cu.sync() == 0
+    compare_records(ra, rb, "oracle prefetch=%d vs host layer (issuer thread %s)" % (prefetch, issuer))
+    assert orc.state() == cu.state()
+    st = cu.stats()
+    assert st["samples_ordered"] == 0 and st["device_errors"] == 0
+
+
+@pytest.mark.parametrize("issuer", ["1", "0"])
+def test_prefetch_errors_surface_at_the_call_that_caused_them(monkeypatch, issuer):
+    """The reference asserts in sample() / updatePriority() (prioritized_replay.h:203-206,236-237);
+    with batches drawn ahead -- by the issuer thread or not -- the host layer raises at the same call."""
+    import torch
+    from rela_b200 import _C
+
+    monkeypatch.setenv("RELA_B200_ISSUER_THREAD", issuer)
+    r = _C.FFPrioritizedReplay(64, 1, 0.6, 0.4, 2)
+    with pytest.raises(RuntimeError, match="empty"):
+        r.sample(4, "cuda:0")
+    K = 16
+    tr = _C.FFTransition({"s": torch.randint(0, 255, (K, 1, 8, 8), dtype=torch.uint8)}, {"a": torch.arange(K)},
+                         torch.randn(K), torch.zeros(K, dtype=torch.bool), torch.ones(K),
+                         {"s": torch.randint(0, 255, (K, 1, 8, 8), dtype=torch.uint8)})
+    r.add(tr, torch.rand(K) + 0.1)
+    with pytest.raises(RuntimeError):
+        r.update_priority(torch.rand(8))  # nothing sampled yet
+    batch, w = r.sample(8, "cuda:0")
+    ids = batch.action["a"].cpu()
+    assert torch.equal(batch.obs["s"].cpu(), tr.obs["s"][ids])
+    with pytest.raises(RuntimeError, match="not been updated"):
+        r.sample(8, "cuda:0")
+    with pytest.raises(RuntimeError):
+        r.update_priority(torch.rand(7))
+    with pytest.raises(RuntimeError, match="1-D"):
+        r.update_priority(torch.rand(8, 1))
+    r.update_priority(torch.rand(8))
+    with pytest.raises(RuntimeError, match="differs"):
+        r.sample(4, "cuda:0")  # batches of 8 are already drawn ahead
+    for _ in range(5):
+        batch, w = r.sample(8, "cuda:0")
+        ids = batch.action["a"].cpu()
+        assert torch.equal(batch.next_obs["s"].cpu(), tr.next_obs["s"][ids])
+        r.update_priority(torch.rand(8).cuda() if _ % 2 else torch.rand(8))  # device / host priorities mixed
+    r.sync()
+    del r  # destruction with batches still drawn ahead
+
+
 def test_device_pow_tolerance():
     """Default C ABI mode (device pow, no RR_PRIO_IS_WEIGHT): stored weights are
     within 1e-6 relative of torch.pow (north_star tolerance for priorities)."""

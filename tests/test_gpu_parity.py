@@ -8,9 +8,9 @@ from harness import (CudaReplay, Oracle, apply_trace, compare_records, ff_schema
 pytestmark = pytest.mark.gpu
 
 
-def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, **cuda_kw):
+def _run_pair(schema, cap, seed, alpha, beta, prefetch, ops, cuda_cls=CudaReplay, **cuda_kw):
     orc = Oracle(schema, cap, seed, alpha, beta, prefetch)
-    cu = CudaReplay(schema, cap, seed, alpha, beta, prefetch, **cuda_kw)
+    cu = cuda_cls(schema, cap, seed, alpha, beta, prefetch, **cuda_kw)
     ra = apply_trace(orc, ops, alpha, False)
     rb = apply_trace(cu, ops, alpha, False)
     assert cu.sync() == 0
@@ -292,6 +292,34 @@ def test_large_batches(B):
     schema = [Field("action.a", "int64", ()), Field("reward", "float32", (3,))]
     cap = 40000
     ops = gen_trace(schema, cap, 13, 6, 5000, B, prefill=cap - 2000, adds_per_cycle=(1, 2))
+    _run_pair(schema, cap, 21, 0.6, 0.4, 0, ops)
+
+
+@pytest.mark.parametrize("B,group_log2", [(700, 6), (1024, 1), (2000, 0)])
+def test_large_batches_drawn_ahead_see_evictions(monkeypatch, B, group_log2):
+    """Batches above kUpdStaged (512) are not staged in shared memory by update_kernel: its group
+    CTAs read ids, priorities and eviction flags from L2 and CTA 0 works in a device scratch area.
+    With batches drawn ahead, later evictions hit slots of a pending batch, so the update must skip
+    them (rela/prioritized_replay.h:110-112) on that path too -- in both candidate modes (groups of
+    64 leaves: a few groups; groups of 1-2 leaves: more groups than a CTA's share)."""
+    from harness import CudaReplayHostPrefetch, Field
+
+    monkeypatch.setenv("RR_GROUP_LOG2", str(group_log2))
+    schema = [Field("action.a", "int64", ()), Field("reward", "float32", (3,))]
+    cap, alpha, prefetch = 20000, 0.6, 2
+    ops = gen_trace(schema, cap, 23 + B, 16, 3000, B, prefill=cap - 1000, adds_per_cycle=(1, 2), zero_frac=0.02)
+    cu = _run_pair(schema, cap, 3, alpha, 0.4, prefetch, ops, cuda_cls=CudaReplayHostPrefetch)
+    assert cu.stats()["samples_ordered"] == 0
+
+
+def test_large_batch_more_groups_than_elements(monkeypatch):
+    """n > kUpdStaged AND ng > n: unstaged update_kernel whose candidates are batch elements."""
+    from harness import Field
+
+    monkeypatch.setenv("RR_GROUP_LOG2", "0")
+    schema = [Field("action.a", "int64", ()), Field("reward", "float32", (3,))]
+    cap = 300000  # 375,000 slots = 1,465 groups of one leaf > 700
+    ops = gen_trace(schema, cap, 5, 8, 20000, 700, prefill=cap - 10000, adds_per_cycle=(1, 2))
     _run_pair(schema, cap, 21, 0.6, 0.4, 0, ops)
 
 

@@ -15,7 +15,8 @@ import rela_b200
 from rela_b200 import capi
 from cycle_probe import fill
 
-NAMES = {1: "S+", 2: "S-", 3: "U+", 4: "U-", 5: "G+", 6: "G-", 7: "Uall-", 8: "Gall-"}
+NAMES = {1: "S+", 2: "S-", 3: "U+", 4: "U-", 5: "G+", 6: "G-", 7: "Uall-", 8: "Gall-", 9: "Ux", 10: "S0", 11: "U0",
+         12: "G0", 13: "Gsig", 14: "Gdone"}
 
 
 def main():
@@ -46,9 +47,9 @@ def main():
         L.rr_debug_timeline(h, 1, buf.ctypes.data, 0)   # switch on
         capi.check(L.rr_cycle_bench(h, B, d, cycles, 0, R, flat, wsp, 16, psp, capi.RR_PRIO_DEVICE, C.byref(ms), C.byref(nl)))
         n = L.rr_debug_timeline(h, 0, buf.ctypes.data, 1024)
-        ev = sorted((int(v) >> 4, int(v) & 15) for v in buf[:n])
+        ev = sorted((int(v) >> 8, int(v) & 15, (int(v) >> 4) & 15) for v in buf[:n])
         t0 = ev[0][0]
-        print("  " + "  ".join("%s@%.1f" % (NAMES.get(c, "?"), (t - t0) / 1e3) for t, c in ev))
+        print("  " + "  ".join("%s:%x@%.1f" % (NAMES.get(c, "?"), g, (t - t0) / 1e3) for t, c, g in ev))
 
 
 if __name__ == "__main__":
