@@ -144,6 +144,10 @@ class ReplayCore {
     // issuer mode: a cudaEvent_t recorded behind the gather that fills this set (shared by the
     // copies of the set; destroyed with the last one)
     std::shared_ptr<void> ready;
+    // Shared by the pool's copy of the set and every copy the host layer itself holds (batches
+    // drawn ahead that have not been handed out): use_count() > 1 = the set is in use. Copies of a
+    // set share their TensorImpls, so the storages' use counts only see the CALLER's aliases.
+    std::shared_ptr<char> lease;
   };
   std::vector<BatchSet> pool_;  // batch tensors reused once the caller has released them
   std::deque<BatchSet> inflight_;  // batches drawn ahead (prefetch), oldest first

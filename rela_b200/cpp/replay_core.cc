@@ -421,12 +421,13 @@ std::vector<int64_t> ReplayCore::batchShape(const LeafSpec& s, int64_t B) const 
   return shape;
 }
 
-// A batch set nobody else holds: a pooled one whose storages are back to a use
-// count of 1, else a new one (pooled if there is room).
+// A batch set nobody else holds: a pooled one that neither the host layer (lease: batches drawn
+// ahead) nor the caller (storages back to a use count of 1) still uses, else a new one (pooled if
+// there is room).
 ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
   for (auto& cand : pool_) {
     if (cand.B != B) continue;
-    bool idle = cand.weights.storage().use_count() == 1;
+    bool idle = cand.lease.use_count() <= 1 && cand.weights.storage().use_count() == 1;
     for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
     if (idle) return cand;
   }
@@ -438,6 +439,7 @@ ReplayCore::BatchSet ReplayCore::acquireSet(int64_t B) {
     set.fields.push_back(torch::empty(batchShape(s, B),
                                       torch::TensorOptions().dtype(s.converted ? s.out_dtype : s.dtype).device(home)));
   if (issuer_) set.ready = newReadyEvent();
+  set.lease = std::make_shared<char>(0);
   if (pool_.size() < (size_t)(4 + prefetch_)) pool_.push_back(set);
   return set;
 }
@@ -482,7 +484,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::samplePrefetched(int batchsize, con
   if (inflight_.empty()) issue();
   // (a caller on the replay's own stream: the prefetch issued below carries the wait for this batch)
   check(rr_take_prefetched(h_, (stream == own_stream_ && prefetch_ > 0) ? RR_STREAM_OWN_DEFERRED : stream), "sample");
-  BatchSet set = std::move(inflight_.front());
+  BatchSet set = std::move(inflight_.front());  // (its lease keeps it out of acquireSet until the aliases exist)
   inflight_.pop_front();
   while ((int)inflight_.size() < prefetch_) issue();
   return handOut(set, device);
@@ -509,7 +511,7 @@ std::pair<Leaves, torch::Tensor> ReplayCore::sample(int batchsize, const std::st
   BatchSet* set = nullptr;
   for (auto& cand : pool_) {
     if (cand.B != B) continue;
-    bool idle = cand.weights.storage().use_count() == 1;
+    bool idle = cand.lease.use_count() <= 1 && cand.weights.storage().use_count() == 1;
     for (size_t i = 0; idle && i < cand.fields.size(); ++i) idle = cand.fields[i].storage().use_count() == 1;
     if (idle) {
       set = &cand;
