@@ -231,6 +231,25 @@ typedef struct rr_route {
  * reuses slots a queued gather may still read). */
 int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* route, void* stream);
 
+/* rr_update_priority without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). Same semantics and results as
+ * rr_update_priority with RR_PRIO_DEVICE (bit-identical stored weights, sum_ and hierarchy), but
+ * the update kernel's work area (12 bytes per element) is a file-scope __device__ array of
+ * RR_NOALLOC_MAX_BATCH elements (96 KB, held by every GPU that loads the library until exit)
+ * instead of device memory the replay allocates on demand, and nothing else is allocated either:
+ * no cudaMalloc / cudaFree / cudaHostAlloc, no event or stream creation.
+ *   - `priority` must be device memory and `flags` must contain RR_PRIO_DEVICE (a host array would
+ *     need a staging buffer); RR_PRIO_IS_WEIGHT as in rr_update_priority.
+ *   - n > RR_NOALLOC_MAX_BATCH is rejected with RR_ERR_ARG (the batch stays outstanding: call
+ *     rr_update_priority instead); a sharded replay is rejected with RR_ERR_STATE.
+ *   - Every call on one device shares the array, and it keeps the last call's contents (the kernel
+ *     writes every word it uses before reading it, so nothing is cleared). Two such updates that
+ *     OVERLAP ON THE GPU -- different replays on different streams -- race; calls on one replay are
+ *     serialised on its internal stream and are safe. */
+#define RR_NOALLOC_MAX_BATCH 8192
+int rr_update_priority_noalloc(rr_replay* r, int n, const float* priority, unsigned flags, void* stream);
+
 /* update_priority on a striped replay: every rank applies the priorities of ALL learners, which
  * the update kernel itself all-gathers through peer memory. This rank contributes n_mine values
  * (priority_mine: host memory, or device memory with RR_PRIO_DEVICE) for elements [offset, offset +

@@ -13,10 +13,11 @@ LIB_PATH = os.path.join(HERE, "librela_b200.so")
 RR_OUT_RAW, RR_OUT_F32_DIV255, RR_OUT_BF16_DIV255 = 0, 1, 2
 RR_OK, RR_ERR_ARG, RR_ERR_CUDA, RR_ERR_STATE, RR_ERR_EMPTY, RR_ERR_NOMEM, RR_ERR_OVERRUN = range(7)
 RR_ROWS_DEVICE, RR_PRIO_DEVICE, RR_PRIO_IS_WEIGHT = 1, 2, 4
+RR_NOALLOC_MAX_BATCH = 8192  # rr_update_priority_noalloc: elements of its static work area
 
 SYMBOLS = [
     "rr_last_error", "rr_create", "rr_destroy", "rr_set_schema", "rr_add", "rr_add_rows", "rr_sample",
-    "rr_update_priority", "rr_update_priority_sharded", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
+    "rr_update_priority", "rr_update_priority_noalloc", "rr_update_priority_sharded", "rr_size", "rr_num_add", "rr_sync", "rr_get_stats", "rr_last_sample_ids",
     "rr_debug_state", "rr_debug_weights", "rr_debug_tiles", "rr_debug_select_probe", "rr_debug_timeline", "rr_stream_fence",
     "rr_get_stream", "rr_stream_wait", "rr_save", "rr_load", "rr_restore_prefetched", "rr_prefetched_batch",
     "rr_record_prefetched",
@@ -73,6 +74,7 @@ def lib():
         L.rr_add_rows.argtypes = [vp, i, vp, vp, u, vp]
         L.rr_sample.argtypes = [vp, i, vp, vp, vp]
         L.rr_update_priority.argtypes = [vp, i, vp, u, vp]
+        L.rr_update_priority_noalloc.argtypes = [vp, i, vp, u, vp]
         L.rr_update_priority_sharded.argtypes = [vp, i, vp, i, i, u, vp, i, C.c_uint32, vp, vp]
         L.rr_size.argtypes = [vp]
         L.rr_num_add.argtypes = [vp]

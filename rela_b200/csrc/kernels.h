@@ -122,6 +122,7 @@ constexpr int kSelThreads = 256;
 constexpr int kSelTargets = 8;     // targets per CTA of select_kernel: one per warp
 constexpr int kInlinePrio = 1024;  // largest update whose priorities travel as kernel parameters
 constexpr int kUpdStaged = 512;    // largest update every CTA stages in shared memory (update_kernel)
+constexpr int kNoAllocMaxBatch = 8192;  // = RR_NOALLOC_MAX_BATCH: elements of the static work area (select.cu)
 constexpr int kMaxBatch = 16384;   // update_kernel stages 12 B per sampled element in shared memory
 constexpr int kTimelineCap = 1024;
 
@@ -250,6 +251,10 @@ struct ExchangeArgs {
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
                           void* scratch, cudaStream_t stream);
+// same kernel, always unstaged, its work area in a file-scope __device__ array (n <= kNoAllocMaxBatch):
+// allocates nothing (rr_update_priority_noalloc)
+cudaError_t launch_update_static(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
+                                 int n, const float* prio, float alpha, int is_weight, cudaStream_t stream);
 // same, n <= kInlinePrio priorities read from HOST memory now and carried in the launch parameters
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,

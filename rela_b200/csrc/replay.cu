@@ -1756,6 +1756,44 @@ int update_impl(rr_replay* r, int n, const float* priority, unsigned flags, cons
 }
 }  // namespace
 
+static_assert(RR_NOALLOC_MAX_BATCH == rr::kNoAllocMaxBatch, "include/rela_b200.h and kernels.h disagree");
+
+int rr_update_priority_noalloc(rr_replay* r, int n, const float* priority, unsigned flags, void* stream) {
+  if (r == nullptr || priority == nullptr || n < 0) return fail(RR_ERR_ARG, "rr_update_priority_noalloc: bad argument");
+  if ((flags & RR_PRIO_DEVICE) == 0)
+    return fail(RR_ERR_ARG, "rr_update_priority_noalloc: the priorities must be device-resident (RR_PRIO_DEVICE); "
+                            "host priorities need a staging buffer, use rr_update_priority");
+  if (n > RR_NOALLOC_MAX_BATCH)
+    return fail(RR_ERR_ARG, "rr_update_priority_noalloc: a batch of %d exceeds the %d elements of the static work "
+                            "area (RR_NOALLOC_MAX_BATCH); use rr_update_priority", n, RR_NOALLOC_MAX_BATCH);
+  if (r->shard_world > 1)
+    return fail(RR_ERR_STATE, "rr_update_priority_noalloc: a sharded replay updates through rr_update_priority_sharded");
+  if (r->cur_ids < 0) return fail(RR_ERR_STATE, "rr_update_priority: no sampled batch is outstanding");
+  if (n != r->cur_B)  // assert((int)sampledIds_.size() == priority.size(0)), line 237
+    return fail(RR_ERR_ARG, "rr_update_priority: %d priorities for a batch of %d", n, r->cur_B);
+  int rc = check_device_error(r, "rr_update_priority_noalloc");
+  if (rc != RR_OK) return rc;
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  DeviceScope dev_scope(r->device);
+  rc = flush_pend_wait(r);
+  if (rc != RR_OK) return rc;
+  std::unique_lock<std::mutex> lk(r->m_);
+  rc = order_after_caller_(r, cs);
+  if (rc != RR_OK) return rc;
+  RR_CUDA(rr::launch_update_static(r->ctl, r->w, tiles_of(r), r->evicted, r->idbuf[r->cur_ids], n, priority, r->alpha,
+                                   (flags & RR_PRIO_IS_WEIGHT) ? 1 : 0, r->main));
+  ++r->main_seq;
+  r->launches++;
+  if (cs != r->main) {
+    RR_CUDA(cudaEventRecord(r->evOut, r->main));
+    RR_CUDA(cudaStreamWaitEvent(cs, r->evOut, 0));
+  }
+  r->idbusy[r->cur_ids] = false;  // sampledIds_.clear(), line 244
+  r->cur_ids = -1;
+  r->cur_B = 0;
+  return RR_OK;
+}
+
 int rr_sync(rr_replay* r) {
   if (r == nullptr) return fail(RR_ERR_ARG, "rr_sync: null");
   DeviceScope dev_scope(r->device);

@@ -24,6 +24,7 @@
 #include <cfloat>
 #include <cstring>
 #include <cmath>
+#include <mutex>
 
 #include "../../include/rela_b200.h"
 #include "kernels.h"
@@ -1141,6 +1142,48 @@ cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t*
   const int grid = update_grid(tiles, n, &by_group);
   return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), smem, stream, ctl, w, evicted, ids, n,
                     prio, alpha, is_weight, tiles, by_group, early, xa ? *xa : none, sc);
+}
+
+// ---- update without any allocation (rr_update_priority_noalloc; no counterpart in the reference,
+// added for callers that cannot call cudaMalloc).
+// update_kernel in its unstaged mode works in 12 bytes per batch element (ids, new weights,
+// differences). The other launches take that area from device memory the replay allocates on
+// demand; this one takes it from a file-scope array, which every GPU that loads the library
+// holds until exit: kNoAllocMaxBatch x 12 B = 96 KB. The kernel writes every word of the area
+// it uses before reading it (CTA 0: ids -> new weights -> old weights / differences), so nothing
+// has to be cleared between calls; the array keeps the last call's contents. ALL calls on one
+// device share it: two such updates that overlap on the GPU (different replays, different
+// streams) race. In host code `g_update_scratch` is only a stand-in for the symbol: the device
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_update_scratch[12 * kNoAllocMaxBatch];
+
+cudaError_t launch_update_static(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
+                                 int n, const float* prio, float alpha, int is_weight, cudaStream_t stream) {
+  if (n < 0 || n > kNoAllocMaxBatch) return cudaErrorInvalidValue;
+  static std::mutex m;
+  static unsigned char* area[64];  // per device
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  unsigned char* scratch;
+  {
+    std::lock_guard<std::mutex> lk(m);
+    if (area[dev] == nullptr) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_update_scratch);
+      if (e != cudaSuccess) return e;
+      area[dev] = static_cast<unsigned char*>(p);
+    }
+    scratch = area[dev];
+  }
+  ExchangeArgs none;
+  memset(&none, 0, sizeof(none));
+  int by_group;
+  const int grid = update_grid(tiles, n, &by_group);
+  // no dynamic shared memory (nothing is staged), early = 0 (always correct)
+  return launch_pdl(update_kernel<const float*>, dim3(grid), dim3(kUpdThreads), 0, stream, ctl, w, evicted, ids, n,
+                    prio, alpha, is_weight, tiles, by_group, 0, none, scratch);
 }
 
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
