@@ -1176,10 +1176,16 @@ def run_striped(args):
         parity = {"cycles": cycles, "against": "oracle/replay_oracle.c: ONE single-buffer oracle of %d transitions drawing "
                                                "batches of %d" % (total_cap, Bg),
                   "ids_equal": True, "rows_equal": True, "weights_max_rel": 0.0, "batch": Bg}
-        sl = slice(rank * B, (rank + 1) * B)
+        per_shard = -(-int(1.25 * total_cap) // world)  # slots per shard (rr_set_shard)
+        local_rows = 0
         for c in range(cycles):
             batch, w = replay.sample(B, dev_str)
+            # this rank's rows are chunk last_chunk() of the stratified batch of world * B: the
+            # chunks are assigned by locality (rr_route::my_chunk), a rotation of the ranks
+            chunk = replay.last_chunk()
+            sl = slice(chunk * B, (chunk + 1) * B)
             ids = last_ids(capi, L, h, Bg)
+            local_rows += int(np.sum(ids[sl] // per_shard == rank))
             rc, rows_o, w_o, ids_o = orc.sample(Bg, True)
             assert rc == 0
             if not np.array_equal(ids, ids_o):
@@ -1208,6 +1214,9 @@ def run_striped(args):
         t = torch.tensor([1.0 if ok else 0.0], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         parity["ok_on_every_rank"] = bool(t.item() == 1.0)
+        t = torch.tensor([float(local_rows)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        parity["rows_local_frac"] = float(t.item()) / (cycles * Bg)  # rows that did not cross NVLink
         orc.close()
         if not parity["ok_on_every_rank"]:
             if rank == 0:
@@ -1387,8 +1396,11 @@ def run_striped(args):
     best_v = min(runs, key=lambda r: r["value_ms"])
     best_e = min(runs, key=lambda r: r["e2e_ms"])
     value = tps(best_v["value_ms"], Bg)
-    ingress = lambda rate: rate / world * ROW_BYTES * (world - 1) / world / 1e9  # noqa: E731  per-GPU GB/s
-    nvlink_cap_rate = world * 900e9 / (ROW_BYTES * (world - 1) / world)
+    # rows of a learner's chunk that live on another GPU: measured over the parity cycles (chunks are
+    # assigned by locality); (N-1)/N without that measurement
+    remote = 1.0 - parity["rows_local_frac"] if parity and "rows_local_frac" in parity else (world - 1) / world
+    ingress = lambda rate: rate / world * ROW_BYTES * remote / 1e9  # noqa: E731  per-GPU GB/s
+    nvlink_cap_rate = world * 900e9 / (ROW_BYTES * max(remote, 1e-9))
     line = {
         "metric": "replay sample+gather transitions/s", "value": value, "unit": "transitions/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": best_v["value_ms"], "higher_is_better": True, "scaling": "weak",
@@ -1413,9 +1425,12 @@ def run_striped(args):
         "roofline": {"bound": "nvlink", "unit": "GB/s", "peak": 900.0,
                      "achieved": ingress(value), "frac": ingress(value) / 900.0, "traffic": None,
                      "peak_source": "NVLink 5, 900 GB/s per direction per GPU (nominal)",
-                     "kernel": "row_copy_kernel (routed gather: %d/%d of every batch crosses NVLink)" % (world - 1, world),
-                     "note": "per-GPU NVLink ingress = (N-1)/N x 56,617 B x rows per GPU per second; the HBM side moves "
-                             "the same bytes at a fraction of its peak",
+                     "kernel": "row_copy_kernel (routed gather: %.0f %% of every batch crosses NVLink, chunks assigned "
+                               "to the GPUs by locality; %.0f %% with a fixed assignment)"
+                               % (100 * remote, 100 * (world - 1) / world),
+                     "rows_crossing_nvlink_frac": remote,
+                     "note": "per-GPU NVLink ingress = remote fraction x 56,617 B x rows per GPU per second; the HBM side "
+                             "moves all rows at a fraction of its peak",
                      "linear_cap": {"n_times_nvlink_ingress_cap": nvlink_cap_rate,
                                     "value_frac_of_cap": value / nvlink_cap_rate},
                      "bounded_by": ("NVLink ingress (>= 2/3 of the 900 GB/s port)" if ingress(value) / 900.0 >= 0.66 else

@@ -220,7 +220,26 @@ typedef struct rr_route {
   float* out_weights;        /* this learner's B importance weights (device), or NULL        */
   int on_demand;             /* != 0: the batch is taken right away (no prefetch): its gather
                                 stays on the internal stream behind its selection             */
+  int* my_chunk;             /* host, out; NULL: chunk c = rows [c * B, (c + 1) * B) goes to
+                                learner c. Non-NULL (every shard a learner, n_learners == world,
+                                the same choice on every rank): the library assigns the chunks
+                                BY LOCALITY -- chunk c goes to learner learner_of_chunk[c] of
+                                rr_route_assignment(head, size, S, world) for the ring range the
+                                selection draws from -- and stores here which chunk THIS learner
+                                receives (-1 without one). The batch is sorted in ring order and
+                                so are the shards' slot ranges: most rows of a chunk are stored
+                                on the GPU that receives it and never cross NVLink. The
+                                learners' batches are still the N chunks of ONE stratified
+                                batch of batch_total; only who gets which chunk changes.       */
 } rr_route;
+
+/* The assignment rr_prefetch_routed chooses (pure host arithmetic, no device needed): `head` and
+ * `size` describe the live ring range after the selection's eviction, `slots` = S, shard r stores
+ * slots [r * ceil(S / world), ...); learner_of_chunk[world] receives the bijection chunk ->
+ * learner under which most slots of the range belong to the shard that receives their chunk.
+ * Every shard computes it from replicated values, so all shards agree without communicating.
+ * No counterpart in the reference (one host buffer). */
+int rr_route_assignment(int head, int size, int slots, int world, int* learner_of_chunk);
 
 /* rr_prefetch_into for a shard of a striped replay: select batch_total ids
  * (identically on every shard), gather the rows this shard owns to their

@@ -23,6 +23,7 @@ SYMBOLS = [
     "rr_record_prefetched",
     "rr_set_output_format", "rr_set_profiling", "rr_gather_bench", "rr_cycle_bench", "rr_nstep_return", "rr_td_priority",
     "rr_aggregate_priority", "rr_sample_select", "rr_sample_gather", "rr_prefetch_into", "rr_prefetch_routed",
+    "rr_route_assignment",
     "rr_take_prefetched", "rr_prefetched", "rr_scatter_rows", "rr_peer_put", "rr_wait_flags", "rr_exchange",
     "rr_set_shard", "rr_shard_range", "rr_slab_ptrs", "rr_add_sharded_rows", "rr_add_sharded_commit",
     "rr_device_alloc", "rr_device_free", "rr_ipc_export", "rr_ipc_open", "rr_ipc_close",
@@ -45,7 +46,8 @@ class RRStats(C.Structure):
 class RRRoute(C.Structure):
     _fields_ = [("n_learners", C.c_int), ("dst_tab", C.c_void_p), ("signal_ptrs", C.POINTER(C.c_void_p)),
                 ("n_signals", C.c_int), ("wait_flags", C.c_void_p), ("wait_n", C.c_int),
-                ("my_learner", C.c_int), ("out_weights", C.c_void_p), ("on_demand", C.c_int)]
+                ("my_learner", C.c_int), ("out_weights", C.c_void_p), ("on_demand", C.c_int),
+                ("my_chunk", C.POINTER(C.c_int))]
 
 
 class ReplayError(RuntimeError):
@@ -108,6 +110,7 @@ def lib():
         L.rr_wait_flags.argtypes = [i, vp, i, C.c_uint64, vp, vp]
         L.rr_exchange.argtypes = [vp, vp, C.c_uint64, vp, vp, i, C.c_uint64, vp, i, vp]
         L.rr_prefetch_routed.argtypes = [vp, i, C.POINTER(RRRoute), vp]
+        L.rr_route_assignment.argtypes = [i, i, i, i, vp]
         L.rr_slab_ptrs.argtypes = [vp, vp, i]
         L.rr_add_sharded_rows.argtypes = [vp, i, i, i, vp, vp, vp]
         L.rr_add_sharded_commit.argtypes = [vp, vp, u]

@@ -83,6 +83,7 @@ void bindCommon(PyClass& c) {
       .def("load", [](Replay& r, const std::string& path) { r.core().load(path); },
            py::call_guard<py::gil_scoped_release>())
       .def("handle", [](Replay& r) { return (uintptr_t)r.core().handle(); })
+      .def("last_chunk", [](Replay& r) { return r.core().lastChunk(); })
       .def("device", [](Replay& r) { return r.core().device(); })
       .def("schema", [](Replay& r) { return schemaOf(r); });
 }

@@ -131,6 +131,10 @@ class ReplayCore {
   static torch::Tensor raiseAtPosition(const torch::Tensor& p, int64_t offset, int64_t total, float alpha);
   int shardRank() const { return shard_.rank; }
   int shardWorld() const { return shard_.world; }
+  // Striped replay, every rank a learner: which B rows of the stratified batch of world * B the
+  // batch returned by the last sample() is -- rows [lastChunk() * B, (lastChunk() + 1) * B). The
+  // chunks are assigned by locality (rr_route::my_chunk), so this is not always the rank. 0 otherwise.
+  int lastChunk() const;
 
  private:
   void ensureSchema(const Leaves& first, bool per_element, bool time_major);

@@ -27,6 +27,7 @@
 // The steady-state cycle contains no host-side communication and no collective
 // library call: rr_group (shared memory) is used at set-up time only, to
 // exchange the CUDA IPC handles of slabs, batch arenas and inboxes.
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -101,8 +102,15 @@ struct ReplayCore::Sharded {
     int next = 0;
   };
   std::map<int64_t, Arena> arenas;
-  std::deque<std::pair<Arena*, int>> inflight;
+  struct Drawn {
+    Arena* arena;
+    int set;
+    int chunk;  // which B rows of the stratified batch of n_learners * B this rank holds (-1: none)
+  };
+  std::deque<Drawn> inflight;
   int64_t cur_B = 0;  // per-learner size of the batch awaiting its priorities
+  int cur_chunk = -1;  // ... and its position in the whole batch: rows [cur_chunk * B, (cur_chunk + 1) * B)
+  bool by_locality = true;  // every rank a learner: chunks go to the GPU that stores most of their rows
 
   int rankOfLearner(int l) const { return learner < 0 ? l : learner; }
 };
@@ -119,6 +127,7 @@ void ReplayCore::startSharded() {
   sh.learner = shard_.learner;
   sh.n_learners = sh.learner < 0 ? sh.world : 1;
   sh.my_learner = sh.learner < 0 ? sh.rank : (sh.rank == sh.learner ? 0 : -1);
+  if (const char* e = std::getenv("RELA_B200_ROUTE_BY_LOCALITY")) sh.by_locality = std::atoi(e) != 0;
   check(rr_get_stream(h_, &sh.main), "sharded replay");
   // every replay of the job gets its own rendezvous: the ranks construct their replays in the same order
   const std::string name = shard_.group + "." + std::to_string(g_group_counter++);
@@ -379,17 +388,20 @@ std::pair<Leaves, torch::Tensor> ReplayCore::shardedSample(int batchsize, const 
     rt.my_learner = sh.my_learner;
     rt.out_weights = a.sets[(size_t)k].weights.data_ptr<float>();
     rt.on_demand = on_demand ? 1 : 0;
+    int chunk = sh.my_learner;
+    rt.my_chunk = (sh.learner < 0 && sh.world > 1 && sh.by_locality) ? &chunk : nullptr;
     check(rr_prefetch_routed(h_, (int)(B * sh.n_learners), &rt, cs), "sample");
-    sh.inflight.push_back({&a, k});
+    sh.inflight.push_back({&a, k, chunk});
   };
-  if (!sh.inflight.empty() && sh.inflight.front().first != &a)
+  if (!sh.inflight.empty() && sh.inflight.front().arena != &a)
     throw std::runtime_error("sample: batch size differs from the prefetched one");
   if (sh.inflight.empty()) issue(prefetch_ == 0);
   // a caller on the replay's own stream with batches drawn ahead: the prefetch issued right below
   // carries the wait for this batch (RR_STREAM_OWN_DEFERRED keeps the update -> select launch chain)
   check(rr_take_prefetched(h_, (cs == sh.main && prefetch_ > 0) ? RR_STREAM_OWN_DEFERRED : cs), "sample");
   sh.cur_B = B;
-  const int k = sh.inflight.front().second;
+  const int k = sh.inflight.front().set;
+  sh.cur_chunk = sh.inflight.front().chunk;
   sh.inflight.pop_front();
   while ((int)sh.inflight.size() < prefetch_) issue(false);
   if (sh.my_learner < 0) return {Leaves(), torch::Tensor()};
@@ -408,6 +420,8 @@ std::pair<Leaves, torch::Tensor> ReplayCore::shardedSample(int batchsize, const 
   }
   return {std::move(out), std::move(weights)};
 }
+
+int ReplayCore::lastChunk() const { return sharded_ ? sharded_->cur_chunk : 0; }
 
 void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   Sharded& sh = *sharded_;
@@ -432,7 +446,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
       f = RR_PRIO_DEVICE;
       xs = cs;
     } else {
-      w = raiseAtPosition(w_in, sh.my_learner * sh.cur_B, sh.cur_B * sh.n_learners, alpha_);
+      w = raiseAtPosition(w_in, sh.cur_chunk * sh.cur_B, sh.cur_B * sh.n_learners, alpha_);
       if (w.is_cuda()) {
         f |= RR_PRIO_DEVICE;
         xs = cs;
@@ -449,7 +463,7 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
   for (int r = 0; r < sh.world; ++r) dst[r] = sh.inbox[(size_t)r] + slots_off;
   const bool learner = sh.my_learner >= 0;
   check(rr_update_priority_sharded(h_, (int)total, learner ? w.data_ptr<float>() : nullptr, learner ? (int)n : 0,
-                                   learner ? (int)((size_t)sh.my_learner * n) : 0, f, dst, sh.world, tag,
+                                   learner ? (int)((size_t)sh.cur_chunk * n) : 0, f, dst, sh.world, tag,
                                    sh.inbox[(size_t)sh.rank] + slots_off, xs),
         "update_priority");
   sh.cur_B = 0;

@@ -59,6 +59,11 @@ struct CopyParams {
   const uint64_t* dst_tab;
   int tab_cols;
   int rows_per_dst;
+  // Locality-aware assignment (every shard a learner): chunk c = b / rows_per_dst of the batch goes
+  // to learner dst_of_chunk[c]. The batch is sorted in ring order and so are the shards' slot
+  // ranges, so most chunks can be given to the shard that stores most of their rows, and those
+  // rows never cross NVLink (replay.cu, route_assignment). Without a route the table is the identity.
+  uint8_t dst_of_chunk[kMaxPeers];
   // Completion signals (sharded gather): when n_signals > 0, the last CTA to
   // finish its stores publishes `signal_val` at every signal[i] with a
   // system-scope release. The pointers may be peer-mapped (the learners' memory).

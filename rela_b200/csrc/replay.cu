@@ -153,6 +153,10 @@ struct rr_replay {
   std::vector<uint64_t> sel_seq;
   // capacity sharding: this replay's slabs hold slots [own_lo, own_hi) only
   int shard_rank = 0, shard_world = 1, own_lo = 0, own_hi = 0;
+  // the chunk -> learner assignment of routed batches, cached per ring range (route_assignment)
+  long long route_head = -1, route_size = -1;
+  int route_n = 0;
+  int route_learner_of[rr::kMaxPeers] = {};
   int sm_count = 148;
   int g_stages = 32, g_piece = 8192, g_ctas = 1, g_simt_only = 0, g_beside_ctas = 0;
   std::vector<FieldInfo> fields;
@@ -1183,7 +1187,57 @@ struct Route {
   int my_learner = -1;
   const unsigned long long* wait_flags = nullptr;  // a learner's gather waits for every shard's flag itself
   int wait_n = 0;
+  bool by_locality = false;  // locality-aware chunk assignment (rr_route::my_chunk)
+  int learner_of[rr::kMaxPeers] = {0, 1, 2, 3, 4, 5, 6, 7};  // out: chunk c of this batch goes to learner_of[c]
 };
+
+// Which learner gets which chunk of a batch, so that as many rows as possible stay on the GPU that
+// stores them. The batch is sorted in ring order from the head (the prefix walk never rewinds,
+// rela/prioritized_replay.h:283-307) and chunk c covers the c-th n-th of the priority mass; shard r
+// stores slots [r * per, (r + 1) * per). With the mass spread evenly over the `size` live slots
+// from `head`, chunk c covers ring positions [head + c * size / n, head + (c + 1) * size / n): the
+// value of giving chunk c to learner l is the number of those slots in l's range, and the
+// assignment is the bijection of the largest total value (dynamic programme over subsets of
+// learners, 2^n * n steps; ties go to the lowest learner). Pure integer arithmetic on values every
+// shard holds identically (the control plane is replicated), so all shards choose the same
+// assignment without talking to each other. The result is cached per (head, size).
+void route_assignment(long long head, long long size, long long S, int n, int* learner_of) {
+  for (int c = 0; c < n; ++c) learner_of[c] = c;
+  if (n <= 1 || n > rr::kMaxPeers || size <= 0 || S <= 0) return;
+  const long long per = (S + n - 1) / n;
+  auto overlap = [&](long long a, long long len, long long lo, long long hi) {  // ring [a, a + len) with [lo, hi)
+    long long tot = 0;
+    a %= S;
+    const long long first = std::min(len, S - a);
+    tot += std::max(0LL, std::min(a + first, hi) - std::max(a, lo));
+    if (len > first) tot += std::max(0LL, std::min(len - first, hi) - std::max(0LL, lo));
+    return tot;
+  };
+  long long val[rr::kMaxPeers][rr::kMaxPeers];
+  for (int c = 0; c < n; ++c) {
+    const long long a = head + c * size / n, b = head + (c + 1) * size / n;
+    for (int l = 0; l < n; ++l) val[c][l] = overlap(a, b - a, std::min(S, l * per), std::min(S, (l + 1) * per));
+  }
+  // best[mask]: chunks 0 .. popcount(mask) - 1 given to exactly the learners in mask
+  const int full = (1 << n) - 1;
+  long long best[1 << rr::kMaxPeers];
+  int8_t pick[1 << rr::kMaxPeers];
+  best[0] = 0;
+  for (int mask = 1; mask <= full; ++mask) {
+    const int c = __builtin_popcount((unsigned)mask) - 1;  // the chunk placed last
+    best[mask] = -1;
+    pick[mask] = -1;
+    for (int l = 0; l < n; ++l) {
+      if (!(mask & (1 << l))) continue;
+      const long long v = best[mask ^ (1 << l)] + val[c][l];
+      if (v > best[mask]) {
+        best[mask] = v;
+        pick[mask] = (int8_t)l;
+      }
+    }
+  }
+  for (int mask = full; mask != 0; mask ^= 1 << pick[mask]) learner_of[__builtin_popcount((unsigned)mask) - 1] = pick[mask];
+}
 
 // sample_ (rela/prioritized_replay.h:258-328) in two stream-ordered steps: (1) selection +
 // eviction + raw importance weights on the internal stream, (2) makeBatch = the gather (which
@@ -1192,7 +1246,7 @@ struct Route {
 // host-side blockPop bookkeeping is applied in step 2: until the gather has been issued, a
 // concurrent add must not be able to reserve (and overwrite) the evicted slots the gather
 // still reads.
-int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
+int select_launch(rr_replay* r, int B, int idslot, int* pop_out, Route* route = nullptr) {
   int rc = ensure_idbuf(r, idslot, B);
   if (rc != RR_OK) return rc;
   std::unique_lock<std::mutex> lk(r->m_);
@@ -1245,6 +1299,16 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
     }
     r->slotPending[(size_t)idslot] = false;
   }
+  if (route && route->by_locality) {  // from the range THIS selection draws from: what is left after its eviction
+    const long long rh = (a.head + a.pop_n) % r->S, rs = a.size - a.pop_n;
+    if (rh != r->route_head || rs != r->route_size || route->n_learners != r->route_n) {
+      route_assignment(rh, rs, r->S, route->n_learners, r->route_learner_of);
+      r->route_head = rh;
+      r->route_size = rs;
+      r->route_n = route->n_learners;
+    }
+    for (int c = 0; c < route->n_learners; ++c) route->learner_of[c] = r->route_learner_of[c];
+  }
   RR_CUDA(rr::launch_select(a, r->main));
   r->rng_par ^= 1;
   r->last_select_seq = r->sel_seq[(size_t)idslot] = ++r->main_seq;
@@ -1255,9 +1319,10 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out) {
 
 // out_w: this caller's importance weights (B floats, or B / n_learners with a route); may be null.
 int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot, int pop_n, bool ahead,
-                  const Route* route) {
+                  Route* route) {
   std::unique_lock<std::mutex> lk(r->m_);
   const int32_t* ids = r->idbuf[idslot];
+
   std::vector<CopyField> cf;
   rr::ConvertParams conv;
   memset(&conv, 0, sizeof(conv));
@@ -1294,6 +1359,7 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
     plan.p.dst_tab = route->dst_tab;
     plan.p.tab_cols = (int)r->fields.size();
     plan.p.rows_per_dst = rows_per_dst;
+    for (int c = 0; c < rr::kMaxPeers; ++c) plan.p.dst_of_chunk[c] = (uint8_t)route->learner_of[c];
     plan.p.done_counter = nullptr;  // chosen with the stream below
     plan.p.n_signals = route->n_signals;
     for (int i = 0; i < route->n_signals; ++i) plan.p.signal[i] = route->signals[i];
@@ -1316,7 +1382,11 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
   if (rc == RR_OK && out_w != nullptr) {
     const int l = route ? route->my_learner : 0;
     if (l >= 0) {
-      plan.p.norm_raw = r->israw[idslot] + (size_t)l * rows_per_dst;
+      int c = 0;  // a learner's rows are the chunk assigned to it
+      if (route)
+        for (int k = 0; k < route->n_learners; ++k)
+          if (route->learner_of[k] == l) c = k;
+      plan.p.norm_raw = r->israw[idslot] + (size_t)c * rows_per_dst;
       plan.p.norm_max = r->ismax[idslot];
       plan.p.norm_out = out_w;
       plan.p.norm_n = rows_per_dst;
@@ -1376,9 +1446,9 @@ int gather_launch(rr_replay* r, int B, void* const* out_fields, float* out_w, in
 }
 
 int sample_into(rr_replay* r, int B, void* const* out_fields, float* out_w, int idslot, bool ahead,
-                const Route* route = nullptr) {
+                Route* route = nullptr) {
   int pop_n = 0;
-  int rc = select_launch(r, B, idslot, &pop_n);
+  int rc = select_launch(r, B, idslot, &pop_n, route);
   if (rc != RR_OK) return rc;
   return gather_launch(r, B, out_fields, out_w, idslot, pop_n, ahead, route);
 }
@@ -1484,7 +1554,7 @@ int rr_sample(rr_replay* r, int batch, void* const* out_fields, float* out_weigh
 }
 
 namespace {
-int prefetch_impl(rr_replay* r, int batch, void* const* out_fields, float* out_weights, const Route* route,
+int prefetch_impl(rr_replay* r, int batch, void* const* out_fields, float* out_weights, Route* route,
                   const unsigned long long* wait_flags, int wait_n, bool take_waits, bool ahead, cudaStream_t cs) {
   if (r->prefetch > 0) return fail(RR_ERR_STATE, "rr_prefetch_into: the replay was created with its own prefetch");
   if (r->pend_slot >= 0) return fail(RR_ERR_STATE, "rr_prefetch_into: an rr_sample_select is pending");
@@ -1549,10 +1619,26 @@ int rr_prefetch_routed(rr_replay* r, int batch_total, const rr_route* rt, void* 
   route.my_learner = rt->my_learner;
   route.wait_flags = static_cast<const unsigned long long*>(rt->wait_flags);
   route.wait_n = rt->wait_flags ? rt->wait_n : 0;
-  return prefetch_impl(r, batch_total, nullptr, rt->my_learner >= 0 ? rt->out_weights : nullptr, &route,
-                       static_cast<const unsigned long long*>(rt->wait_flags), rt->wait_flags ? rt->wait_n : 0,
-                       false /* a learner's gather kernel waits itself */, rt->on_demand == 0,
-                       static_cast<cudaStream_t>(stream));
+  route.by_locality = rt->my_chunk != nullptr && rt->n_learners > 1;
+  if (route.by_locality && rt->n_learners != r->shard_world)
+    return fail(RR_ERR_ARG, "rr_prefetch_routed: chunks are assigned by locality only when every shard is a learner");
+  rc = prefetch_impl(r, batch_total, nullptr, rt->my_learner >= 0 ? rt->out_weights : nullptr, &route,
+                     static_cast<const unsigned long long*>(rt->wait_flags), rt->wait_flags ? rt->wait_n : 0,
+                     false /* a learner's gather kernel waits itself */, rt->on_demand == 0,
+                     static_cast<cudaStream_t>(stream));
+  if (rc == RR_OK && rt->my_chunk != nullptr) {
+    *rt->my_chunk = -1;
+    for (int c = 0; c < rt->n_learners; ++c)
+      if (route.learner_of[c] == rt->my_learner) *rt->my_chunk = c;
+  }
+  return rc;
+}
+
+int rr_route_assignment(int head, int size, int slots, int world, int* learner_of_chunk) {
+  if (world < 1 || world > rr::kMaxPeers || learner_of_chunk == nullptr || head < 0 || size < 0 || slots <= 0)
+    return fail(RR_ERR_ARG, "rr_route_assignment: bad argument");
+  route_assignment(head, size, slots, world, learner_of_chunk);
+  return RR_OK;
 }
 
 int rr_take_prefetched(rr_replay* r, void* stream) {

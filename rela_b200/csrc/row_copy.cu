@@ -54,8 +54,9 @@ __device__ __forceinline__ uint8_t* row_dst(const CopyParams& p, const CopyField
                                             uint32_t off, uint32_t local) {
   if (p.ids != nullptr) {  // gather: batch [t, b, :]
     if (p.dst_tab != nullptr) {  // ... of the learner that owns batch row b
-      const uint32_t learner = b / (uint32_t)p.rows_per_dst;
-      const uint32_t bl = b - learner * (uint32_t)p.rows_per_dst;
+      const uint32_t chunk = b / (uint32_t)p.rows_per_dst;
+      const uint32_t bl = b - chunk * (uint32_t)p.rows_per_dst;
+      const uint32_t learner = p.dst_of_chunk[chunk];
       uint8_t* base = reinterpret_cast<uint8_t*>(__ldg(p.dst_tab + (size_t)learner * p.tab_cols + f.tab));
       return base + (uint64_t)t * f.dst_chunk_stride + (uint64_t)bl * f.dst_row_stride + off;
     }

@@ -9,8 +9,11 @@ the ranks (rank r contributes rows [r*K/N, (r+1)*K/N)), which is how the striped
 replay orders a collective block, so ONE single-buffer oracle fed the unsplit
 blocks must produce the same ids, bytes and weights:
 
-  learner = -1   every rank samples B rows: rows [r*B, (r+1)*B) of the oracle's
-                 batch of N*B; every rank passes the priorities of its rows
+  learner = -1   every rank samples B rows: chunk c = rows [c*B, (c+1)*B) of the oracle's
+                 batch of N*B, c = last_chunk() (the chunks are assigned by locality:
+                 rr_route::my_chunk); every rank passes the
+                 priorities of its rows. The chunk of every sample is printed, the parent
+                 test checks that the ranks' chunks are a permutation every time
   learner = r    rank r receives the oracle's whole batch of B
 """
 import argparse
@@ -73,6 +76,9 @@ def main():
     h = C.c_void_p(rep.handle())
     my_learner = rank if a.learner < 0 else (0 if rank == a.learner else -1)
     n_samples = 0
+    chunks = []
+    chunk = my_learner
+    drawn_from = []  # ring state (head, size) each batch still queued was selected from, oldest first
     for op in ops:
         if op[0] == "add":
             rows, prio = op[1], op[2]
@@ -87,13 +93,29 @@ def main():
         elif op[0] == "sample":
             rc, want_rows, want_w, want_ids = orc.sample(Btot)
             assert rc == 0
+            # the first sample() selects 1 + prefetch batches, every later one tops the queue up by one;
+            # no add runs in between, and an eviction belongs to the first of them: every new
+            # selection drew from the ring range the oracle shows now
+            st = orc.state()
+            while len(drawn_from) < a.prefetch + 1:
+                drawn_from.append((st["head"], st["safe_size"]))
+            head_sel, size_sel = drawn_from.pop(0)
             batch, w = rep.sample(a.B, "cuda:%d" % dev_index)
             ids = np.zeros(Btot, dtype=np.int32)
             capi.check(L.rr_last_sample_ids(h, Btot, ids.ctypes.data))
             np.testing.assert_array_equal(ids, want_ids, err_msg="rank %d sample %d: ids" % (rank, n_samples))
             assert rep.size() == orc.size()
             if my_learner >= 0:
-                sl = slice(my_learner * a.B, (my_learner + 1) * a.B)
+                chunk = rep.last_chunk()
+                assert 0 <= chunk < n_learn
+                if a.learner < 0:
+                    # the assignment is a pure function of the ring range the batch was selected from
+                    # (after that selection's eviction), which every shard holds identically
+                    to = (C.c_int * world)()
+                    capi.check(L.rr_route_assignment(head_sel, size_sel, int(1.25 * a.capacity), world, to))
+                    assert to[chunk] == rank, (rank, chunk, list(to))
+                chunks.append(chunk)
+                sl = slice(chunk * a.B, (chunk + 1) * a.B)
                 torch.cuda.synchronize(dev)
                 np.testing.assert_allclose(w.cpu().numpy(), want_w[sl], rtol=1e-6, atol=0,
                                            err_msg="rank %d sample %d: IS weights" % (rank, n_samples))
@@ -112,7 +134,7 @@ def main():
             prio = op[1]
             orc.update(torch_pow(prio, alpha))
             if my_learner >= 0:
-                mine = prio[my_learner * a.B:(my_learner + 1) * a.B]
+                mine = prio[chunk * a.B:(chunk + 1) * a.B]
             else:
                 mine = np.zeros(0, np.float32)
             rep.update_priority(torch.from_numpy(np.ascontiguousarray(mine)))
@@ -125,6 +147,7 @@ def main():
     assert (v[0].value, v[1].value, v[2].value, v[3].value) == (st["head"], st["tail"], st["size"], st["safe_size"])
     assert s.value == st["sum"], (s.value, st["sum"])
     del rep
+    print("SHARDED_CHUNKS rank=%d %s" % (rank, ",".join(map(str, chunks))), flush=True)
     print("SHARDED_OK rank=%d world=%d samples=%d" % (rank, world, n_samples), flush=True)
 
 
