@@ -121,6 +121,49 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+class PhaseWatchdog:
+    """A striped run is N processes whose kernels wait for one another across GPUs; if one phase of it
+    ever hangs, the run must still end within minutes and report what it has. Every rank runs one of
+    these: `enter(name, budget_s)` arms a deadline for the phase that starts, `done()` disarms it; a
+    daemon thread calls `on_timeout(name)` when a phase overruns (the callback prints what has been
+    measured so far on rank 0 and ends the process; it does not return). Every call the main thread
+    can hang in releases the GIL (ctypes, pybind call guards, torch synchronisation), so the thread
+    gets to run."""
+
+    def __init__(self, on_timeout, poll_s=0.25):
+        self.on_timeout = on_timeout
+        self.poll_s = poll_s
+        self.lock = threading.Lock()
+        self.phase, self.deadline = None, None
+        self.history = []
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def enter(self, name, budget_s):
+        with self.lock:
+            now = time.monotonic()
+            if self.phase is not None:
+                self.history.append((self.phase, round(now - self.t0, 2)))
+            self.phase, self.deadline, self.t0 = name, now + budget_s, now
+
+    def done(self):
+        with self.lock:
+            if self.phase is not None:
+                self.history.append((self.phase, round(time.monotonic() - self.t0, 2)))
+            self.phase, self.deadline = None, None
+
+    def _run(self):
+        while True:
+            time.sleep(self.poll_s)
+            with self.lock:
+                late = self.deadline is not None and time.monotonic() > self.deadline
+                name = self.phase
+                if late:
+                    self.deadline = None
+            if late:
+                self.on_timeout(name)
+
+
 def host_info():
     model = "?"
     try:
@@ -1137,6 +1180,32 @@ def run_striped(args):
     n_local = 2048                       # rows per rank per collective add
     n_block = n_local * world
     n_adds = (total_cap + 64 + n_block - 1) // n_block
+    state = {"args": args, "world": world, "B": B, "Bg": Bg, "K": K, "W": W, "total_cap": total_cap, "parity": None,
+             "runs": [], "peak": (peak, peak_src), "t_start": t_start}
+
+    def end_run(why):
+        """A phase overran its budget (or raised): rank 0 prints the line of what has been measured, or
+        an error object if there is nothing yet; every rank ends its process (no clean-up: kernels of
+        this or another rank may be waiting for one another)."""
+        rc = 0
+        if rank == 0:
+            try:
+                if state["runs"]:
+                    print(json.dumps(striped_line(state, why)), flush=True)
+                else:
+                    print(json.dumps({"error": "striped run ended without a number: %s" % why, "n_gpus": world,
+                                      "phases_s": wd.history, "parity": state["parity"]}), flush=True)
+                    rc = 3
+            except Exception as e:  # noqa: BLE001  (never hang in the exit path)
+                print("bench.py: could not build the partial line: %r" % (e,), file=sys.stderr, flush=True)
+                rc = 3
+        sys.stderr.write("bench.py rank %d: ending the run: %s\n" % (rank, why))
+        sys.stderr.flush()
+        os._exit(rc)
+
+    wd = PhaseWatchdog(end_run)
+    state["wd"] = wd
+    _STRIPED["end_run"], _STRIPED["rank"] = end_run, rank
 
     def make(prefetch, learner):
         return rela.FFPrioritizedReplay(total_cap, 7, args.alpha, args.beta, prefetch, local_rank, rank, world, learner,
@@ -1160,6 +1229,7 @@ def run_striped(args):
         return torch.from_numpy(np.ascontiguousarray(ids_oracle_rows))
 
     # ---- replay 1: every rank a learner, prefetch 0: parity, value (serial), e2e (prefetch 0)
+    wd.enter("set-up and fill of the first replay (with the oracle beside it)", 240)
     replay = make(0, -1)
     parity = None
     orc = None
@@ -1168,6 +1238,8 @@ def run_striped(args):
     t0 = time.time()
     fill(replay, orc)
     fill_s = time.time() - t0
+    state["fill_s"] = fill_s
+    wd.enter("parity cycles against the oracle", 120)
     h = C.c_void_p(replay.handle())
     dev_str = "cuda:%d" % local_rank
     if orc is not None:
@@ -1217,6 +1289,7 @@ def run_striped(args):
         t = torch.tensor([float(local_rows)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         parity["rows_local_frac"] = float(t.item()) / (cycles * Bg)  # rows that did not cross NVLink
+        state["parity"] = parity
         orc.close()
         if not parity["ok_on_every_rank"]:
             if rank == 0:
@@ -1286,23 +1359,38 @@ def run_striped(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def measure(rep, learners):
+    def measure(rep, learners, prefetch, publish):
+        """One replay's numbers, published as each one is known (a later leg that hangs must not take
+        the earlier ones with it): value from the interpreter's loop, then from the C++ loop, then e2e."""
         value_cycle, e2e_cycle, own_stream = loops(rep)
         hh = C.c_void_p(rep.handle())
+        tag = "prefetch %d, %d learner(s)" % (prefetch, learners)
+        res = {"prefetch": prefetch, "learners": learners}
+        wd.enter("warm-up + value loop from the interpreter (%s)" % tag, 60)
         for k in range(W):
             value_cycle(k)
         ms_py = timed(rep, value_cycle, max(1, K // 4), own_stream) / max(1, K // 4)
+        st = get_stats(capi, L, hh)
+        res.update(value_ms=ms_py, value_ms_python_loop=ms_py, value_loop="interpreter", e2e_ms=None,
+                   gpu_launches=None, slab_gb=st["slab_bytes"] / 1e9)
+        publish(dict(res))
+        wd.enter("value loop from C++ (%s)" % tag, 60)
         s0 = get_stats(capi, L, hh)
         ms_v = timed_cpp(rep, K, own_stream)
         s1 = get_stats(capi, L, hh)
+        res.update(value_ms=ms_v / K, value_loop="C++", gpu_launches=int(s1["kernel_launches"] - s0["kernel_launches"]))
+        publish(dict(res))
+        wd.enter("e2e loop (%s)" % tag, 60)
         for k in range(W):
             e2e_cycle(k)
         ms_e = timed(rep, e2e_cycle, K, stream)
         rep.sync()
         st = get_stats(capi, L, hh)
         assert st["samples_ordered"] == 0 and st["device_errors"] == 0
-        return {"value_ms": ms_v / K, "value_ms_python_loop": ms_py, "e2e_ms": ms_e / K,
-                "gpu_launches": int(s1["kernel_launches"] - s0["kernel_launches"]), "slab_gb": st["slab_bytes"] / 1e9}
+        res.update(e2e_ms=ms_e / K)
+        publish(dict(res))
+        wd.done()
+        return res
 
     def kernel_timeline(rep, cycles=16):
         """GPU-side durations of this rank's kernels in the pipelined value loop (rr_debug_timeline:
@@ -1348,53 +1436,82 @@ def run_striped(args):
                 "note": "rank 0, pipelined value loop, medians over %d steps; select/update from the kernel's "
                         "dependency wait to CTA 0's end, *_all_ctas to the last CTA's end" % cycles}
 
+    # ---- the measured replays, the most exercised configuration first. `state` always holds what is
+    # known so far: if a later phase overruns its budget the watchdog prints the line built from it
+    # (marked "incomplete") instead of leaving the run without a number.
+    state["runs"] = []
+
+    def publish_run(res):
+        runs = state["runs"]
+        for i, r in enumerate(runs):
+            if r["prefetch"] == res["prefetch"] and r["learners"] == res["learners"]:
+                runs[i] = res
+                return
+        runs.append(res)
+
+    def publish_single(res):
+        state["single"] = res
+
+    def fresh(prefetch, learner):
+        wd.enter("fill of the replay with prefetch %d, learner %d" % (prefetch, learner), 120)
+        gc.collect()
+        torch.cuda.empty_cache()
+        barrier()
+        rep = make(prefetch, learner)
+        fill(rep)
+        return rep
+
     clocks = ClockSampler(local_rank)
+    state["clocks"] = clocks
     if rank == 0:
         clocks.start()
-    runs = []
-    m0 = measure(replay, world)
-    runs.append(dict(m0, prefetch=0, learners=world))
-    slab_gb = m0["slab_gb"]
+    # ---- replay 1 (already filled, parity-checked): every rank a learner, prefetch 0
+    m0 = measure(replay, world, 0, publish_run)
+    state["slab_gb"] = m0["slab_gb"]
     replay = None
-    gc.collect()
-    torch.cuda.empty_cache()
-    barrier()
     # ---- replay 2: every rank a learner, prefetch 2
-    replay = make(2, -1)
-    fill(replay)
-    runs.append(dict(measure(replay, world), prefetch=2, learners=world))
-    timeline = kernel_timeline(replay)
+    replay = fresh(2, -1)
+    measure(replay, world, 2, publish_run)
+    wd.enter("kernel timeline (prefetch 2)", 60)
+    state["timeline"] = kernel_timeline(replay)
     replay = None
-    gc.collect()
-    torch.cuda.empty_cache()
-    barrier()
     # ---- replay 2b: prefetch 4. A batch's path -- selection, gather over NVLink, completion flags of
     # all shards, the all-gather of its priorities -- crosses GPUs twice; more batches in flight
     # hide more of that latency (the reference's prefetch is a constructor argument, any depth)
-    replay = make(4, -1)
-    fill(replay)
-    runs.append(dict(measure(replay, world), prefetch=4, learners=world))
+    replay = fresh(4, -1)
+    measure(replay, world, 4, publish_run)
     replay = None
-    gc.collect()
-    torch.cuda.empty_cache()
-    barrier()
     # ---- replay 3: ONE learner (GPU 0) receiving whole batches of `batch` rows over NVLink, prefetch 4
-    replay = make(4, 0)
-    fill(replay)
-    single = dict(measure(replay, 1), prefetch=4, learners=1)
+    replay = fresh(4, 0)
+    measure(replay, 1, 4, publish_single)
     replay = None
+    wd.enter("teardown", 60)
     gc.collect()
     torch.cuda.empty_cache()
-    clk = clocks.stop() if rank == 0 else None
-    if rank != 0:
-        dist.destroy_process_group()
-        return
+    wd.done()
+    if rank == 0:
+        print(json.dumps(striped_line(state, None)), flush=True)
+    dist.destroy_process_group()
+
+
+_STRIPED = {}  # run_striped's exit hook, for main()
+
+
+def striped_line(state, incomplete):
+    """The JSON line of a striped run from what `state` holds (all of it, or -- when a phase hung and
+    the watchdog ends the run -- what had been measured until then; `incomplete` then names the phase)."""
+    args, world, B, Bg, K, W = (state[k] for k in ("args", "world", "B", "Bg", "K", "W"))
+    total_cap, parity, runs, single = state["total_cap"], state["parity"], state["runs"], state.get("single")
+    peak, peak_src = state["peak"]
+    clk = state["clocks"].stop() if state.get("clocks") is not None else None
+    slab_gb = state.get("slab_gb") or (runs[0]["slab_gb"] if runs else None)
 
     def tps(ms, rows):
         return rows / (ms * 1e-3)
 
     best_v = min(runs, key=lambda r: r["value_ms"])
-    best_e = min(runs, key=lambda r: r["e2e_ms"])
+    with_e2e = [r for r in runs if r.get("e2e_ms")]
+    best_e = min(with_e2e, key=lambda r: r["e2e_ms"]) if with_e2e else None
     value = tps(best_v["value_ms"], Bg)
     # rows of a learner's chunk that live on another GPU: measured over the parity cycles (chunks are
     # assigned by locality); (N-1)/N without that measurement
@@ -1406,21 +1523,22 @@ def run_striped(args):
         "steps": K, "warmup": W, "ms_per_step": best_v["value_ms"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(total_cap, Bg, args.alpha, args.beta),
-        "parallelism": "ONE replay of %d transitions striped over %d GPUs (%.1f GB of slabs each); every GPU draws its %d "
-                       "rows of one stratified batch of %d per step; rows travel GPU to GPU over NVLink"
-                       % (total_cap, world, slab_gb, B, Bg),
+        "parallelism": "ONE replay of %d transitions striped over %d GPUs (%.1f GB of slabs each); every GPU draws %d "
+                       "rows of one stratified batch of %d per step (the batch's chunks go to the GPUs by locality); "
+                       "rows travel GPU to GPU over NVLink" % (total_cap, world, slab_gb or 0.0, B, Bg),
         "value_runs": [{"prefetch": r["prefetch"], "ms_per_step": r["value_ms"], "transitions_per_s": tps(r["value_ms"], Bg),
-                        "ms_per_step_python_loop": r["value_ms_python_loop"], "gpu_launches": r["gpu_launches"]}
-                       for r in runs],
+                        "loop": r["value_loop"], "ms_per_step_python_loop": r["value_ms_python_loop"],
+                        "gpu_launches": r["gpu_launches"]} for r in runs],
         "value_note": "sample(B) + update_priority(device priorities) of the C++ host layer on every rank, on the replay's "
                       "own stream, issued by a C++ loop (pybind cycle_loop); ms_per_step_python_loop: the same calls "
                       "issued from the interpreter",
-        "e2e": {"value": tps(best_e["e2e_ms"], Bg), "unit": "transitions/s", "h2d_bytes_per_step": 4 * B * world,
-                "d2h_bytes_per_step": 4 * B * world, "ms_per_step": best_e["e2e_ms"], "prefetch": best_e["prefetch"],
-                "runs": [{"prefetch": r["prefetch"], "ms_per_step": r["e2e_ms"], "transitions_per_s": tps(r["e2e_ms"], Bg)}
-                         for r in runs],
-                "api": "rela_b200.rela.FFPrioritizedReplay(..., shard_rank, shard_world) on every rank: sample(B) + weights "
-                       "-> pinned host copy + stream sync + update_priority(pinned cpu tensor)"},
+        "e2e": None if best_e is None else {
+            "value": tps(best_e["e2e_ms"], Bg), "unit": "transitions/s", "h2d_bytes_per_step": 4 * B * world,
+            "d2h_bytes_per_step": 4 * B * world, "ms_per_step": best_e["e2e_ms"], "prefetch": best_e["prefetch"],
+            "runs": [{"prefetch": r["prefetch"], "ms_per_step": r["e2e_ms"], "transitions_per_s": tps(r["e2e_ms"], Bg)}
+                     for r in with_e2e],
+            "api": "rela_b200.rela.FFPrioritizedReplay(..., shard_rank, shard_world) on every rank: sample(B) + weights "
+                   "-> pinned host copy + stream sync + update_priority(pinned cpu tensor)"},
         "gpu_launches": best_v["gpu_launches"], "parity": parity, "clocks": clk,
         "roofline": {"bound": "nvlink", "unit": "GB/s", "peak": 900.0,
                      "achieved": ingress(value), "frac": ingress(value) / 900.0, "traffic": None,
@@ -1439,17 +1557,21 @@ def run_striped(args):
                                     "the NVLink port is at %.0f %%" % (Bg, best_v["value_ms"] * 1e3,
                                                                        100 * ingress(value) / 900.0)),
                      "hbm_peak": peak, "hbm_peak_source": peak_src},
-        "single_learner": {"value": tps(single["value_ms"], B), "e2e": tps(single["e2e_ms"], B), "unit": "transitions/s",
-                           "ms_per_step": single["value_ms"], "prefetch": 4, "batch": B,
-                           "learner_nvlink_ingress_gbs": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9,
-                           "frac_of_900": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9 / 900.0,
-                           "note": "the same striped replay with GPU 0 as the only learner: whole batches of %d rows "
-                                   "assembled on GPU 0" % B},
-        "kernel_timeline": timeline,
-        "fill_s": fill_s, "slab_gb": slab_gb, "wall_s": time.time() - t_start,
+        "single_learner": None if not single else {
+            "value": tps(single["value_ms"], B), "e2e": tps(single["e2e_ms"], B) if single.get("e2e_ms") else None,
+            "unit": "transitions/s", "ms_per_step": single["value_ms"], "prefetch": 4, "batch": B,
+            "learner_nvlink_ingress_gbs": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9,
+            "frac_of_900": tps(single["value_ms"], B) * ROW_BYTES * (world - 1) / world / 1e9 / 900.0,
+            "note": "the same striped replay with GPU 0 as the only learner: whole batches of %d rows "
+                    "assembled on GPU 0" % B},
+        "kernel_timeline": state.get("timeline"),
+        "phases_s": state["wd"].history if state.get("wd") is not None else None,
+        "fill_s": state.get("fill_s"), "slab_gb": slab_gb, "wall_s": time.time() - state["t_start"],
     }
-    print(json.dumps(line))
-    dist.destroy_process_group()
+    if incomplete is not None:
+        line["incomplete"] = ("the phase '%s' did not finish within its time budget; the run was ended there and this "
+                              "line holds what had been measured until then" % incomplete)
+    return line
 
 
 def main():
@@ -1457,7 +1579,23 @@ def main():
     if args.impl == "reference":
         run_reference(args)
     elif int(os.environ.get("WORLD_SIZE", "1")) > 1:
-        run_striped(args)
+        try:
+            run_striped(args)
+        except SystemExit:
+            raise
+        except BaseException as e:  # noqa: BLE001
+            # One rank failing must not cost the run what it has measured: torchrun tears every rank
+            # down as soon as one exits non-zero. The failing rank reports on stderr; rank 0 prints
+            # the line of what is known (its watchdog does, if it is waiting for the failed rank).
+            import traceback
+
+            traceback.print_exc()
+            if "end_run" not in _STRIPED:
+                raise
+            if _STRIPED["rank"] == 0:
+                _STRIPED["end_run"]("rank 0 raised %r" % (e,))
+            time.sleep(150)
+            os._exit(0)
     else:
         run_single(args)
 
