@@ -276,7 +276,11 @@ int rr_update_priority_noalloc(rr_replay* r, int n, const float* priority, unsig
  * bits), valid when its upper half equals `epoch`: slot_ptrs[i] = rank i's array of n_total such
  * words (peer-mapped, n_dst = world, this rank included), my_slots = this rank's own array.
  * `epoch`: the same non-zero value on every rank, different from the value of the previous
- * exchange through the same arrays (the caller alternates between two arrays per rank).
+ * exchange through the same arrays. The caller rotates through several arrays per rank, enough
+ * that no rank can still be polling the array a faster rank writes next: two when every rank
+ * contributes (a contributor needed every other contributor's values to finish its previous
+ * update), prefetch + 2 when some ranks only receive (the one learner of a striped replay is held
+ * back by the gathers only and can be `prefetch` updates ahead of a shard; sharded_core.cc).
  * A rank that is no learner passes n_mine == 0 and only receives. All ranks pass the same `flags`. */
 int rr_update_priority_sharded(rr_replay* r, int n_total, const float* priority_mine, int n_mine, int offset,
                                unsigned flags, void* const* slot_ptrs, int n_dst, uint32_t epoch,

@@ -27,6 +27,7 @@
 // The steady-state cycle contains no host-side communication and no collective
 // library call: rr_group (shared memory) is used at set-up time only, to
 // exchange the CUDA IPC handles of slabs, batch arenas and inboxes.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -59,9 +60,17 @@ inline void* streamOf(int device) {
 constexpr size_t kInboxFloats = 1u << 20;  // largest block of weights one exchange moves (adds)
 constexpr size_t kInboxHeader = 256;       // 2 parities x 16 ranks x 8-byte flags
 constexpr size_t kUpdateSlots = 16384;     // largest batch (all learners) of one update_priority: kMaxBatch
-// an inbox: [flags][weights of an add, parity 0][parity 1][update slots, parity 0][parity 1]
+// an inbox: [flags][weights of an add, parity 0][parity 1][update slots, array 0][array 1]...
 constexpr size_t kInboxSlotsOff = kInboxHeader + 2 * kInboxFloats * sizeof(float);
-constexpr size_t kInboxBytes = kInboxSlotsOff + 2 * kUpdateSlots * sizeof(uint64_t);
+// How many slot arrays the updates rotate through. A rank that contributes priorities needed every
+// contributor's values to finish its previous update, so contributors are never more than one
+// exchange apart -- but a rank WITHOUT a contribution (a shard of a replay with one learner) holds
+// nobody back that way: the learner is held back only by the gathers, it issues update y after it
+// took batch y, i.e. after every shard's gather of batch y, which that shard launched behind its
+// selection y and therefore behind its update y - prefetch - 1. The learner can thus be `prefetch`
+// exchanges ahead of a shard that is still polling: prefetch + 2 arrays keep it off that array.
+inline size_t updateArrays(int prefetch) { return (size_t)std::max(2, prefetch + 2); }
+inline size_t inboxBytes(int prefetch) { return kInboxSlotsOff + updateArrays(prefetch) * kUpdateSlots * sizeof(uint64_t); }
 constexpr size_t kAlign = 256;
 
 inline size_t alignUp(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
@@ -136,8 +145,8 @@ void ReplayCore::startSharded() {
   c10::cuda::CUDAGuard guard((c10::DeviceIndex)device_);
   // inbox for the all-gather of weights (rr_exchange)
   void* mine = nullptr;
-  check(rr_device_alloc(device_, kInboxBytes, &mine), "sharded replay (inbox)");
-  cuda(cudaMemset(mine, 0, kInboxBytes), "sharded replay (inbox)");  // no slot carries a valid tag yet
+  check(rr_device_alloc(device_, inboxBytes(prefetch_), &mine), "sharded replay (inbox)");
+  cuda(cudaMemset(mine, 0, inboxBytes(prefetch_)), "sharded replay (inbox)");  // no slot carries a valid tag yet
   sh.owned.push_back(mine);
   uint8_t handle[64];
   check(rr_ipc_export(device_, mine, handle), "sharded replay (inbox)");
@@ -454,11 +463,10 @@ void ReplayCore::shardedUpdate(const torch::Tensor& w_in, unsigned /*flags*/) {
     }
   }
   // the update kernel all-gathers the learners' priorities itself (ExchangeArgs): 8-byte words
-  // tagged with the sequence number, two slot arrays alternating -- a rank can be at most one
-  // update ahead of the slowest one, whose values it needed to finish the previous update
+  // tagged with the sequence number, in one of prefetch + 2 slot arrays taken in turn (updateArrays)
   const uint64_t x = ++sh.useq;
   const uint32_t tag = (uint32_t)(x % 0xffffffffull) + 1u;  // never 0 (the cleared arrays)
-  const size_t slots_off = kInboxSlotsOff + (size_t)(x & 1) * kUpdateSlots * sizeof(uint64_t);
+  const size_t slots_off = kInboxSlotsOff + (size_t)(x % updateArrays(prefetch_)) * kUpdateSlots * sizeof(uint64_t);
   void* dst[8];
   for (int r = 0; r < sh.world; ++r) dst[r] = sh.inbox[(size_t)r] + slots_off;
   const bool learner = sh.my_learner >= 0;

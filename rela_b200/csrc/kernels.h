@@ -238,8 +238,10 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
 // slot array (dst[i], its own included) with plain 64-bit stores -- no fence, no flag: a word is
 // valid when its upper half equals `epoch`. A CTA that needs element j polls word j of THIS rank's
 // array (`slots`) until then. One NVLink crossing per value instead of data, fence, flag.
-// Two arrays alternate by the parity of the exchange sequence: a sender can be at most one
-// exchange ahead of the slowest receiver (it needed that receiver's values to finish the previous one).
+// The host rotates through several arrays (rela_b200/cpp/sharded_core.cc, updateArrays): a
+// contributing sender can be at most one exchange ahead of another contributor (it needed that
+// rank's values to finish the previous one), the single learner of a striped replay at most
+// `prefetch` exchanges ahead of a shard that only receives.
 struct ExchangeArgs {
   int on;                        // 0: no exchange, `prio` holds all n priorities
   int n_mine;
