@@ -1188,7 +1188,7 @@ def run_striped(args):
         an error object if there is nothing yet; every rank ends its process (no clean-up: kernels of
         this or another rank may be waiting for one another)."""
         rc = 0
-        if rank == 0:
+        if rank == 0 and not state.get("printed"):
             try:
                 if state["runs"]:
                     print(json.dumps(striped_line(state, why)), flush=True)
@@ -1389,7 +1389,8 @@ def run_striped(args):
         assert st["samples_ordered"] == 0 and st["device_errors"] == 0
         res.update(e2e_ms=ms_e / K)
         publish(dict(res))
-        wd.done()
+        # (the caller enters the next phase: the replay's teardown is a collective step too)
+        wd.enter("teardown of the replay (%s)" % tag, 120)
         return res
 
     def kernel_timeline(rep, cycles=16):
@@ -1488,10 +1489,12 @@ def run_striped(args):
     wd.enter("teardown", 60)
     gc.collect()
     torch.cuda.empty_cache()
-    wd.done()
     if rank == 0:
         print(json.dumps(striped_line(state, None)), flush=True)
+    state["printed"] = True
+    wd.enter("process group teardown", 30)  # (a hang here must not turn a finished run into a timeout)
     dist.destroy_process_group()
+    wd.done()
 
 
 _STRIPED = {}  # run_striped's exit hook, for main()

@@ -226,7 +226,9 @@ struct SelectArgs {
 };
 
 cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cudaStream_t stream);
-cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream);
+// sm_count, gather_reserve: see launch_select (select.cu) -- whether the kernel may start early behind
+// the kernel in front of it (programmatic dependent launch)
+cudaError_t launch_select(const SelectArgs& a, int sm_count, size_t gather_reserve, cudaStream_t stream);
 
 // add commit (K2 + weights write + sum_, prioritized_replay.h:58-73,188)
 cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int start, int n, const float* prio,

@@ -158,14 +158,16 @@ inline cudaError_t ensure_dynamic_smem(Kernel kernel, size_t bytes) {
   return cudaSuccess;
 }
 
-// Host: launch with the PDL attribute (RR_PDL=0 disables it).
+// Host: launch with the PDL attribute (RR_PDL=0 disables it); `pdl` = false: a plain stream-ordered
+// launch of the same kernel (its griddepcontrol.wait then returns at once).
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
-                              Args&&... args) {
-  static const bool enabled = [] {
+inline cudaError_t launch_pdl_if(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t stream, Args&&... args) {
+  static const bool allowed = [] {
     const char* v = getenv("RR_PDL");
     return !(v && v[0] == '0');
   }();
+  const bool enabled = allowed && pdl;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -177,6 +179,12 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   cfg.attrs = attr;
   cfg.numAttrs = enabled ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  return launch_pdl_if(true, kernel, grid, block, smem, stream, static_cast<Args&&>(args)...);
 }
 
 }  // namespace rr

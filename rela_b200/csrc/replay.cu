@@ -1309,7 +1309,8 @@ int select_launch(rr_replay* r, int B, int idslot, int* pop_out, Route* route = 
     }
     for (int c = 0; c < route->n_learners; ++c) route->learner_of[c] = r->route_learner_of[c];
   }
-  RR_CUDA(rr::launch_select(a, r->main));
+  // (only a striped replay's update waits for other GPUs: elsewhere the selection always starts early)
+  RR_CUDA(rr::launch_select(a, r->sm_count, r->shard_world > 1 ? kGatherReserve : (size_t)-1, r->main));
   r->rng_par ^= 1;
   r->last_select_seq = r->sel_seq[(size_t)idslot] = ++r->main_seq;
   r->launches++;

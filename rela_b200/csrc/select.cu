@@ -1091,13 +1091,26 @@ cudaError_t launch_build_hierarchy(const float* w, const Tiles& t, int S_pad, cu
   return launch_pdl(build_groups_kernel, dim3((t.ng + 7) / 8), dim3(256), 0, stream, t);
 }
 
-cudaError_t launch_select(const SelectArgs& a, cudaStream_t stream) {
+cudaError_t launch_select(const SelectArgs& a, int sm_count, size_t gather_reserve, cudaStream_t stream) {
   const size_t ng_pad = ((size_t)a.t.ng + 3) & ~(size_t)3;
   const size_t smem = ng_pad * (sizeof(double) + sizeof(float)) + 16;
   cudaError_t e = ensure_dynamic_smem(select_kernel, smem);
   if (e != cudaSuccess) return e;
   const int grid = (a.B + kSelTargets - 1) / kSelTargets;
-  return launch_pdl(select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
+  // A selection launched as a programmatic dependent becomes resident while the update in front of
+  // it is still running, and waits there holding its shared memory. In a striped replay that update
+  // can spend tens of microseconds waiting for the other shards' priorities; if the waiting
+  // selection CTAs plus two update CTAs per SM take more than a gather drawn ahead leaves free
+  // (gather_reserve), no gather CTA gets onto those SMs meanwhile -- and the rows of the next
+  // batches are exactly what the other shards are waiting for. Large striped replays (group sums
+  // of 12 B per 16,384 slots in every CTA; 4 or more shards at 2^21 transitions each) therefore
+  // launch the selection in plain stream order; two shards are below the bound, and an unsharded
+  // replay passes no bound at all (its update waits for nobody).
+  const size_t per_cta = smem + 4 * 1024;  // + the kernel's static shared memory
+  const size_t per_sm = (size_t)((grid + sm_count - 1) / std::max(sm_count, 1));
+  const size_t update_ctas = 2 * 10 * 1024;  // update_grid: two CTAs per SM, ~9.2 KB static each
+  const bool early_start = per_sm * per_cta + update_ctas <= gather_reserve;
+  return launch_pdl_if(early_start, select_kernel, dim3(grid), dim3(kSelThreads), smem, stream, a);
 }
 
 cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int start, int n, const float* prio,
