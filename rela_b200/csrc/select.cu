@@ -1120,13 +1120,6 @@ cudaError_t launch_commit(Ctl* ctl, float* w, const Tiles& tiles, int S, int sta
 }
 
 namespace {
-inline int upd_staged_max() {  // EXPERIMENT (to be removed): RR_UPD_STAGED overrides kUpdStaged
-  static const int v = [] {
-    const char* e = getenv("RR_UPD_STAGED");
-    return e ? atoi(e) : kUpdStaged;
-  }();
-  return v;
-}
 inline int update_grid(const Tiles& tiles, int n, int* by_group) {
   *by_group = tiles.ng <= n ? 1 : 0;
   // CTA 0: sum_ and weights; the others: candidate groups, at most two CTAs per SM -- with a fused
@@ -1144,8 +1137,8 @@ inline int update_grid(const Tiles& tiles, int n, int* by_group) {
 cudaError_t launch_update(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids, int n,
                           const float* prio, float alpha, int is_weight, int early, const ExchangeArgs* xa,
                           void* scratch, cudaStream_t stream) {
-  if (n > upd_staged_max() && scratch == nullptr) return cudaErrorInvalidValue;
-  uint8_t* sc = n > upd_staged_max() ? static_cast<uint8_t*>(scratch) : nullptr;
+  if (n > kUpdStaged && scratch == nullptr) return cudaErrorInvalidValue;
+  uint8_t* sc = n > kUpdStaged ? static_cast<uint8_t*>(scratch) : nullptr;
   const size_t smem = sc ? 0 : (size_t)n * 12;
   ExchangeArgs none;
   memset(&none, 0, sizeof(none));
@@ -1202,8 +1195,8 @@ cudaError_t launch_update_static(Ctl* ctl, float* w, const Tiles& tiles, const u
 cudaError_t launch_update_inline(Ctl* ctl, float* w, const Tiles& tiles, const uint8_t* evicted, const int32_t* ids,
                                  int n, const float* prio_host, float alpha, int is_weight, int early,
                                  const ExchangeArgs* xa, void* scratch, cudaStream_t stream) {
-  if (n > upd_staged_max() && scratch == nullptr) return cudaErrorInvalidValue;
-  uint8_t* sc = n > upd_staged_max() ? static_cast<uint8_t*>(scratch) : nullptr;
+  if (n > kUpdStaged && scratch == nullptr) return cudaErrorInvalidValue;
+  uint8_t* sc = n > kUpdStaged ? static_cast<uint8_t*>(scratch) : nullptr;
   const int n_host = xa ? xa->n_mine : n;  // with an exchange the launch carries this rank's share only
   if (n_host > kInlinePrio) return cudaErrorInvalidValue;
   PrioInline pin;
