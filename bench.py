@@ -130,9 +130,10 @@ class PhaseWatchdog:
     can hang in releases the GIL (ctypes, pybind call guards, torch synchronisation), so the thread
     gets to run."""
 
-    def __init__(self, on_timeout, poll_s=0.25):
+    def __init__(self, on_timeout, poll_s=0.25, log=None):
         self.on_timeout = on_timeout
         self.poll_s = poll_s
+        self.log = log  # called with one line per phase entered (a trail on stderr, should all else fail)
         self.lock = threading.Lock()
         self.phase, self.deadline = None, None
         self.history = []
@@ -145,6 +146,8 @@ class PhaseWatchdog:
             if self.phase is not None:
                 self.history.append((self.phase, round(now - self.t0, 2)))
             self.phase, self.deadline, self.t0 = name, now + budget_s, now
+        if self.log is not None:
+            self.log("bench.py phase: %s (budget %d s)" % (name, budget_s))
 
     def done(self):
         with self.lock:
@@ -1169,17 +1172,11 @@ def run_striped(args):
         os.sched_setaffinity(0, set(cpus[local_rank * per:(local_rank + 1) * per]) or set(cpus))
     except (AttributeError, OSError):
         pass
-    dist.init_process_group("nccl", device_id=dev)  # barriers and the max-over-ranks of the timings only
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
     Bg = B * world
     total_cap = args.capacity * world
-    L = capi.lib()
     peak, peak_src = peaks()
-    group = "bench%s" % os.environ.get("MASTER_PORT", "0")
     t_start = time.time()
-    n_local = 2048                       # rows per rank per collective add
-    n_block = n_local * world
-    n_adds = (total_cap + 64 + n_block - 1) // n_block
     state = {"args": args, "world": world, "B": B, "Bg": Bg, "K": K, "W": W, "total_cap": total_cap, "parity": None,
              "runs": [], "peak": (peak, peak_src), "t_start": t_start}
 
@@ -1203,9 +1200,16 @@ def run_striped(args):
         sys.stderr.flush()
         os._exit(rc)
 
-    wd = PhaseWatchdog(end_run)
+    wd = PhaseWatchdog(end_run, log=(lambda m: print(m, file=sys.stderr, flush=True)) if rank == 0 else None)
     state["wd"] = wd
     _STRIPED["end_run"], _STRIPED["rank"] = end_run, rank
+    wd.enter("NCCL process group of %d ranks (torch.distributed)" % world, 240)
+    dist.init_process_group("nccl", device_id=dev)  # barriers and the max-over-ranks of the timings only
+    L = capi.lib()
+    group = "bench%s" % os.environ.get("MASTER_PORT", "0")
+    n_local = 2048                       # rows per rank per collective add
+    n_block = n_local * world
+    n_adds = (total_cap + 64 + n_block - 1) // n_block
 
     def make(prefetch, learner):
         return rela.FFPrioritizedReplay(total_cap, 7, args.alpha, args.beta, prefetch, local_rank, rank, world, learner,
