@@ -211,7 +211,10 @@ __global__ void __launch_bounds__(256) row_copy_kernel(const __grid_constant__ C
   // completion IS the batch's (the flags are in this GPU's memory; one CTA polls them)
   if (tid < p.wait_n) {
     const unsigned long long t0 = globaltimer_ns();
-    for (;;) {
+    // (a replay already in error -- some wait has timed out -- does not wait again: the host raises
+    // at its next call, and what is queued until then drains at once)
+    const bool failed = *reinterpret_cast<volatile int*>(p.wait_error) != 0;
+    for (; !failed;) {
       unsigned long long v;
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p.wait_flags + tid) : "memory");
       if (v >= p.signal_val) break;
@@ -237,7 +240,8 @@ __global__ void wait_signals_kernel(const unsigned long long* flags, int n, unsi
   const int lane = threadIdx.x;
   if (lane >= n) return;
   const unsigned long long t0 = globaltimer_ns();
-  for (;;) {
+  const bool failed = *reinterpret_cast<volatile int*>(error) != 0;  // (already in error: no further waits)
+  for (; !failed;) {
     unsigned long long v;
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + lane) : "memory");
     if (v >= val) break;
@@ -305,7 +309,8 @@ __global__ void __launch_bounds__(256) exchange_kernel(const uint8_t* __restrict
   if (tid < n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.flag[tid]), "l"(val) : "memory");
   if (tid < n_wait) {
     const unsigned long long t0 = globaltimer_ns();
-    for (;;) {
+    const bool failed = *reinterpret_cast<volatile int*>(error) != 0;  // (already in error: no further waits)
+    for (; !failed;) {
       unsigned long long v;
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(wait_flags + tid) : "memory");
       if (v >= val) break;

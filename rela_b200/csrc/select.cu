@@ -631,7 +631,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectArgs a)
   }
   if (blockIdx.x == 0 && tid < a.wait_n) {  // SelectArgs::wait_flags: normally long published
     const unsigned long long t0 = globaltimer_ns();
-    for (;;) {
+    // (once the replay is in error -- a wait somewhere has timed out -- no kernel waits again: the
+    // host raises at its next call, and what is queued until then drains at once)
+    const bool failed = *reinterpret_cast<volatile int*>(&ctl->error) != 0;
+    for (; !failed;) {
       unsigned long long v;
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.wait_flags + tid) : "memory");
       if (v >= a.wait_val) break;
@@ -851,7 +854,9 @@ __global__ void __launch_bounds__(kUpdThreads) update_kernel(Ctl* ctl, float* w,
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
     if ((unsigned int)(v >> 32) != xa.epoch) {
       const unsigned long long t0 = globaltimer_ns();
-      for (;;) {
+      // (a replay already in error does not wait again: see select_kernel's wait)
+      const bool failed = *reinterpret_cast<volatile int*>(&ctl->error) != 0;
+      for (; !failed;) {
         asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
         if ((unsigned int)(v >> 32) == xa.epoch) break;
         if (globaltimer_ns() - t0 > 10ull * 1000 * 1000 * 1000) {
