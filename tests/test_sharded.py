@@ -160,10 +160,12 @@ def test_priorities_are_raised_at_their_position_in_the_block():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("world", [2, 3])
-@pytest.mark.parametrize("learner,prefetch", [(-1, 0), (0, 0), (-1, 2), (1, 1)])
+@pytest.mark.parametrize("learner,prefetch", [(-1, 0), (0, 0), (-1, 2), (1, 1), (0, 3)])
 def test_striped_replay_matches_one_oracle(world, learner, prefetch):
     """learner -1: every rank draws its share of one stratified batch of world * B (a
-    data-parallel learner); learner r: one learner rank. With and without batches drawn ahead."""
+    data-parallel learner); learner r: one learner rank. With and without batches drawn ahead
+    (one learner with three: its updates rotate through prefetch + 2 slot arrays, because nothing
+    but the gathers holds it back and it may be that far ahead of a shard that only receives)."""
     chunks = _run(world, ("--learner", str(learner), "--prefetch", str(prefetch), "--K", str(12 * world)))
     if learner < 0:
         _check_chunks(chunks, world)
