@@ -1181,24 +1181,7 @@ def run_striped(args):
              "runs": [], "peak": (peak, peak_src), "t_start": t_start}
 
     def end_run(why):
-        """A phase overran its budget (or raised): rank 0 prints the line of what has been measured, or
-        an error object if there is nothing yet; every rank ends its process (no clean-up: kernels of
-        this or another rank may be waiting for one another)."""
-        rc = 0
-        if rank == 0 and not state.get("printed"):
-            try:
-                if state["runs"]:
-                    print(json.dumps(striped_line(state, why)), flush=True)
-                else:
-                    print(json.dumps({"error": "striped run ended without a number: %s" % why, "n_gpus": world,
-                                      "phases_s": wd.history, "parity": state["parity"]}), flush=True)
-                    rc = 3
-            except Exception as e:  # noqa: BLE001  (never hang in the exit path)
-                print("bench.py: could not build the partial line: %r" % (e,), file=sys.stderr, flush=True)
-                rc = 3
-        sys.stderr.write("bench.py rank %d: ending the run: %s\n" % (rank, why))
-        sys.stderr.flush()
-        os._exit(rc)
+        striped_end_run(state, rank, world, why)
 
     wd = PhaseWatchdog(end_run, log=(lambda m: print(m, file=sys.stderr, flush=True)) if rank == 0 else None)
     state["wd"] = wd
@@ -1502,6 +1485,29 @@ def run_striped(args):
 
 
 _STRIPED = {}  # run_striped's exit hook, for main()
+
+
+def striped_end_run(state, rank, world, why):
+    """A phase of a striped run overran its budget (or raised): rank 0 prints the line of what has
+    been measured, or an error object if there is nothing yet; every rank ends its process (no
+    clean-up: kernels of this or another rank may be waiting for one another). Does not return."""
+    rc = 0
+    if rank == 0 and not state.get("printed"):
+        try:
+            if state["runs"]:
+                print(json.dumps(striped_line(state, why)), flush=True)
+            else:
+                wd = state.get("wd")
+                print(json.dumps({"error": "striped run ended without a number: %s" % why, "n_gpus": world,
+                                  "phases_s": wd.history if wd is not None else None, "parity": state["parity"]}),
+                      flush=True)
+                rc = 3
+        except Exception as e:  # noqa: BLE001  (never hang in the exit path)
+            print("bench.py: could not build the partial line: %r" % (e,), file=sys.stderr, flush=True)
+            rc = 3
+    sys.stderr.write("bench.py rank %d: ending the run: %s\n" % (rank, why))
+    sys.stderr.flush()
+    os._exit(rc)
 
 
 def striped_line(state, incomplete):

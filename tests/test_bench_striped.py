@@ -2,6 +2,8 @@
 its phases hangs: the watchdog and the line builder, on the CPU."""
 import json
 import os
+import socket
+import subprocess
 import sys
 import threading
 import time
@@ -69,3 +71,34 @@ def test_striped_line_complete_and_partial():
     assert part["e2e"] is None and part["single_learner"] is None and part["kernel_timeline"] is None
     assert "value loop from C++" in part["incomplete"] and part["value_runs"][0]["loop"] == "interpreter"
     assert part["value"] > 0 and part["gpu_launches"] is None
+
+
+def test_a_hung_rank_ends_the_run_with_a_partial_line():
+    """World 2 over gloo: one rank hangs in a leg, the other waits for it in a collective. Both
+    processes must end by themselves with exit code 0 (torchrun tears a job down when a rank exits
+    non-zero) and rank 0 must have printed the line of the leg that had been measured."""
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "striped_hang_worker.py")], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=120))
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    assert [p.returncode for p in procs] == [0, 0], outs
+    assert "NOT REACHED" not in outs[0][0] + outs[1][0]
+    lines = [ln for ln in outs[0][0].splitlines() if ln.startswith("{")]
+    assert len(lines) == 1 and outs[1][0].strip() == ""
+    line = json.loads(lines[0])
+    assert "a leg that hangs" in line["incomplete"] and line["n_gpus"] == 2
+    assert line["value"] == 1024 / 0.05e-3 and line["e2e"] is None
+    assert [n for n, _ in line["phases_s"]] == ["a leg that works"]
+    assert "ending the run" in outs[1][1]
