@@ -414,8 +414,10 @@ std::pair<Leaves, torch::Tensor> ReplayCore::shardedSample(int batchsize, const 
   sh.inflight.pop_front();
   while ((int)sh.inflight.size() < prefetch_) issue(false);
   if (sh.my_learner < 0) return {Leaves(), torch::Tensor()};
-  // The tensors alias a ring of prefetch + 2 batch sets in peer-visible memory: a batch stays
-  // valid until the second next sample() call.
+  // The tensors alias a ring of prefetch + 2 batch sets in peer-visible memory: batch y stays
+  // valid until this rank calls update_priority for batch y + 1 (a shard re-gathers into the set
+  // of batch y for batch y + prefetch + 2, behind its selection of that batch and therefore behind
+  // its update y + 1, which cannot finish before this learner's update y + 1 has started).
   const BatchSet& set = a.sets[(size_t)k];
   Leaves out;
   out.reserve(nf);
