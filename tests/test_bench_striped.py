@@ -102,3 +102,125 @@ def test_a_hung_rank_ends_the_run_with_a_partial_line():
     assert line["value"] == 1024 / 0.05e-3 and line["e2e"] is None
     assert [n for n, _ in line["phases_s"]] == ["a leg that works"]
     assert "ending the run" in outs[1][1]
+
+
+def test_run_striped_control_flow_with_fakes(monkeypatch, capsys):
+    """bench.run_striped from its first line to its printed JSON line with everything that needs a
+    GPU replaced by a stand-in (the replay class, the C library handle, CUDA events and streams,
+    NCCL -> gloo): the orchestration -- phases, the legs published one by one, the four replays,
+    the line -- first runs for real on multi-GPU boxes this container does not have."""
+    import argparse
+    import contextlib
+    import types
+
+    import torch
+    import torch.distributed as dist
+
+    import rela_b200
+    from rela_b200 import capi
+
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    for k, v in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1"), ("MASTER_ADDR", "127.0.0.1"),
+                 ("MASTER_PORT", str(port))):
+        monkeypatch.setenv(k, v)
+
+    real_device = torch.device
+
+    class FakeDeviceMeta(type):
+        def __instancecheck__(cls, obj):
+            return isinstance(obj, real_device)
+
+    class FakeDevice(metaclass=FakeDeviceMeta):
+        def __new__(cls, *a, **k):
+            if a and a[0] == "cuda":
+                return real_device("cpu")
+            return real_device(*a, **k)
+
+    class FakeEvent:
+        def __init__(self, enable_timing=False):
+            pass
+
+        def record(self, stream=None):
+            self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return max((other.t - self.t) * 1e3, 1e-3)
+
+    class FakeStream:
+        cuda_stream = 0
+
+        def synchronize(self):
+            pass
+
+    made = []
+
+    class FakeReplay:
+        def __init__(self, cap, seed, alpha, beta, prefetch, local_rank, rank, world, learner, group):
+            self.prefetch, self.learner, self.n = prefetch, learner, 0
+            made.append(self)
+
+        def add(self, t, p):
+            self.n += 1
+
+        def sync(self):
+            pass
+
+        def handle(self):
+            return 1
+
+        def sample(self, B, dev):
+            return object(), torch.zeros(B)
+
+        def update_priority(self, p):
+            pass
+
+        def last_chunk(self):
+            return 0
+
+        def cycle_loop(self, B, dev, pool, steps):
+            for _ in range(steps):
+                self.sample(B, dev)
+
+    class FakeL:
+        def __getattr__(self, name):
+            return lambda *a: 0
+
+    fake_rela = types.SimpleNamespace(FFPrioritizedReplay=FakeReplay, FFTransition=lambda *a: a)
+    monkeypatch.setitem(sys.modules, "rela_b200.rela", fake_rela)
+    monkeypatch.setattr(rela_b200, "rela", fake_rela, raising=False)
+    monkeypatch.setattr(capi, "lib", lambda: FakeL())
+    monkeypatch.setattr(torch, "device", FakeDevice)
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(torch.cuda, "set_device", lambda d: None)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda d=None: None)
+    monkeypatch.setattr(torch.cuda, "empty_cache", lambda: None)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda d=None: FakeStream())
+    monkeypatch.setattr(torch.cuda, "ExternalStream", lambda ptr, device=None: FakeStream())
+    monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
+    monkeypatch.setattr(torch.cuda, "Event", FakeEvent)
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
+    monkeypatch.setattr(os, "sched_setaffinity", lambda pid, cpus: None)
+    real_init = dist.init_process_group
+    monkeypatch.setattr(dist, "init_process_group", lambda backend, device_id=None: real_init("gloo", rank=0, world_size=1))
+
+    args = argparse.Namespace(batch=8, steps=4, warmup=3, capacity=2048, alpha=0.6, beta=0.4, no_parity=True,
+                              parity_cycles=8, gpus=1)
+    try:
+        bench.run_striped(args)
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    out = [ln for ln in capsys.readouterr().out.splitlines() if ln.startswith("{")]
+    assert len(out) == 1
+    line = json.loads(out[0])
+    assert "incomplete" not in line and "error" not in line
+    assert [(r["prefetch"], r["loop"]) for r in line["value_runs"]] == [(0, "C++"), (2, "C++"), (4, "C++")]
+    assert line["e2e"] is not None and len(line["e2e"]["runs"]) == 3
+    assert line["single_learner"] is not None and line["kernel_timeline"] is not None
+    assert [(m.prefetch, m.learner) for m in made] == [(0, -1), (2, -1), (4, -1), (4, 0)]
+    assert all(m.n == made[0].n and m.n > 0 for m in made)          # every replay was filled
+    names = [n for n, _ in line["phases_s"]]
+    assert names[0].startswith("NCCL process group") and any(n.startswith("kernel timeline") for n in names)
+    assert line["steps"] == 4 and line["warmup"] == 3 and line["n_gpus"] == 1
